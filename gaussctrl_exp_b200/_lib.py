@@ -1,0 +1,98 @@
+"""ctypes binding of the C ABI declared in include/gs_b200.h.
+
+There is NO fallback: if libgs_b200.so is missing or a call fails, an exception is raised.
+The library is built in-tree (gaussctrl_exp_b200/libgs_b200.so) by `build()` /
+`__graft_entry__.build()` with nvcc for sm_100a.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libgs_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+_lib = None
+
+_vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/gs_b200.h line by line
+SIGNATURES = {
+    "gs_version": (_i, []),
+    "gs_built_arch": (_i, []),
+    "gs_launch_count": (_i64, []),
+    "gs_project_fwd": (_i, [_i, _vp, _vp, _f, _vp, _vp, _vp, _f, _f, _f, _f, _i, _i, _i, _i, _f,
+                            _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_project_bwd": (_i, [_i, _vp, _vp, _f, _vp, _vp, _vp, _f, _f, _i, _i, _vp, _vp, _vp, _vp,
+                            _vp, _vp, _vp, _vp]),
+    "gs_sh_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
+    "gs_sh_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
+    "gs_scan_scratch_bytes": (_sz, [_i]),
+    "gs_bin_scan": (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gs_bin_emit": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "gs_sort_scratch_bytes": (_sz, [_i64]),
+    "gs_bin_sort": (_i, [_i64, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gs_bin_edges": (_i, [_i64, _i, _vp, _vp, _vp]),
+    "gs_bin_fast_scratch_bytes": (_sz, [_i, _i64, _i]),
+    "gs_bin_fast": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gs_raster_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_raster_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                           _vp, _vp, _vp, _vp, _vp]),
+}
+
+_ERRORS = {-1: "GS_ERR_BAD_ARG", -2: "GS_ERR_SCRATCH_SMALL", -3: "GS_ERR_UNSUPPORTED", -4: "GS_ERR_MISALIGNED"}
+
+
+class GsError(RuntimeError):
+    pass
+
+
+def build(verbose: bool = False) -> str:
+    """Compile every CUDA source for sm_100a into the in-tree shared library."""
+    cmd = ["make", "-C", CSRC, "-j8"]
+    if not verbose:
+        cmd.insert(1, "-s")
+    subprocess.check_call(cmd)
+    if not os.path.exists(SO_PATH):
+        raise GsError(f"build did not produce {SO_PATH}")
+    return SO_PATH
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise GsError(
+                f"{SO_PATH} is missing: the CUDA extension was not built (run __graft_entry__.build()). "
+                "There is no CPU or PyTorch fallback for this path.")
+        L = C.CDLL(SO_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str):
+    if rc == 0:
+        return
+    if rc < 0:
+        raise GsError(f"{what}: {_ERRORS.get(rc, rc)}")
+    raise GsError(f"{what}: CUDA error {rc}")
+
+
+def ptr(t):
+    """Device pointer of a (contiguous) torch tensor, or NULL for None."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def launch_count() -> int:
+    return int(lib().gs_launch_count())

@@ -1,0 +1,59 @@
+// Shared device/host helpers for the sm_100a kernels. Not part of the ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/gs_b200.h"
+
+#define GS_ALPHA_MAX 0.999f
+#define GS_ALPHA_MIN (1.0f / 255.0f)
+#define GS_T_EPS 1e-4f
+#define GS_BLUR 0.3f
+// gsplat 0.1.2 samples pixel (i,j) at integer coordinates.
+#define GS_PIX_CENTER 0.0f
+
+#define GS_NUM_SMS 148  // B200; used only to size persistent grids
+
+extern int64_t g_gs_launches;  // defined in abi.cu
+
+#define GS_LAUNCH_CHECK()                                    \
+    do {                                                     \
+        ++g_gs_launches;                                     \
+        cudaError_t _e = cudaPeekAtLastError();              \
+        if (_e != cudaSuccess) return (int)_e;               \
+    } while (0)
+
+#define GS_CUDA(x)                                           \
+    do {                                                     \
+        cudaError_t _e = (x);                                \
+        if (_e != cudaSuccess) return (int)_e;               \
+    } while (0)
+
+static inline bool gs_aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+static inline int gs_ceil_log2(int v) { int b = 0; while ((1 << b) < v) ++b; return b; }
+static inline size_t gs_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+__device__ __forceinline__ int gs_clampi(int v, int lo, int hi) { return min(hi, max(lo, v)); }
+
+// A.1.6: tile bbox of a splat (pixel centre, integer radius); C truncation toward zero.
+__device__ __forceinline__ void gs_tile_bbox(float x, float y, float radius, int tiles_x, int tiles_y,
+                                             int &x0, int &y0, int &x1, int &y1) {
+    const float tcx = __fdiv_rn(x, 16.0f), tcy = __fdiv_rn(y, 16.0f), tr = __fdiv_rn(radius, 16.0f);
+    x0 = gs_clampi((int)__fsub_rn(tcx, tr), 0, tiles_x);
+    x1 = gs_clampi((int)__fadd_rn(__fadd_rn(tcx, tr), 1.0f), 0, tiles_x);
+    y0 = gs_clampi((int)__fsub_rn(tcy, tr), 0, tiles_y);
+    y1 = gs_clampi((int)__fadd_rn(__fadd_rn(tcy, tr), 1.0f), 0, tiles_y);
+}
+
+__device__ __forceinline__ unsigned gs_lanemask_lt() {
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// streaming (read-once) loads that bypass L1 allocation
+__device__ __forceinline__ float4 gs_ldg_stream4(const float4 *p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}

@@ -1,0 +1,191 @@
+// Stage 3 — forward alpha compositing (replaces gsplat's
+// rasterize_forward / nd_rasterize_forward reached from
+// /root/reference/gaussctrl/gc_model.py:208-220 and :225-236).
+//
+// One CTA per 16x16 tile, one pixel per thread. The tile's depth-sorted Gaussians are
+// gathered in batches of 256 into a double-buffered shared-memory stage: the gather for
+// batch b+1 is issued into registers before batch b is composited, so its latency hides
+// behind the arithmetic; one barrier per batch (__syncthreads_count) both publishes the
+// stage and retires the tile as soon as every pixel has saturated.
+// Bound: SM issue rate (FP32 + MUFU.EX2) and shared-memory broadcast reads, not HBM.
+#include "raster_common.cuh"
+
+namespace {
+
+constexpr int RF_BATCH = 256;
+
+struct StageRGB {
+    float4 a[RF_BATCH];  // x, y, opac, conic.a
+    float4 b[RF_BATCH];  // conic.b, conic.c, r, g
+    float c[RF_BATCH];   // b
+};
+
+__global__ void __launch_bounds__(256)
+raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_sorted,
+                   const int2 *__restrict__ tile_bins, const float2 *__restrict__ xys,
+                   const float *__restrict__ conics, const float *__restrict__ colors,
+                   const float *__restrict__ opac, const float *__restrict__ bg, float *__restrict__ out_img,
+                   float *__restrict__ final_T, int32_t *__restrict__ final_idx) {
+    __shared__ StageRGB st[2];
+    const int tile = blockIdx.x;
+    const int tile_x = tile % tiles_x, tile_y = tile / tiles_x;
+    int px, py;
+    gs_pixel_of_thread(tile_x, tile_y, px, py);
+    const bool inside = px < W && py < H;
+    const float fx = (float)px + GS_PIX_CENTER, fy = (float)py + GS_PIX_CENTER;
+    const int2 range = tile_bins[tile];
+    const int n = range.y - range.x;
+    const int nbatch = (n + RF_BATCH - 1) / RF_BATCH;
+    const int tid = threadIdx.x;
+
+    float T = 1.0f, r = 0.f, g = 0.f, b = 0.f;
+    int last = range.x;
+    bool done = !inside;
+
+    // register prefetch of the first batch
+    float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pb = pa;
+    float pc = 0.f;
+    auto gather = [&](int batch) {
+        const int k = range.x + batch * RF_BATCH + tid;
+        if (k < range.y) {
+            const int id = ids_sorted[k];
+            const float2 xy = xys[id];
+            pa = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
+            pb = make_float4(conics[3 * id + 1], conics[3 * id + 2], colors[3 * id], colors[3 * id + 1]);
+            pc = colors[3 * id + 2];
+        }
+    };
+    if (nbatch > 0) gather(0);
+    for (int batch = 0; batch < nbatch; ++batch) {
+        StageRGB &s = st[batch & 1];
+        s.a[tid] = pa; s.b[tid] = pb; s.c[tid] = pc;
+        if (__syncthreads_count(done) == 256) break;
+        if (batch + 1 < nbatch) gather(batch + 1);
+        if (!done) {
+            const int cnt = min(RF_BATCH, n - batch * RF_BATCH);
+            const int kbase = range.x + batch * RF_BATCH;
+            for (int j = 0; j < cnt; ++j) {
+                const float4 A = s.a[j];
+                const float4 B = s.b[j];
+                GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};
+                float dx, dy, vis, alpha;
+                if (!gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha)) continue;
+                const float Tn = T * (1.0f - alpha);
+                if (Tn <= GS_T_EPS) { done = true; break; }
+                const float w = alpha * T;
+                r += w * B.z; g += w * B.w; b += w * s.c[j];
+                T = Tn;
+                last = kbase + j + 1;
+            }
+        }
+    }
+    if (inside) {
+        const size_t pix = (size_t)py * W + px;
+        out_img[3 * pix] = r + T * bg[0];
+        out_img[3 * pix + 1] = g + T * bg[1];
+        out_img[3 * pix + 2] = b + T * bg[2];
+        final_T[pix] = T;
+        final_idx[pix] = last;
+    }
+}
+
+// Generic channel count (C <= CPAD): geometry staged in shared memory, colours read
+// through L1 from global for contributing pairs only.
+struct StageGeo {
+    float4 a[RF_BATCH];  // x, y, opac, conic.a
+    float2 b[RF_BATCH];  // conic.b, conic.c
+    int id[RF_BATCH];
+};
+
+template <int CPAD>
+__global__ void __launch_bounds__(256)
+raster_fwdN_kernel(int C, int H, int W, int tiles_x, const int32_t *__restrict__ ids_sorted,
+                   const int2 *__restrict__ tile_bins, const float2 *__restrict__ xys,
+                   const float *__restrict__ conics, const float *__restrict__ colors,
+                   const float *__restrict__ opac, const float *__restrict__ bg, float *__restrict__ out_img,
+                   float *__restrict__ final_T, int32_t *__restrict__ final_idx) {
+    __shared__ StageGeo s;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % tiles_x, tile_y = tile / tiles_x;
+    int px, py;
+    gs_pixel_of_thread(tile_x, tile_y, px, py);
+    const bool inside = px < W && py < H;
+    const float fx = (float)px + GS_PIX_CENTER, fy = (float)py + GS_PIX_CENTER;
+    const int2 range = tile_bins[tile];
+    const int n = range.y - range.x;
+    const int nbatch = (n + RF_BATCH - 1) / RF_BATCH;
+    const int tid = threadIdx.x;
+    float T = 1.0f;
+    float acc[CPAD];
+#pragma unroll
+    for (int c = 0; c < CPAD; ++c) acc[c] = 0.f;
+    int last = range.x;
+    bool done = !inside;
+    for (int batch = 0; batch < nbatch; ++batch) {
+        if (__syncthreads_count(done) == 256) break;
+        const int k = range.x + batch * RF_BATCH + tid;
+        if (k < range.y) {
+            const int id = ids_sorted[k];
+            const float2 xy = xys[id];
+            s.a[tid] = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
+            s.b[tid] = make_float2(conics[3 * id + 1], conics[3 * id + 2]);
+            s.id[tid] = id;
+        }
+        __syncthreads();
+        if (!done) {
+            const int cnt = min(RF_BATCH, n - batch * RF_BATCH);
+            const int kbase = range.x + batch * RF_BATCH;
+            for (int j = 0; j < cnt; ++j) {
+                const float4 A = s.a[j];
+                const float2 B = s.b[j];
+                GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};
+                float dx, dy, vis, alpha;
+                if (!gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha)) continue;
+                const float Tn = T * (1.0f - alpha);
+                if (Tn <= GS_T_EPS) { done = true; break; }
+                const float w = alpha * T;
+                const float *col = colors + (size_t)s.id[j] * C;
+#pragma unroll
+                for (int c = 0; c < CPAD; ++c)
+                    if (c < C) acc[c] += w * col[c];
+                T = Tn;
+                last = kbase + j + 1;
+            }
+        }
+    }
+    if (inside) {
+        const size_t pix = (size_t)py * W + px;
+#pragma unroll
+        for (int c = 0; c < CPAD; ++c)
+            if (c < C) out_img[pix * C + c] = acc[c] + T * bg[c];
+        final_T[pix] = T;
+        final_idx[pix] = last;
+    }
+}
+
+}  // namespace
+
+extern "C" int gs_raster_fwd(int C, int H, int W, int tiles_x, int tiles_y,
+                             const int32_t *ids_sorted, const int32_t *tile_bins,
+                             const float *xys, const float *conics, const float *colors, const float *opac,
+                             const float *bg, float *out_img, float *final_T, int32_t *final_idx,
+                             void *stream) {
+    if (C <= 0 || H <= 0 || W <= 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (C > 32) return GS_ERR_UNSUPPORTED;
+    if (!tile_bins || !xys || !conics || !colors || !opac || !bg || !out_img || !final_T || !final_idx)
+        return GS_ERR_BAD_ARG;
+    if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int tiles = tiles_x * tiles_y;
+    const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
+    const float2 *xy2 = reinterpret_cast<const float2 *>(xys);
+#define GS_FWD_ARGS H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg, out_img, final_T, final_idx
+    if (C == 3) raster_fwd3_kernel<<<tiles, 256, 0, st>>>(GS_FWD_ARGS);
+    else if (C <= 4) raster_fwdN_kernel<4><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
+    else if (C <= 8) raster_fwdN_kernel<8><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
+    else if (C <= 16) raster_fwdN_kernel<16><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
+    else raster_fwdN_kernel<32><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
+#undef GS_FWD_ARGS
+    GS_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,94 @@
+"""Seeded synthetic scenes and cameras.
+
+The reference ships no trained Gaussians, so benchmarks and tests use
+synthetic splatfacto-shaped parameter sets: the six leaf tensors of
+/root/reference/gaussctrl/gc_model.py:157-170 and cameras with the intrinsics of
+/root/reference/data/garden/transforms.json:2-7.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List
+
+import torch
+
+# fx, fy, cx, cy, W, H of data/garden/transforms.json:2-7
+GARDEN_INTRINSICS = dict(fx=585.78, fy=585.51, cx=255.98, cy=253.71, W=512, H=512)
+HD_INTRINSICS = dict(fx=1200.0, fy=1200.0, cx=960.0, cy=540.0, W=1920, H=1080)
+
+PARAM_NAMES = ("means", "scales", "quats", "features_dc", "features_rest", "opacities")
+
+
+def default_scale(n: int) -> float:
+    """s0 per Gaussian count so that I/N stays at 3-5 at 512^2."""
+    if n <= 50_000:
+        return 0.005
+    if n <= 500_000:
+        return 0.004
+    if n <= 1_000_000:
+        return 0.003
+    return 0.002
+
+
+def make_scene(n: int, seed: int = 0, s0: float | None = None, device="cpu") -> Dict[str, torch.Tensor]:
+    """Leaf parameters in splatfacto's raw (pre-activation) form."""
+    g = torch.Generator().manual_seed(seed)
+    s0 = default_scale(n) if s0 is None else s0
+    p = {
+        "means": torch.randn(n, 3, generator=g) * 0.3,
+        "scales": math.log(s0) + 0.5 * torch.randn(n, 3, generator=g),
+        "quats": torch.randn(n, 4, generator=g),
+        "features_dc": torch.randn(n, 3, generator=g),
+        "features_rest": 0.1 * torch.randn(n, 15, 3, generator=g),
+        "opacities": 2.0 * torch.randn(n, 1, generator=g),
+    }
+    return {k: v.float().contiguous().to(device) for k, v in p.items()}
+
+
+@dataclass
+class Camera:
+    """The fields of nerfstudio `Cameras` that gc_model.py:115-145 reads, for one camera."""
+    c2w: torch.Tensor  # (3,4) OpenGL convention (-z forward, +y up), float32, CPU
+    fx: float
+    fy: float
+    cx: float
+    cy: float
+    W: int
+    H: int
+
+    def as_dict(self):
+        return dict(c2w=self.c2w.numpy(), fx=self.fx, fy=self.fy, cx=self.cx, cy=self.cy, W=self.W, H=self.H)
+
+
+def look_at(pos: torch.Tensor, target: torch.Tensor, up=(0.0, 0.0, 1.0)) -> torch.Tensor:
+    """c2w (3,4) of a camera at `pos` looking at `target`; columns = right, up, back."""
+    pos = pos.double()
+    fwd = target.double() - pos
+    fwd = fwd / fwd.norm()
+    upv = torch.tensor(up, dtype=torch.float64)
+    right = torch.linalg.cross(fwd, upv)
+    if right.norm() < 1e-6:
+        right = torch.linalg.cross(fwd, torch.tensor([0.0, 1.0, 0.0], dtype=torch.float64))
+    right = right / right.norm()
+    true_up = torch.linalg.cross(right, fwd)
+    c2w = torch.stack([right, true_up, -fwd, pos], dim=1)
+    return c2w.float()
+
+
+def make_cameras(v: int, seed: int = 0, radius: float = 1.5, intrinsics=None) -> List[Camera]:
+    """V poses on a sphere (Fibonacci lattice + seeded jitter) looking at the origin."""
+    intr = dict(GARDEN_INTRINSICS if intrinsics is None else intrinsics)
+    g = torch.Generator().manual_seed(1000 + seed)
+    cams = []
+    golden = math.pi * (3.0 - math.sqrt(5.0))
+    for i in range(v):
+        z = 1.0 - 2.0 * (i + 0.5) / v
+        z = 0.8 * z  # keep away from the poles so the up vector stays well defined
+        r = math.sqrt(max(0.0, 1.0 - z * z))
+        th = golden * i
+        d = torch.tensor([r * math.cos(th), r * math.sin(th), z], dtype=torch.float64)
+        d = d + 0.02 * torch.randn(3, generator=g, dtype=torch.float64)
+        pos = radius * d / d.norm()
+        cams.append(Camera(look_at(pos, torch.zeros(3, dtype=torch.float64)), **intr))
+    return cams

@@ -1,0 +1,122 @@
+/*
+ * gs_b200.h — C ABI of the B200-native 3D Gaussian splatting render path.
+ *
+ * Drop-in boundary for the gsplat-0.1.2 operators that the reference calls at
+ *   /root/reference/gaussctrl/gc_model.py:174-188  project_gaussians
+ *   /root/reference/gaussctrl/gc_model.py:199-200  spherical_harmonics
+ *   /root/reference/gaussctrl/gc_model.py:208-220  rasterize_gaussians (RGB + alpha)
+ *   /root/reference/gaussctrl/gc_model.py:225-236  rasterize_gaussians (depth)
+ *   /root/reference/gaussctrl/gc_trainer.py:275    loss.backward() through all of the above
+ * (imports at gc_model.py:32-36). In gsplat these are bound through a pybind11
+ * torch extension (`gsplat.cuda._C`); here they are plain `extern "C"` entry
+ * points taking raw DEVICE pointers, sizes and a `cudaStream_t` (passed as
+ * void*), so that any host language can bind them (INTEGRATION.md shows the
+ * ctypes binding the Python wrappers use).
+ *
+ * Conventions
+ *   - all tensors fp32 / int32 / int64, row-major, contiguous, device memory;
+ *     pointers must be 16-byte aligned (torch allocations are).
+ *   - every function enqueues work on `stream` and returns immediately;
+ *     nothing here synchronises the device except where stated.
+ *   - return value: 0 = ok, >0 = cudaError_t, <0 = GS_ERR_* below.
+ *   - the library never allocates persistent device memory: scratch is passed
+ *     in by pointer + size (sizes from gs_*_scratch_bytes).
+ */
+#ifndef GS_B200_H
+#define GS_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS_ERR_BAD_ARG        (-1)
+#define GS_ERR_SCRATCH_SMALL  (-2)
+#define GS_ERR_UNSUPPORTED    (-3)
+#define GS_ERR_MISALIGNED     (-4)
+
+#define GS_TILE 16
+
+/* ABI version (major*100 + minor) and the SM arch the kernels were built for. */
+int gs_version(void);
+int gs_built_arch(void);
+/* count of kernel launches issued by this library since load (bench.py's gpu_launches). */
+int64_t gs_launch_count(void);
+
+/* ---- stage 1: projection (gc_model.py:174-188) ------------------------- */
+/* viewmat: >=12 floats (3x4 row-major), projmat: 16 floats (P@V); both DEVICE pointers.
+ * Outputs are fully written (culled rows = 0). */
+int gs_project_fwd(int N, const float *means, const float *scales, float glob_scale,
+                   const float *quats, const float *viewmat, const float *projmat,
+                   float fx, float fy, float cx, float cy, int H, int W,
+                   int tiles_x, int tiles_y, float clip_thresh,
+                   float *cov3d, float *xys, float *depths, int32_t *radii,
+                   float *conics, int32_t *tiles_hit, void *stream);
+
+/* exact vjp of gs_project_fwd w.r.t. means, scales, quats. v_* inputs may not be NULL. */
+int gs_project_bwd(int N, const float *means, const float *scales, float glob_scale,
+                   const float *quats, const float *viewmat, const float *projmat,
+                   float fx, float fy, int H, int W, const int32_t *radii,
+                   const float *v_xys, const float *v_depths, const float *v_conics,
+                   float *v_means, float *v_scales, float *v_quats, void *stream);
+
+/* ---- stage 1b: spherical harmonics (gc_model.py:199-200; App. A.2) ------------------------- */
+/* coeffs (N,K,3); deg <= 4 and (deg+1)^2 <= K. */
+int gs_sh_fwd(int N, int K, int deg, const float *dirs, const float *coeffs, float *colors,
+              void *stream);
+/* v_coeffs (N,K,3) fully written (unused bases = 0). */
+int gs_sh_bwd(int N, int K, int deg, const float *dirs, const float *v_colors, float *v_coeffs,
+              void *stream);
+
+/* ---- stage 2: tile binning (inside rasterize_gaussians; App. A.3) -------------------------- */
+size_t gs_scan_scratch_bytes(int N);
+/* inclusive int32 scan of tiles_hit -> cum; the total is also written to *total_dev
+ * (device int32) so the caller can copy it to pinned memory without reading cum[N-1]. */
+int gs_bin_scan(int N, const int32_t *tiles_hit, int32_t *cum, int32_t *total_dev,
+                void *scratch, size_t scratch_bytes, void *stream);
+/* 64-bit keys (tile_id << 32 | depth bits) + Gaussian ids, in emission order. */
+int gs_bin_emit(int N, const float *xys, const float *depths, const int32_t *radii,
+                const int32_t *cum, int tiles_x, int tiles_y, int64_t *keys, int32_t *ids,
+                void *stream);
+size_t gs_sort_scratch_bytes(int64_t I);
+/* stable ascending radix sort over the live key bits [0, 32 + ceil(log2(T))). */
+int gs_bin_sort(int64_t I, int T, const int64_t *keys, const int32_t *ids,
+                int64_t *keys_sorted, int32_t *ids_sorted,
+                void *scratch, size_t scratch_bytes, void *stream);
+/* tile_bins (T,2) int32 = [start,end) per tile; fully written (empty tiles = 0,0). */
+int gs_bin_edges(int64_t I, int T, const int64_t *keys_sorted, int32_t *tile_bins, void *stream);
+
+/* Traffic-lean binning with the SAME outputs as scan+emit+sort+edges (ids_sorted, tile_bins)
+ * but without materialising 64-bit keys: depth-sort the Gaussians once, emit in that order,
+ * one stable partition by tile id. I_cap = capacity of ids_sorted; if the true I exceeds it,
+ * nothing out of bounds is written and *total_dev (> I_cap) tells the caller to retry. */
+size_t gs_bin_fast_scratch_bytes(int N, int64_t I_cap, int T);
+int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, const int32_t *radii,
+                const int32_t *tiles_hit, int tiles_x, int tiles_y,
+                int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
+                void *scratch, size_t scratch_bytes, void *stream);
+
+/* ---- stage 3: forward compositing (App. A.4) ----------------------------------------------- */
+/* colors (N,C); opac (N); bg (C) device; out_img (H,W,C); final_T (H,W); final_idx (H,W) =
+ * 1 + index into ids_sorted of the last composited Gaussian (tile range start if none). */
+int gs_raster_fwd(int C, int H, int W, int tiles_x, int tiles_y,
+                  const int32_t *ids_sorted, const int32_t *tile_bins,
+                  const float *xys, const float *conics, const float *colors, const float *opac,
+                  const float *bg, float *out_img, float *final_T, int32_t *final_idx,
+                  void *stream);
+
+/* ---- stage 4: backward compositing (App. A.5) ---------------------------------------------- */
+/* v_out (H,W,C); v_out_alpha (H,W) or NULL. Outputs are ACCUMULATED INTO: caller zero-fills
+ * v_xys (N,2), v_conics (N,3), v_colors (N,C), v_opac (N). */
+int gs_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y,
+                  const int32_t *ids_sorted, const int32_t *tile_bins,
+                  const float *xys, const float *conics, const float *colors, const float *opac,
+                  const float *bg, const float *final_T, const int32_t *final_idx,
+                  const float *v_out, const float *v_out_alpha,
+                  float *v_xys, float *v_conics, float *v_colors, float *v_opac, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
