@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""bench.py — views/sec, forward+backward, 1 M Gaussians, 512x512 (BASELINE.json `metric`).
+
+One "step" = one training view through the host mirror of GaussCtrlModel.get_outputs
+(gc_model.py:77-241, training branch) + loss.backward() down to the six leaf gradients
+(gc_trainer.py:275): pre-activations, project_gaussians, spherical_harmonics (deg 3),
+tile binning, forward compositing, backward compositing, SH backward, projection backward.
+N > 1 (torchrun): parameters replicated, each rank takes a different view per step, one NCCL
+allreduce of the parameter gradients per step; value = all ranks' views
+/ max-over-ranks time.
+
+    python bench.py [--gpus N --steps K --warmup W]            our CUDA path
+    python bench.py --impl reference [...]                      the CPU oracle on the host cores
+
+Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_GAUSS = 1_000_000
+SH_DEG = 3
+N_CAMS = 40            # gc_datamanager.py:61-66: 4 subsets x 10 views
+BG = (0.1, 0.2, 0.3)
+METRIC = "views/sec fwd+bwd (1M Gaussians, 512^2)"
+
+
+def workload_config(n_gauss, world):
+    return {
+        "workload": f"synthetic {n_gauss} Gaussians (seed 0, s0 per SURVEY 8d), SH deg {SH_DEG}, 512x512, "
+                    f"{N_CAMS} cameras on a sphere r=1.5 (garden intrinsics), one view fwd+bwd per step per GPU, "
+                    f"upstream grad randn/(H*W), bg {BG}",
+        "n_gaussians": n_gauss, "image": [512, 512], "sh_degree": SH_DEG, "views_per_step": world,
+        "parallelism": f"view-parallel dp{world}" + (" + allreduce(grads)" if world > 1 else ""),
+        "l2": "working set (236 MB params + 236 MB grads) exceeds the 126 MB L2; no explicit flush",
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+class CpuReference:
+    """The oracle (CPU restatement of the path, kind 'port') on the same workload, all host threads."""
+
+    def __init__(self, n_gauss, threads=None):
+        import numpy as np
+        from gaussctrl_exp_b200 import scene
+        from oracle import oracle as orc
+        orc.build()
+        if threads:
+            orc.set_num_threads(threads)
+        self.orc = orc
+        self.cores = orc.num_threads()
+        self.p = {k: v.numpy() for k, v in scene.make_scene(n_gauss, 0).items()}
+        self.cams = scene.make_cameras(N_CAMS, 0)
+        self.v_out = (np.random.default_rng(1234).standard_normal((512, 512, 3)) / (512 * 512)).astype(np.float32)
+
+    def view(self, i):
+        out, ctx = self.orc.render_view(self.p, self.cams[i % N_CAMS].as_dict(), SH_DEG, bg=BG, training=True)
+        self.orc.render_view_backward(self.p, ctx, self.v_out)
+
+    def run(self, views, first=0):
+        t0 = time.perf_counter()
+        for i in range(views):
+            self.view(first + i)
+        dt = time.perf_counter() - t0
+        return views / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    ref = CpuReference(args.n_gaussians)
+    ref.run(min(max(args.warmup, 0), 2))
+    _, dt = ref.run(args.steps, first=2)                  # one step = one view, fwd + bwd
+    ms = 1e3 * dt / args.steps
+    val = 1e3 / ms
+    sample = "1 view (fwd+bwd) of the same 1M-Gaussian/512^2 workload per step, C oracle + OpenMP"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "views/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, 1),
+        "cpu_baseline": {"value": val, "unit": "views/s", "cores": ref.cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "gsplat 0.1.2 (the reference's implementation of this path) is not in /root/reference and not "
+                "installable offline; this arm times the CPU restatement (oracle/) on the host cores",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def stage_breakdown(model, cams, v_out, iters=20):
+    """Per-stage device times (CUDA events on the current stream) and rooflines for one view.
+    Algorithmic bytes per SURVEY.md §8d."""
+    import torch
+    from gaussctrl_exp_b200 import project_gaussians, rasterize_gaussians, spherical_harmonics
+    from gaussctrl_exp_b200 import utils as U
+    from gaussctrl_exp_b200.model import camera_matrices
+    dev = model.device
+    cam = cams[0]
+    H, W = cam.H, cam.W
+    V, P, _, _, tb = camera_matrices(cam.c2w, cam.fx, cam.fy, W, H)
+    Vd, PVd = V[:3].contiguous().to(dev), (P @ V).to(dev)
+    N = model.num_points
+    with torch.no_grad():
+        means, scales = model.means.detach(), model.scales.detach().exp()
+        quats = model.quats.detach() / model.quats.detach().norm(dim=-1, keepdim=True)
+        coeffs = torch.cat((model.features_dc.detach()[:, None, :], model.features_rest.detach()), 1).contiguous()
+        dirs = means - cam.c2w[:3, 3].to(dev)
+        dirs = dirs / dirs.norm(dim=-1, keepdim=True)
+        opac = torch.sigmoid(model.opacities.detach())
+    bg = torch.tensor(BG, device=dev)
+
+    def timed(fn, n=iters):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n * 1e-3
+
+    from gaussctrl_exp_b200 import _lib
+    L = _lib.lib()
+    st = {}
+    with torch.no_grad():
+        xys, depths, radii, conics, hit, cov3d = project_gaussians(means, scales, 1, quats, Vd, PVd, cam.fx, cam.fy,
+                                                                   cam.cx, cam.cy, H, W, tb)
+        rgbs = torch.clamp(spherical_harmonics(SH_DEG, dirs, coeffs) + 0.5, min=0.0)
+        ids_sorted, bins, I = U.bin_fast(xys, depths, radii, hit, tb)
+        T = tb[0] * tb[1]
+        st["project_fwd"] = (timed(lambda: project_gaussians(means, scales, 1, quats, Vd, PVd, cam.fx, cam.fy, cam.cx,
+                                                             cam.cy, H, W, tb)), 96 * N)
+        st["sh_fwd"] = (timed(lambda: spherical_harmonics(SH_DEG, dirs, coeffs)), 216 * N)
+        # binning through the raw ABI (no host read inside the timed loop)
+        cap = ids_sorted.numel()
+        scratch = torch.empty(L.gs_bin_fast_scratch_bytes(N, cap, T), device=dev, dtype=torch.uint8)
+        total = torch.zeros(1, device=dev, dtype=torch.int32)
+        st["bin_fast"] = (timed(lambda: L.gs_bin_fast(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(),
+                                                       hit.data_ptr(), tb[0], tb[1], ids_sorted.data_ptr(),
+                                                       bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
+                                                       scratch.numel(), _lib.stream_ptr())),
+                          8 * N + 20 * N + 12 * I + 24 * I + 8 * I + 8 * T)
+        out = torch.empty((H, W, 3), device=dev)
+        fT = torch.empty((H, W), device=dev)
+        fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
+        opv = opac.view(-1).contiguous()
+        fwd = lambda: L.gs_raster_fwd(3, H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                      conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), bg.data_ptr(), out.data_ptr(),
+                                      fT.data_ptr(), fidx.data_ptr(), _lib.stream_ptr())
+        st["raster_fwd"] = (timed(fwd), None)
+        g = [torch.zeros((N, k), device=dev) for k in (2, 3, 3, 1)]
+        bwd = lambda: L.gs_raster_bwd(3, H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                      conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), bg.data_ptr(), fT.data_ptr(),
+                                      fidx.data_ptr(), v_out.data_ptr(), None, g[0].data_ptr(), g[1].data_ptr(),
+                                      g[2].data_ptr(), g[3].data_ptr(), _lib.stream_ptr())
+        st["raster_bwd"] = (timed(bwd), None)
+        vcoef = torch.empty((N, 16, 3), device=dev)
+        st["sh_bwd"] = (timed(lambda: L.gs_sh_bwd(N, 16, SH_DEG, dirs.data_ptr(), g[2].data_ptr(), vcoef.data_ptr(),
+                                                  _lib.stream_ptr())), 216 * N)
+        vm, vs, vq = torch.empty_like(means), torch.empty_like(means), torch.empty_like(quats)
+        vdep = torch.zeros(N, device=dev)
+        st["project_bwd"] = (timed(lambda: L.gs_project_bwd(N, means.data_ptr(), scales.data_ptr(), 1.0, quats.data_ptr(),
+                                                            Vd.data_ptr(), PVd.data_ptr(), cam.fx, cam.fy, H, W,
+                                                            radii.data_ptr(), g[0].data_ptr(), vdep.data_ptr(),
+                                                            g[1].data_ptr(), vm.data_ptr(), vs.data_ptr(), vq.data_ptr(),
+                                                            _lib.stream_ptr())), 144 * N)
+    return st, I, int((radii > 0).sum().item())
+
+
+def run_ours(args):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)")
+    from gaussctrl_exp_b200 import _lib, scene
+    from gaussctrl_exp_b200 import dist as gdist
+    from gaussctrl_exp_b200.model import GaussianModel
+    import torch.distributed as dist
+    _lib.lib()
+    rank, local, world = gdist.init_from_env("nccl")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    H = W = 512
+    model = GaussianModel(scene.make_scene(args.n_gaussians, 0), sh_degree=SH_DEG,
+                          background_color=torch.tensor(BG)).to(dev)
+    model.train()
+    params = [model.means, model.scales, model.quats, model.features_dc, model.features_rest, model.opacities]
+    cams = scene.make_cameras(N_CAMS, 0)
+    g = torch.Generator().manual_seed(1234)
+    v_host = (torch.randn(H, W, 3, generator=g) / (H * W)).pin_memory()
+    v_out = v_host.to(dev)
+    tgt_host = torch.rand(H, W, 3, generator=g).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(i):
+        cam = cams[(i * world + rank) % N_CAMS]
+        for p in params:
+            p.grad = None
+        out = model(cam)
+        (out["rgb"] * v_out).sum().backward()
+        gdist.allreduce_grads(params)
+
+    def step_e2e(i):
+        cam = cams[(i * world + rank) % N_CAMS]
+        tgt = tgt_host.to(dev, non_blocking=True)           # H2D of the step's target image (pinned)
+        for p in params:
+            p.grad = None
+        out = model(cam)
+        loss = (out["rgb"] - tgt).abs().mean()
+        loss.backward()
+        gdist.allreduce_grads(params)
+        return float(loss.item())                            # D2H of the step's result
+
+    def timed_loop(fn, warmup, steps):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = _lib.launch_count()
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), _lib.launch_count() - l0
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_total, launches = timed_loop(step, args.warmup, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e, _ = timed_loop(step_e2e, max(3, args.warmup // 2), args.steps)
+
+    line = None
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        value = world * 1e3 / ms_step
+        line = {
+            "metric": METRIC, "value": value, "unit": "views/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
+            "clocks": clocks, "gpu_launches": int(launches),
+            "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "views/s",
+                    "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4},
+        }
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak, peak_src = (peaks.get("hbm_gbs"), "measured") if peaks.get("hbm_gbs") else (6650.0, "fallback")
+        if not args.no_stages:
+            st, I, vis = stage_breakdown(model, cams, v_out)
+            stages = {}
+            for k, (sec, byts) in st.items():
+                stages[k] = {"us": sec * 1e6}
+                if byts:
+                    stages[k].update({"alg_bytes": int(byts), "GBps": byts / sec / 1e9, "frac_hbm": byts / sec / 1e9 / hbm_peak})
+            line["stages"] = stages
+            line["intersections"] = I
+            line["visible"] = vis
+            hbm_stages = {k: v for k, v in stages.items() if "GBps" in v}
+            top = max(hbm_stages, key=lambda k: hbm_stages[k]["us"])
+            line["roofline"] = {"bound": "hbm", "kernel": top, "achieved": hbm_stages[top]["GBps"], "peak": hbm_peak,
+                                "peak_source": peak_src, "unit": "GB/s", "frac": hbm_stages[top]["frac_hbm"],
+                                "traffic": None}
+        if world == 1 and not args.no_cpu:
+            ref = CpuReference(args.n_gaussians)
+            ref.run(1)
+            vps, dt = ref.run(args.cpu_views, first=1)
+            line["cpu_baseline"] = {"value": vps, "unit": "views/s", "cores": ref.cores, "kind": "port",
+                                    "sample": f"{args.cpu_views} views of the same workload (fwd+bwd), C oracle + OpenMP, {dt:.1f} s"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n-gaussians", type=int, default=N_GAUSS)
+    ap.add_argument("--cpu-views", type=int, default=8)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-stages", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,80 @@
+"""View-parallel multi-GPU plumbing: one process per GPU, Gaussian parameters
+replicated, cameras sharded round-robin, and — for the edit fine-tune step
+(/root/reference/gaussctrl/gc_trainer.py:258-301) — one sum-allreduce of the six parameter
+gradients (59 floats per Gaussian; the optimiser groups of gc_config.py:58-87).
+
+The all-view render (gc_pipeline.py:222-228) needs no collective; `gather_views` exists for a
+consumer that wants every image on rank 0.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Sequence
+
+import torch
+import torch.distributed as dist
+
+GRAD_PARAMS = ("means", "scales", "quats", "features_dc", "features_rest", "opacities")
+
+
+def init_from_env(backend: str | None = None):
+    """Initialise torch.distributed from torchrun's env (RANK/LOCAL_RANK/WORLD_SIZE/MASTER_*).
+    Returns (rank, local_rank, world). world == 1 without torchrun: no process group is made."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
+    return rank, local, world
+
+
+def shard_views(num_views: int, rank: int, world: int) -> List[int]:
+    """Round-robin: rank r renders views {v : v mod world == r} (balances per-view cost variance
+    better than contiguous blocks)."""
+    return list(range(rank, num_views, world))
+
+
+def owner_of_view(view: int, world: int) -> int:
+    return view % world
+
+
+def allreduce_grads(params: Dict[str, torch.Tensor] | Sequence[torch.Tensor], average: bool = True) -> None:
+    """Sum (or mean) the gradients of the replicated Gaussian parameters across ranks, in place.
+    `average=True` keeps the reference's per-view learning-rate semantics."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    tensors = list(params.values()) if isinstance(params, dict) else list(params)
+    grads = [p.grad for p in tensors if p.grad is not None]
+    works = [dist.all_reduce(g, op=dist.ReduceOp.SUM, async_op=True) for g in grads]
+    for w in works:
+        w.wait()
+    if average:
+        torch._foreach_div_(grads, float(dist.get_world_size()))
+
+
+def gather_views(local: Dict[int, torch.Tensor], num_views: int, dst: int = 0):
+    """Collect per-view tensors (same shape/dtype everywhere) on rank `dst`; returns a list
+    indexed by view on dst, None elsewhere."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return [local[v] for v in range(num_views)]
+    world, rank = dist.get_world_size(), dist.get_rank()
+    out = [None] * num_views if rank == dst else None
+    sample = next(iter(local.values()))
+    for v in range(num_views):
+        src = owner_of_view(v, world)
+        if src == dst:
+            if rank == dst:
+                out[v] = local[v]
+        elif rank == src:
+            dist.send(local[v].contiguous(), dst)
+        elif rank == dst:
+            buf = torch.empty_like(sample)
+            dist.recv(buf, src)
+            out[v] = buf
+    return out
