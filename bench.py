@@ -236,7 +236,7 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     H = W = 512
     model = GaussianModel(scene.make_scene(args.n_gaussians, 0), sh_degree=SH_DEG,
-                          background_color=torch.tensor(BG)).to(dev)
+                          background_color=torch.tensor(BG), fused=(args.path == "fused")).to(dev)
     model.train()
     params = [model.means, model.scales, model.quats, model.features_dc, model.features_rest, model.opacities]
     cams = scene.make_cameras(N_CAMS, 0)
@@ -250,13 +250,22 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def reduce_grads():
+        if world == 1:
+            return
+        flat = model.view_state.flat_grads if model.fused else None
+        if flat is not None:
+            gdist.allreduce_flat(flat)
+        else:
+            gdist.allreduce_grads(params)
+
     def step(i):
         cam = cams[(i * world + rank) % N_CAMS]
         for p in params:
             p.grad = None
         out = model(cam)
         (out["rgb"] * v_out).sum().backward()
-        gdist.allreduce_grads(params)
+        reduce_grads()
 
     def step_e2e(i):
         cam = cams[(i * world + rank) % N_CAMS]
@@ -266,7 +275,7 @@ def run_ours(args):
         out = model(cam)
         loss = (out["rgb"] - tgt).abs().mean()
         loss.backward()
-        gdist.allreduce_grads(params)
+        reduce_grads()
         return float(loss.item())                            # D2H of the step's result
 
     def timed_loop(fn, warmup, steps):
@@ -301,7 +310,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": "views/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
-            "clocks": clocks, "gpu_launches": int(launches),
+            "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
             "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "views/s",
                     "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4},
         }
@@ -348,6 +357,9 @@ def main():
     ap.add_argument("--cpu-views", type=int, default=8)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
+    ap.add_argument("--path", default="fused", choices=["fused", "api"],
+                    help="fused: one autograd node / 5 kernels per view (render.py); api: the literal "
+                         "gsplat-0.1.2 three-operator sequence of gc_model.py")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

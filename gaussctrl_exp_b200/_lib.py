@@ -27,6 +27,9 @@ SIGNATURES = {
                             _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_project_bwd": (_i, [_i, _vp, _vp, _f, _vp, _vp, _vp, _f, _f, _i, _i, _vp, _vp, _vp, _vp,
                             _vp, _vp, _vp, _vp]),
+    "gs_preprocess_fwd": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_preprocess_bwd": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                               _vp, _vp, _vp, _vp, _vp]),
     "gs_sh_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "gs_sh_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "gs_scan_scratch_bytes": (_sz, [_i]),
@@ -41,6 +44,16 @@ SIGNATURES = {
     "gs_raster_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                            _vp, _vp, _vp, _vp, _vp]),
 }
+
+
+
+class GsCamera(C.Structure):
+    """Mirror of `struct GsCamera` in include/gs_b200.h (host memory, passed by pointer)."""
+    _fields_ = [("viewmat", C.c_float * 12), ("projmat", C.c_float * 16), ("cam_pos", C.c_float * 3),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("glob_scale", C.c_float), ("clip", C.c_float),
+                ("H", C.c_int32), ("W", C.c_int32), ("tiles_x", C.c_int32), ("tiles_y", C.c_int32)]
+
 
 _ERRORS = {-1: "GS_ERR_BAD_ARG", -2: "GS_ERR_SCRATCH_SMALL", -3: "GS_ERR_UNSUPPORTED", -4: "GS_ERR_MISALIGNED"}
 

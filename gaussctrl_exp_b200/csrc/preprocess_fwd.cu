@@ -1,0 +1,140 @@
+// Fused per-view preprocess, forward: everything the reference's host code does per Gaussian
+// between the leaf parameters and rasterize_gaussians, in ONE pass over HBM
+// (/root/reference/gaussctrl/gc_model.py:172-203 + :215):
+//   cat(features_dc, features_rest) | exp(scales) | quats/|quats| | project_gaussians |
+//   normalise(means - cam_pos) | spherical_harmonics | clamp(+0.5, min 0) | sigmoid(opacities)
+// The unfused path moves ~1.1 GB per 1 M Gaussians for this (the cat alone re-writes the 192 MB
+// SH block); fused it is the compulsory 236 B in + 48 B out per Gaussian.
+//
+// The (N,15,3) features_rest block of a 128-Gaussian CTA is one dense 23 040 B span: it is
+// fetched by ONE TMA bulk copy (cp.async.bulk, completion on an mbarrier) that overlaps the
+// projection arithmetic; rows are 45 floats (odd) so per-thread row reads are bank-conflict free.
+//
+// COMPILED WITH -fmad=false (shares the bit-exact projection math with project_fwd.cu).
+#include "project_math.cuh"
+#include "sh_math.cuh"
+
+namespace {
+
+constexpr int PP_TPB = 128;
+constexpr int PP_REST = 45;  // floats of features_rest per Gaussian (15 bases x 3 channels)
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__global__ void __launch_bounds__(PP_TPB)
+preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__restrict__ log_scales,
+                      const float4 *__restrict__ quats, const float *__restrict__ opac_logits,
+                      const float *__restrict__ feat_dc, const float *__restrict__ feat_rest, int use_sh, int deg,
+                      const __grid_constant__ GsCamera cam, float2 *__restrict__ xys, float *__restrict__ depths,
+                      int32_t *__restrict__ radii, float *__restrict__ conics, int32_t *__restrict__ tiles_hit,
+                      float *__restrict__ rgbs, float *__restrict__ opac) {
+    __shared__ __align__(128) float rest_s[PP_TPB * PP_REST];
+    __shared__ __align__(8) unsigned long long mbar;
+    const int tid = threadIdx.x;
+    const int g0 = blockIdx.x * PP_TPB;
+    const int rows = min(PP_TPB, N - g0);
+    const bool need_rest = use_sh && deg >= 1;
+
+    if (need_rest) {
+        const int rows4 = rows & ~3;                      // 4 rows = 720 B: keeps the bulk size a multiple of 16
+        const unsigned bytes = (unsigned)rows4 * PP_REST * 4u;
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mbar)));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&mbar)), "r"(bytes)
+                         : "memory");
+            if (bytes)
+                asm volatile(
+                    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                        smem_u32(rest_s)),
+                    "l"(feat_rest + (size_t)g0 * PP_REST), "r"(bytes), "r"(smem_u32(&mbar))
+                    : "memory");
+        }
+        for (int f = rows4 * PP_REST + tid; f < rows * PP_REST; f += PP_TPB)
+            rest_s[f] = feat_rest[(size_t)g0 * PP_REST + f];
+    }
+
+    const int i = g0 + tid;
+    float p0 = 0.f, p1 = 0.f, p2 = 0.f;
+    ProjOut o;
+    o.radius = 0;
+    if (i < N) {
+        p0 = means[3 * i]; p1 = means[3 * i + 1]; p2 = means[3 * i + 2];
+        const float s0 = expf(log_scales[3 * i]), s1 = expf(log_scales[3 * i + 1]), s2 = expf(log_scales[3 * i + 2]);
+        float4 q = quats[i];
+        const float qn = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);   // quats / quats.norm()
+        q.x = q.x / qn; q.y = q.y / qn; q.z = q.z / qn; q.w = q.w / qn;
+        gs_project_one(cam.viewmat, cam.projmat, p0, p1, p2, s0, s1, s2, cam.glob_scale, q, cam.fx, cam.fy, cam.cx,
+                       cam.cy, cam.H, cam.W, cam.tiles_x, cam.tiles_y, cam.clip, o);
+        xys[i] = o.xy;
+        depths[i] = o.depth;
+        radii[i] = o.radius;
+        conics[3 * i] = o.ca; conics[3 * i + 1] = o.cb; conics[3 * i + 2] = o.cc;
+        tiles_hit[i] = o.hit;
+        opac[i] = 1.0f / (1.0f + expf(-opac_logits[i]));
+    }
+
+    if (need_rest) {
+        __syncthreads();  // mbarrier init + remainder rows visible
+        unsigned done = 0;
+        while (!done)
+            asm volatile(
+                "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n selp.u32 %0, 1, 0, p;\n}"
+                : "=r"(done)
+                : "r"(smem_u32(&mbar))
+                : "memory");
+    }
+    if (i >= N) return;
+
+    float r = 0.f, g = 0.f, b = 0.f;
+    if (o.radius > 0) {      // culled Gaussians never reach the compositor: colour left at 0
+        const float d0 = feat_dc[3 * i], d1 = feat_dc[3 * i + 1], d2 = feat_dc[3 * i + 2];
+        if (use_sh) {
+            // viewdirs = normalise(means - cam_pos)  (gc_model.py:197-198); the SH routine normalises again
+            float vx = p0 - cam.cam_pos[0], vy = p1 - cam.cam_pos[1], vz = p2 - cam.cam_pos[2];
+            const float vn = sqrtf(vx * vx + vy * vy + vz * vz);
+            vx = vx / vn; vy = vy / vn; vz = vz / vn;
+            float Y[16];
+            sh_basis<3>(deg, vx, vy, vz, Y);
+            r = Y[0] * d0; g = Y[0] * d1; b = Y[0] * d2;
+            const int nb = sh_num_bases(deg);
+            const float *row = rest_s + tid * PP_REST;
+#pragma unroll
+            for (int k = 1; k < 16; ++k)
+                if (k < nb) {
+                    r += Y[k] * row[3 * (k - 1)];
+                    g += Y[k] * row[3 * (k - 1) + 1];
+                    b += Y[k] * row[3 * (k - 1) + 2];
+                }
+            r = fmaxf(r + 0.5f, 0.0f); g = fmaxf(g + 0.5f, 0.0f); b = fmaxf(b + 0.5f, 0.0f);   // :201
+        } else {
+            r = 1.0f / (1.0f + expf(-d0)); g = 1.0f / (1.0f + expf(-d1)); b = 1.0f / (1.0f + expf(-d2));   // :203
+        }
+    }
+    rgbs[3 * i] = r; rgbs[3 * i + 1] = g; rgbs[3 * i + 2] = b;
+}
+
+}  // namespace
+
+extern "C" int gs_preprocess_fwd(int N, const float *means, const float *log_scales, const float *quats,
+                                 const float *opac_logits, const float *feat_dc, const float *feat_rest,
+                                 int use_sh, int sh_deg, const GsCamera *cam_host,
+                                 float *xys, float *depths, int32_t *radii, float *conics, int32_t *tiles_hit,
+                                 float *rgbs, float *opac, void *stream) {
+    if (N < 0 || !cam_host) return GS_ERR_BAD_ARG;
+    if (sh_deg < 0 || sh_deg > 3) return GS_ERR_UNSUPPORTED;
+    if (cam_host->H <= 0 || cam_host->W <= 0 || cam_host->tiles_x <= 0 || cam_host->tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (N == 0) return 0;
+    if (!means || !log_scales || !quats || !opac_logits || !feat_dc || !xys || !depths || !radii || !conics ||
+        !tiles_hit || !rgbs || !opac)
+        return GS_ERR_BAD_ARG;
+    if (use_sh && sh_deg >= 1 && !feat_rest) return GS_ERR_BAD_ARG;
+    if (!gs_aligned16(quats) || !gs_aligned16(feat_rest) || (reinterpret_cast<uintptr_t>(xys) & 7u))
+        return GS_ERR_MISALIGNED;
+    const int blocks = (N + PP_TPB - 1) / PP_TPB;
+    preprocess_fwd_kernel<<<blocks, PP_TPB, 0, (cudaStream_t)stream>>>(
+        N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
+        *cam_host, reinterpret_cast<float2 *>(xys), depths, radii, conics, tiles_hit, rgbs, opac);
+    GS_LAUNCH_CHECK();
+    return 0;
+}

@@ -5,7 +5,8 @@
 // Exact derivative of raster_fwd.cu. One CTA per tile, one pixel per thread, back-to-front
 // replay from each pixel's final_idx. gsplat 0.1.2 issues >= 9 global float atomics per
 // (pixel, Gaussian) hit; here the 9 partial gradients of a Gaussian are
-//   (1) skipped outright when no lane of the warp hit it (warp ballot),
+//   (1) skipped outright when the splat's alpha >= 1/255 box misses the warp's 8x4 pixel rect
+//       (per-warp compacted survivor lists) or no lane of the warp hit it (warp ballot),
 //   (2) reduced across the warp with a halving butterfly (9 + 5 shuffles instead of 45),
 //   (3) accumulated, conflict- and atomic-free, into per-warp shared-memory rows,
 //   (4) summed over the 8 warps and flushed with ONE red.global.add per (tile, Gaussian,
@@ -67,8 +68,10 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     __shared__ float4 sa[RB_BATCH];  // x, y, opac, conic.a
     __shared__ float4 sb[RB_BATCH];  // conic.b, conic.c, r, g
     __shared__ float sc[RB_BATCH];   // b
+    __shared__ float2 se[RB_BATCH];  // alpha >= 1/255 half-extents
     __shared__ int sid[RB_BATCH];
     __shared__ float acc[8][RB_BATCH * RB_NV];
+    __shared__ unsigned char wlist[8][RB_BATCH];
     __shared__ int s_wmax[8];
 
     const int tile = blockIdx.x;
@@ -78,6 +81,9 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     gs_pixel_of_thread(tile_x, tile_y, px, py);
     const bool inside = px < W && py < H;
     const float fx = (float)px + GS_PIX_CENTER, fy = (float)py + GS_PIX_CENTER;
+    float rx0, ry0;
+    gs_warp_rect(tile_x, tile_y, rx0, ry0);
+    const float rx1 = rx0 + 7.0f, ry1 = ry0 + 3.0f;
     const int2 range = tile_bins[tile];
     const size_t pix = inside ? (size_t)py * W + px : 0;
 
@@ -102,20 +108,40 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     for (int w = 0; w < 8; ++w) bmax = max(bmax, s_wmax[w]);
 
     float *my_acc = acc[warp];
+    unsigned char *mylist = wlist[warp];
     for (int hi = bmax; hi > range.x; hi -= RB_BATCH) {
         const int lo = max(range.x, hi - RB_BATCH);
         const int cnt = hi - lo;
         if (tid < cnt) {
             const int id = ids_sorted[lo + tid];
             const float2 xy = xys[id];
-            sa[tid] = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
-            sb[tid] = make_float4(conics[3 * id + 1], conics[3 * id + 2], colors[3 * id], colors[3 * id + 1]);
+            const float4 A = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
+            const float4 B = make_float4(conics[3 * id + 1], conics[3 * id + 2], colors[3 * id], colors[3 * id + 1]);
+            sa[tid] = A; sb[tid] = B;
             sc[tid] = colors[3 * id + 2];
+            se[tid] = gs_alpha_extent(A.z, A.w, B.x, B.y);
             sid[tid] = id;
         }
         __syncthreads();
-        const int jtop = min(cnt, wmax - lo) - 1;  // warp-uniform
-        for (int j = jtop; j >= 0; --j) {
+        // ---- per-warp culling (same exact-skip argument as the forward) ----
+        const int jend = min(cnt, wmax - lo);   // warp-uniform: nothing past this warp's last contributor
+        int nl = 0;
+        for (int j0 = 0; j0 < jend; j0 += 32) {
+            const int j = j0 + lane;
+            bool keep = false;
+            if (j < jend) {
+                const float4 A = sa[j];
+                const float2 E = se[j];
+                keep = (A.x + E.x >= rx0) && (A.x - E.x <= rx1) && (A.y + E.y >= ry0) && (A.y - E.y <= ry1);
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) mylist[nl + __popc(m & gs_lanemask_lt())] = (unsigned char)j;
+            nl += __popc(m);
+        }
+        __syncwarp();
+        // ---- back-to-front replay over the survivors ----
+        for (int t = nl - 1; t >= 0; --t) {
+            const int j = mylist[t];
             const float4 A = sa[j];
             const float4 B = sb[j];
             GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};

@@ -25,3 +25,26 @@ __device__ __forceinline__ bool gs_eval_alpha(const GsSplat &g, float fx, float 
     alpha = fminf(GS_ALPHA_MAX, g.opac * vis);
     return !(sigma < 0.0f || alpha < GS_ALPHA_MIN);
 }
+
+// Conservative half-extents (in pixels) of the region where a splat can reach alpha >= 1/255:
+//   alpha = opac * exp(-sigma) >= 1/255  <=>  sigma <= tau = ln(255 * opac)
+//   {sigma <= tau} is the ellipse 1/2 d^T Q d <= tau (Q = conic), whose bounding box is
+//   |dx| <= sqrt(2 tau c / det Q), |dy| <= sqrt(2 tau a / det Q).
+// Pairs outside the box would be skipped by the alpha test anyway, so culling them changes no
+// output bit; the 1e-4 inflation keeps the test on the safe side of fp32 / __expf rounding.
+__device__ __forceinline__ float2 gs_alpha_extent(float opac, float ca, float cb, float cc) {
+    const float det = ca * cc - cb * cb;
+    if (!(det > 0.0f) || !(ca > 0.0f) || !(cc > 0.0f)) return make_float2(3.0e38f, 3.0e38f);  // not PD: never cull
+    const float t = 255.0f * opac;
+    if (!(t > 1.0f)) return make_float2(-1.0f, -1.0f);                                        // can never pass
+    const float tau2 = 2.0f * __logf(t) * 1.001f + 1e-4f;
+    const float inv = 1.0f / det;
+    return make_float2(sqrtf(tau2 * cc * inv) * 1.0001f + 1e-4f, sqrtf(tau2 * ca * inv) * 1.0001f + 1e-4f);
+}
+
+// origin (pixel-centre coordinates) of the calling warp's 8x4 pixel rect
+__device__ __forceinline__ void gs_warp_rect(int tile_x, int tile_y, float &x0, float &y0) {
+    const int warp = threadIdx.x >> 5;
+    x0 = (float)(tile_x * GS_TILE + (warp & 1) * 8) + GS_PIX_CENTER;
+    y0 = (float)(tile_y * GS_TILE + (warp >> 1) * 4) + GS_PIX_CENTER;
+}

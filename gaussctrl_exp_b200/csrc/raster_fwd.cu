@@ -18,6 +18,7 @@ struct StageRGB {
     float4 a[RF_BATCH];  // x, y, opac, conic.a
     float4 b[RF_BATCH];  // conic.b, conic.c, r, g
     float c[RF_BATCH];   // b
+    float2 e[RF_BATCH];  // alpha >= 1/255 half-extents (gs_alpha_extent)
 };
 
 __global__ void __launch_bounds__(256)
@@ -27,24 +28,30 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                    const float *__restrict__ opac, const float *__restrict__ bg, float *__restrict__ out_img,
                    float *__restrict__ final_T, int32_t *__restrict__ final_idx) {
     __shared__ StageRGB st[2];
+    __shared__ unsigned char wlist[8][RF_BATCH];   // per-warp compacted survivors of the current batch
     const int tile = blockIdx.x;
     const int tile_x = tile % tiles_x, tile_y = tile / tiles_x;
     int px, py;
     gs_pixel_of_thread(tile_x, tile_y, px, py);
     const bool inside = px < W && py < H;
     const float fx = (float)px + GS_PIX_CENTER, fy = (float)py + GS_PIX_CENTER;
+    float rx0, ry0;
+    gs_warp_rect(tile_x, tile_y, rx0, ry0);
+    const float rx1 = rx0 + 7.0f, ry1 = ry0 + 3.0f;
     const int2 range = tile_bins[tile];
     const int n = range.y - range.x;
     const int nbatch = (n + RF_BATCH - 1) / RF_BATCH;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned char *mylist = wlist[warp];
 
     float T = 1.0f, r = 0.f, g = 0.f, b = 0.f;
     int last = range.x;
     bool done = !inside;
 
-    // register prefetch of the first batch
+    // register prefetch of the next batch: the gather latency hides behind the compositing
     float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pb = pa;
     float pc = 0.f;
+    float2 pe = make_float2(-1.f, -1.f);
     auto gather = [&](int batch) {
         const int k = range.x + batch * RF_BATCH + tid;
         if (k < range.y) {
@@ -53,30 +60,53 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             pa = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
             pb = make_float4(conics[3 * id + 1], conics[3 * id + 2], colors[3 * id], colors[3 * id + 1]);
             pc = colors[3 * id + 2];
+            pe = gs_alpha_extent(pa.z, pa.w, pb.x, pb.y);
         }
     };
     if (nbatch > 0) gather(0);
     for (int batch = 0; batch < nbatch; ++batch) {
         StageRGB &s = st[batch & 1];
-        s.a[tid] = pa; s.b[tid] = pb; s.c[tid] = pc;
+        s.a[tid] = pa; s.b[tid] = pb; s.c[tid] = pc; s.e[tid] = pe;
         if (__syncthreads_count(done) == 256) break;
         if (batch + 1 < nbatch) gather(batch + 1);
-        if (!done) {
-            const int cnt = min(RF_BATCH, n - batch * RF_BATCH);
-            const int kbase = range.x + batch * RF_BATCH;
-            for (int j = 0; j < cnt; ++j) {
+        if (__all_sync(0xffffffffu, done)) continue;          // warp-uniform: this warp's pixels are saturated
+        const int cnt = min(RF_BATCH, n - batch * RF_BATCH);
+        const int kbase = range.x + batch * RF_BATCH;
+        // ---- per-warp culling: keep the Gaussians whose alpha-extent box touches this warp's 8x4 rect ----
+        int nl = 0;
+        for (int j0 = 0; j0 < cnt; j0 += 32) {
+            const int j = j0 + lane;
+            bool keep = false;
+            if (j < cnt) {
                 const float4 A = s.a[j];
-                const float4 B = s.b[j];
-                GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};
-                float dx, dy, vis, alpha;
-                if (!gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha)) continue;
-                const float Tn = T * (1.0f - alpha);
-                if (Tn <= GS_T_EPS) { done = true; break; }
-                const float w = alpha * T;
-                r += w * B.z; g += w * B.w; b += w * s.c[j];
-                T = Tn;
-                last = kbase + j + 1;
+                const float2 E = s.e[j];
+                keep = (A.x + E.x >= rx0) && (A.x - E.x <= rx1) && (A.y + E.y >= ry0) && (A.y - E.y <= ry1);
             }
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) mylist[nl + __popc(m & gs_lanemask_lt())] = (unsigned char)j;
+            nl += __popc(m);
+        }
+        __syncwarp();
+        // ---- front-to-back compositing over the survivors ----
+        for (int t = 0; t < nl; ++t) {
+            const int j = mylist[t];
+            const float4 A = s.a[j];
+            const float4 B = s.b[j];
+            GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};
+            float dx, dy, vis, alpha;
+            const bool ok = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
+            if (!done && ok) {
+                const float Tn = T * (1.0f - alpha);
+                if (Tn <= GS_T_EPS) {
+                    done = true;
+                } else {
+                    const float w = alpha * T;
+                    r += w * B.z; g += w * B.w; b += w * s.c[j];
+                    T = Tn;
+                    last = kbase + j + 1;
+                }
+            }
+            if (__all_sync(0xffffffffu, done)) break;
         }
     }
     if (inside) {

@@ -44,6 +44,16 @@ def owner_of_view(view: int, world: int) -> int:
     return view % world
 
 
+def allreduce_flat(flat: torch.Tensor, average: bool = True) -> None:
+    """The fused render path writes all six leaf gradients into ONE flat buffer (59 floats per
+    Gaussian, render.ViewState.flat_grads) and the .grad tensors are views of it: one NCCL call."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    if average:
+        flat.div_(float(dist.get_world_size()))
+
+
 def allreduce_grads(params: Dict[str, torch.Tensor] | Sequence[torch.Tensor], average: bool = True) -> None:
     """Sum (or mean) the gradients of the replicated Gaussian parameters across ranks, in place.
     `average=True` keeps the reference's per-view learning-rate semantics."""

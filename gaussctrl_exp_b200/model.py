@@ -15,6 +15,7 @@ from typing import Dict, Optional, Union
 import torch
 from torch import Tensor, nn
 
+from . import render as _render
 from .project_gaussians import project_gaussians
 from .rasterize import rasterize_gaussians
 from .scene import Camera
@@ -87,7 +88,7 @@ class GaussianModel(nn.Module):
     """The six splatfacto leaf tensors + the render host code of GaussCtrlModel."""
 
     def __init__(self, params: Dict[str, Tensor], sh_degree: int = 3, sh_degree_interval: int = 1000,
-                 background_color: Union[str, Tensor] = "random", step: int = 30000):
+                 background_color: Union[str, Tensor] = "random", step: int = 30000, fused: bool = True):
         super().__init__()
         self.means = nn.Parameter(params["means"].clone())
         self.scales = nn.Parameter(params["scales"].clone())
@@ -99,6 +100,11 @@ class GaussianModel(nn.Module):
         self.sh_degree_interval = sh_degree_interval
         self.background_color = background_color
         self.step = step                       # a 30k-step splatfacto checkpoint (scripts/garden.sh:3)
+        # fused=True: one autograd node / five kernels per view (render.py); fused=False: the
+        # reference's literal three-operator sequence through the gsplat-compatible functions.
+        self.fused = fused
+        self.view_state = _render.ViewState()
+        self._mat_cache = {}
         self.xys: Optional[Tensor] = None
         self.radii: Optional[Tensor] = None
         self.last_size = None
@@ -121,7 +127,54 @@ class GaussianModel(nn.Module):
             return torch.ones(3, device=self.device)
         return torch.zeros(3, device=self.device)
 
+    def _caller_matrices(self, camera: Camera):
+        """mat_view / mat_proj of gc_model.py:121-126, :148 (cached per camera object)."""
+        hit = self._mat_cache.get(id(camera))
+        if hit is None or hit[0] is not camera:
+            _, _, viewmat0, projmat0, _ = camera_matrices(camera.c2w, camera.fx, camera.fy, int(camera.W), int(camera.H))
+            if len(self._mat_cache) > 4096:
+                self._mat_cache.clear()
+            hit = (camera, viewmat0, projmat0)
+            self._mat_cache[id(camera)] = hit
+        return hit[1], hit[2]
+
+    def _get_outputs_fused(self, camera: Camera) -> Dict[str, Optional[Tensor]]:
+        """Same outputs as the literal path below, through render.render_view."""
+        background = self._background()
+        W, H = int(camera.W), int(camera.H)
+        self.last_size = (H, W)
+        dev = self.device
+        use_sh = self.sh_degree > 0
+        n = min(self.step // self.sh_degree_interval, self.sh_degree) if use_sh else 0
+        cam = _render.gs_camera(camera)
+        if torch.is_grad_enabled() and self.training:
+            rgb, alpha, depths, radii, hit = _render.render_view(
+                self.means, self.scales, self.quats, self.opacities, self.features_dc, self.features_rest, camera,
+                n, use_sh, background, self.view_state)
+            self.xys, self.radii = self.view_state.xys, radii
+            viewmat0, projmat0 = self._caller_matrices(camera)
+            return {"rgb": torch.clamp(rgb, max=1.0), "depth": None, "accumulation": alpha[..., None],
+                    "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
+        with torch.no_grad(), torch.cuda.device(dev):
+            bg = background.to(dev).float().contiguous()
+            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I) = _render._forward_impl(
+                self.means.detach(), self.scales.detach(), self.quats.detach(), self.opacities.detach(),
+                self.features_dc.detach(), self.features_rest.detach(), cam, use_sh, n, bg)
+            self.xys, self.radii = xys, radii
+            alpha = (1.0 - fT)[..., None]
+            rgb = torch.clamp(out, max=1.0)
+            depth_im = None
+            if not self.training:                                     # gc_model.py:224-238, binning reused
+                depth_im = _render.composite_extra((xys, conics, opac, ids_sorted, bins), depths[:, None], camera,
+                                                   torch.zeros(1, device=dev))
+                depth_im = torch.where(alpha > 0, depth_im / alpha, torch.full_like(depth_im, 1000.0))
+        viewmat0, projmat0 = self._caller_matrices(camera)
+        return {"rgb": rgb, "depth": depth_im, "accumulation": alpha,
+                "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
+
     def get_outputs(self, camera: Camera) -> Dict[str, Optional[Tensor]]:
+        if self.fused:
+            return self._get_outputs_fused(camera)
         background = self._background()
         W, H = int(camera.W), int(camera.H)
         self.last_size = (H, W)

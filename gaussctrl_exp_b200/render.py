@@ -1,0 +1,254 @@
+"""Fused per-view render: ONE autograd node from the six splatfacto leaf tensors to (rgb, alpha).
+
+Same result as the three-operator sequence of /root/reference/gaussctrl/gc_model.py:172-222
+(pre-activations -> project_gaussians -> spherical_harmonics -> rasterize_gaussians) and its
+backward (gc_trainer.py:275), but as five kernel launches per training view:
+    forward : gs_preprocess_fwd -> gs_bin_fast -> gs_raster_fwd
+    backward: gs_raster_bwd -> gs_preprocess_bwd
+with no device->host synchronisation other than one 4-byte read of the intersection count, which
+is overlapped with the compositing kernel (the tile lists are allocated speculatively; the read
+only confirms the capacity was enough, otherwise the binning is redone).
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+from torch import Tensor
+from torch.autograd import Function
+
+from . import _lib
+from .scene import Camera
+
+_cam_cache = {}
+_cap_hint = {}
+_scratch = {}
+_pinned = {}
+
+
+def gs_camera(camera: Camera, glob_scale: float = 1.0, clip: float = 0.01) -> _lib.GsCamera:
+    """Host-side matrices of gc_model.py:117-155 packed into the C struct (cached per camera)."""
+    key = id(camera)
+    hit = _cam_cache.get(key)
+    if hit is not None and hit[0] is camera:
+        return hit[1]
+    c2w = camera.c2w.detach().cpu().numpy().astype(np.float32)
+    W, H = int(camera.W), int(camera.H)
+    R = c2w[:3, :3] @ np.diag(np.array([1, -1, -1], np.float32))       # :129-130
+    T = c2w[:3, 3:4]
+    Rinv = R.T
+    viewmat = np.eye(4, dtype=np.float32)
+    viewmat[:3, :3] = Rinv
+    viewmat[:3, 3:4] = -Rinv @ T
+    fovx = 2 * math.atan(W / (2 * camera.fx))                           # :143-144
+    fovy = 2 * math.atan(H / (2 * camera.fy))
+    n, f = 0.001, 1000.0                                                # :147
+    t = n * math.tan(0.5 * fovy)
+    r = n * math.tan(0.5 * fovx)
+    P = np.array([[2 * n / (2 * r), 0.0, 0.0, 0.0],
+                  [0.0, 2 * n / (2 * t), 0.0, 0.0],
+                  [0.0, 0.0, (f + n) / (f - n), -1.0 * f * n / (f - n)],
+                  [0.0, 0.0, 1.0, 0.0]], dtype=np.float32)
+    PV = (P @ viewmat).astype(np.float32)
+    cam = _lib.GsCamera()
+    cam.viewmat[:] = viewmat[:3].reshape(-1).tolist()
+    cam.projmat[:] = PV.reshape(-1).tolist()
+    cam.cam_pos[:] = c2w[:3, 3].tolist()
+    cam.fx, cam.fy, cam.cx, cam.cy = float(camera.fx), float(camera.fy), float(camera.cx), float(camera.cy)
+    cam.glob_scale, cam.clip = float(glob_scale), float(clip)
+    cam.H, cam.W = H, W
+    cam.tiles_x, cam.tiles_y = (W + 15) // 16, (H + 15) // 16
+    if len(_cam_cache) > 4096:
+        _cam_cache.clear()
+    _cam_cache[key] = (camera, cam)
+    return cam
+
+
+def _get_scratch(dev, nbytes):
+    buf = _scratch.get(dev.index)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(int(nbytes * 1.25) + 256, device=dev, dtype=torch.uint8)
+        _scratch[dev.index] = buf
+    return buf
+
+
+def _get_pinned(dev):
+    p = _pinned.get(dev.index)
+    if p is None:
+        p = (torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event())
+        _pinned[dev.index] = p
+    return p
+
+
+class ViewState:
+    """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii)."""
+    __slots__ = ("xys", "radii", "depths", "num_intersects", "xys_grad", "flat_grads")
+
+    def __init__(self):
+        self.xys = self.radii = self.depths = self.xys_grad = self.flat_grads = None
+        self.num_intersects = 0
+
+
+def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg):
+    L = _lib.lib()
+    dev = means.device
+    N = means.shape[0]
+    H, W, tx, ty = cam.H, cam.W, cam.tiles_x, cam.tiles_y
+    T = tx * ty
+    Np = (N + 3) // 4 * 4
+    fbuf = torch.empty(10 * Np, device=dev, dtype=torch.float32)
+    ibuf = torch.empty(2 * Np, device=dev, dtype=torch.int32)
+    xys = fbuf[0:2 * N].view(N, 2)
+    depths = fbuf[2 * Np:2 * Np + N]
+    conics = fbuf[3 * Np:3 * Np + 3 * N].view(N, 3)
+    rgbs = fbuf[6 * Np:6 * Np + 3 * N].view(N, 3)
+    opac = fbuf[9 * Np:9 * Np + N]
+    radii, hit = ibuf[0:N], ibuf[Np:Np + N]
+    st = _lib.stream_ptr()
+    rc = L.gs_preprocess_fwd(N, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(),
+                             features_dc.data_ptr(), features_rest.data_ptr(), int(use_sh), int(deg),
+                             _ctypes_addr(cam), xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), conics.data_ptr(),
+                             hit.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), st)
+    _lib.check(rc, "gs_preprocess_fwd")
+    key = (dev.index, N, T)
+    cap = _cap_hint.get(key, max(4 * N, 1024))
+    bins = torch.empty((T, 2), device=dev, dtype=torch.int32)
+    total = torch.empty(1, device=dev, dtype=torch.int32)
+    pinned, ev = _get_pinned(dev)
+    out = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
+    fT = torch.empty((H, W), device=dev, dtype=torch.float32)
+    fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
+    while True:
+        ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
+        scratch = _get_scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T))
+        rc = L.gs_bin_fast(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), hit.data_ptr(), tx, ty,
+                           ids_sorted.data_ptr(), bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
+                           scratch.numel(), st)
+        _lib.check(rc, "gs_bin_fast")
+        pinned.copy_(total, non_blocking=True)
+        ev.record()
+        # compositing is enqueued BEFORE the host looks at the count: it only reads tile_bins
+        rc = L.gs_raster_fwd(3, H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(), conics.data_ptr(),
+                             rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(), out.data_ptr(), fT.data_ptr(),
+                             fidx.data_ptr(), st)
+        _lib.check(rc, "gs_raster_fwd")
+        ev.synchronize()
+        I = int(pinned[0])
+        if I <= cap:
+            _cap_hint[key] = max(int(I * 1.25) + 1024, 1024)
+            break
+        cap = int(I * 1.25) + 1024      # capacity was too small: nothing was composited from a torn list; redo
+    return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I)
+
+
+def _ctypes_addr(struct):
+    import ctypes
+    return ctypes.addressof(struct)
+
+
+class _RenderView(Function):
+    @staticmethod
+    def forward(ctx, means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, state):
+        for t, shape in ((means, 3), (scales, 3), (quats, 4), (features_dc, 3)):
+            if t.ndim != 2 or t.shape[1] != shape or t.shape[0] != means.shape[0]:
+                raise ValueError("means/scales (N,3), quats (N,4), features_dc (N,3) expected")
+        if not means.is_cuda:
+            raise ValueError("render_view needs CUDA tensors (no CPU fallback)")
+        if features_rest.shape[1:] != (15, 3):
+            raise ValueError("features_rest must have dimensions (N, 15, 3)")
+        args = [t.detach().float().contiguous() for t in (means, scales, quats, opacities, features_dc, features_rest)]
+        bg = bg.detach().to(means.device).float().contiguous()
+        with torch.cuda.device(means.device):
+            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I) = _forward_impl(
+                *args, cam, use_sh, deg, bg)
+        ctx.save_for_backward(*args, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT, fidx)
+        ctx.cam, ctx.use_sh, ctx.deg, ctx.state = cam, use_sh, deg, state
+        if state is not None:
+            state.xys, state.radii, state.depths, state.num_intersects = xys, radii, depths, I
+        alpha = 1.0 - fT
+        ctx.mark_non_differentiable(depths, radii, hit)
+        return out, alpha, depths, radii, hit
+
+    @staticmethod
+    def backward(ctx, v_out, v_alpha, *_unused):
+        (means, scales, quats, opacities, fdc, frest, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT,
+         fidx) = ctx.saved_tensors
+        cam = ctx.cam
+        L = _lib.lib()
+        dev = means.device
+        N = means.shape[0]
+        H, W, tx, ty = cam.H, cam.W, cam.tiles_x, cam.tiles_y
+        v_out = v_out.float().contiguous()
+        va_ptr = None
+        if v_alpha is not None:
+            v_alpha = v_alpha.float().contiguous()
+            va_ptr = v_alpha.data_ptr()
+        Np = (N + 3) // 4 * 4
+        with torch.cuda.device(dev):
+            st = _lib.stream_ptr()
+            g = torch.zeros(9 * Np, device=dev, dtype=torch.float32)         # accumulated into by atomics
+            v_xys = g[0:2 * N].view(N, 2)
+            v_conics = g[2 * Np:2 * Np + 3 * N].view(N, 3)
+            v_rgbs = g[5 * Np:5 * Np + 3 * N].view(N, 3)
+            v_opac = g[8 * Np:8 * Np + N]
+            rc = L.gs_raster_bwd(3, H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(), conics.data_ptr(),
+                                 rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(), fT.data_ptr(), fidx.data_ptr(),
+                                 v_out.data_ptr(), va_ptr, v_xys.data_ptr(), v_conics.data_ptr(), v_rgbs.data_ptr(),
+                                 v_opac.data_ptr(), st)
+            _lib.check(rc, "gs_raster_bwd")
+            # the six leaf gradients live in ONE flat buffer (59 floats / Gaussian) so that the
+            # data-parallel step can all-reduce them with a single NCCL call
+            flat = torch.empty(59 * Np, device=dev, dtype=torch.float32)
+            v_means = flat[0:3 * N].view(N, 3)
+            v_scales = flat[3 * Np:3 * Np + 3 * N].view(N, 3)
+            v_quats = flat[6 * Np:6 * Np + 4 * N].view(N, 4)
+            v_opl = flat[10 * Np:10 * Np + N].view(opacities.shape)
+            v_dc = flat[11 * Np:11 * Np + 3 * N].view(N, 3)
+            v_rest = flat[14 * Np:14 * Np + 45 * N].view(N, 15, 3)
+            rc = L.gs_preprocess_bwd(N, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(),
+                                     int(ctx.use_sh), int(ctx.deg), _ctypes_addr(cam), radii.data_ptr(), rgbs.data_ptr(),
+                                     v_xys.data_ptr(), v_conics.data_ptr(), v_rgbs.data_ptr(), v_opac.data_ptr(),
+                                     v_means.data_ptr(), v_scales.data_ptr(), v_quats.data_ptr(), v_opl.data_ptr(),
+                                     v_dc.data_ptr(), v_rest.data_ptr(), st)
+            _lib.check(rc, "gs_preprocess_bwd")
+        if ctx.state is not None:
+            ctx.state.xys_grad = v_xys       # what gc_model.py:193-194 keeps via xys.retain_grad()
+            ctx.state.flat_grads = flat
+        return v_means, v_scales, v_quats, v_opl, v_dc, v_rest, None, None, None, None, None
+
+
+def render_view(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, features_dc: Tensor,
+                features_rest: Tensor, camera: Camera, sh_degree_to_use: int, use_sh: bool = True,
+                background: Optional[Tensor] = None, state: Optional[ViewState] = None
+                ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+    """RAW splatfacto leaves (log-scales, un-normalised wxyz quats, opacity logits (N,1),
+    features_dc (N,3), features_rest (N,15,3)) + one camera -> (rgb (H,W,3) before the caller's
+    clamp(max=1), alpha (H,W), depths (N), radii (N) i32, num_tiles_hit (N) i32)."""
+    if background is None:
+        background = torch.ones(3, dtype=torch.float32, device=means.device)
+    cam = gs_camera(camera)
+    return _RenderView.apply(means, scales, quats, opacities, features_dc, features_rest, cam, bool(use_sh),
+                             int(sh_degree_to_use), background, state)
+
+
+def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: Tensor) -> Tensor:
+    """Second compositing pass over the SAME binning (the eval depth pass of gc_model.py:225-236
+    re-bins and re-sorts in gsplat; here the tile lists of the RGB pass are reused).
+    state_tensors = (xys, conics, opac, ids_sorted, bins); colors (N,C) -> (H,W,C). No autograd."""
+    xys, conics, opac, ids_sorted, bins = state_tensors
+    cam = gs_camera(camera)
+    dev = xys.device
+    C = colors.shape[1]
+    colors = colors.float().contiguous()
+    bg = background.to(dev).float().contiguous()
+    out = torch.empty((cam.H, cam.W, C), device=dev, dtype=torch.float32)
+    fT = torch.empty((cam.H, cam.W), device=dev, dtype=torch.float32)
+    fidx = torch.empty((cam.H, cam.W), device=dev, dtype=torch.int32)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().gs_raster_fwd(C, cam.H, cam.W, cam.tiles_x, cam.tiles_y, ids_sorted.data_ptr(), bins.data_ptr(),
+                                      xys.data_ptr(), conics.data_ptr(), colors.data_ptr(), opac.data_ptr(),
+                                      bg.data_ptr(), out.data_ptr(), fT.data_ptr(), fidx.data_ptr(), _lib.stream_ptr())
+    _lib.check(rc, "gs_raster_fwd")
+    return out

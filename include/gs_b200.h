@@ -44,6 +44,19 @@ int gs_built_arch(void);
 /* count of kernel launches issued by this library since load (bench.py's gpu_launches). */
 int64_t gs_launch_count(void);
 
+/* One camera, by value, HOST memory (gc_model.py:117-155 builds exactly these numbers):
+ * viewmat = rows 0-2 of the y/z-flipped world->camera matrix, projmat = P @ viewmat,
+ * cam_pos = camera_to_worlds[:3,3]. */
+typedef struct GsCamera {
+    float viewmat[12];
+    float projmat[16];
+    float cam_pos[3];
+    float fx, fy, cx, cy;
+    float glob_scale;   /* 1 in the reference (gc_model.py:177) */
+    float clip;         /* near clip, 0.01 */
+    int32_t H, W, tiles_x, tiles_y;
+} GsCamera;
+
 /* ---- stage 1: projection (gc_model.py:174-188) ------------------------- */
 /* viewmat: >=12 floats (3x4 row-major), projmat: 16 floats (P@V); both DEVICE pointers.
  * Outputs are fully written (culled rows = 0). */
@@ -68,6 +81,28 @@ int gs_sh_fwd(int N, int K, int deg, const float *dirs, const float *coeffs, flo
 /* v_coeffs (N,K,3) fully written (unused bases = 0). */
 int gs_sh_bwd(int N, int K, int deg, const float *dirs, const float *v_colors, float *v_coeffs,
               void *stream);
+
+/* ---- stage 1, fused: pre-activations + projection + SH in one pass over the leaf parameters -----
+ * Replaces, for one view, gc_model.py:172-203 and :215: cat(features_dc, features_rest),
+ * exp(scales), quats/|quats|, project_gaussians, normalise(means - cam_pos), spherical_harmonics,
+ * clamp(+0.5, min 0) [use_sh != 0] or sigmoid(features_dc) [use_sh == 0], sigmoid(opacities).
+ * Inputs are the RAW splatfacto leaves: log-scales, un-normalised quats (wxyz), opacity logits,
+ * features_dc (N,3), features_rest (N,15,3). Outputs: xys (N,2), depths, radii, conics (N,3),
+ * tiles_hit as gs_project_fwd; rgbs (N,3) post-activation colours; opac (N) in (0,1).
+ * sh_deg <= 3 = degrees actually used (min(step // interval, sh_degree)). */
+int gs_preprocess_fwd(int N, const float *means, const float *log_scales, const float *quats,
+                      const float *opac_logits, const float *feat_dc, const float *feat_rest,
+                      int use_sh, int sh_deg, const GsCamera *cam_host,
+                      float *xys, float *depths, int32_t *radii, float *conics, int32_t *tiles_hit,
+                      float *rgbs, float *opac, void *stream);
+/* exact vjp of gs_preprocess_fwd: compositor gradients -> the six leaf gradients (all fully
+ * written; culled Gaussians get zeros). rgbs = the forward's colour output (activation masks). */
+int gs_preprocess_bwd(int N, const float *means, const float *log_scales, const float *quats,
+                      const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host,
+                      const int32_t *radii, const float *rgbs, const float *v_xys, const float *v_conics,
+                      const float *v_rgbs, const float *v_opac, float *v_means, float *v_log_scales,
+                      float *v_quats, float *v_opac_logits, float *v_feat_dc, float *v_feat_rest,
+                      void *stream);
 
 /* ---- stage 2: tile binning (inside rasterize_gaussians; App. A.3) -------------------------- */
 size_t gs_scan_scratch_bytes(int N);

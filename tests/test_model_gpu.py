@@ -11,18 +11,19 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-4
 
 
-def _model(p, dev, deg=3, bg=(0.1, 0.2, 0.3)):
+def _model(p, dev, deg=3, bg=(0.1, 0.2, 0.3), fused=True):
     from gaussctrl_exp_b200.model import GaussianModel
-    m = GaussianModel(to_dev(p, dev), sh_degree=deg, background_color=torch.tensor(bg)).to(dev)
+    m = GaussianModel(to_dev(p, dev), sh_degree=deg, background_color=torch.tensor(bg), fused=fused).to(dev)
     return m
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("N,W,H,deg,s0", [(20000, 160, 128, 3, 0.02), (50000, 512, 512, 0, 0.005), (4000, 75, 50, 2, 0.05)])
-def test_eval_outputs(oracle, cuda_dev, N, W, H, deg, s0):
+def test_eval_outputs(oracle, cuda_dev, N, W, H, deg, s0, fused):
     p = np_params(N, seed=11, s0=s0)
     cam = small_cam(W, H, 11) if W != 512 else __import__("gaussctrl_exp_b200.scene", fromlist=["x"]).make_cameras(1, 0)[0]
     ref, _ = oracle.render_view(p, cam.as_dict(), deg, training=False)
-    m = _model(p, cuda_dev, deg)
+    m = _model(p, cuda_dev, deg, fused=fused)
     out = m.get_outputs_for_camera(cam)
     assert m.training
     rgb, depth, acc = (out[k].cpu().numpy() for k in ("rgb", "depth", "accumulation"))
@@ -36,15 +37,16 @@ def test_eval_outputs(oracle, cuda_dev, N, W, H, deg, s0):
     assert out["mat_view"].shape == (4, 4) and out["mat_proj"].shape == (4, 4) and out["mat_c2w"].shape == (3, 4)
 
 
-@pytest.mark.parametrize("N,W,H,deg,s0", [(20000, 160, 128, 3, 0.02), (50000, 512, 512, 0, 0.005)])
-def test_train_gradients(oracle, cuda_dev, N, W, H, deg, s0):
+@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("N,W,H,deg,s0", [(20000, 160, 128, 3, 0.02), (50000, 512, 512, 0, 0.005), (3001, 70, 50, 1, 0.05)])
+def test_train_gradients(oracle, cuda_dev, N, W, H, deg, s0, fused):
     p = np_params(N, seed=12, s0=s0)
     from gaussctrl_exp_b200 import scene
     cam = small_cam(W, H, 12) if W != 512 else scene.make_cameras(1, 0)[0]
     ref, ctx = oracle.render_view(p, cam.as_dict(), deg, training=True)
     v = (np.random.default_rng(1234).standard_normal((H, W, 3)) / (H * W)).astype(np.float32)
     g = oracle.render_view_backward(p, ctx, v)
-    m = _model(p, cuda_dev, deg)
+    m = _model(p, cuda_dev, deg, fused=fused)
     m.train()
     out = m(cam)
     (out["rgb"] * torch.from_numpy(v).to(cuda_dev)).sum().backward()
@@ -56,7 +58,8 @@ def test_train_gradients(oracle, cuda_dev, N, W, H, deg, s0):
             assert np.abs(got).max() == 0
             continue
         assert rel_linf(got, g[name]) < tol, name
-    assert rel_linf(m.xys.grad.cpu().numpy(), g["xys"]) < tol   # kept for densification stats (gc_model.py:193-194)
+    xys_grad = m.view_state.xys_grad if fused else m.xys.grad   # kept for densification stats (gc_model.py:193-194)
+    assert rel_linf(xys_grad.cpu().numpy(), g["xys"]) < tol
 
 
 def test_full_size_properties(cuda_dev):

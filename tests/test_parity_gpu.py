@@ -208,3 +208,76 @@ def test_argument_errors(cuda_dev):
     with pytest.raises(ValueError):  # CPU tensors: no CPU fallback
         project_gaussians(torch.zeros((4, 3)), torch.zeros((4, 3)), 1, torch.zeros((4, 4)), torch.eye(4), torch.eye(4),
                           1, 1, 0, 0, 16, 16, (1, 1, 1))
+
+
+@pytest.mark.parametrize("N,W,H,deg,use_sh", [(30000, 160, 128, 3, True), (5003, 96, 64, 1, True), (999, 64, 48, 0, False),
+                                              (130, 64, 48, 2, True)])
+def test_fused_preprocess_matches_operator_chain(oracle, cuda_dev, N, W, H, deg, use_sh):
+    """gs_preprocess_fwd/bwd == the reference's op chain (gc_model.py:172-203, :215) evaluated with
+    torch ops + the unfused operators, on the same raw leaves."""
+    import ctypes
+    from gaussctrl_exp_b200 import _lib, project_gaussians, render, spherical_harmonics
+    dev = cuda_dev
+    p = to_dev(np_params(N, seed=31, s0=0.03), dev)
+    cam = small_cam(W, H, 31)
+    gc = render.gs_camera(cam)
+    leaves = {k: v.clone().requires_grad_() for k, v in p.items()}
+    V = torch.tensor(list(gc.viewmat), device=dev).view(3, 4)
+    PV = torch.tensor(list(gc.projmat), device=dev).view(4, 4)
+    tb = (gc.tiles_x, gc.tiles_y, 1)
+    xys, depths, radii, conics, hit, _ = project_gaussians(
+        leaves["means"], torch.exp(leaves["scales"]), 1, leaves["quats"] / leaves["quats"].norm(dim=-1, keepdim=True),
+        V, PV, cam.fx, cam.fy, cam.cx, cam.cy, H, W, tb)
+    coeffs = torch.cat((leaves["features_dc"][:, None, :], leaves["features_rest"]), dim=1)
+    if use_sh:
+        d = leaves["means"].detach() - cam.c2w[:3, 3].to(dev)
+        d = d / d.norm(dim=-1, keepdim=True)
+        rgbs = torch.clamp(spherical_harmonics(deg, d, coeffs) + 0.5, min=0.0)
+    else:
+        rgbs = torch.sigmoid(coeffs[:, 0, :])
+    opac = torch.sigmoid(leaves["opacities"])
+
+    L = _lib.lib()
+    o = dict(xys=torch.empty(N, 2, device=dev), depths=torch.empty(N, device=dev),
+             radii=torch.empty(N, device=dev, dtype=torch.int32), conics=torch.empty(N, 3, device=dev),
+             hit=torch.empty(N, device=dev, dtype=torch.int32), rgbs=torch.empty(N, 3, device=dev),
+             opac=torch.empty(N, device=dev))
+    rc = L.gs_preprocess_fwd(N, p["means"].data_ptr(), p["scales"].data_ptr(), p["quats"].data_ptr(),
+                             p["opacities"].data_ptr(), p["features_dc"].data_ptr(), p["features_rest"].data_ptr(),
+                             int(use_sh), deg, ctypes.addressof(gc), o["xys"].data_ptr(), o["depths"].data_ptr(),
+                             o["radii"].data_ptr(), o["conics"].data_ptr(), o["hit"].data_ptr(), o["rgbs"].data_ptr(),
+                             o["opac"].data_ptr(), _lib.stream_ptr())
+    assert rc == 0
+    vis = radii > 0
+    # exp/sigmoid are evaluated by different libraries (torch vs CUDA libm): 1-ulp input differences may move a
+    # radius across an integer for a vanishing fraction of Gaussians
+    same = (o["radii"] == radii) & (o["hit"] == hit)
+    assert (~same).float().mean().item() <= 1e-4
+    m = (vis & same).cpu().numpy()
+    for k, ref in (("xys", xys), ("depths", depths), ("conics", conics), ("opac", opac[:, 0])):
+        assert rel_linf(o[k].cpu().numpy()[m], ref.detach().cpu().numpy()[m]) < 1e-5, k
+    assert rel_linf(o["rgbs"].cpu().numpy()[m], rgbs.detach().cpu().numpy()[m]) < 2e-5
+    assert (o["rgbs"][~(o["radii"] > 0)] == 0).all()
+
+    g = torch.Generator().manual_seed(3)
+    v_xys = torch.randn(N, 2, generator=g).to(dev) * vis[:, None]
+    v_con = torch.randn(N, 3, generator=g).to(dev) * vis[:, None]
+    v_rgb = torch.randn(N, 3, generator=g).to(dev) * vis[:, None]
+    v_op = torch.randn(N, generator=g).to(dev) * vis
+    ((xys * v_xys).sum() + (conics * v_con).sum() + (rgbs * v_rgb).sum() + (opac[:, 0] * v_op).sum()).backward()
+    go = {k: torch.empty_like(v) for k, v in p.items()}
+    rc = L.gs_preprocess_bwd(N, p["means"].data_ptr(), p["scales"].data_ptr(), p["quats"].data_ptr(),
+                             p["opacities"].data_ptr(), int(use_sh), deg, ctypes.addressof(gc), o["radii"].data_ptr(),
+                             o["rgbs"].data_ptr(), v_xys.data_ptr(), v_con.data_ptr(), v_rgb.data_ptr(), v_op.data_ptr(),
+                             go["means"].data_ptr(), go["scales"].data_ptr(), go["quats"].data_ptr(),
+                             go["opacities"].data_ptr(), go["features_dc"].data_ptr(), go["features_rest"].data_ptr(),
+                             _lib.stream_ptr())
+    assert rc == 0
+    mm = same.cpu().numpy()
+    for k in ("means", "scales", "quats", "opacities", "features_dc", "features_rest"):
+        ref = leaves[k].grad.cpu().numpy()[mm]
+        got = go[k].cpu().numpy()[mm]
+        if np.abs(ref).max() == 0:
+            assert np.abs(got).max() == 0, k
+        else:
+            assert rel_linf(got, ref) < 1e-4, k
