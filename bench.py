@@ -212,6 +212,24 @@ def stage_breakdown(model, cams, v_out, iters=20):
         vcoef = torch.empty((N, 16, 3), device=dev)
         st["sh_bwd"] = (timed(lambda: L.gs_sh_bwd(N, 16, SH_DEG, dirs.data_ptr(), g[2].data_ptr(), vcoef.data_ptr(),
                                                   _lib.stream_ptr())), 216 * N)
+        # fused per-view kernels (render.py path)
+        import ctypes
+        from gaussctrl_exp_b200 import render
+        gc = render.gs_camera(cam)
+        raw = [t.detach().contiguous() for t in (model.means, model.scales, model.quats, model.opacities,
+                                                 model.features_dc, model.features_rest)]
+        o_xy, o_d, o_c, o_rgb, o_op = (torch.empty_like(t) for t in (xys, depths, conics, rgbs, opv))
+        o_r, o_h = torch.empty_like(radii), torch.empty_like(hit)
+        st["preprocess_fwd"] = (timed(lambda: L.gs_preprocess_fwd(
+            N, raw[0].data_ptr(), raw[1].data_ptr(), raw[2].data_ptr(), raw[3].data_ptr(), raw[4].data_ptr(),
+            raw[5].data_ptr(), 1, SH_DEG, ctypes.addressof(gc), o_xy.data_ptr(), o_d.data_ptr(), o_r.data_ptr(),
+            o_c.data_ptr(), o_h.data_ptr(), o_rgb.data_ptr(), o_op.data_ptr(), _lib.stream_ptr())), 284 * N)
+        gl = [torch.empty_like(t) for t in raw]
+        st["preprocess_bwd"] = (timed(lambda: L.gs_preprocess_bwd(
+            N, raw[0].data_ptr(), raw[1].data_ptr(), raw[2].data_ptr(), raw[3].data_ptr(), 1, SH_DEG,
+            ctypes.addressof(gc), o_r.data_ptr(), o_rgb.data_ptr(), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
+            g[3].data_ptr(), gl[0].data_ptr(), gl[1].data_ptr(), gl[2].data_ptr(), gl[3].data_ptr(), gl[4].data_ptr(),
+            gl[5].data_ptr(), _lib.stream_ptr())), 332 * N)
         vm, vs, vq = torch.empty_like(means), torch.empty_like(means), torch.empty_like(quats)
         vdep = torch.zeros(N, device=dev)
         st["project_bwd"] = (timed(lambda: L.gs_project_bwd(N, means.data_ptr(), scales.data_ptr(), 1.0, quats.data_ptr(),

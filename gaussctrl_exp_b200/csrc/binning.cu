@@ -5,7 +5,6 @@
 #include "radix.cuh"
 
 namespace {
-namespace cg = cooperative_groups;
 
 // ------------------------------------------------------------------------------------------
 // Inclusive int32 scan, single pass, decoupled look-back (warp-parallel window of 32 tiles).
@@ -22,8 +21,8 @@ struct ScanCtl {
 };
 
 __global__ void __launch_bounds__(SCAN_TPB)
-scan_kernel(int N, const int32_t *__restrict__ in, int32_t *__restrict__ out, int32_t *__restrict__ total,
-            ScanCtl *ctl, unsigned long long *status) {
+scan_kernel(int N, const int32_t *__restrict__ in, const uint32_t *__restrict__ gather, int exclusive,
+            int32_t *__restrict__ out, int32_t *__restrict__ total, ScanCtl *ctl, unsigned long long *status) {
     __shared__ unsigned int s_tile;
     __shared__ int s_warp[SCAN_TPB / 32];
     __shared__ int s_prefix;
@@ -32,8 +31,11 @@ scan_kernel(int N, const int32_t *__restrict__ in, int32_t *__restrict__ out, in
     __syncthreads();
     const int tile = (int)s_tile;
     const int base = tile * SCAN_TILE + tid * SCAN_IPT;
-    int v[SCAN_IPT];
-    if (base + SCAN_IPT <= N) {
+    int v[SCAN_IPT], raw[SCAN_IPT];
+    if (gather) {   // in[gather[i]]: scan of tiles_hit in depth order
+#pragma unroll
+        for (int j = 0; j < SCAN_IPT; ++j) v[j] = base + j < N ? in[gather[base + j]] : 0;
+    } else if (base + SCAN_IPT <= N) {
         const int4 a = *reinterpret_cast<const int4 *>(in + base);
         const int4 b = *reinterpret_cast<const int4 *>(in + base + 4);
         v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
@@ -41,6 +43,8 @@ scan_kernel(int N, const int32_t *__restrict__ in, int32_t *__restrict__ out, in
 #pragma unroll
         for (int j = 0; j < SCAN_IPT; ++j) v[j] = base + j < N ? in[base + j] : 0;
     }
+#pragma unroll
+    for (int j = 0; j < SCAN_IPT; ++j) raw[j] = v[j];
 #pragma unroll
     for (int j = 1; j < SCAN_IPT; ++j) v[j] += v[j - 1];
     int inc = v[SCAN_IPT - 1];
@@ -86,6 +90,10 @@ scan_kernel(int N, const int32_t *__restrict__ in, int32_t *__restrict__ out, in
     }
     __syncthreads();
     const int off = s_prefix + thread_off;
+    if (exclusive) {
+#pragma unroll
+        for (int j = 0; j < SCAN_IPT; ++j) v[j] -= raw[j];
+    }
     if (base + SCAN_IPT <= N) {
         *reinterpret_cast<int4 *>(out + base) = make_int4(v[0] + off, v[1] + off, v[2] + off, v[3] + off);
         *reinterpret_cast<int4 *>(out + base + 4) = make_int4(v[4] + off, v[5] + off, v[6] + off, v[7] + off);
@@ -143,34 +151,6 @@ emit_kernel(int N, const float2 *__restrict__ xys, const float *__restrict__ dep
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// 64-bit (tile, depth) key sort: cooperative persistent LSD radix over the live bits only.
-// ------------------------------------------------------------------------------------------
-struct SortPlan {
-    int npass;
-    int shift[8];
-    int bits[8];
-};
-
-__global__ void __launch_bounds__(gsradix::TPB)
-sort64_kernel(int64_t n, const uint64_t *k0, const uint32_t *v0, uint64_t *ka, uint32_t *va, uint64_t *kb,
-              uint32_t *vb, SortPlan plan, uint32_t *mat) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    auto &s = *reinterpret_cast<gsradix::Smem<uint64_t, 8> *>(smem_raw);
-    cg::grid_group grid = cg::this_grid();
-    const uint64_t *kin = k0;
-    const uint32_t *vin = v0;
-    // the final pass must land in (ka, va) = the caller's sorted outputs
-    bool to_a = (plan.npass & 1) != 0;
-    for (int p = 0; p < plan.npass; ++p) {
-        uint64_t *ko = to_a ? ka : kb;
-        uint32_t *vo = to_a ? va : vb;
-        gsradix::radix_pass<uint64_t, 8>(grid, s, n, kin, vin, ko, vo, plan.shift[p], plan.bits[p], mat, nullptr);
-        kin = ko; vin = vo;
-        to_a = !to_a;
-    }
-}
-
 // tile_bins[t] = [first index with tile t, last+1); zero-filled beforehand.
 __global__ void __launch_bounds__(256)
 edges_kernel(int64_t I, const int64_t *__restrict__ ks, int32_t *__restrict__ bins) {
@@ -179,21 +159,6 @@ edges_kernel(int64_t I, const int64_t *__restrict__ ks, int32_t *__restrict__ bi
     const int32_t t = (int32_t)(ks[k] >> 32);
     if (k == 0 || (int32_t)(ks[k - 1] >> 32) != t) bins[2 * t] = (int32_t)k;
     if (k == I - 1 || (int32_t)(ks[k + 1] >> 32) != t) bins[2 * t + 1] = (int32_t)(k + 1);
-}
-
-int g_coop_blocks_sort64 = 0;
-
-int coop_grid(const void *kernel, size_t smem, int *cached) {
-    if (*cached > 0) return *cached;
-    int dev = 0, sms = 0, occ = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-    if (smem > 48 * 1024)
-        if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, gsradix::TPB, smem) != cudaSuccess) return 0;
-    if (occ > 4) occ = 4;
-    *cached = occ * sms;
-    return *cached;
 }
 
 }  // namespace
@@ -220,7 +185,7 @@ extern "C" int gs_bin_scan(int N, const int32_t *tiles_hit, int32_t *cum, int32_
     ScanCtl *ctl = reinterpret_cast<ScanCtl *>(scratch);
     unsigned long long *status = reinterpret_cast<unsigned long long *>(ctl + 1);
     const int blocks = (N + SCAN_TILE - 1) / SCAN_TILE;
-    scan_kernel<<<blocks, SCAN_TPB, 0, st>>>(N, tiles_hit, cum, total_dev, ctl, status);
+    scan_kernel<<<blocks, SCAN_TPB, 0, st>>>(N, tiles_hit, nullptr, 0, cum, total_dev, ctl, status);
     GS_LAUNCH_CHECK();
     return 0;
 }
@@ -239,9 +204,9 @@ extern "C" int gs_bin_emit(int N, const float *xys, const float *depths, const i
 }
 
 extern "C" size_t gs_sort_scratch_bytes(int64_t I) {
-    // ping-pong buffers + CTA x digit matrix (sized for the largest grid we ever launch)
+    // ping-pong buffers + CTA x digit matrix
     const size_t keys = gs_align_up((size_t)I * 8, 256), vals = gs_align_up((size_t)I * 4, 256);
-    return keys + vals + (size_t)(1024 + 1) * 256 * sizeof(uint32_t) + 256;
+    return keys + vals + gs_align_up(gsradix::mat_entries(I, 256) * sizeof(uint32_t), 256) + 256;
 }
 
 extern "C" int gs_bin_sort(int64_t I, int T, const int64_t *keys, const int32_t *ids,
@@ -253,32 +218,28 @@ extern "C" int gs_bin_sort(int64_t I, int T, const int64_t *keys, const int32_t 
     if (!keys || !ids || !keys_sorted || !ids_sorted || !scratch) return GS_ERR_BAD_ARG;
     if (scratch_bytes < gs_sort_scratch_bytes(I)) return GS_ERR_SCRATCH_SMALL;
     if (!gs_aligned16(scratch)) return GS_ERR_MISALIGNED;
-    const size_t smem = sizeof(gsradix::Smem<uint64_t, 8>);
-    const int blocks = coop_grid((const void *)sort64_kernel, smem, &g_coop_blocks_sort64);
-    if (blocks <= 0 || blocks > 1024) return GS_ERR_UNSUPPORTED;
     unsigned char *p = reinterpret_cast<unsigned char *>(scratch);
     uint64_t *kb = reinterpret_cast<uint64_t *>(p); p += gs_align_up((size_t)I * 8, 256);
     uint32_t *vb = reinterpret_cast<uint32_t *>(p); p += gs_align_up((size_t)I * 4, 256);
     uint32_t *mat = reinterpret_cast<uint32_t *>(p);
     // live bits: 32 depth bits + ceil(log2 T) tile bits, split evenly into <= 8-bit digits
     const int total_bits = 32 + (T > 1 ? gs_ceil_log2(T) : 1);
-    SortPlan plan;
-    plan.npass = (total_bits + 7) / 8;
-    int at = 0;
-    for (int q = 0; q < plan.npass; ++q) {
-        const int left = total_bits - at, passes_left = plan.npass - q;
-        const int b = (left + passes_left - 1) / passes_left;
-        plan.shift[q] = at; plan.bits[q] = b; at += b;
-    }
-    int64_t n = I;
-    const uint64_t *k0 = reinterpret_cast<const uint64_t *>(keys);
-    const uint32_t *v0 = reinterpret_cast<const uint32_t *>(ids);
+    const int npass = (total_bits + 7) / 8;
+    const uint64_t *kin = reinterpret_cast<const uint64_t *>(keys);
+    const uint32_t *vin = reinterpret_cast<const uint32_t *>(ids);
     uint64_t *ka = reinterpret_cast<uint64_t *>(keys_sorted);
     uint32_t *va = reinterpret_cast<uint32_t *>(ids_sorted);
-    void *args[] = {&n, &k0, &v0, &ka, &va, &kb, &vb, &plan, &mat};
-    GS_CUDA(cudaLaunchCooperativeKernel((const void *)sort64_kernel, dim3(blocks), dim3(gsradix::TPB), args, smem,
-                                        (cudaStream_t)stream));
-    GS_LAUNCH_CHECK();
+    bool to_a = (npass & 1) != 0;   // the final pass must land in the caller's sorted outputs
+    int at = 0;
+    for (int q = 0; q < npass; ++q) {
+        const int left = total_bits - at, passes_left = npass - q;
+        const int b = (left + passes_left - 1) / passes_left;
+        uint64_t *ko = to_a ? ka : kb;
+        uint32_t *vo = to_a ? va : vb;
+        const int rc = gsradix::launch_pass<uint64_t, 8>(I, nullptr, kin, vin, ko, vo, at, b, mat, (cudaStream_t)stream);
+        if (rc) return rc;
+        kin = ko; vin = vo; to_a = !to_a; at += b;
+    }
     return 0;
 }
 
@@ -290,6 +251,192 @@ extern "C" int gs_bin_edges(int64_t I, int T, const int64_t *keys_sorted, int32_
     if (!keys_sorted) return GS_ERR_BAD_ARG;
     const int blocks = (int)((I + 255) / 256);
     edges_kernel<<<blocks, 256, 0, st>>>(I, keys_sorted, tile_bins);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ==========================================================================================
+// Traffic-lean binning (gs_bin_fast): same ids_sorted / tile_bins as scan + emit + 64-bit sort +
+// edges, without ever materialising 64-bit keys (SURVEY.md §7 "sort bandwidth"):
+//   1. stable radix sort of the N Gaussians by depth bits (32-bit keys, passes over N, not I)
+//   2. exclusive scan of tiles_hit in that order (single-pass look-back, gathered input)
+//   3. emission of (tile id, Gaussian id) in that order
+//   4. ONE stable partition by tile id (<= 2048 tiles: a single pass over I)
+//   5. tile ranges from the partitioned tile ids
+// sort-by-depth then stable-partition-by-tile == sort by (tile, depth) with ties in id order,
+// i.e. exactly the order of a stable sort of the 64-bit keys. The intersection count never
+// leaves the device: steps 3-5 read it from total_dev and are launched for the capacity.
+// ==========================================================================================
+namespace {
+
+__global__ void __launch_bounds__(256)
+depth_keys_kernel(int N, const float *__restrict__ depths, const int32_t *__restrict__ radii,
+                  uint32_t *__restrict__ keys) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < N) keys[i] = radii[i] > 0 ? __float_as_uint(depths[i]) : 0xFFFFFFFFu;   // culled: to the end
+}
+
+__global__ void __launch_bounds__(256)
+emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ order,
+                   const int32_t *__restrict__ start, const float2 *__restrict__ xys,
+                   const int32_t *__restrict__ radii, int tiles_x, int tiles_y, uint32_t *__restrict__ tkey,
+                   uint32_t *__restrict__ tval) {
+    if ((int64_t)*total_dev > I_cap) return;   // capacity too small: write nothing, the host retries
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    int x0 = 0, y0 = 0, x1 = 0, y1 = 0, st = 0, g = 0;
+    if (j < N) {
+        g = (int)order[j];
+        const int r = radii[g];
+        if (r > 0) {
+            const float2 c = xys[g];
+            gs_tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, x0, y0, x1, y1);
+            st = start[j];
+        }
+    }
+    const int bw = x1 - x0, area = bw * (y1 - y0);
+    if (area > 0 && area <= 8) {
+        int at = st;
+        for (int ty = y0; ty < y1; ++ty)
+            for (int tx = x0; tx < x1; ++tx) {
+                tkey[at] = (uint32_t)(ty * tiles_x + tx);
+                tval[at] = (uint32_t)g;
+                ++at;
+            }
+    }
+    unsigned big = __ballot_sync(0xffffffffu, area > 8);
+    while (big) {
+        const int src = __ffs(big) - 1;
+        big &= big - 1;
+        const int sx0 = __shfl_sync(0xffffffffu, x0, src), sy0 = __shfl_sync(0xffffffffu, y0, src);
+        const int sbw = __shfl_sync(0xffffffffu, bw, src), sarea = __shfl_sync(0xffffffffu, area, src);
+        const int sst = __shfl_sync(0xffffffffu, st, src), sg = __shfl_sync(0xffffffffu, g, src);
+        for (int k = lane; k < sarea; k += 32) {
+            tkey[sst + k] = (uint32_t)((sy0 + k / sbw) * tiles_x + sx0 + k % sbw);
+            tval[sst + k] = (uint32_t)sg;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+edges32_kernel(int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ tk,
+               int32_t *__restrict__ bins) {
+    const int64_t I = *total_dev;
+    if (I > I_cap) return;
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= I) return;
+    const uint32_t t = tk[k];
+    if (k == 0 || tk[k - 1] != t) bins[2 * t] = (int32_t)k;
+    if (k == I - 1 || tk[k + 1] != t) bins[2 * t + 1] = (int32_t)(k + 1);
+}
+
+struct FastLayout {
+    size_t keyA, valA, keyB, valB, start, tkey, tval, tkey2, tval2, mat, ctl, total;
+};
+
+FastLayout fast_layout(int N, int64_t I_cap) {
+    FastLayout L;
+    size_t at = 0;
+    auto take = [&](size_t bytes) { size_t o = at; at += gs_align_up(bytes, 256); return o; };
+    const size_t n4 = (size_t)(N > 0 ? N : 1) * 4, i4 = (size_t)(I_cap > 0 ? I_cap : 1) * 4;
+    L.keyA = take(n4); L.valA = take(n4); L.keyB = take(n4); L.valB = take(n4); L.start = take(n4);
+    L.tkey = take(i4); L.tval = take(i4); L.tkey2 = take(i4); L.tval2 = take(i4);
+    const size_t m = gsradix::mat_entries(N, 256), mi = gsradix::mat_entries(I_cap, 2048);
+    L.mat = take((m > mi ? m : mi) * 4);
+    L.ctl = take(gs_scan_scratch_bytes(N));
+    L.total = at;
+    return L;
+}
+
+template <int BITS>
+int partition_pass(int64_t I_cap, const int32_t *total_dev, const uint32_t *kin, const uint32_t *vin, uint32_t *kout,
+                   uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st) {
+    return gsradix::launch_pass<uint32_t, BITS>(I_cap, total_dev, kin, vin, kout, vout, shift, bits, mat, st);
+}
+
+}  // namespace
+
+extern "C" size_t gs_bin_fast_scratch_bytes(int N, int64_t I_cap, int T) {
+    (void)T;
+    return fast_layout(N, I_cap).total;
+}
+
+extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, const int32_t *radii,
+                           const int32_t *tiles_hit, int tiles_x, int tiles_y,
+                           int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
+                           void *scratch, size_t scratch_bytes, void *stream) {
+    if (N < 0 || I_cap < 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (!tile_bins || !total_dev || !scratch) return GS_ERR_BAD_ARG;
+    if (I_cap >= (1ll << 31)) return GS_ERR_UNSUPPORTED;
+    const int T = tiles_x * tiles_y;
+    const int tile_bits = T > 1 ? gs_ceil_log2(T) : 1;
+    if (tile_bits > 22) return GS_ERR_UNSUPPORTED;
+    cudaStream_t st = (cudaStream_t)stream;
+    GS_CUDA(cudaMemsetAsync(tile_bins, 0, sizeof(int32_t) * 2 * (size_t)T, st));
+    if (N == 0) {
+        GS_CUDA(cudaMemsetAsync(total_dev, 0, sizeof(int32_t), st));
+        return 0;
+    }
+    if (!xys || !depths || !radii || !tiles_hit || (!ids_sorted && I_cap > 0)) return GS_ERR_BAD_ARG;
+    const FastLayout L = fast_layout(N, I_cap);
+    if (scratch_bytes < L.total) return GS_ERR_SCRATCH_SMALL;
+    if (!gs_aligned16(scratch)) return GS_ERR_MISALIGNED;
+    unsigned char *p = reinterpret_cast<unsigned char *>(scratch);
+    uint32_t *keyA = (uint32_t *)(p + L.keyA), *valA = (uint32_t *)(p + L.valA);
+    uint32_t *keyB = (uint32_t *)(p + L.keyB), *valB = (uint32_t *)(p + L.valB);
+    int32_t *start = (int32_t *)(p + L.start);
+    uint32_t *tkey = (uint32_t *)(p + L.tkey), *tval = (uint32_t *)(p + L.tval);
+    uint32_t *tkey2 = (uint32_t *)(p + L.tkey2), *tval2 = (uint32_t *)(p + L.tval2);
+    uint32_t *mat = (uint32_t *)(p + L.mat);
+    ScanCtl *ctl = reinterpret_cast<ScanCtl *>(p + L.ctl);
+    unsigned long long *status = reinterpret_cast<unsigned long long *>(ctl + 1);
+    const int nblk = (N + 255) / 256;
+    int rc;
+
+    // 1. depth sort: A -> B -> A -> B -> A (values start as the element index)
+    depth_keys_kernel<<<nblk, 256, 0, st>>>(N, depths, radii, keyA);
+    GS_LAUNCH_CHECK();
+    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyA, nullptr, keyB, valB, 0, 8, mat, st))) return rc;
+    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyB, valB, keyA, valA, 8, 8, mat, st))) return rc;
+    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyA, valA, keyB, valB, 16, 8, mat, st))) return rc;
+    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyB, valB, keyA, valA, 24, 8, mat, st))) return rc;
+    const uint32_t *order = valA;
+
+    // 2. exclusive scan of tiles_hit in depth order; total -> total_dev
+    GS_CUDA(cudaMemsetAsync(ctl, 0, gs_scan_scratch_bytes(N), st));
+    scan_kernel<<<(N + SCAN_TILE - 1) / SCAN_TILE, SCAN_TPB, 0, st>>>(N, tiles_hit, order, 1, start, total_dev, ctl, status);
+    GS_LAUNCH_CHECK();
+    if (I_cap == 0) return 0;
+
+    // 3. emission in depth order
+    emit_sorted_kernel<<<nblk, 256, 0, st>>>(N, I_cap, total_dev, order, start, reinterpret_cast<const float2 *>(xys),
+                                             radii, tiles_x, tiles_y, tkey, tval);
+    GS_LAUNCH_CHECK();
+
+    // 4. stable partition by tile id
+    uint32_t *ids_out = reinterpret_cast<uint32_t *>(ids_sorted);
+    const uint32_t *tk_sorted = tkey2;
+    if (tile_bits <= 8) {
+        rc = partition_pass<8>(I_cap, total_dev, tkey, tval, tkey2, ids_out, 0, tile_bits, mat, st);
+    } else if (tile_bits <= 10) {
+        rc = partition_pass<10>(I_cap, total_dev, tkey, tval, tkey2, ids_out, 0, tile_bits, mat, st);
+    } else if (tile_bits <= 11) {
+        rc = partition_pass<11>(I_cap, total_dev, tkey, tval, tkey2, ids_out, 0, tile_bits, mat, st);
+    } else {
+        const int lo_bits = (tile_bits + 1) / 2, hi_bits = tile_bits - lo_bits;
+        if (lo_bits <= 8) {
+            rc = partition_pass<8>(I_cap, total_dev, tkey, tval, tkey2, tval2, 0, lo_bits, mat, st);
+            if (!rc) rc = partition_pass<8>(I_cap, total_dev, tkey2, tval2, tkey, ids_out, lo_bits, hi_bits, mat, st);
+        } else {
+            rc = partition_pass<11>(I_cap, total_dev, tkey, tval, tkey2, tval2, 0, lo_bits, mat, st);
+            if (!rc) rc = partition_pass<11>(I_cap, total_dev, tkey2, tval2, tkey, ids_out, lo_bits, hi_bits, mat, st);
+        }
+        tk_sorted = tkey;
+    }
+    if (rc) return rc;
+
+    // 5. tile ranges
+    edges32_kernel<<<(int)((I_cap + 255) / 256), 256, 0, st>>>(I_cap, total_dev, tk_sorted, tile_bins);
     GS_LAUNCH_CHECK();
     return 0;
 }

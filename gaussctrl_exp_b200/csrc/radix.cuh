@@ -1,50 +1,36 @@
-// Persistent, cooperative LSD radix-sort building blocks (keys + 32-bit values).
+// Stable LSD radix-sort building blocks (keys + 32-bit values), one pass = three small kernels:
+//     hist    : CTA b histograms its 2048-key chunk                  -> mat[b][digit]
+//     colscan : one warp per digit scans its column over the CTAs    -> mat (exclusive), totals[digit]
+//     scatter : CTA b ranks its chunk (warp match-any, stable), stages it in shared memory in
+//               digit order and writes coalesced runs at  digit_base + mat[b][digit] + local rank
 //
-// Design for B200: at the sizes of this path (I ~ 3 M intersections, 36 B each) the whole
-// sort working set sits in the 126 MB L2, so a pass is bound by L2 latency and launch
-// count, not HBM. Instead of a decoupled look-back over hundreds of co-resident tiles,
-// one cooperative grid (occupancy x #SMs CTAs) owns a contiguous chunk per CTA:
-//     phase H: CTA histograms its chunk            -> mat[cta][digit]
-//     grid.sync
-//     phase X: one warp per digit scans its column of `mat` over the CTAs (exclusive)
-//     grid.sync
-//     phase S: CTA reads its row of `mat` + the digit totals -> per-digit write cursors,
-//              then walks its chunk in 2048-key sub-tiles: warp match-any
-//              ranking (stable), shared-memory staging, coalesced scatter.
-//     grid.sync
-// Stability: chunk order == CTA order, sub-tiles in order, warp-striped items in order.
+// Design for B200: at the sizes of this path (N ~ 1 M Gaussians, I ~ 3 M intersections) the whole
+// working set sits in the 126 MB L2, so a pass is bound by latency and launch count, not HBM.
+// A first version ran everything as ONE cooperative persistent kernel with grid.sync between
+// phases; ncu showed 10 % issue-active (19 grid syncs at 16 warps/SM, profiles/r01). Splitting into
+// ordinary kernels lets every phase run at full occupancy with stream order as the barrier, and
+// every kernel takes its element count from DEVICE memory (n_dev), so no host read is needed
+// between the scan that produces the count and the passes that consume it.
+// Stability: chunk order == CTA order, warp-striped items ranked in order.
 #pragma once
-#include <cooperative_groups.h>
 #include "gs_common.cuh"
 
 namespace gsradix {
-namespace cg = cooperative_groups;
 
 constexpr int TPB = 256;
 constexpr int WARPS = TPB / 32;
 constexpr int IPT = 8;
-constexpr int SUB = TPB * IPT;  // keys per sub-tile
+constexpr int SUB = TPB * IPT;  // keys per CTA
 
-// Data written by other CTAs earlier in the same kernel must be read through L2 (.cg).
-template <typename T> __device__ __forceinline__ T ld_cg(const T *p) { return __ldcg(p); }
-template <> __device__ __forceinline__ uint64_t ld_cg<uint64_t>(const uint64_t *p) {
-    return (uint64_t)__ldcg(reinterpret_cast<const unsigned long long *>(p));
+// element count: host value, or (n_dev != nullptr) the device value clamped by the capacity;
+// returns -1 when the device value exceeds the capacity (caller retries with a larger buffer).
+__device__ __forceinline__ int64_t resolve_n(int64_t n_cap, const int32_t *n_dev) {
+    if (!n_dev) return n_cap;
+    const int64_t v = *n_dev;
+    return v > n_cap ? -1 : v;
 }
 
-template <typename KeyT, int BITS>
-struct Smem {
-    static constexpr int RADIX = 1 << BITS;
-    KeyT stage_k[SUB];
-    uint32_t stage_v[SUB];
-    uint32_t hist[RADIX];           // phase H histogram / phase S per-sub-tile counts
-    uint32_t cursor[RADIX];         // running global write cursor per digit (this CTA)
-    int32_t dbase[RADIX];           // cursor - local start, per sub-tile
-    uint16_t wc[WARPS][RADIX];      // per-warp digit counters
-    uint32_t scan_tmp[TPB];
-};
-
-// block-wide exclusive scan of one value per thread (TPB threads); returns exclusive prefix,
-// *total = block sum. Uses s.scan_tmp.
+// block-wide exclusive scan of one value per thread (TPB threads). tmp: >= 64 uint32.
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, uint32_t *total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t inc = v;
@@ -72,186 +58,220 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, u
     return r;
 }
 
-// One LSD pass over n (key,value) pairs. Must be called by every thread of a cooperative
-// grid. kin/kout: keys; vin may be nullptr (value = element index); kout may be nullptr
-// (keys dropped, e.g. final partition). `mat` holds (gridDim.x + 1) * RADIX uint32.
-// If digit_excl_out != nullptr, CTA 0 writes the exclusive digit prefix (RADIX+1 entries)
-// there: for a tile-id partition this is exactly the per-tile [start,end) table.
+// ---------------------------------------------------------------------------------------------
 template <typename KeyT, int BITS>
-__device__ void radix_pass(cg::grid_group &grid, Smem<KeyT, BITS> &s, int64_t n, const KeyT *kin,
-                           const uint32_t *vin, KeyT *kout, uint32_t *vout, int shift, int bits,
-                           uint32_t *mat, uint32_t *digit_excl_out) {
+__global__ void __launch_bounds__(TPB)
+hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin, int shift, int bits,
+            uint32_t *__restrict__ mat) {
     constexpr int RADIX = 1 << BITS;
-    constexpr int DPT = (RADIX + TPB - 1) / TPB;  // digits per thread (contiguous)
+    __shared__ uint32_t hist[RADIX];
+    const int64_t n = resolve_n(n_cap, n_dev);
+    const int64_t base = (int64_t)blockIdx.x * SUB;
+    if (n < 0 || base >= n) return;
     const uint32_t mask = (1u << bits) - 1u;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nb = gridDim.x, b = blockIdx.x;
-    // chunk of this CTA, aligned to SUB so sub-tiles never straddle CTAs
-    const int64_t nsub = (n + SUB - 1) / SUB;
-    const int64_t sub_per = (nsub + nb - 1) / nb;
-    const int64_t c0 = min(n, (int64_t)b * sub_per * SUB), c1 = min(n, (int64_t)(b + 1) * sub_per * SUB);
-
-    // ---------------- phase H ----------------
-    for (int d = tid; d < RADIX; d += TPB) s.hist[d] = 0;
+    for (int d = threadIdx.x; d < RADIX; d += TPB) hist[d] = 0;
     __syncthreads();
-    for (int64_t i = c0 + tid; i < c1; i += TPB) {
-        const uint32_t d = (uint32_t)(ld_cg(kin + i) >> shift) & mask;
-        atomicAdd(&s.hist[d], 1u);
-    }
-    __syncthreads();
-    for (int d = tid; d < RADIX; d += TPB) mat[(size_t)b * RADIX + d] = s.hist[d];
-    grid.sync();
-
-    // ---------------- phase X: distributed column scan ----------------
-    // One warp per digit (round-robin over the whole grid): exclusive prefix over CTAs of
-    // mat[.][d], written back in place; the column total goes to totals[d].
-    uint32_t *totals = mat + (size_t)nb * RADIX;
-    {
-        const int gw = b * WARPS + warp, nw = nb * WARPS;
-        for (int d = gw; d < RADIX; d += nw) {
-            uint32_t carry = 0;
-            for (int cb = 0; cb < nb; cb += 32) {
-                const int bb = cb + lane;
-                const uint32_t c = bb < nb ? __ldcg(&mat[(size_t)bb * RADIX + d]) : 0u;
-                uint32_t inc = c;
+    KeyT key[IPT];
 #pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const uint32_t nn = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += nn;
-                }
-                if (bb < nb) mat[(size_t)bb * RADIX + d] = carry + inc - c;
-                carry += __shfl_sync(0xffffffffu, inc, 31);
+    for (int i = 0; i < IPT; ++i) {
+        const int64_t at = base + i * TPB + threadIdx.x;
+        key[i] = at < n ? kin[at] : (KeyT)0;
+    }
+#pragma unroll
+    for (int i = 0; i < IPT; ++i)
+        if (base + i * TPB + threadIdx.x < n) atomicAdd(&hist[(uint32_t)(key[i] >> shift) & mask], 1u);
+    __syncthreads();
+    for (int d = threadIdx.x; d < RADIX; d += TPB) mat[(size_t)blockIdx.x * RADIX + d] = hist[d];
+}
+
+// One warp per digit: exclusive prefix over the CTA rows of mat[.][d], in place; totals[d] = sum.
+template <int BITS>
+__global__ void __launch_bounds__(TPB)
+colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat,
+               uint32_t *__restrict__ totals) {
+    constexpr int RADIX = 1 << BITS;
+    const int64_t n = resolve_n(n_cap, n_dev);
+    if (n < 0) return;
+    const int nb = (int)((n + SUB - 1) / SUB);
+    const int lane = threadIdx.x & 31;
+    const int d = blockIdx.x * WARPS + (threadIdx.x >> 5);
+    if (d >= RADIX) return;
+    uint32_t carry = 0;
+    for (int cb = 0; cb < nb; cb += 32 * 4) {
+        uint32_t c[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {   // 4 independent loads in flight per lane
+            const int bb = cb + u * 32 + lane;
+            c[u] = bb < nb ? mat[(size_t)bb * RADIX + d] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int bb = cb + u * 32 + lane;
+            uint32_t inc = c[u];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t nn = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += nn;
             }
-            if (lane == 0) totals[d] = carry;
+            if (bb < nb) mat[(size_t)bb * RADIX + d] = carry + inc - c[u];
+            carry += __shfl_sync(0xffffffffu, inc, 31);
         }
     }
-    grid.sync();
+    if (lane == 0) totals[d] = carry;
+}
 
-    // ---------------- phase S: cursors ----------------
-    uint32_t tot[DPT], below[DPT];
-    uint32_t tsum = 0;
+template <typename KeyT, int BITS>
+struct ScatterSmem {
+    static constexpr int RADIX = 1 << BITS;
+    KeyT stage_k[SUB];
+    uint32_t stage_v[SUB];
+    uint32_t dstart[RADIX];         // local start of each digit inside the CTA's chunk
+    int32_t dbase[RADIX];           // global cursor - local start
+    uint16_t wc[WARPS][RADIX];      // per-warp digit counters
+    uint32_t scan_tmp[64];
+};
+
+// vin == nullptr: value = element index. kout == nullptr: keys dropped.
+template <typename KeyT, int BITS>
+__global__ void __launch_bounds__(TPB)
+scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
+               const uint32_t *__restrict__ vin, KeyT *__restrict__ kout, uint32_t *__restrict__ vout, int shift,
+               int bits, const uint32_t *__restrict__ mat, const uint32_t *__restrict__ totals) {
+    constexpr int RADIX = 1 << BITS;
+    constexpr int DPT = (RADIX + TPB - 1) / TPB;  // digits per thread (contiguous)
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ScatterSmem<KeyT, BITS> &s = *reinterpret_cast<ScatterSmem<KeyT, BITS> *>(smem_raw);
+    const int64_t n = resolve_n(n_cap, n_dev);
+    const int64_t base = (int64_t)blockIdx.x * SUB;
+    if (n < 0 || base >= n) return;
+    const int valid = (int)min((int64_t)SUB, n - base);
+    const uint32_t mask = (1u << bits) - 1u;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    for (int i = tid; i < WARPS * RADIX; i += TPB) (&s.wc[0][0])[i] = 0;
+    // keys (warp-striped: item i of lane l sits at warp*256 + i*32 + l) and values, loaded up front
+    KeyT key[IPT];
+    uint32_t val[IPT];
+    const int woff = warp * 32 * IPT;
+#pragma unroll
+    for (int i = 0; i < IPT; ++i) {
+        const int li = woff + i * 32 + lane;
+        key[i] = li < valid ? kin[base + li] : (KeyT) ~(KeyT)0;
+        val[i] = li < valid ? (vin ? vin[base + li] : (uint32_t)(base + li)) : 0u;
+    }
+    // global cursors of this CTA: digit base (exclusive scan of totals) + rows below (mat, already exclusive)
+    uint32_t tot[DPT], below[DPT], tsum = 0;
 #pragma unroll
     for (int j = 0; j < DPT; ++j) {
         const int d = tid * DPT + j;
-        tot[j] = d < RADIX ? __ldcg(&totals[d]) : 0u;
-        below[j] = d < RADIX ? __ldcg(&mat[(size_t)b * RADIX + d]) : 0u;
+        tot[j] = d < RADIX ? totals[d] : 0u;
+        below[j] = d < RADIX ? mat[(size_t)blockIdx.x * RADIX + d] : 0u;
         tsum += tot[j];
     }
-    uint32_t run = block_excl_scan(tsum, s.scan_tmp, nullptr);
+    uint32_t run = block_excl_scan(tsum, s.scan_tmp, nullptr);   // also orders the wc zeroing
+    uint32_t cursor[DPT];
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) { cursor[j] = run + below[j]; run += tot[j]; }
+
+    // stable ranking inside each warp
+    uint16_t rank[IPT];
+#pragma unroll
+    for (int i = 0; i < IPT; ++i) {
+        const int li = woff + i * 32 + lane;
+        // out-of-range items get digit RADIX-1 and sort behind every valid key of the chunk
+        const uint32_t d = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const int leader = __ffs(peers) - 1;
+        uint32_t pre = 0;
+        if (lane == leader) {
+            pre = s.wc[warp][d];
+            s.wc[warp][d] = (uint16_t)(pre + __popc(peers));
+        }
+        pre = __shfl_sync(0xffffffffu, pre, leader);
+        rank[i] = (uint16_t)(pre + __popc(peers & gs_lanemask_lt()));
+        __syncwarp();
+    }
+    __syncthreads();
+    // per digit: exclusive over warps, chunk count
+    uint32_t cnt[DPT], csum = 0;
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) {
+        const int d = tid * DPT + j;
+        cnt[j] = 0;
+        if (d < RADIX) {
+            uint32_t r = 0;
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w) {
+                const uint32_t c = s.wc[w][d];
+                s.wc[w][d] = (uint16_t)r;
+                r += c;
+            }
+            cnt[j] = r;
+        }
+        csum += cnt[j];
+    }
+    uint32_t dstart = block_excl_scan(csum, s.scan_tmp, nullptr);
 #pragma unroll
     for (int j = 0; j < DPT; ++j) {
         const int d = tid * DPT + j;
         if (d < RADIX) {
-            s.cursor[d] = run + below[j];
-            if (digit_excl_out && b == 0) {
-                digit_excl_out[d] = run;
-                if (d == RADIX - 1) digit_excl_out[RADIX] = run + tot[j];
-            }
+            s.dstart[d] = dstart;
+            s.dbase[d] = (int32_t)(cursor[j] - dstart);   // dst = dbase + local position
         }
-        run += tot[j];
+        dstart += cnt[j];
     }
     __syncthreads();
-
-    // ---------------- phase S: sub-tiles ----------------
-    for (int64_t base = c0; base < c1; base += SUB) {
-        const int valid = (int)min((int64_t)SUB, c1 - base);
-        for (int i = tid; i < WARPS * RADIX; i += TPB) (&s.wc[0][0])[i] = 0;
-        __syncthreads();
-        KeyT key[IPT];
-        uint16_t rank[IPT];
-        const int woff = warp * 32 * IPT;
 #pragma unroll
-        for (int i = 0; i < IPT; ++i) {
-            const int li = woff + i * 32 + lane;
-            key[i] = li < valid ? ld_cg(kin + base + li) : (KeyT)~(KeyT)0;
-        }
-#pragma unroll
-        for (int i = 0; i < IPT; ++i) {
-            const int li = woff + i * 32 + lane;
-            // out-of-range items get digit RADIX-1 and sort behind every valid key of the tile
-            const uint32_t d = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
-            const unsigned peers = __match_any_sync(0xffffffffu, d);
-            const int leader = __ffs(peers) - 1;
-            uint32_t pre = 0;
-            if (lane == leader) {
-                pre = s.wc[warp][d];
-                s.wc[warp][d] = (uint16_t)(pre + __popc(peers));
-            }
-            pre = __shfl_sync(0xffffffffu, pre, leader);
-            rank[i] = (uint16_t)(pre + __popc(peers & gs_lanemask_lt()));
-            __syncwarp();
-        }
-        __syncthreads();
-        // per digit: exclusive over warps, sub-tile count
-        uint32_t cnt[DPT];
-        uint32_t csum = 0;
-#pragma unroll
-        for (int j = 0; j < DPT; ++j) {
-            const int d = tid * DPT + j;
-            cnt[j] = 0;
-            if (d < RADIX) {
-                uint32_t r = 0;
-#pragma unroll
-                for (int w = 0; w < WARPS; ++w) {
-                    const uint32_t c = s.wc[w][d];
-                    s.wc[w][d] = (uint16_t)r;
-                    r += c;
-                }
-                cnt[j] = r;
-            }
-            csum += cnt[j];
-        }
-        uint32_t dstart = block_excl_scan(csum, s.scan_tmp, nullptr);
-#pragma unroll
-        for (int j = 0; j < DPT; ++j) {
-            const int d = tid * DPT + j;
-            if (d < RADIX) {
-                s.hist[d] = dstart;                                    // local start of digit d
-                s.dbase[d] = (int32_t)(s.cursor[d] - dstart);          // dst = dbase + local pos
-                // padding items (digit RADIX-1) must not advance the cursor
-                uint32_t real = cnt[j];
-                if (d == RADIX - 1) real -= (uint32_t)(SUB - valid);
-                s.cursor[d] += real;
-            }
-            dstart += cnt[j];
-        }
-        __syncthreads();
-        uint16_t pos[IPT];
-#pragma unroll
-        for (int i = 0; i < IPT; ++i) {
-            const int li = woff + i * 32 + lane;
-            const uint32_t d = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
-            pos[i] = (uint16_t)(s.hist[d] + s.wc[warp][d] + rank[i]);
-            s.stage_k[pos[i]] = key[i];
-        }
-        __syncthreads();
-        int64_t dst[IPT];
-#pragma unroll
-        for (int k = 0; k < IPT; ++k) {
-            const int p = tid + k * TPB;
-            dst[k] = -1;
-            if (p < valid) {
-                const KeyT kk = s.stage_k[p];
-                const uint32_t d = (uint32_t)(kk >> shift) & mask;
-                dst[k] = (int64_t)(uint32_t)(s.dbase[d] + p);
-                if (kout) kout[dst[k]] = kk;
-            }
-        }
-        // values
-#pragma unroll
-        for (int i = 0; i < IPT; ++i) {
-            const int li = woff + i * 32 + lane;
-            uint32_t v = 0;
-            if (li < valid) v = vin ? ld_cg(vin + base + li) : (uint32_t)(base + li);
-            s.stage_v[pos[i]] = v;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int k = 0; k < IPT; ++k)
-            if (dst[k] >= 0) vout[dst[k]] = s.stage_v[tid + k * TPB];
-        __syncthreads();
+    for (int i = 0; i < IPT; ++i) {
+        const int li = woff + i * 32 + lane;
+        const uint32_t d = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
+        const uint32_t pos = s.dstart[d] + s.wc[warp][d] + rank[i];
+        s.stage_k[pos] = key[i];
+        s.stage_v[pos] = val[i];
     }
-    grid.sync();
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < IPT; ++k) {
+        const int p = tid + k * TPB;
+        if (p < valid) {   // padding items sit behind every valid one
+            const KeyT kk = s.stage_k[p];
+            const uint32_t d = (uint32_t)(kk >> shift) & mask;
+            const uint32_t dst = (uint32_t)(s.dbase[d] + p);
+            if (kout) kout[dst] = kk;
+            vout[dst] = s.stage_v[p];
+        }
+    }
+}
+
+// host-side launcher of one pass. mat: (ceil(n_cap/SUB)+1) * RADIX uint32 (last row = totals).
+template <typename KeyT, int BITS>
+inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, const uint32_t *vin, KeyT *kout,
+                       uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st) {
+    constexpr int RADIX = 1 << BITS;
+    if (n_cap <= 0) return 0;
+    const int nb = (int)((n_cap + SUB - 1) / SUB);
+    uint32_t *totals = mat + (size_t)nb * RADIX;
+    const size_t smem = sizeof(ScatterSmem<KeyT, BITS>);
+    static bool attr_set = false;   // one per template instantiation
+    if (!attr_set) {
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute((const void *)scatter_kernel<KeyT, BITS>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return (int)e;
+        }
+        attr_set = true;
+    }
+    hist_kernel<KeyT, BITS><<<nb, TPB, 0, st>>>(n_cap, n_dev, kin, shift, bits, mat);
+    GS_LAUNCH_CHECK();
+    colscan_kernel<BITS><<<(RADIX + WARPS - 1) / WARPS, TPB, 0, st>>>(n_cap, n_dev, mat, totals);
+    GS_LAUNCH_CHECK();
+    scatter_kernel<KeyT, BITS><<<nb, TPB, smem, st>>>(n_cap, n_dev, kin, vin, kout, vout, shift, bits, mat, totals);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+inline size_t mat_entries(int64_t n_cap, int radix) {
+    return ((size_t)((n_cap + SUB - 1) / SUB) + 1) * (size_t)radix;
 }
 
 }  // namespace gsradix
