@@ -157,7 +157,7 @@ class GaussianModel(nn.Module):
                     "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
         with torch.no_grad(), torch.cuda.device(dev):
             bg = background.to(dev).float().contiguous()
-            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I) = _render._forward_impl(
+            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, _) = _render._forward_impl(
                 self.means.detach(), self.scales.detach(), self.quats.detach(), self.opacities.detach(),
                 self.features_dc.detach(), self.features_rest.detach(), cam, use_sh, n, bg)
             self.xys, self.radii = xys, radii

@@ -22,6 +22,11 @@ from torch.autograd import Function
 from . import _lib
 from .scene import Camera
 
+# Training views (render_view under autograd): do not read the intersection count in the forward; verify it
+# at the end of backward instead (raises CapacityOverflow, before any gradient is returned, in the unlikely
+# case the count grew by more than 50 % between consecutive views of the same shape).
+SPECULATE = True
+
 _cam_cache = {}
 _cap_hint = {}
 _scratch = {}
@@ -74,12 +79,37 @@ def _get_scratch(dev, nbytes):
     return buf
 
 
+_RING = 16
+
+
 def _get_pinned(dev):
-    p = _pinned.get(dev.index)
-    if p is None:
-        p = (torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event())
-        _pinned[dev.index] = p
-    return p
+    """Next (pinned int32[1], event) slot of a small per-device ring: several views may be in flight
+    before the host looks at their intersection counts."""
+    ring = _pinned.get(dev.index)
+    if ring is None:
+        ring = {"slots": [(torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event()) for _ in range(_RING)],
+                "next": 0}
+        _pinned[dev.index] = ring
+    slot = ring["slots"][ring["next"]]
+    ring["next"] = (ring["next"] + 1) % _RING
+    return slot
+
+
+class CapacityOverflow(RuntimeError):
+    """Raised by the deferred check of a speculative (non-strict) forward: the tile lists did not fit the
+    speculative capacity, so that view's image/gradients are invalid. The capacity hint has already been
+    raised: re-running the step succeeds."""
+
+
+def _check_pending(pending):
+    pinned, ev, cap, key = pending
+    ev.synchronize()
+    I = int(pinned[0])
+    if I > cap:
+        _cap_hint[key] = int(I * 1.5) + 1024
+        raise CapacityOverflow(f"{I} intersections exceed the speculative capacity {cap}; re-run this view")
+    _cap_hint[key] = max(_cap_hint.get(key, 0), int(I * 1.5) + 1024)
+    return I
 
 
 class ViewState:
@@ -91,7 +121,10 @@ class ViewState:
         self.num_intersects = 0
 
 
-def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg):
+def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, strict=True):
+    """strict=True: the host confirms the tile-list capacity before returning (one 4-byte read, overlapped
+    with the compositing kernel; overflow -> redo). strict=False: nothing is read; the caller must run
+    _check_pending(result[-1]) before trusting the view (render_view does it at the end of backward)."""
     L = _lib.lib()
     dev = means.device
     N = means.shape[0]
@@ -113,10 +146,11 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
                              hit.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), st)
     _lib.check(rc, "gs_preprocess_fwd")
     key = (dev.index, N, T)
+    known = key in _cap_hint
     cap = _cap_hint.get(key, max(4 * N, 1024))
+    strict = strict or not known           # never speculate blindly on the first view of a shape
     bins = torch.empty((T, 2), device=dev, dtype=torch.int32)
     total = torch.empty(1, device=dev, dtype=torch.int32)
-    pinned, ev = _get_pinned(dev)
     out = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
     fT = torch.empty((H, W), device=dev, dtype=torch.float32)
     fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
@@ -127,6 +161,7 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
                            ids_sorted.data_ptr(), bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
                            scratch.numel(), st)
         _lib.check(rc, "gs_bin_fast")
+        pinned, ev = _get_pinned(dev)
         pinned.copy_(total, non_blocking=True)
         ev.record()
         # compositing is enqueued BEFORE the host looks at the count: it only reads tile_bins
@@ -134,13 +169,16 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
                              rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(), out.data_ptr(), fT.data_ptr(),
                              fidx.data_ptr(), st)
         _lib.check(rc, "gs_raster_fwd")
+        if not strict:
+            return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, None,
+                    (pinned, ev, cap, key))
         ev.synchronize()
         I = int(pinned[0])
         if I <= cap:
-            _cap_hint[key] = max(int(I * 1.25) + 1024, 1024)
+            _cap_hint[key] = max(int(I * 1.5) + 1024, 1024)
             break
-        cap = int(I * 1.25) + 1024      # capacity was too small: nothing was composited from a torn list; redo
-    return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I)
+        cap = int(I * 1.5) + 1024      # capacity was too small: nothing was composited from a torn list; redo
+    return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, None)
 
 
 def _ctypes_addr(struct):
@@ -161,8 +199,9 @@ class _RenderView(Function):
         args = [t.detach().float().contiguous() for t in (means, scales, quats, opacities, features_dc, features_rest)]
         bg = bg.detach().to(means.device).float().contiguous()
         with torch.cuda.device(means.device):
-            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I) = _forward_impl(
-                *args, cam, use_sh, deg, bg)
+            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, pending) = _forward_impl(
+                *args, cam, use_sh, deg, bg, strict=not SPECULATE)
+        ctx.pending = pending
         ctx.save_for_backward(*args, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT, fidx)
         ctx.cam, ctx.use_sh, ctx.deg, ctx.state = cam, use_sh, deg, state
         if state is not None:
@@ -213,6 +252,10 @@ class _RenderView(Function):
                                      v_means.data_ptr(), v_scales.data_ptr(), v_quats.data_ptr(), v_opl.data_ptr(),
                                      v_dc.data_ptr(), v_rest.data_ptr(), st)
             _lib.check(rc, "gs_preprocess_bwd")
+        if ctx.pending is not None:
+            I = _check_pending(ctx.pending)      # long since complete: does not stall the device
+            if ctx.state is not None:
+                ctx.state.num_intersects = I
         if ctx.state is not None:
             ctx.state.xys_grad = v_xys       # what gc_model.py:193-194 keeps via xys.retain_grad()
             ctx.state.flat_grads = flat

@@ -102,3 +102,30 @@ def test_full_size_properties(cuda_dev):
     z = torch.zeros(3, device=dev)
     r = [rasterize_gaussians(xys, depths, radii, conics, hit, c, op, cam.H, cam.W, background=z) for c in (c1, c2, c1 + c2)]
     assert (r[0] + r[1] - r[2]).abs().max().item() < 1e-5
+
+
+def test_speculative_capacity_overflow_is_detected(cuda_dev):
+    """Training views do not read the intersection count in the forward; an undersized speculative
+    capacity must be caught (before gradients are returned) and the retry must succeed."""
+    from gaussctrl_exp_b200 import render, scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    dev = cuda_dev
+    p = scene.make_scene(30000, 5, s0=0.02, device=dev)
+    cam = small_cam(160, 128, 5)
+    m = GaussianModel(p, background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
+    m.train()
+    ref = m(cam)["rgb"].detach().clone()          # first view of this shape: strict, sets the hint
+    key = (dev.index, 30000, 10 * 8)
+    assert key in render._cap_hint
+    I_true = render._cap_hint[key]
+    render._cap_hint[key] = 2048                   # sabotage: far too small
+    out = m(cam)
+    with pytest.raises(render.CapacityOverflow):
+        out["rgb"].sum().backward()
+    assert render._cap_hint[key] >= I_true // 2    # hint was raised by the failed check
+    for q in m.parameters():
+        q.grad = None
+    out = m(cam)                                   # retry succeeds and matches
+    out["rgb"].sum().backward()
+    assert torch.equal(out["rgb"].detach(), ref) and m.means.grad.abs().max() > 0
+    assert m.view_state.num_intersects > 2048
