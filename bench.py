@@ -296,6 +296,8 @@ def run_ours(args):
         reduce_grads()
         return float(loss.item())                            # D2H of the step's result
 
+    host_ms = [0.0]
+
     def timed_loop(fn, warmup, steps):
         for i in range(warmup):
             fn(i)
@@ -303,8 +305,10 @@ def run_ours(args):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = _lib.launch_count()
         e0.record()
+        h0 = time.perf_counter()
         for i in range(steps):
             fn(warmup + i)
+        host_ms[0] = 1e3 * (time.perf_counter() - h0) / steps     # host enqueue time per step (diagnostic)
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -317,6 +321,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     ms_total, launches = timed_loop(step, args.warmup, args.steps)
+    host_enqueue_ms = host_ms[0]
     clocks = sampler.stop() if rank == 0 else None
     ms_e2e, _ = timed_loop(step_e2e, max(3, args.warmup // 2), args.steps)
 
@@ -329,6 +334,7 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
             "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
+            "host_enqueue_ms_per_step": host_enqueue_ms,
             "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "views/s",
                     "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4},
         }

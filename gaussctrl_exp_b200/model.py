@@ -120,7 +120,9 @@ class GaussianModel(nn.Module):
     def _background(self) -> Tensor:
         bc = self.background_color                                    # gc_model.py:93-106
         if isinstance(bc, Tensor):
-            return bc.to(self.device)
+            if bc.device != self.device:      # move once: a pageable H2D copy per view would sync the stream
+                self.background_color = bc = bc.to(self.device)
+            return bc
         if self.training and bc == "random":
             return torch.rand(3, device=self.device)
         if bc == "white":
