@@ -350,8 +350,9 @@ FastLayout fast_layout(int N, int64_t I_cap) {
 
 template <int BITS>
 int partition_pass(int64_t I_cap, const int32_t *total_dev, const uint32_t *kin, const uint32_t *vin, uint32_t *kout,
-                   uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st) {
-    return gsradix::launch_pass<uint32_t, BITS>(I_cap, total_dev, kin, vin, kout, vout, shift, bits, mat, st);
+                   uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st, int32_t *bins = nullptr,
+                   int T = 0) {
+    return gsradix::launch_pass<uint32_t, BITS>(I_cap, total_dev, kin, vin, kout, vout, shift, bits, mat, st, bins, T);
 }
 
 }  // namespace
@@ -415,13 +416,15 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
 
     // 4. stable partition by tile id
     uint32_t *ids_out = reinterpret_cast<uint32_t *>(ids_sorted);
-    const uint32_t *tk_sorted = tkey2;
+    // single pass: the digit is the tile id, so the tile ranges are the exclusive scan of the digit totals
+    // (written by the pass itself) and the sorted tile ids need not be materialised at all
+    const uint32_t *tk_sorted = nullptr;
     if (tile_bits <= 8) {
-        rc = partition_pass<8>(I_cap, total_dev, tkey, tval, tkey2, ids_out, 0, tile_bits, mat, st);
+        rc = partition_pass<8>(I_cap, total_dev, tkey, tval, nullptr, ids_out, 0, tile_bits, mat, st, tile_bins, T);
     } else if (tile_bits <= 10) {
-        rc = partition_pass<10>(I_cap, total_dev, tkey, tval, tkey2, ids_out, 0, tile_bits, mat, st);
+        rc = partition_pass<10>(I_cap, total_dev, tkey, tval, nullptr, ids_out, 0, tile_bits, mat, st, tile_bins, T);
     } else if (tile_bits <= 11) {
-        rc = partition_pass<11>(I_cap, total_dev, tkey, tval, tkey2, ids_out, 0, tile_bits, mat, st);
+        rc = partition_pass<11>(I_cap, total_dev, tkey, tval, nullptr, ids_out, 0, tile_bits, mat, st, tile_bins, T);
     } else {
         const int lo_bits = (tile_bits + 1) / 2, hi_bits = tile_bits - lo_bits;
         if (lo_bits <= 8) {
@@ -435,8 +438,10 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
     }
     if (rc) return rc;
 
-    // 5. tile ranges
-    edges32_kernel<<<(int)((I_cap + 255) / 256), 256, 0, st>>>(I_cap, total_dev, tk_sorted, tile_bins);
-    GS_LAUNCH_CHECK();
+    // 5. tile ranges (two-pass partition only)
+    if (tk_sorted) {
+        edges32_kernel<<<(int)((I_cap + 255) / 256), 256, 0, st>>>(I_cap, total_dev, tk_sorted, tile_bins);
+        GS_LAUNCH_CHECK();
+    }
     return 0;
 }

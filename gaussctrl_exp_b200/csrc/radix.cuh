@@ -1,5 +1,5 @@
 // Stable LSD radix-sort building blocks (keys + 32-bit values), one pass = three small kernels:
-//     hist    : CTA b histograms its 2048-key chunk                  -> mat[b][digit]
+//     hist    : CTA b histograms its 2048-key chunk                  -> mat[digit][b]
 //     colscan : one warp per digit scans its column over the CTAs    -> mat (exclusive), totals[digit]
 //     scatter : CTA b ranks its chunk (warp match-any, stable), stages it in shared memory in
 //               digit order and writes coalesced runs at  digit_base + mat[b][digit] + local rank
@@ -62,7 +62,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, u
 template <typename KeyT, int BITS>
 __global__ void __launch_bounds__(TPB)
 hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin, int shift, int bits,
-            uint32_t *__restrict__ mat) {
+            uint32_t *__restrict__ mat, int pitch) {
     constexpr int RADIX = 1 << BITS;
     __shared__ uint32_t hist[RADIX];
     const int64_t n = resolve_n(n_cap, n_dev);
@@ -81,14 +81,14 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
     for (int i = 0; i < IPT; ++i)
         if (base + i * TPB + threadIdx.x < n) atomicAdd(&hist[(uint32_t)(key[i] >> shift) & mask], 1u);
     __syncthreads();
-    for (int d = threadIdx.x; d < RADIX; d += TPB) mat[(size_t)blockIdx.x * RADIX + d] = hist[d];
+    for (int d = threadIdx.x; d < RADIX; d += TPB) mat[(size_t)d * pitch + blockIdx.x] = hist[d];
 }
 
 // One warp per digit: exclusive prefix over the CTA rows of mat[.][d], in place; totals[d] = sum.
 template <int BITS>
 __global__ void __launch_bounds__(TPB)
-colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat,
-               uint32_t *__restrict__ totals) {
+colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat, int pitch,
+               uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T) {
     constexpr int RADIX = 1 << BITS;
     const int64_t n = resolve_n(n_cap, n_dev);
     if (n < 0) return;
@@ -96,13 +96,14 @@ colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__res
     const int lane = threadIdx.x & 31;
     const int d = blockIdx.x * WARPS + (threadIdx.x >> 5);
     if (d >= RADIX) return;
+    uint32_t *row = mat + (size_t)d * pitch;   // mat[digit][cta]: the scan walks contiguous memory
     uint32_t carry = 0;
     for (int cb = 0; cb < nb; cb += 32 * 4) {
         uint32_t c[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {   // 4 independent loads in flight per lane
             const int bb = cb + u * 32 + lane;
-            c[u] = bb < nb ? mat[(size_t)bb * RADIX + d] : 0u;
+            c[u] = bb < nb ? row[bb] : 0u;
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -113,11 +114,44 @@ colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__res
                 const uint32_t nn = __shfl_up_sync(0xffffffffu, inc, o);
                 if (lane >= o) inc += nn;
             }
-            if (bb < nb) mat[(size_t)bb * RADIX + d] = carry + inc - c[u];
+            if (bb < nb) row[bb] = carry + inc - c[u];
             carry += __shfl_sync(0xffffffffu, inc, 31);
         }
     }
     if (lane == 0) totals[d] = carry;
+    (void)bins_out; (void)bins_T;
+}
+
+// Exclusive scan of the digit totals -> digit_base[RADIX]; when the digit IS the tile id (single-pass
+// partition) the tile ranges fall out for free: bins[t] = [base, base + total) (0,0 for empty tiles).
+template <int BITS>
+__global__ void __launch_bounds__(TPB)
+digit_base_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const uint32_t *__restrict__ totals,
+                  uint32_t *__restrict__ digit_base, int32_t *__restrict__ bins_out, int bins_T) {
+    constexpr int RADIX = 1 << BITS;
+    constexpr int DPT = (RADIX + TPB - 1) / TPB;
+    __shared__ uint32_t tmp[64];
+    if (resolve_n(n_cap, n_dev) < 0) return;
+    uint32_t tot[DPT], sum = 0;
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) {
+        const int d = threadIdx.x * DPT + j;
+        tot[j] = d < RADIX ? totals[d] : 0u;
+        sum += tot[j];
+    }
+    uint32_t run = block_excl_scan(sum, tmp, nullptr);
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) {
+        const int d = threadIdx.x * DPT + j;
+        if (d < RADIX) {
+            digit_base[d] = run;
+            if (bins_out && d < bins_T) {
+                bins_out[2 * d] = tot[j] ? (int32_t)run : 0;
+                bins_out[2 * d + 1] = tot[j] ? (int32_t)(run + tot[j]) : 0;
+            }
+        }
+        run += tot[j];
+    }
 }
 
 template <typename KeyT, int BITS>
@@ -136,7 +170,7 @@ template <typename KeyT, int BITS>
 __global__ void __launch_bounds__(TPB)
 scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
                const uint32_t *__restrict__ vin, KeyT *__restrict__ kout, uint32_t *__restrict__ vout, int shift,
-               int bits, const uint32_t *__restrict__ mat, const uint32_t *__restrict__ totals) {
+               int bits, const uint32_t *__restrict__ mat, int pitch, const uint32_t *__restrict__ digit_base) {
     constexpr int RADIX = 1 << BITS;
     constexpr int DPT = (RADIX + TPB - 1) / TPB;  // digits per thread (contiguous)
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -159,36 +193,37 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
         key[i] = li < valid ? kin[base + li] : (KeyT) ~(KeyT)0;
         val[i] = li < valid ? (vin ? vin[base + li] : (uint32_t)(base + li)) : 0u;
     }
-    // global cursors of this CTA: digit base (exclusive scan of totals) + rows below (mat, already exclusive)
-    uint32_t tot[DPT], below[DPT], tsum = 0;
+    // global cursors of this CTA: digit base + keys of the same digit in the CTAs below (mat is exclusive)
+    uint32_t cursor[DPT];
 #pragma unroll
     for (int j = 0; j < DPT; ++j) {
         const int d = tid * DPT + j;
-        tot[j] = d < RADIX ? totals[d] : 0u;
-        below[j] = d < RADIX ? mat[(size_t)blockIdx.x * RADIX + d] : 0u;
-        tsum += tot[j];
+        cursor[j] = d < RADIX ? digit_base[d] + mat[(size_t)d * pitch + blockIdx.x] : 0u;
     }
-    uint32_t run = block_excl_scan(tsum, s.scan_tmp, nullptr);   // also orders the wc zeroing
-    uint32_t cursor[DPT];
-#pragma unroll
-    for (int j = 0; j < DPT; ++j) { cursor[j] = run + below[j]; run += tot[j]; }
+    __syncthreads();   // wc zeroed
 
-    // stable ranking inside each warp
+    // stable ranking inside each warp: the 8 match.any are independent and issue back to back; only the
+    // counter read-modify-write chain is sequential
     uint16_t rank[IPT];
+    unsigned peers[IPT];
+    uint32_t dig[IPT];
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
         const int li = woff + i * 32 + lane;
         // out-of-range items get digit RADIX-1 and sort behind every valid key of the chunk
-        const uint32_t d = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(peers) - 1;
+        dig[i] = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
+        peers[i] = __match_any_sync(0xffffffffu, dig[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < IPT; ++i) {
+        const int leader = __ffs(peers[i]) - 1;
         uint32_t pre = 0;
         if (lane == leader) {
-            pre = s.wc[warp][d];
-            s.wc[warp][d] = (uint16_t)(pre + __popc(peers));
+            pre = s.wc[warp][dig[i]];
+            s.wc[warp][dig[i]] = (uint16_t)(pre + __popc(peers[i]));
         }
         pre = __shfl_sync(0xffffffffu, pre, leader);
-        rank[i] = (uint16_t)(pre + __popc(peers & gs_lanemask_lt()));
+        rank[i] = (uint16_t)(pre + __popc(peers[i] & gs_lanemask_lt()));
         __syncwarp();
     }
     __syncthreads();
@@ -223,8 +258,7 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
-        const int li = woff + i * 32 + lane;
-        const uint32_t d = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
+        const uint32_t d = dig[i];
         const uint32_t pos = s.dstart[d] + s.wc[warp][d] + rank[i];
         s.stage_k[pos] = key[i];
         s.stage_v[pos] = val[i];
@@ -243,14 +277,17 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
     }
 }
 
-// host-side launcher of one pass. mat: (ceil(n_cap/SUB)+1) * RADIX uint32 (last row = totals).
+// host-side launcher of one pass. mat: RADIX * pitch + 2 * RADIX uint32 (pitch = ceil(n_cap/SUB); the tail
+// holds totals[RADIX] and digit_base[RADIX]). bins_out != nullptr: the digit is the tile id -> write tile ranges.
 template <typename KeyT, int BITS>
 inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, const uint32_t *vin, KeyT *kout,
-                       uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st) {
+                       uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st,
+                       int32_t *bins_out = nullptr, int bins_T = 0) {
     constexpr int RADIX = 1 << BITS;
     if (n_cap <= 0) return 0;
     const int nb = (int)((n_cap + SUB - 1) / SUB);
     uint32_t *totals = mat + (size_t)nb * RADIX;
+    uint32_t *digit_base = totals + RADIX;
     const size_t smem = sizeof(ScatterSmem<KeyT, BITS>);
     static bool attr_set = false;   // one per template instantiation
     if (!attr_set) {
@@ -261,17 +298,20 @@ inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, con
         }
         attr_set = true;
     }
-    hist_kernel<KeyT, BITS><<<nb, TPB, 0, st>>>(n_cap, n_dev, kin, shift, bits, mat);
+    hist_kernel<KeyT, BITS><<<nb, TPB, 0, st>>>(n_cap, n_dev, kin, shift, bits, mat, nb);
     GS_LAUNCH_CHECK();
-    colscan_kernel<BITS><<<(RADIX + WARPS - 1) / WARPS, TPB, 0, st>>>(n_cap, n_dev, mat, totals);
+    colscan_kernel<BITS><<<(RADIX + WARPS - 1) / WARPS, TPB, 0, st>>>(n_cap, n_dev, mat, nb, totals, nullptr, 0);
     GS_LAUNCH_CHECK();
-    scatter_kernel<KeyT, BITS><<<nb, TPB, smem, st>>>(n_cap, n_dev, kin, vin, kout, vout, shift, bits, mat, totals);
+    digit_base_kernel<BITS><<<1, TPB, 0, st>>>(n_cap, n_dev, totals, digit_base, bins_out, bins_T);
+    GS_LAUNCH_CHECK();
+    scatter_kernel<KeyT, BITS><<<nb, TPB, smem, st>>>(n_cap, n_dev, kin, vin, kout, vout, shift, bits, mat, nb,
+                                                      digit_base);
     GS_LAUNCH_CHECK();
     return 0;
 }
 
 inline size_t mat_entries(int64_t n_cap, int radix) {
-    return ((size_t)((n_cap + SUB - 1) / SUB) + 1) * (size_t)radix;
+    return ((size_t)((n_cap + SUB - 1) / SUB) + 2) * (size_t)radix;
 }
 
 }  // namespace gsradix

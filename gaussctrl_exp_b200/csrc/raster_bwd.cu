@@ -65,8 +65,8 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                    const float *__restrict__ v_out, const float *__restrict__ v_out_alpha,
                    float *__restrict__ v_xys, float *__restrict__ v_conics, float *__restrict__ v_colors,
                    float *__restrict__ v_opac) {
-    __shared__ float4 sa[RB_BATCH];  // x, y, opac, conic.a
-    __shared__ float4 sb[RB_BATCH];  // conic.b, conic.c, r, g
+    __shared__ float4 sa[RB_BATCH];  // x, y, opac, qa   (q* = pre-scaled conic, raster_common.cuh)
+    __shared__ float4 sb[RB_BATCH];  // qb, qc, r, g
     __shared__ float sc[RB_BATCH];   // b
     __shared__ float2 se[RB_BATCH];  // alpha >= 1/255 half-extents
     __shared__ int sid[RB_BATCH];
@@ -97,7 +97,7 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     }
     // d out / d alpha_k through the background and the alpha output: Tf/(1-a) * (voa - bg.vo)
     const float tail = Tf * (voa - (bg[0] * vo0 + bg[1] * vo1 + bg[2] * vo2));
-    float S0 = 0.f, S1 = 0.f, S2 = 0.f;
+    float Svo = 0.f;
 
     const int wmax = warp_max(my_end);
     if (lane == 0) s_wmax[warp] = wmax;
@@ -115,11 +115,14 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
         if (tid < cnt) {
             const int id = ids_sorted[lo + tid];
             const float2 xy = xys[id];
-            const float4 A = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
-            const float4 B = make_float4(conics[3 * id + 1], conics[3 * id + 2], colors[3 * id], colors[3 * id + 1]);
-            sa[tid] = A; sb[tid] = B;
+            const float ca = conics[3 * id], cb = conics[3 * id + 1], cc = conics[3 * id + 2];
+            const float o = opac[id];
+            float qa, qb, qc;
+            gs_prescale_conic(ca, cb, cc, qa, qb, qc);
+            sa[tid] = make_float4(xy.x, xy.y, o, qa);
+            sb[tid] = make_float4(qb, qc, colors[3 * id], colors[3 * id + 1]);
             sc[tid] = colors[3 * id + 2];
-            se[tid] = gs_alpha_extent(A.z, A.w, B.x, B.y);
+            se[tid] = gs_alpha_extent(o, ca, cb, cc);
             sid[tid] = id;
         }
         __syncthreads();
@@ -140,6 +143,9 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
         }
         __syncwarp();
         // ---- back-to-front replay over the survivors ----
+        // Per lane only the raw moments of v_sigma are formed; the conic / xy gradients are linear in
+        // them and are assembled once per (tile, Gaussian) in the flush. S.vo (colour accumulated behind,
+        // dotted with the upstream gradient) is carried as ONE running scalar.
         for (int t = nl - 1; t >= 0; --t) {
             const int j = mylist[t];
             const float4 A = sa[j];
@@ -152,21 +158,18 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             float v8 = 0.f;
             if (hit) {
-                const float cb_ = sc[j];
                 const float ra = 1.0f / (1.0f - alpha);
                 T *= ra;
                 const float fac = alpha * T;
                 v[6] = fac * vo0; v[7] = fac * vo1; v8 = fac * vo2;
-                float v_alpha = (B.z * T - S0 * ra) * vo0 + (B.w * T - S1 * ra) * vo1 + (cb_ * T - S2 * ra) * vo2;
-                v_alpha += tail * ra;
-                S0 += B.z * fac; S1 += B.w * fac; S2 += cb_ * fac;
+                const float cvo = B.z * vo0 + B.w * vo1 + sc[j] * vo2;
+                const float v_alpha = T * cvo - ra * (Svo - tail);
+                Svo += fac * cvo;
                 if (A.z * vis <= GS_ALPHA_MAX) {
                     const float v_sigma = -A.z * vis * v_alpha;
-                    v[0] = v_sigma * (A.w * dx + B.x * dy);
-                    v[1] = v_sigma * (B.x * dx + B.y * dy);
-                    v[2] = 0.5f * v_sigma * dx * dx;
-                    v[3] = v_sigma * dx * dy;
-                    v[4] = 0.5f * v_sigma * dy * dy;
+                    const float mx = v_sigma * dx, my = v_sigma * dy;
+                    v[0] = mx; v[1] = my;
+                    v[2] = mx * dx; v[3] = mx * dy; v[4] = my * dy;
                     v[5] = vis * v_alpha;
                 }
             }
@@ -176,23 +179,35 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             if (lane == 1) my_acc[j * RB_NV + 8] += r9;
         }
         __syncthreads();
-        // flush: sum the 8 warp rows, one global reduction per (Gaussian, component)
-        for (int idx = tid; idx < cnt * RB_NV; idx += 256) {
-            float sum = 0.f;
+        // flush: one thread per Gaussian sums the 8 warp rows, turns the moments into gradients
+        //   v_xy = (a mx + b my, b mx + c my),  v_conic = (mxx/2, mxy, myy/2)
+        // and issues one global reduction per (tile, Gaussian, component)
+        if (tid < cnt) {
+            float m[RB_NV];
 #pragma unroll
-            for (int w = 0; w < 8; ++w) {
-                sum += acc[w][idx];
-                acc[w][idx] = 0.f;
+            for (int c = 0; c < RB_NV; ++c) {
+                float sum = 0.f;
+#pragma unroll
+                for (int w = 0; w < 8; ++w) {
+                    sum += acc[w][tid * RB_NV + c];
+                    acc[w][tid * RB_NV + c] = 0.f;
+                }
+                m[c] = sum;
             }
-            if (sum != 0.f) {
-                const int j = idx / RB_NV, c = idx - j * RB_NV;
-                const int id = sid[j];
-                float *dst = c < 2 ? v_xys + 2 * id + c
-                           : c < 5 ? v_conics + 3 * id + (c - 2)
-                           : c == 5 ? v_opac + id
-                                    : v_colors + 3 * id + (c - 6);
-                atomicAdd(dst, sum);
+            const int id = sid[tid];
+            float ca, cb, cc;
+            gs_unscale_conic(sa[tid].w, sb[tid].x, sb[tid].y, ca, cb, cc);
+            if (m[0] != 0.f || m[1] != 0.f) {
+                atomicAdd(v_xys + 2 * id, ca * m[0] + cb * m[1]);
+                atomicAdd(v_xys + 2 * id + 1, cb * m[0] + cc * m[1]);
             }
+            if (m[2] != 0.f) atomicAdd(v_conics + 3 * id, 0.5f * m[2]);
+            if (m[3] != 0.f) atomicAdd(v_conics + 3 * id + 1, m[3]);
+            if (m[4] != 0.f) atomicAdd(v_conics + 3 * id + 2, 0.5f * m[4]);
+            if (m[5] != 0.f) atomicAdd(v_opac + id, m[5]);
+            if (m[6] != 0.f) atomicAdd(v_colors + 3 * id, m[6]);
+            if (m[7] != 0.f) atomicAdd(v_colors + 3 * id + 1, m[7]);
+            if (m[8] != 0.f) atomicAdd(v_colors + 3 * id + 2, m[8]);
         }
         __syncthreads();
     }
@@ -245,8 +260,10 @@ raster_bwdN_kernel(int C, int H, int W, int tiles_x, const int32_t *__restrict__
         if (tid < cnt) {
             const int id = ids_sorted[lo + tid];
             const float2 xy = xys[id];
-            sa[tid] = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
-            sb[tid] = make_float2(conics[3 * id + 1], conics[3 * id + 2]);
+            float qa, qb, qc;
+            gs_prescale_conic(conics[3 * id], conics[3 * id + 1], conics[3 * id + 2], qa, qb, qc);
+            sa[tid] = make_float4(xy.x, xy.y, opac[id], qa);
+            sb[tid] = make_float2(qb, qc);
             sid[tid] = id;
         }
         __syncthreads();
@@ -285,8 +302,10 @@ raster_bwdN_kernel(int C, int H, int W, int tiles_x, const int32_t *__restrict__
             float g[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (hit && A.z * vis <= GS_ALPHA_MAX) {
                 const float v_sigma = -A.z * vis * v_alpha;
-                g[0] = v_sigma * (A.w * dx + B.x * dy);
-                g[1] = v_sigma * (B.x * dx + B.y * dy);
+                float ca, cb, cc;
+                gs_unscale_conic(A.w, B.x, B.y, ca, cb, cc);
+                g[0] = v_sigma * (ca * dx + cb * dy);
+                g[1] = v_sigma * (cb * dx + cc * dy);
                 g[2] = 0.5f * v_sigma * dx * dx;
                 g[3] = v_sigma * dx * dy;
                 g[4] = 0.5f * v_sigma * dy * dy;

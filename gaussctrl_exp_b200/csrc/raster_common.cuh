@@ -11,19 +11,35 @@ __device__ __forceinline__ void gs_pixel_of_thread(int tile_x, int tile_y, int &
     py = tile_y * GS_TILE + (warp >> 1) * 4 + (lane >> 3);
 }
 
+// Splat as staged in shared memory. The conic (a,b,c) is stored pre-scaled so that the exponent is one
+// short FMA chain feeding MUFU.EX2 directly:  qa = -a/2 * log2(e), qb = -b * log2(e), qc = -c/2 * log2(e)
+//   exp(-sigma) = exp2(qa dx^2 + qb dx dy + qc dy^2)
+#define GS_LOG2E 1.4426950408889634f
 struct GsSplat {
-    float x, y, opac, ca, cb, cc;
+    float x, y, opac, qa, qb, qc;
 };
+__device__ __forceinline__ void gs_prescale_conic(float a, float b, float c, float &qa, float &qb, float &qc) {
+    qa = -0.5f * GS_LOG2E * a; qb = -GS_LOG2E * b; qc = -0.5f * GS_LOG2E * c;
+}
+// true conic back from the staged form (backward flush)
+__device__ __forceinline__ void gs_unscale_conic(float qa, float qb, float qc, float &a, float &b, float &c) {
+    a = qa * (-2.0f / GS_LOG2E); b = qb * (-1.0f / GS_LOG2E); c = qc * (-2.0f / GS_LOG2E);
+}
+__device__ __forceinline__ float gs_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 // returns false when the pair is skipped (sigma < 0 or alpha < 1/255)
 __device__ __forceinline__ bool gs_eval_alpha(const GsSplat &g, float fx, float fy, float &dx, float &dy,
                                               float &vis, float &alpha) {
     dx = g.x - fx;
     dy = g.y - fy;
-    const float sigma = 0.5f * (g.ca * dx * dx + g.cc * dy * dy) + g.cb * dx * dy;
-    vis = __expf(-sigma);
+    const float p = dx * (g.qa * dx + g.qb * dy) + (g.qc * dy) * dy;   // = -sigma * log2(e)
+    vis = gs_ex2(p);
     alpha = fminf(GS_ALPHA_MAX, g.opac * vis);
-    return !(sigma < 0.0f || alpha < GS_ALPHA_MIN);
+    return !(p > 0.0f) && (alpha >= GS_ALPHA_MIN);
 }
 
 // Conservative half-extents (in pixels) of the region where a splat can reach alpha >= 1/255:

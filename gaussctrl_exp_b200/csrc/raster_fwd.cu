@@ -15,8 +15,8 @@ namespace {
 constexpr int RF_BATCH = 256;
 
 struct StageRGB {
-    float4 a[RF_BATCH];  // x, y, opac, conic.a
-    float4 b[RF_BATCH];  // conic.b, conic.c, r, g
+    float4 a[RF_BATCH];  // x, y, opac, qa          (q* = pre-scaled conic, raster_common.cuh)
+    float4 b[RF_BATCH];  // qb, qc, r, g
     float c[RF_BATCH];   // b
     float2 e[RF_BATCH];  // alpha >= 1/255 half-extents (gs_alpha_extent)
 };
@@ -57,10 +57,14 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
         if (k < range.y) {
             const int id = ids_sorted[k];
             const float2 xy = xys[id];
-            pa = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
-            pb = make_float4(conics[3 * id + 1], conics[3 * id + 2], colors[3 * id], colors[3 * id + 1]);
+            const float ca = conics[3 * id], cb = conics[3 * id + 1], cc = conics[3 * id + 2];
+            const float o = opac[id];
+            float qa, qb, qc;
+            gs_prescale_conic(ca, cb, cc, qa, qb, qc);
+            pa = make_float4(xy.x, xy.y, o, qa);
+            pb = make_float4(qb, qc, colors[3 * id], colors[3 * id + 1]);
             pc = colors[3 * id + 2];
-            pe = gs_alpha_extent(pa.z, pa.w, pb.x, pb.y);
+            pe = gs_alpha_extent(o, ca, cb, cc);
         }
     };
     if (nbatch > 0) gather(0);
@@ -157,8 +161,10 @@ raster_fwdN_kernel(int C, int H, int W, int tiles_x, const int32_t *__restrict__
         if (k < range.y) {
             const int id = ids_sorted[k];
             const float2 xy = xys[id];
-            s.a[tid] = make_float4(xy.x, xy.y, opac[id], conics[3 * id]);
-            s.b[tid] = make_float2(conics[3 * id + 1], conics[3 * id + 2]);
+            float qa, qb, qc;
+            gs_prescale_conic(conics[3 * id], conics[3 * id + 1], conics[3 * id + 2], qa, qb, qc);
+            s.a[tid] = make_float4(xy.x, xy.y, opac[id], qa);
+            s.b[tid] = make_float2(qb, qc);
             s.id[tid] = id;
         }
         __syncthreads();
