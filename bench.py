@@ -41,7 +41,7 @@ def workload_config(n_gauss, world):
                     f"{N_CAMS} cameras on a sphere r=1.5 (garden intrinsics), one view fwd+bwd per step per GPU, "
                     f"upstream grad randn/(H*W), bg {BG}",
         "n_gaussians": n_gauss, "image": [512, 512], "sh_degree": SH_DEG, "views_per_step": world,
-        "parallelism": f"view-parallel dp{world}" + (" + allreduce(grads)" if world > 1 else ""),
+        "parallelism": f"view-parallel dp{world}" + (" + grad exchange every step" if world > 1 else ""),
         "l2": "working set (236 MB params + 236 MB grads) exceeds the 126 MB L2; no explicit flush",
     }
 
@@ -268,8 +268,14 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    gather_mode = world > 1 and model.fused and args.reduce == "gather"
+    model.view_state.defer_leaf_grads = gather_mode
+
     def reduce_grads():
         if world == 1:
+            return
+        if gather_mode:
+            gdist.reduce_view_grads(model)        # all-gather 36 B/Gaussian, replay the leaf backward per view
             return
         flat = model.view_state.flat_grads if model.fused else None
         if flat is not None:
@@ -359,6 +365,7 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
             "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
+            "grad_exchange": (args.reduce if world > 1 else None),
             "host_enqueue_ms_per_step": host_enqueue_ms,
             "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "views/s",
                     "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4},
@@ -406,6 +413,9 @@ def main():
     ap.add_argument("--cpu-views", type=int, default=8)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
+    ap.add_argument("--reduce", default="gather", choices=["gather", "allreduce"],
+                    help="N>1 gradient exchange: gather = all-gather compositor-level grads (36 B/Gaussian) + replayed "
+                         "leaf backward; allreduce = NCCL all-reduce of the 236 B/Gaussian leaf grads")
     ap.add_argument("--path", default="fused", choices=["fused", "api"],
                     help="fused: one autograd node / 5 kernels per view (render.py); api: the literal "
                          "gsplat-0.1.2 three-operator sequence of gc_model.py")

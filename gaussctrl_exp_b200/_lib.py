@@ -30,6 +30,10 @@ SIGNATURES = {
     "gs_preprocess_fwd": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_preprocess_bwd": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                _vp, _vp, _vp, _vp, _vp]),
+    "gs_view_block_floats": (_i, [_i]),
+    "gs_finish_view_block": (_i, [_i, _i, _vp, _vp, _vp, _vp]),
+    "gs_preprocess_bwd_multi": (_i, [_i, _i, _vp, _i64, _f, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp,
+                                     _vp, _vp]),
     "gs_sh_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "gs_sh_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "gs_scan_scratch_bytes": (_sz, [_i]),

@@ -123,3 +123,164 @@ extern "C" int gs_preprocess_bwd(int N, const float *means, const float *log_sca
     GS_LAUNCH_CHECK();
     return 0;
 }
+
+// ==========================================================================================
+// Multi-view variant for the data-parallel fine-tune step.
+// Every rank holds all parameters, so instead of all-reducing the 59-float leaf gradients
+// (236 B/Gaussian) the ranks all-GATHER the 9 compositor-level gradients of their view
+// (v_xy, v_conic, v_rgb [clamp already applied], v_opacity = 36 B/Gaussian, plus the camera)
+// and each rank replays this kernel over all views: 6.5x fewer NVLink bytes at 2 GPUs, 1.6x
+// at 8, and the leaf gradients are produced already summed.
+// Block layout of one view in `views` (stride floats apart), Np = N rounded up to 4:
+//   [0,2Np) v_xys | [2Np,5Np) v_conics | [5Np,8Np) v_rgbs | [8Np,9Np) v_opac | [9Np, 9Np+64) GsCamera
+// A Gaussian whose 9 values are all zero in a view is skipped for that view (culled or unseen).
+// ==========================================================================================
+namespace {
+
+__global__ void __launch_bounds__(PB_TPB)
+preprocess_bwd_multi_kernel(int N, int Np, int V, const float *__restrict__ views, size_t stride, float scale,
+                            const float *__restrict__ means, const float *__restrict__ log_scales,
+                            const float4 *__restrict__ quats, const float *__restrict__ opac_logits, int use_sh,
+                            int deg, float *__restrict__ v_means, float *__restrict__ v_log_scales,
+                            float4 *__restrict__ v_quats, float *__restrict__ v_opac_logits,
+                            float *__restrict__ v_dc, float *__restrict__ v_rest) {
+    __shared__ __align__(128) float rest_s[PB_TPB * PB_REST];
+    __shared__ GsCamera cam_s;
+    const int tid = threadIdx.x;
+    const int g0 = blockIdx.x * PB_TPB;
+    const int rows = min(PB_TPB, N - g0);
+    const int i = g0 + tid;
+    float *row = rest_s + tid * PB_REST;
+#pragma unroll
+    for (int k = 0; k < PB_REST; ++k) row[k] = 0.f;
+
+    float vm[3] = {0.f, 0.f, 0.f}, vls[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
+    float4 vq = make_float4(0.f, 0.f, 0.f, 0.f);
+    float vop = 0.f;
+    float p0 = 0.f, p1 = 0.f, p2 = 0.f, s0 = 1.f, s1 = 1.f, s2 = 1.f, iq = 1.f, o = 0.f;
+    float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+    if (i < N) {
+        p0 = means[3 * i]; p1 = means[3 * i + 1]; p2 = means[3 * i + 2];
+        s0 = expf(log_scales[3 * i]); s1 = expf(log_scales[3 * i + 1]); s2 = expf(log_scales[3 * i + 2]);
+        const float4 qr = quats[i];
+        iq = 1.0f / sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
+        q = make_float4(qr.x * iq, qr.y * iq, qr.z * iq, qr.w * iq);
+        o = 1.0f / (1.0f + expf(-opac_logits[i]));
+    }
+    for (int v = 0; v < V; ++v) {
+        const float *blk = views + (size_t)v * stride;
+        __syncthreads();
+        if (tid < (int)(sizeof(GsCamera) / 4)) reinterpret_cast<float *>(&cam_s)[tid] = blk[(size_t)9 * Np + tid];
+        __syncthreads();
+        if (i >= N) continue;
+        const float2 vxy = reinterpret_cast<const float2 *>(blk)[i];
+        const float *vc = blk + (size_t)2 * Np + 3 * (size_t)i;
+        const float *vr = blk + (size_t)5 * Np + 3 * (size_t)i;
+        const float vA = vc[0], vB = vc[1], vC = vc[2];
+        const float u0 = vr[0], u1 = vr[1], u2 = vr[2];
+        const float vo = blk[(size_t)8 * Np + i];
+        if (vxy.x == 0.f && vxy.y == 0.f && vA == 0.f && vB == 0.f && vC == 0.f && u0 == 0.f && u1 == 0.f &&
+            u2 == 0.f && vo == 0.f)
+            continue;
+        ProjGrad g;
+        gs_project_one_bwd(cam_s.viewmat, cam_s.projmat, p0, p1, p2, s0, s1, s2, cam_s.glob_scale, q, cam_s.fx,
+                           cam_s.fy, cam_s.H, cam_s.W, vxy, 0.0f, vA, vB, vC, g);
+        vm[0] += g.vp[0]; vm[1] += g.vp[1]; vm[2] += g.vp[2];
+        vls[0] += g.vs[0]; vls[1] += g.vs[1]; vls[2] += g.vs[2];
+        vq.x += g.vq.x; vq.y += g.vq.y; vq.z += g.vq.z; vq.w += g.vq.w;
+        vop += vo;
+        if (use_sh) {
+            float dx = p0 - cam_s.cam_pos[0], dy = p1 - cam_s.cam_pos[1], dz = p2 - cam_s.cam_pos[2];
+            const float vn = sqrtf(dx * dx + dy * dy + dz * dz);
+            dx = dx / vn; dy = dy / vn; dz = dz / vn;
+            float Y[16];
+            sh_basis<3>(deg, dx, dy, dz, Y);
+            const int nb = sh_num_bases(deg);
+            vd[0] += Y[0] * u0; vd[1] += Y[0] * u1; vd[2] += Y[0] * u2;
+#pragma unroll
+            for (int k = 1; k < 16; ++k)
+                if (k < nb) {
+                    row[3 * (k - 1)] += Y[k] * u0; row[3 * (k - 1) + 1] += Y[k] * u1; row[3 * (k - 1) + 2] += Y[k] * u2;
+                }
+        } else {
+            vd[0] += u0; vd[1] += u1; vd[2] += u2;     // sender already applied d sigmoid
+        }
+    }
+    if (i < N) {
+        v_means[3 * i] = vm[0] * scale; v_means[3 * i + 1] = vm[1] * scale; v_means[3 * i + 2] = vm[2] * scale;
+        v_log_scales[3 * i] = vls[0] * s0 * scale; v_log_scales[3 * i + 1] = vls[1] * s1 * scale;
+        v_log_scales[3 * i + 2] = vls[2] * s2 * scale;
+        const float dq = vq.x * q.x + vq.y * q.y + vq.z * q.z + vq.w * q.w;
+        v_quats[i] = make_float4((vq.x - q.x * dq) * iq * scale, (vq.y - q.y * dq) * iq * scale,
+                                 (vq.z - q.z * dq) * iq * scale, (vq.w - q.w * dq) * iq * scale);
+        v_opac_logits[i] = vop * o * (1.0f - o) * scale;
+        v_dc[3 * i] = vd[0] * scale; v_dc[3 * i + 1] = vd[1] * scale; v_dc[3 * i + 2] = vd[2] * scale;
+#pragma unroll
+        for (int k = 0; k < PB_REST; ++k) row[k] *= scale;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    const int rows4 = rows & ~3;
+    float *dst = v_rest + (size_t)g0 * PB_REST;
+    if (tid == 0 && rows4 > 0) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(rest_s)),
+                     "r"((unsigned)rows4 * PB_REST * 4u)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    for (int f = rows4 * PB_REST + tid; f < rows * PB_REST; f += PB_TPB) dst[f] = rest_s[f];
+    if (tid == 0 && rows4 > 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// sender side: apply the colour activation's derivative to v_rgbs in place and append the camera
+__global__ void __launch_bounds__(256)
+finish_view_block_kernel(int N, int use_sh, const float *__restrict__ rgbs, float *__restrict__ v_rgbs,
+                         const __grid_constant__ GsCamera cam, float *__restrict__ cam_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x < (int)(sizeof(GsCamera) / 4))
+        cam_out[threadIdx.x] = reinterpret_cast<const float *>(&cam)[threadIdx.x];
+    if (i >= 3 * N) return;
+    const float c = rgbs[i];
+    v_rgbs[i] = use_sh ? (c > 0.f ? v_rgbs[i] : 0.f) : v_rgbs[i] * c * (1.0f - c);
+}
+
+}  // namespace
+
+extern "C" int gs_view_block_floats(int N) { return 9 * ((N + 3) / 4 * 4) + 64; }
+
+extern "C" int gs_finish_view_block(int N, int use_sh, const GsCamera *cam_host, const float *rgbs, float *block,
+                                    void *stream) {
+    if (N < 0 || !cam_host || !block || (N > 0 && !rgbs)) return GS_ERR_BAD_ARG;
+    static_assert(sizeof(GsCamera) <= 64 * 4, "camera must fit the 64-float tail of a view block");
+    const int Np = (N + 3) / 4 * 4;
+    const int blocks = (3 * N + 255) / 256;
+    finish_view_block_kernel<<<blocks > 0 ? blocks : 1, 256, 0, (cudaStream_t)stream>>>(
+        N, use_sh, rgbs, block + (size_t)5 * Np, *cam_host, block + (size_t)9 * Np);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int gs_preprocess_bwd_multi(int N, int V, const float *views, int64_t stride_floats, float scale,
+                                       const float *means, const float *log_scales, const float *quats,
+                                       const float *opac_logits, int use_sh, int sh_deg, float *v_means,
+                                       float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
+                                       float *v_feat_rest, void *stream) {
+    if (N < 0 || V <= 0 || !views) return GS_ERR_BAD_ARG;
+    if (sh_deg < 0 || sh_deg > 3) return GS_ERR_UNSUPPORTED;
+    if (N == 0) return 0;
+    if (!means || !log_scales || !quats || !opac_logits || !v_means || !v_log_scales || !v_quats || !v_opac_logits ||
+        !v_feat_dc || !v_feat_rest)
+        return GS_ERR_BAD_ARG;
+    if (!gs_aligned16(quats) || !gs_aligned16(v_quats) || !gs_aligned16(v_feat_rest) || !gs_aligned16(views) ||
+        (stride_floats & 3))
+        return GS_ERR_MISALIGNED;
+    const int Np = (N + 3) / 4 * 4;
+    if (stride_floats < 9 * (int64_t)Np + 64) return GS_ERR_BAD_ARG;
+    const int blocks = (N + PB_TPB - 1) / PB_TPB;
+    preprocess_bwd_multi_kernel<<<blocks, PB_TPB, 0, (cudaStream_t)stream>>>(
+        N, Np, V, views, (size_t)stride_floats, scale, means, log_scales, reinterpret_cast<const float4 *>(quats),
+        opac_logits, use_sh, sh_deg, v_means, v_log_scales, reinterpret_cast<float4 *>(v_quats), v_opac_logits,
+        v_feat_dc, v_feat_rest);
+    GS_LAUNCH_CHECK();
+    return 0;
+}

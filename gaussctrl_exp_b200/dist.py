@@ -88,3 +88,30 @@ def gather_views(local: Dict[int, torch.Tensor], num_views: int, dst: int = 0):
             dist.recv(buf, src)
             out[v] = buf
     return out
+
+
+def reduce_view_grads(model, average: bool = True) -> None:
+    """Data-parallel gradient step for the fused path WITHOUT a 236 B/Gaussian all-reduce.
+
+    Precondition: `model.view_state.defer_leaf_grads = True` during this step's backward, so each rank holds
+    the compositor-level gradients of ITS view (36 B/Gaussian + camera) in `view_state.view_block`.
+    The blocks are all-gathered (one NCCL call) and every rank replays the preprocess backward over all of
+    them (gs_preprocess_bwd_multi): identical summed (or averaged) leaf gradients on every rank, written
+    into one flat buffer and installed as the parameters' .grad. Works for world_size 1 too."""
+    from . import render
+    st = model.view_state
+    block = st.view_block
+    assert block is not None, "run backward with view_state.defer_leaf_grads = True first"
+    use_sh, deg, _ = st.view_meta
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    if world > 1:
+        gathered = torch.empty(world * block.numel(), device=block.device, dtype=block.dtype)
+        dist.all_gather_into_tensor(gathered, block)
+    else:
+        gathered = block
+    params = {k: getattr(model, k) for k in GRAD_PARAMS}
+    flat, grads = render.leaf_grads_from_view_blocks(params, gathered, world, bool(use_sh), deg,
+                                                     1.0 / world if average else 1.0)
+    for k in GRAD_PARAMS:
+        getattr(model, k).grad = grads[k]
+    st.flat_grads = flat

@@ -114,11 +114,17 @@ def _check_pending(pending):
 
 class ViewState:
     """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii)."""
-    __slots__ = ("xys", "radii", "depths", "num_intersects", "xys_grad", "flat_grads")
+    __slots__ = ("xys", "radii", "depths", "num_intersects", "xys_grad", "flat_grads", "defer_leaf_grads",
+                 "view_block", "view_meta")
 
     def __init__(self):
         self.xys = self.radii = self.depths = self.xys_grad = self.flat_grads = None
         self.num_intersects = 0
+        # data-parallel mode (dist.reduce_view_grads): backward stops at the compositor-level gradients,
+        # leaves them (+ the camera) in view_block and returns no leaf gradients
+        self.defer_leaf_grads = False
+        self.view_block = None
+        self.view_meta = None
 
 
 def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, strict=True):
@@ -227,7 +233,7 @@ class _RenderView(Function):
         Np = (N + 3) // 4 * 4
         with torch.cuda.device(dev):
             st = _lib.stream_ptr()
-            g = torch.zeros(9 * Np, device=dev, dtype=torch.float32)         # accumulated into by atomics
+            g = torch.zeros(9 * Np + 64, device=dev, dtype=torch.float32)    # accumulated into by atomics
             v_xys = g[0:2 * N].view(N, 2)
             v_conics = g[2 * Np:2 * Np + 3 * N].view(N, 3)
             v_rgbs = g[5 * Np:5 * Np + 3 * N].view(N, 3)
@@ -237,6 +243,15 @@ class _RenderView(Function):
                                  v_out.data_ptr(), va_ptr, v_xys.data_ptr(), v_conics.data_ptr(), v_rgbs.data_ptr(),
                                  v_opac.data_ptr(), st)
             _lib.check(rc, "gs_raster_bwd")
+            if ctx.state is not None and ctx.state.defer_leaf_grads:
+                rc = L.gs_finish_view_block(N, int(ctx.use_sh), _ctypes_addr(cam), rgbs.data_ptr(), g.data_ptr(), st)
+                _lib.check(rc, "gs_finish_view_block")
+                if ctx.pending is not None:
+                    ctx.state.num_intersects = _check_pending(ctx.pending)
+                ctx.state.xys_grad = v_xys
+                ctx.state.view_block = g
+                ctx.state.view_meta = (int(ctx.use_sh), int(ctx.deg), tuple(opacities.shape))
+                return (None,) * 11
             # the six leaf gradients live in ONE flat buffer (59 floats / Gaussian) so that the
             # data-parallel step can all-reduce them with a single NCCL call
             flat = torch.empty(59 * Np, device=dev, dtype=torch.float32)
@@ -295,3 +310,28 @@ def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: T
                                       bg.data_ptr(), out.data_ptr(), fT.data_ptr(), fidx.data_ptr(), _lib.stream_ptr())
     _lib.check(rc, "gs_raster_fwd")
     return out
+
+
+def leaf_grads_from_view_blocks(params, blocks: Tensor, num_views: int, use_sh: bool, deg: int, scale: float = 1.0):
+    """gs_preprocess_bwd_multi: `blocks` = num_views view blocks back to back (as all-gathered). Returns
+    (flat, dict of the six leaf gradients as views of flat), gradients = scale * sum over the views."""
+    means, scales, quats, opacities = params["means"], params["scales"], params["quats"], params["opacities"]
+    dev = means.device
+    N = means.shape[0]
+    Np = (N + 3) // 4 * 4
+    L = _lib.lib()
+    stride = L.gs_view_block_floats(N)
+    assert blocks.numel() == num_views * stride and blocks.is_contiguous()
+    flat = torch.empty(59 * Np, device=dev, dtype=torch.float32)
+    out = {"means": flat[0:3 * N].view(N, 3), "scales": flat[3 * Np:3 * Np + 3 * N].view(N, 3),
+           "quats": flat[6 * Np:6 * Np + 4 * N].view(N, 4), "opacities": flat[10 * Np:10 * Np + N].view(opacities.shape),
+           "features_dc": flat[11 * Np:11 * Np + 3 * N].view(N, 3),
+           "features_rest": flat[14 * Np:14 * Np + 45 * N].view(N, 15, 3)}
+    with torch.cuda.device(dev):
+        rc = L.gs_preprocess_bwd_multi(
+            N, int(num_views), blocks.data_ptr(), stride, float(scale), means.detach().data_ptr(),
+            scales.detach().data_ptr(), quats.detach().data_ptr(), opacities.detach().data_ptr(), int(use_sh), int(deg),
+            out["means"].data_ptr(), out["scales"].data_ptr(), out["quats"].data_ptr(), out["opacities"].data_ptr(),
+            out["features_dc"].data_ptr(), out["features_rest"].data_ptr(), _lib.stream_ptr())
+    _lib.check(rc, "gs_preprocess_bwd_multi")
+    return flat, out

@@ -104,6 +104,21 @@ int gs_preprocess_bwd(int N, const float *means, const float *log_scales, const 
                       float *v_quats, float *v_opac_logits, float *v_feat_dc, float *v_feat_rest,
                       void *stream);
 
+/* Data-parallel fine-tune step without a 236 B/Gaussian all-reduce: a "view block" holds
+ * the 9 compositor-level gradients of one view (v_xys 2Np | v_conics 3Np | v_rgbs 3Np | v_opac Np, Np = N
+ * rounded up to 4) followed by the 64-float camera slot = gs_view_block_floats(N) floats. It is the
+ * buffer gs_raster_bwd accumulates into; gs_finish_view_block applies the colour activation's derivative
+ * to v_rgbs in place and appends the camera. Ranks all-gather their blocks (36 B/Gaussian) and each runs
+ * gs_preprocess_bwd_multi over all V blocks: leaf gradients = scale * sum over views. */
+int gs_view_block_floats(int N);
+int gs_finish_view_block(int N, int use_sh, const GsCamera *cam_host, const float *rgbs, float *block,
+                         void *stream);
+int gs_preprocess_bwd_multi(int N, int V, const float *views, int64_t stride_floats, float scale,
+                            const float *means, const float *log_scales, const float *quats,
+                            const float *opac_logits, int use_sh, int sh_deg, float *v_means,
+                            float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
+                            float *v_feat_rest, void *stream);
+
 /* ---- stage 2: tile binning (inside rasterize_gaussians; App. A.3) -------------------------- */
 size_t gs_scan_scratch_bytes(int N);
 /* inclusive int32 scan of tiles_hit -> cum; the total is also written to *total_dev

@@ -129,3 +129,47 @@ def test_speculative_capacity_overflow_is_detected(cuda_dev):
     out["rgb"].sum().backward()
     assert torch.equal(out["rgb"].detach(), ref) and m.means.grad.abs().max() > 0
     assert m.view_state.num_intersects > 2048
+
+
+def test_view_block_replay_equals_summed_leaf_grads(cuda_dev):
+    """The data-parallel exchange (dist.reduce_view_grads): leaf grads replayed from the gathered per-view
+    compositor gradients == sum of the per-view leaf grads of the ordinary backward. Two 'ranks' are two
+    cameras on one GPU; world_size-1 path of reduce_view_grads is exercised too."""
+    from gaussctrl_exp_b200 import dist as gd
+    from gaussctrl_exp_b200 import render, scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    dev = cuda_dev
+    p = scene.make_scene(20000, 7, s0=0.02, device=dev)
+    cams = [small_cam(160, 128, s) for s in (7, 8)]
+    v = torch.randn(128, 160, 3, generator=torch.Generator().manual_seed(1)).to(dev) / (128 * 160)
+    for deg in (3, 0):
+        m = GaussianModel(p, sh_degree=deg, background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
+        m.train()
+        want = {}
+        for cam in cams:
+            for q in m.parameters():
+                q.grad = None
+            (m(cam)["rgb"] * v).sum().backward()
+            for k in gd.GRAD_PARAMS:
+                want[k] = want.get(k, 0) + getattr(m, k).grad.clone()
+        m.view_state.defer_leaf_grads = True
+        blocks = []
+        for cam in cams:
+            for q in m.parameters():
+                q.grad = None
+            (m(cam)["rgb"] * v).sum().backward()
+            assert m.means.grad is None
+            blocks.append(m.view_state.view_block.clone())
+        use_sh, d, _ = m.view_state.view_meta
+        flat, got = render.leaf_grads_from_view_blocks({k: getattr(m, k) for k in gd.GRAD_PARAMS}, torch.cat(blocks), 2,
+                                                       bool(use_sh), d, 1.0)
+        for k in gd.GRAD_PARAMS:
+            den = want[k].abs().max().item()
+            if den == 0:
+                assert got[k].abs().max().item() == 0
+            else:
+                assert (got[k] - want[k]).abs().max().item() / den < 2e-5, k
+        gd.reduce_view_grads(m)             # world size 1: own block only == last camera's ordinary grads
+        for q in m.parameters():
+            q.grad = None
+        m.view_state.defer_leaf_grads = False
