@@ -356,6 +356,24 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
     ms_e2e, _ = timed_loop(step_e2e, max(3, args.warmup // 2), args.steps, drain=drain_losses)
 
+    # config 3: all-view eval render, RGB + depth + alpha, 40 views sharded over the ranks
+    model.eval_render = True
+    def render_all():
+        return model.render_views(cams, rank, world, num_streams=args.render_streams)
+    for _ in range(2):
+        render_all()
+    barrier()
+    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    r0.record()
+    for _ in range(args.render_reps):
+        render_all()
+    r1.record()
+    barrier()
+    t_r = torch.tensor([r0.elapsed_time(r1)], device=dev)
+    if world > 1:
+        dist.all_reduce(t_r, op=dist.ReduceOp.MAX)
+    render_vps = N_CAMS * args.render_reps / (float(t_r.item()) * 1e-3)
+
     line = None
     if rank == 0:
         ms_step = ms_total / args.steps
@@ -366,6 +384,8 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
             "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
             "grad_exchange": (args.reduce if world > 1 else None),
+            "eval_render": {"views_per_s": render_vps, "what": f"all-view RGB+depth+alpha render of {N_CAMS} cameras "
+                            f"(gc_pipeline.py:222-228), view-sharded over {world} GPU(s), {args.render_streams} streams/GPU"},
             "host_enqueue_ms_per_step": host_enqueue_ms,
             "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "views/s",
                     "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4},
@@ -413,6 +433,8 @@ def main():
     ap.add_argument("--cpu-views", type=int, default=8)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
+    ap.add_argument("--render-streams", type=int, default=2)
+    ap.add_argument("--render-reps", type=int, default=3)
     ap.add_argument("--reduce", default="gather", choices=["gather", "allreduce"],
                     help="N>1 gradient exchange: gather = all-gather compositor-level grads (36 B/Gaussian) + replayed "
                          "leaf backward; allreduce = NCCL all-reduce of the 236 B/Gaussian leaf grads")

@@ -17,15 +17,20 @@ constexpr int RF_BATCH = 256;
 struct StageRGB {
     float4 a[RF_BATCH];  // x, y, opac, qa          (q* = pre-scaled conic, raster_common.cuh)
     float4 b[RF_BATCH];  // qb, qc, r, g
-    float c[RF_BATCH];   // b
+    float2 c[RF_BATCH];  // b, view-space depth (RGB-D variant)
     float2 e[RF_BATCH];  // alpha >= 1/255 half-extents (gs_alpha_extent)
 };
 
+// WITH_DEPTH: a 4th channel (the Gaussian's view-space depth, zero background) is composited in the
+// same pass: the eval path of gc_model.py:208-238 needs RGB + alpha + depth and gsplat renders (and
+// bins, and sorts) twice for it.
+template <bool WITH_DEPTH>
 __global__ void __launch_bounds__(256)
 raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_sorted,
                    const int2 *__restrict__ tile_bins, const float2 *__restrict__ xys,
                    const float *__restrict__ conics, const float *__restrict__ colors,
-                   const float *__restrict__ opac, const float *__restrict__ bg, float *__restrict__ out_img,
+                   const float *__restrict__ opac, const float *__restrict__ depths,
+                   const float *__restrict__ bg, float *__restrict__ out_img, float *__restrict__ out_depth,
                    float *__restrict__ final_T, int32_t *__restrict__ final_idx) {
     __shared__ StageRGB st[2];
     __shared__ unsigned char wlist[8][RF_BATCH];   // per-warp compacted survivors of the current batch
@@ -44,13 +49,13 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned char *mylist = wlist[warp];
 
-    float T = 1.0f, r = 0.f, g = 0.f, b = 0.f;
+    float T = 1.0f, r = 0.f, g = 0.f, b = 0.f, dacc = 0.f;
     int last = range.x;
     bool done = !inside;
 
     // register prefetch of the next batch: the gather latency hides behind the compositing
     float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pb = pa;
-    float pc = 0.f;
+    float2 pc = make_float2(0.f, 0.f);
     float2 pe = make_float2(-1.f, -1.f);
     auto gather = [&](int batch) {
         const int k = range.x + batch * RF_BATCH + tid;
@@ -63,7 +68,7 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             gs_prescale_conic(ca, cb, cc, qa, qb, qc);
             pa = make_float4(xy.x, xy.y, o, qa);
             pb = make_float4(qb, qc, colors[3 * id], colors[3 * id + 1]);
-            pc = colors[3 * id + 2];
+            pc = make_float2(colors[3 * id + 2], WITH_DEPTH ? depths[id] : 0.f);
             pe = gs_alpha_extent(o, ca, cb, cc);
         }
     };
@@ -105,7 +110,9 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                     done = true;
                 } else {
                     const float w = alpha * T;
-                    r += w * B.z; g += w * B.w; b += w * s.c[j];
+                    const float2 Cc = s.c[j];
+                    r += w * B.z; g += w * B.w; b += w * Cc.x;
+                    if (WITH_DEPTH) dacc += w * Cc.y;
                     T = Tn;
                     last = kbase + j + 1;
                 }
@@ -118,6 +125,7 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
         out_img[3 * pix] = r + T * bg[0];
         out_img[3 * pix + 1] = g + T * bg[1];
         out_img[3 * pix + 2] = b + T * bg[2];
+        if (WITH_DEPTH) out_depth[pix] = dacc;
         final_T[pix] = T;
         final_idx[pix] = last;
     }
@@ -216,12 +224,31 @@ extern "C" int gs_raster_fwd(int C, int H, int W, int tiles_x, int tiles_y,
     const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
     const float2 *xy2 = reinterpret_cast<const float2 *>(xys);
 #define GS_FWD_ARGS H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg, out_img, final_T, final_idx
-    if (C == 3) raster_fwd3_kernel<<<tiles, 256, 0, st>>>(GS_FWD_ARGS);
+    if (C == 3)
+        raster_fwd3_kernel<false><<<tiles, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, nullptr,
+                                                         bg, out_img, nullptr, final_T, final_idx);
     else if (C <= 4) raster_fwdN_kernel<4><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
     else if (C <= 8) raster_fwdN_kernel<8><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
     else if (C <= 16) raster_fwdN_kernel<16><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
     else raster_fwdN_kernel<32><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
 #undef GS_FWD_ARGS
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
+                                  const int32_t *ids_sorted, const int32_t *tile_bins,
+                                  const float *xys, const float *conics, const float *colors, const float *opac,
+                                  const float *depths, const float *bg, float *out_img, float *out_depth,
+                                  float *final_T, int32_t *final_idx, void *stream) {
+    if (H <= 0 || W <= 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (!tile_bins || !xys || !conics || !colors || !opac || !depths || !bg || !out_img || !out_depth || !final_T ||
+        !final_idx)
+        return GS_ERR_BAD_ARG;
+    if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
+    raster_fwd3_kernel<true><<<tiles_x * tiles_y, 256, 0, (cudaStream_t)stream>>>(
+        H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys),
+        conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx);
     GS_LAUNCH_CHECK();
     return 0;
 }

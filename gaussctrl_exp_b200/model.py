@@ -159,16 +159,18 @@ class GaussianModel(nn.Module):
                     "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
         with torch.no_grad(), torch.cuda.device(dev):
             bg = background.to(dev).float().contiguous()
-            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, _) = _render._forward_impl(
+            want_depth = not self.training
+            res = _render._forward_impl(
                 self.means.detach(), self.scales.detach(), self.quats.detach(), self.opacities.detach(),
-                self.features_dc.detach(), self.features_rest.detach(), cam, use_sh, n, bg)
+                self.features_dc.detach(), self.features_rest.detach(), cam, use_sh, n, bg, strict=True,
+                with_depth=want_depth)
+            xys, radii, out, fT, depth_acc = res[0], res[5], res[9], res[10], res[13]
             self.xys, self.radii = xys, radii
             alpha = (1.0 - fT)[..., None]
             rgb = torch.clamp(out, max=1.0)
             depth_im = None
-            if not self.training:                                     # gc_model.py:224-238, binning reused
-                depth_im = _render.composite_extra((xys, conics, opac, ids_sorted, bins), depths[:, None], camera,
-                                                   torch.zeros(1, device=dev))
+            if want_depth:                                            # gc_model.py:224-238 in the same pass
+                depth_im = depth_acc[..., None]
                 depth_im = torch.where(alpha > 0, depth_im / alpha, torch.full_like(depth_im, 1000.0))
         viewmat0, projmat0 = self._caller_matrices(camera)
         return {"rgb": rgb, "depth": depth_im, "accumulation": alpha,
@@ -240,6 +242,31 @@ class GaussianModel(nn.Module):
 
     def forward(self, camera: Camera):
         return self.get_outputs(camera)
+
+    @torch.no_grad()
+    def render_views(self, cameras, rank: int = 0, world: int = 1, num_streams: int = 2, keep=("rgb", "depth", "accumulation")):
+        """The all-view render loop of gc_pipeline.py:222-228 / gc_render.py:196-203, view-sharded
+        (rank renders views v with v % world == rank) and software-pipelined over `num_streams` CUDA
+        streams: the latency-bound binning of one view overlaps the compositing of another.
+        Returns {view index: {name: tensor}} for this rank's views."""
+        from .dist import shard_views
+        dev = self.device
+        mine = shard_views(len(cameras), rank, world)
+        streams = [torch.cuda.Stream(device=dev) for _ in range(max(1, num_streams))]
+        cur = torch.cuda.current_stream(dev)
+        for s_ in streams:
+            s_.wait_stream(cur)
+        results = {}
+        for k, v in enumerate(mine):
+            with torch.cuda.stream(streams[k % len(streams)]):
+                out = self.get_outputs_for_camera(cameras[v])
+                results[v] = {name: out[name] for name in keep}
+                for t in results[v].values():
+                    if t is not None and t.is_cuda:
+                        t.record_stream(cur)        # handed to the caller's stream
+        for s_ in streams:
+            cur.wait_stream(s_)
+        return results
 
 
 __all__ = ["GaussianModel", "camera_matrices", "projection_matrix", "projection_matrix_ogl", "num_sh_bases"]

@@ -1,0 +1,95 @@
+"""Callers either side of the render path: what the reference does with a
+rendered view before ControlNet, and where the Gaussians come from.
+
+* depth -> world points      /root/reference/gaussctrl/gc_pipeline.py:286-314 (+ ray builder :503-536)
+* depth -> disparity         gc_pipeline.py:449-457
+* splatfacto checkpoint I/O  gc_trainer.py:147-174 (torch.save dict; parameter names gc_model.py:157-170)
+
+Plain tensor ops on whatever device the inputs live on (these are O(H*W) post-ops, not kernels worth
+hand-writing); the reference's per-pixel Python double loop for the ray directions is vectorised and
+cached. Pinned against the reference's own functions by tests/golden/reference_postops.npz.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Tuple
+
+import torch
+from torch import Tensor
+
+_ray_cache: Dict[Tuple, Tensor] = {}
+
+PARAM_KEYS = ("means", "scales", "quats", "features_dc", "features_rest", "opacities")
+
+
+def compute_ray_directions(resolution: Tuple[int, int], fov_y_rad: float = 0.8880228256678113, near: float = 0.001,
+                           far: float = 1000.0, device="cpu") -> Tensor:
+    """gc_pipeline.py:503-536, vectorised. NOTE the reference unpacks `width, height = resolution` while its
+    caller passes (h, w) (gc_pipeline.py:299): reproduced as is (identical for the square 512x512 views)."""
+    width, height = resolution
+    key = (width, height, fov_y_rad, near, str(device))
+    hit = _ray_cache.get(key)
+    if hit is not None:
+        return hit
+    aspect_ratio = width / height
+    viewport_height = 2 * math.tan(fov_y_rad / 2) * near
+    viewport_width = viewport_height * aspect_ratio
+    center_x, center_y = viewport_width / 2, viewport_height / 2
+    xs = (torch.arange(width, dtype=torch.float64) + 0.5) / width * viewport_width - center_x
+    ys = (torch.arange(height, dtype=torch.float64) + 0.5) / height * viewport_height - center_y
+    d = torch.empty((height, width, 3), dtype=torch.float32)
+    d[..., 0] = xs.float()[None, :]
+    d[..., 1] = ys.float()[:, None]
+    d[..., 2] = -near
+    d = d / d.norm(dim=-1, keepdim=True)
+    d = d.to(device)
+    _ray_cache[key] = d
+    return d
+
+
+def depth_map_screen_to_world(depth_map: Tensor, mats_view: Tensor) -> Tensor:
+    """gc_pipeline.py:286-314: depth (h,w,1) along the per-pixel ray, un-projected with inverse(mat_view)
+    (the un-flipped world->camera matrix returned as outputs['mat_view']). -> (h,w,3)."""
+    h, w, _ = depth_map.shape
+    rays_d = compute_ray_directions((h, w), device=depth_map.device)
+    pts_view = rays_d * depth_map
+    pts_view = torch.cat((pts_view, torch.ones((h, w, 1), dtype=rays_d.dtype, device=rays_d.device)), dim=-1)
+    inv_view = torch.linalg.inv(mats_view.to(depth_map.device).float())
+    pts_world = pts_view.reshape(-1, 4).float() @ inv_view.T
+    pts_world = pts_world / pts_world[:, 3:4]
+    return pts_world.reshape(h, w, 4)[:, :, :3]
+
+
+def depth2disparity(depth: Tensor) -> Tensor:
+    """gc_pipeline.py:449-457: depth (1,h,w) -> normalised disparity (1,3,h,w) for the depth ControlNet."""
+    disparity = 1 / (depth + 1e-5)
+    disparity_map = disparity / torch.max(disparity)
+    return torch.cat([disparity_map, disparity_map, disparity_map], dim=0)[None]
+
+
+def load_splatfacto_checkpoint(path: str, map_location="cpu") -> Tuple[Dict[str, Tensor], int]:
+    """Reads the dict written at gc_trainer.py:158-168 ({'step', 'pipeline', 'optimizers', 'scalers'}) and
+    returns (the six leaf tensors, step). Accepts nerfstudio 1.0.0 names (`_model.means`) and the later
+    `_model.gauss_params.means` spelling."""
+    ckpt = torch.load(path, map_location=map_location, weights_only=False)
+    sd = ckpt["pipeline"] if "pipeline" in ckpt else ckpt
+    out = {}
+    for k in PARAM_KEYS:
+        for name in (f"_model.{k}", f"_model.gauss_params.{k}", f"module._model.{k}", k):
+            if name in sd:
+                out[k] = sd[name].detach().float().contiguous()
+                break
+        else:
+            raise KeyError(f"checkpoint has no parameter '{k}' (keys: {list(sd)[:8]} ...)")
+    n = out["means"].shape[0]
+    if out["features_dc"].ndim == 3:           # some exporters keep (N,1,3)
+        out["features_dc"] = out["features_dc"].reshape(n, 3)
+    out["opacities"] = out["opacities"].reshape(n, 1)
+    return out, int(ckpt.get("step", 0))
+
+
+def save_splatfacto_checkpoint(path: str, params: Dict[str, Tensor], step: int) -> None:
+    """Writes the same layout (pipeline state dict with `_model.<name>` keys) so the reference's
+    `_load_checkpoint` (gc_trainer.py:75) can read it back."""
+    sd = {f"_model.{k}": params[k].detach().cpu() for k in PARAM_KEYS}
+    torch.save({"step": int(step), "pipeline": sd, "optimizers": {}, "scalers": {}}, path)

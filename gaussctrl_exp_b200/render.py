@@ -72,10 +72,13 @@ def gs_camera(camera: Camera, glob_scale: float = 1.0, clip: float = 0.01) -> _l
 
 
 def _get_scratch(dev, nbytes):
-    buf = _scratch.get(dev.index)
+    """Grow-only scratch arena per (device, stream): views rendered concurrently on different streams must
+    not share radix ping-pong buffers."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    buf = _scratch.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(int(nbytes * 1.25) + 256, device=dev, dtype=torch.uint8)
-        _scratch[dev.index] = buf
+        _scratch[key] = buf
     return buf
 
 
@@ -127,7 +130,8 @@ class ViewState:
         self.view_meta = None
 
 
-def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, strict=True):
+def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, strict=True,
+                  with_depth=False):
     """strict=True: the host confirms the tile-list capacity before returning (one 4-byte read, overlapped
     with the compositing kernel; overflow -> redo). strict=False: nothing is read; the caller must run
     _check_pending(result[-1]) before trusting the view (render_view does it at the end of backward)."""
@@ -160,6 +164,7 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
     out = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
     fT = torch.empty((H, W), device=dev, dtype=torch.float32)
     fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
+    out_depth = torch.empty((H, W), device=dev, dtype=torch.float32) if with_depth else None
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
         scratch = _get_scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T))
@@ -171,9 +176,15 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
         pinned.copy_(total, non_blocking=True)
         ev.record()
         # compositing is enqueued BEFORE the host looks at the count: it only reads tile_bins
-        rc = L.gs_raster_fwd(3, H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(), conics.data_ptr(),
-                             rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(), out.data_ptr(), fT.data_ptr(),
-                             fidx.data_ptr(), st)
+        if with_depth:     # RGB + depth in one pass over the same tile lists (gc_model.py:208-238)
+            rc = L.gs_raster_fwd_rgbd(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                      conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), depths.data_ptr(),
+                                      bg.data_ptr(), out.data_ptr(), out_depth.data_ptr(), fT.data_ptr(),
+                                      fidx.data_ptr(), st)
+        else:
+            rc = L.gs_raster_fwd(3, H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                 conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(), out.data_ptr(),
+                                 fT.data_ptr(), fidx.data_ptr(), st)
         _lib.check(rc, "gs_raster_fwd")
         if not strict:
             return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, None,
@@ -184,6 +195,8 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
             _cap_hint[key] = max(int(I * 1.5) + 1024, 1024)
             break
         cap = int(I * 1.5) + 1024      # capacity was too small: nothing was composited from a torn list; redo
+    if with_depth:
+        return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, out_depth)
     return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, None)
 
 

@@ -156,6 +156,15 @@ int gs_raster_fwd(int C, int H, int W, int tiles_x, int tiles_y,
                   const float *bg, float *out_img, float *final_T, int32_t *final_idx,
                   void *stream);
 
+/* RGB + depth in ONE pass over the same tile lists (the eval path of gc_model.py:208-238 composites twice
+ * and gsplat re-bins and re-sorts for the second call). out_depth (H,W) = sum_k alpha_k T_k depth_k with a
+ * zero background, i.e. channel 0 of the reference's second rasterize call before its division by alpha. */
+int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
+                       const int32_t *ids_sorted, const int32_t *tile_bins,
+                       const float *xys, const float *conics, const float *colors, const float *opac,
+                       const float *depths, const float *bg, float *out_img, float *out_depth,
+                       float *final_T, int32_t *final_idx, void *stream);
+
 /* ---- stage 4: backward compositing (App. A.5) ---------------------------------------------- */
 /* v_out (H,W,C); v_out_alpha (H,W) or NULL. Outputs are ACCUMULATED INTO: caller zero-fills
  * v_xys (N,2), v_conics (N,3), v_colors (N,C), v_opac (N). */

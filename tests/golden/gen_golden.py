@@ -53,6 +53,29 @@ def main():
         out[f"ad_render_ogl_{i}"] = env_ad["projection_matrix_ogl"](fovx, fovy)
     np.savez(os.path.join(HERE, "reference_matrices.npz"), **out)
 
+    # 3. reference_postops.npz — the reference's own depth post-ops (gc_pipeline.py:286-314, :449-457,
+    #    :503-536), extracted by AST and executed unmodified on seeded inputs.
+    from einops import rearrange
+    env_p = {"np": np, "torch": torch, "rearrange": rearrange}
+    extract(os.path.join(REF, "gc_pipeline.py"), {"compute_ray_directions"}, env_p)
+    tree = ast.parse(open(os.path.join(REF, "gc_pipeline.py")).read())
+    for node in ast.walk(tree):
+        if isinstance(node, ast.FunctionDef) and node.name in ("depth_map_screen_to_world", "depth2disparity_torch"):
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "gc_pipeline.py", "exec"), env_p)
+    g = torch.Generator().manual_seed(9)
+    h = w = 48
+    depth = torch.rand(h, w, 1, generator=g) * 3 + 0.2
+    c2w = torch.eye(4)
+    A = torch.linalg.qr(torch.randn(3, 3, generator=g))[0]
+    c2w[:3, :3] = A
+    c2w[:3, 3] = torch.randn(3, generator=g)
+    mat_view = torch.linalg.inv(c2w)
+    rays = env_p["compute_ray_directions"](resolution=(h, w))
+    pts = env_p["depth_map_screen_to_world"](None, depth, mat_view)
+    disp = env_p["depth2disparity_torch"](None, depth[:, :, 0][None])
+    np.savez(os.path.join(HERE, "reference_postops.npz"), depth=depth.numpy(), mat_view=mat_view.numpy(), rays=rays,
+             pts_world=pts.numpy(), disparity=disp.numpy(), rays_rect=env_p["compute_ray_directions"](resolution=(20, 12)))
+
     from oracle import oracle as orc
     from util import np_params, small_cam
     N, W, H = 600, 64, 48

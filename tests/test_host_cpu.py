@@ -169,3 +169,28 @@ def test_bench_reference_arm_cli_contract():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
                        env=env, capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_postops_match_reference_goldens(tmp_path):
+    """depth -> world points / disparity and the ray builder against the reference's OWN functions
+    (gc_pipeline.py:286-314, :449-457, :503-536; executed unmodified by tests/golden/gen_golden.py)."""
+    from gaussctrl_exp_b200 import postops
+    g = np.load(os.path.join(GOLD, "reference_postops.npz"))
+    h, w, _ = g["depth"].shape
+    rays = postops.compute_ray_directions((h, w)).numpy()
+    assert rays.shape == g["rays"].shape and np.abs(rays - g["rays"]).max() < 1e-6
+    rr = postops.compute_ray_directions((20, 12)).numpy()
+    assert rr.shape == g["rays_rect"].shape and np.abs(rr - g["rays_rect"]).max() < 1e-6
+    pts = postops.depth_map_screen_to_world(torch.from_numpy(g["depth"]), torch.from_numpy(g["mat_view"])).numpy()
+    assert np.abs(pts - g["pts_world"]).max() < 1e-5
+    disp = postops.depth2disparity(torch.from_numpy(g["depth"][:, :, 0][None])).numpy()
+    assert disp.shape == g["disparity"].shape and np.abs(disp - g["disparity"]).max() < 1e-6
+    # checkpoint round trip in the layout of gc_trainer.py:158-168
+    from gaussctrl_exp_b200 import scene
+    p = scene.make_scene(50, 1)
+    f = str(tmp_path / "step-000029999.ckpt")
+    postops.save_splatfacto_checkpoint(f, p, 29999)
+    q, step = postops.load_splatfacto_checkpoint(f)
+    assert step == 29999 and all(torch.equal(p[k], q[k]) for k in p)
+    raw = torch.load(f, weights_only=False)
+    assert set(raw) == {"step", "pipeline", "optimizers", "scalers"} and "_model.features_rest" in raw["pipeline"]

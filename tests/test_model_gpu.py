@@ -173,3 +173,31 @@ def test_view_block_replay_equals_summed_leaf_grads(cuda_dev):
         for q in m.parameters():
             q.grad = None
         m.view_state.defer_leaf_grads = False
+
+
+def test_render_views_matches_single_view_calls(oracle, cuda_dev):
+    """The view-sharded, multi-stream all-view loop (gc_pipeline.py:222-228) returns exactly what
+    per-camera get_outputs_for_camera returns; the fused RGB-D pass equals the reference's two passes."""
+    from gaussctrl_exp_b200 import scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    dev = cuda_dev
+    p = scene.make_scene(40000, 9, s0=0.01, device=dev)
+    cams = scene.make_cameras(7, 3, intrinsics=dict(fx=300.0, fy=299.0, cx=127.6, cy=96.3, W=256, H=192))
+    m = GaussianModel(p, background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
+    lit = GaussianModel(p, background_color=torch.tensor([0.1, 0.2, 0.3]), fused=False).to(dev)
+    single = {v: m.get_outputs_for_camera(c) for v, c in enumerate(cams)}
+    got = {}
+    for rank in range(3):
+        part = m.render_views(cams, rank, 3, num_streams=2)
+        assert sorted(part) == list(range(rank, 7, 3))
+        got.update(part)
+    torch.cuda.synchronize()
+    for v in range(7):
+        for k in ("rgb", "depth", "accumulation"):
+            assert torch.equal(got[v][k], single[v][k]), (v, k)
+    two_pass = lit.get_outputs_for_camera(cams[2])      # literal path: separate 3-channel depth pass
+    assert (two_pass["rgb"] - single[2]["rgb"]).abs().max().item() < 2e-5
+    assert (two_pass["accumulation"] - single[2]["accumulation"]).abs().max().item() < 2e-5
+    seen = single[2]["accumulation"][..., 0] > 1e-3
+    rel = ((two_pass["depth"] - single[2]["depth"]).abs() / two_pass["depth"].abs())[..., 0][seen]
+    assert rel.max().item() < 1e-4
