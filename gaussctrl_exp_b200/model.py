@@ -105,6 +105,7 @@ class GaussianModel(nn.Module):
         self.fused = fused
         self.view_state = _render.ViewState()
         self._mat_cache = {}
+        self._streams = []
         self.xys: Optional[Tensor] = None
         self.radii: Optional[Tensor] = None
         self.last_size = None
@@ -252,7 +253,11 @@ class GaussianModel(nn.Module):
         from .dist import shard_views
         dev = self.device
         mine = shard_views(len(cameras), rank, world)
-        streams = [torch.cuda.Stream(device=dev) for _ in range(max(1, num_streams))]
+        # streams are created once and reused: the caching allocator keeps one memory pool per stream, so
+        # fresh streams on every call would mean fresh cudaMallocs on every call
+        while len(self._streams) < max(1, num_streams):
+            self._streams.append(torch.cuda.Stream(device=dev))
+        streams = self._streams[:max(1, num_streams)]
         cur = torch.cuda.current_stream(dev)
         for s_ in streams:
             s_.wait_stream(cur)
