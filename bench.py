@@ -199,15 +199,23 @@ def stage_breakdown(model, cams, v_out, iters=20):
         fT = torch.empty((H, W), device=dev)
         fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
         opv = opac.view(-1).contiguous()
-        fwd = lambda: L.gs_raster_fwd(3, H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                      conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), bg.data_ptr(), out.data_ptr(),
-                                      fT.data_ptr(), fidx.data_ptr(), _lib.stream_ptr())
+        order_f = torch.empty(T, device=dev, dtype=torch.int32)
+        order_b = torch.empty(T, device=dev, dtype=torch.int32)
+        twork = torch.empty(T, device=dev, dtype=torch.int32)
+        L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), _lib.stream_ptr())
+        st["tile_order"] = (timed(lambda: L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), _lib.stream_ptr())), None)
+        fwd = lambda: L.gs_raster_fwd_ordered(H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                              conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), None, bg.data_ptr(),
+                                              out.data_ptr(), None, fT.data_ptr(), fidx.data_ptr(), order_f.data_ptr(),
+                                              twork.data_ptr(), _lib.stream_ptr())
         st["raster_fwd"] = (timed(fwd), None)
         g = [torch.zeros((N, k), device=dev) for k in (2, 3, 3, 1)]
-        bwd = lambda: L.gs_raster_bwd(3, H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                      conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), bg.data_ptr(), fT.data_ptr(),
-                                      fidx.data_ptr(), v_out.data_ptr(), None, g[0].data_ptr(), g[1].data_ptr(),
-                                      g[2].data_ptr(), g[3].data_ptr(), _lib.stream_ptr())
+        L.gs_tile_order(T, twork.data_ptr(), 0, order_b.data_ptr(), _lib.stream_ptr())
+        bwd = lambda: L.gs_raster_bwd_ordered(H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                              conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), bg.data_ptr(),
+                                              fT.data_ptr(), fidx.data_ptr(), v_out.data_ptr(), None, g[0].data_ptr(),
+                                              g[1].data_ptr(), g[2].data_ptr(), g[3].data_ptr(), order_b.data_ptr(),
+                                              _lib.stream_ptr())
         st["raster_bwd"] = (timed(bwd), None)
         vcoef = torch.empty((N, 16, 3), device=dev)
         st["sh_bwd"] = (timed(lambda: L.gs_sh_bwd(N, 16, SH_DEG, dirs.data_ptr(), g[2].data_ptr(), vcoef.data_ptr(),

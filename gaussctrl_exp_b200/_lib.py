@@ -46,6 +46,9 @@ SIGNATURES = {
     "gs_bin_fast": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gs_raster_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_raster_fwd_rgbd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_tile_order": (_i, [_i, _vp, _i, _vp, _vp]),
+    "gs_raster_fwd_ordered": (_i, [_i, _i, _i, _i] + [_vp] * 15),
+    "gs_raster_bwd_ordered": (_i, [_i, _i, _i, _i] + [_vp] * 17),
     "gs_raster_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                            _vp, _vp, _vp, _vp, _vp]),
 }

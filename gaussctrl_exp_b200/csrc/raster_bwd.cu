@@ -64,7 +64,7 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                    const float *__restrict__ final_T, const int32_t *__restrict__ final_idx,
                    const float *__restrict__ v_out, const float *__restrict__ v_out_alpha,
                    float *__restrict__ v_xys, float *__restrict__ v_conics, float *__restrict__ v_colors,
-                   float *__restrict__ v_opac) {
+                   float *__restrict__ v_opac, const int32_t *__restrict__ tile_order) {
     __shared__ float4 sa[RB_BATCH];  // x, y, opac, qa   (q* = pre-scaled conic, raster_common.cuh)
     __shared__ float4 sb[RB_BATCH];  // qb, qc, r, g
     __shared__ float sc[RB_BATCH];   // b
@@ -74,7 +74,7 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     __shared__ unsigned char wlist[8][RB_BATCH];
     __shared__ int s_wmax[8];
 
-    const int tile = blockIdx.x;
+    const int tile = tile_order ? tile_order[blockIdx.x] : blockIdx.x;   // heaviest tiles first
     const int tile_x = tile % tiles_x, tile_y = tile / tiles_x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int px, py;
@@ -346,11 +346,29 @@ extern "C" int gs_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y,
     if (C == 3)
         raster_bwd3_kernel<<<tiles, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg,
                                                   final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics,
-                                                  v_colors, v_opac);
+                                                  v_colors, v_opac, nullptr);
     else
         raster_bwdN_kernel<<<tiles, 256, 0, st>>>(C, H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac,
                                                   bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics,
                                                   v_colors, v_opac);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int gs_raster_bwd_ordered(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                                     const int32_t *tile_bins, const float *xys, const float *conics,
+                                     const float *colors, const float *opac, const float *bg, const float *final_T,
+                                     const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
+                                     float *v_xys, float *v_conics, float *v_colors, float *v_opac,
+                                     const int32_t *tile_order, void *stream) {
+    if (H <= 0 || W <= 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (!tile_bins || !xys || !conics || !colors || !opac || !bg || !final_T || !final_idx || !v_out || !v_xys ||
+        !v_conics || !v_colors || !v_opac)
+        return GS_ERR_BAD_ARG;
+    if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
+    raster_bwd3_kernel<<<tiles_x * tiles_y, 256, 0, (cudaStream_t)stream>>>(
+        H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys),
+        conics, colors, opac, bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order);
     GS_LAUNCH_CHECK();
     return 0;
 }

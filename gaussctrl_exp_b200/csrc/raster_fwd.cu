@@ -31,10 +31,15 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                    const float *__restrict__ conics, const float *__restrict__ colors,
                    const float *__restrict__ opac, const float *__restrict__ depths,
                    const float *__restrict__ bg, float *__restrict__ out_img, float *__restrict__ out_depth,
-                   float *__restrict__ final_T, int32_t *__restrict__ final_idx) {
+                   float *__restrict__ final_T, int32_t *__restrict__ final_idx,
+                   const int32_t *__restrict__ tile_order, int32_t *__restrict__ tile_work) {
     __shared__ StageRGB st[2];
     __shared__ unsigned char wlist[8][RF_BATCH];   // per-warp compacted survivors of the current batch
-    const int tile = blockIdx.x;
+    __shared__ int s_work;
+    // heaviest tiles first (LPT): CTAs are dispatched in blockIdx order, so a descending-work permutation
+    // keeps the long tiles out of the tail of the launch
+    const int tile = tile_order ? tile_order[blockIdx.x] : blockIdx.x;
+    if (threadIdx.x == 0) s_work = 0;
     const int tile_x = tile % tiles_x, tile_y = tile / tiles_x;
     int px, py;
     gs_pixel_of_thread(tile_x, tile_y, px, py);
@@ -128,6 +133,11 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
         if (WITH_DEPTH) out_depth[pix] = dacc;
         final_T[pix] = T;
         final_idx[pix] = last;
+    }
+    if (tile_work) {   // depth of the deepest contributor: the backward's work for this tile
+        atomicMax(&s_work, last - range.x);
+        __syncthreads();
+        if (threadIdx.x == 0) tile_work[tile] = s_work;
     }
 }
 
@@ -226,7 +236,7 @@ extern "C" int gs_raster_fwd(int C, int H, int W, int tiles_x, int tiles_y,
 #define GS_FWD_ARGS H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg, out_img, final_T, final_idx
     if (C == 3)
         raster_fwd3_kernel<false><<<tiles, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, nullptr,
-                                                         bg, out_img, nullptr, final_T, final_idx);
+                                                         bg, out_img, nullptr, final_T, final_idx, nullptr, nullptr);
     else if (C <= 4) raster_fwdN_kernel<4><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
     else if (C <= 8) raster_fwdN_kernel<8><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
     else if (C <= 16) raster_fwdN_kernel<16><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
@@ -248,7 +258,62 @@ extern "C" int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
     if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
     raster_fwd3_kernel<true><<<tiles_x * tiles_y, 256, 0, (cudaStream_t)stream>>>(
         H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys),
-        conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx);
+        conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx, nullptr, nullptr);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tile scheduling: rank tiles by descending work (ties by tile id). All-pairs counting in shared
+// memory: T <= a few thousand, so this is a few microseconds.
+namespace {
+__global__ void __launch_bounds__(256)
+tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, int32_t *__restrict__ order) {
+    // one warp per tile: rank = number of tiles with more work (ties: lower tile id first)
+    const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (t >= T) return;
+    auto load = [&](int u) { return work_is_range ? work[2 * u + 1] - work[2 * u] : work[u]; };
+    const int mine = load(t);
+    int rank = 0;
+    for (int u = lane; u < T; u += 32) {
+        const int w = load(u);
+        rank += (w > mine) || (w == mine && u < t);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rank += __shfl_xor_sync(0xffffffffu, rank, o);
+    if (lane == 0) order[rank] = t;
+}
+}  // namespace
+
+extern "C" int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream) {
+    if (T <= 0 || !work || !order) return GS_ERR_BAD_ARG;
+    tile_order_kernel<<<(T * 32 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(T, work, work_is_range, order);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int gs_raster_fwd_ordered(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                                     const int32_t *tile_bins, const float *xys, const float *conics,
+                                     const float *colors, const float *opac, const float *depths, const float *bg,
+                                     float *out_img, float *out_depth, float *final_T, int32_t *final_idx,
+                                     const int32_t *tile_order, int32_t *tile_work, void *stream) {
+    if (H <= 0 || W <= 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (!tile_bins || !xys || !conics || !colors || !opac || !bg || !out_img || !final_T || !final_idx)
+        return GS_ERR_BAD_ARG;
+    if ((depths == nullptr) != (out_depth == nullptr)) return GS_ERR_BAD_ARG;
+    if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
+    const float2 *xy2 = reinterpret_cast<const float2 *>(xys);
+    if (depths)
+        raster_fwd3_kernel<true><<<tiles_x * tiles_y, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors,
+                                                                    opac, depths, bg, out_img, out_depth, final_T,
+                                                                    final_idx, tile_order, tile_work);
+    else
+        raster_fwd3_kernel<false><<<tiles_x * tiles_y, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors,
+                                                                     opac, nullptr, bg, out_img, nullptr, final_T,
+                                                                     final_idx, tile_order, tile_work);
     GS_LAUNCH_CHECK();
     return 0;
 }

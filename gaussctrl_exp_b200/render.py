@@ -165,6 +165,8 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
     fT = torch.empty((H, W), device=dev, dtype=torch.float32)
     fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
     out_depth = torch.empty((H, W), device=dev, dtype=torch.float32) if with_depth else None
+    order_f = torch.empty((T,), device=dev, dtype=torch.int32)
+    tile_work = torch.empty((T,), device=dev, dtype=torch.int32)
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
         scratch = _get_scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T))
@@ -176,19 +178,19 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
         pinned.copy_(total, non_blocking=True)
         ev.record()
         # compositing is enqueued BEFORE the host looks at the count: it only reads tile_bins
-        if with_depth:     # RGB + depth in one pass over the same tile lists (gc_model.py:208-238)
-            rc = L.gs_raster_fwd_rgbd(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                      conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), depths.data_ptr(),
-                                      bg.data_ptr(), out.data_ptr(), out_depth.data_ptr(), fT.data_ptr(),
-                                      fidx.data_ptr(), st)
-        else:
-            rc = L.gs_raster_fwd(3, H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                 conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(), out.data_ptr(),
-                                 fT.data_ptr(), fidx.data_ptr(), st)
+        # tiles are launched heaviest-first (list length as the forward's work proxy); the forward records
+        # each tile's true depth of composition, which orders the backward
+        rc = L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), st)
+        _lib.check(rc, "gs_tile_order")
+        rc = L.gs_raster_fwd_ordered(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                     conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(),
+                                     depths.data_ptr() if with_depth else None, bg.data_ptr(), out.data_ptr(),
+                                     out_depth.data_ptr() if with_depth else None, fT.data_ptr(), fidx.data_ptr(),
+                                     order_f.data_ptr(), tile_work.data_ptr(), st)
         _lib.check(rc, "gs_raster_fwd")
         if not strict:
             return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, None,
-                    (pinned, ev, cap, key))
+                    (pinned, ev, cap, key), tile_work)
         ev.synchronize()
         I = int(pinned[0])
         if I <= cap:
@@ -196,8 +198,8 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
             break
         cap = int(I * 1.5) + 1024      # capacity was too small: nothing was composited from a torn list; redo
     if with_depth:
-        return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, out_depth)
-    return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, None)
+        return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, out_depth, tile_work)
+    return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, None, tile_work)
 
 
 def _ctypes_addr(struct):
@@ -218,10 +220,10 @@ class _RenderView(Function):
         args = [t.detach().float().contiguous() for t in (means, scales, quats, opacities, features_dc, features_rest)]
         bg = bg.detach().to(means.device).float().contiguous()
         with torch.cuda.device(means.device):
-            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, pending) = _forward_impl(
-                *args, cam, use_sh, deg, bg, strict=not SPECULATE)
+            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, pending,
+             tile_work) = _forward_impl(*args, cam, use_sh, deg, bg, strict=not SPECULATE)
         ctx.pending = pending
-        ctx.save_for_backward(*args, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT, fidx)
+        ctx.save_for_backward(*args, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT, fidx, tile_work)
         ctx.cam, ctx.use_sh, ctx.deg, ctx.state = cam, use_sh, deg, state
         if state is not None:
             state.xys, state.radii, state.depths, state.num_intersects = xys, radii, depths, I
@@ -232,7 +234,7 @@ class _RenderView(Function):
     @staticmethod
     def backward(ctx, v_out, v_alpha, *_unused):
         (means, scales, quats, opacities, fdc, frest, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT,
-         fidx) = ctx.saved_tensors
+         fidx, tile_work) = ctx.saved_tensors
         cam = ctx.cam
         L = _lib.lib()
         dev = means.device
@@ -251,10 +253,14 @@ class _RenderView(Function):
             v_conics = g[2 * Np:2 * Np + 3 * N].view(N, 3)
             v_rgbs = g[5 * Np:5 * Np + 3 * N].view(N, 3)
             v_opac = g[8 * Np:8 * Np + N]
-            rc = L.gs_raster_bwd(3, H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(), conics.data_ptr(),
-                                 rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(), fT.data_ptr(), fidx.data_ptr(),
-                                 v_out.data_ptr(), va_ptr, v_xys.data_ptr(), v_conics.data_ptr(), v_rgbs.data_ptr(),
-                                 v_opac.data_ptr(), st)
+            order_b = torch.empty_like(tile_work)
+            rc = L.gs_tile_order(tx * ty, tile_work.data_ptr(), 0, order_b.data_ptr(), st)
+            _lib.check(rc, "gs_tile_order")
+            rc = L.gs_raster_bwd_ordered(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                         conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(),
+                                         fT.data_ptr(), fidx.data_ptr(), v_out.data_ptr(), va_ptr, v_xys.data_ptr(),
+                                         v_conics.data_ptr(), v_rgbs.data_ptr(), v_opac.data_ptr(), order_b.data_ptr(),
+                                         st)
             _lib.check(rc, "gs_raster_bwd")
             if ctx.state is not None and ctx.state.defer_leaf_grads:
                 rc = L.gs_finish_view_block(N, int(ctx.use_sh), _ctypes_addr(cam), rgbs.data_ptr(), g.data_ptr(), st)

@@ -165,6 +165,25 @@ int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
                        const float *depths, const float *bg, float *out_img, float *out_depth,
                        float *final_T, int32_t *final_idx, void *stream);
 
+/* Tile scheduling (3-channel kernels): CTAs are dispatched in blockIdx order, so launching the tiles in
+ * descending-work order (LPT) keeps the long tiles out of the tail. gs_tile_order ranks T tiles by
+ * work[t] (work_is_range = 0) or by tile_bins[t].end - tile_bins[t].start (work_is_range = 1), ties by
+ * tile id. The *_ordered variants take the permutation (NULL = natural order); the forward also writes
+ * tile_work[t] = depth of the deepest contributor of tile t (NULL = skip), which is the backward's work.
+ * depths/out_depth NULL = RGB only. Results are identical to the un-ordered entry points. */
+int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream);
+int gs_raster_fwd_ordered(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                          const int32_t *tile_bins, const float *xys, const float *conics,
+                          const float *colors, const float *opac, const float *depths, const float *bg,
+                          float *out_img, float *out_depth, float *final_T, int32_t *final_idx,
+                          const int32_t *tile_order, int32_t *tile_work, void *stream);
+int gs_raster_bwd_ordered(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                          const int32_t *tile_bins, const float *xys, const float *conics,
+                          const float *colors, const float *opac, const float *bg, const float *final_T,
+                          const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
+                          float *v_xys, float *v_conics, float *v_colors, float *v_opac,
+                          const int32_t *tile_order, void *stream);
+
 /* ---- stage 4: backward compositing (App. A.5) ---------------------------------------------- */
 /* v_out (H,W,C); v_out_alpha (H,W) or NULL. Outputs are ACCUMULATED INTO: caller zero-fills
  * v_xys (N,2), v_conics (N,3), v_colors (N,C), v_opac (N). */
