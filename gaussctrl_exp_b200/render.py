@@ -27,6 +27,11 @@ from .scene import Camera
 # case the count grew by more than 50 % between consecutive views of the same shape).
 SPECULATE = True
 
+# "tile": count / scan / scatter / per-tile shared-memory sort (gs_bin_tile, 5 launches);
+# "lsd": global depth sort + stable partition by tile (gs_bin_fast). Identical outputs.
+import os as _os
+BIN_IMPL = _os.environ.get("GS_BIN_IMPL", "lsd")
+
 _cam_cache = {}
 _cap_hint = {}
 _scratch = {}
@@ -169,11 +174,17 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
     tile_work = torch.empty((T,), device=dev, dtype=torch.int32)
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
-        scratch = _get_scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T))
-        rc = L.gs_bin_fast(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), hit.data_ptr(), tx, ty,
-                           ids_sorted.data_ptr(), bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
-                           scratch.numel(), st)
-        _lib.check(rc, "gs_bin_fast")
+        if BIN_IMPL == "tile":
+            scratch = _get_scratch(dev, L.gs_bin_tile_scratch_bytes(N, cap, T))
+            rc = L.gs_bin_tile(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), tx, ty,
+                               ids_sorted.data_ptr(), bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
+                               scratch.numel(), st)
+        else:
+            scratch = _get_scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T))
+            rc = L.gs_bin_fast(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), hit.data_ptr(), tx, ty,
+                               ids_sorted.data_ptr(), bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
+                               scratch.numel(), st)
+        _lib.check(rc, "gs_bin_tile/fast")
         pinned, ev = _get_pinned(dev)
         pinned.copy_(total, non_blocking=True)
         ev.record()

@@ -113,7 +113,7 @@ _cap_hint = {}
 
 
 def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
-             tile_bounds: Tuple[int, int, int]) -> Tuple[Tensor, Tensor, int]:
+             tile_bounds: Tuple[int, int, int], impl: Optional[str] = None) -> Tuple[Tensor, Tensor, int]:
     """Traffic-lean binning (gs_bin_fast): -> (ids_sorted int32 [>=I], tile_bins (T,2), I).
 
     The capacity of ids_sorted is speculative (1.25x the last total for this N); the single host
@@ -129,15 +129,22 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
     L = _lib.lib()
     bins = torch.empty((T, 2), device=dev, dtype=torch.int32)
     total = torch.empty(1, device=dev, dtype=torch.int32)
+    if impl is None:
+        from .render import BIN_IMPL as impl
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
-        nbytes = L.gs_bin_fast_scratch_bytes(N, cap, T)
-        scratch = _scratch(dev, nbytes, "binfast")
         with torch.cuda.device(dev):
-            rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
-                               _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
-                               scratch.numel(), _lib.stream_ptr())
-        _lib.check(rc, "gs_bin_fast")
+            if impl == "tile":      # per-tile shared-memory sort (gs_bin_tile)
+                scratch = _scratch(dev, L.gs_bin_tile_scratch_bytes(N, cap, T), "bintile")
+                rc = L.gs_bin_tile(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), tx, ty,
+                                   _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
+                                   scratch.numel(), _lib.stream_ptr())
+            else:                   # global depth sort + partition (gs_bin_fast)
+                scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")
+                rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
+                                   _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
+                                   scratch.numel(), _lib.stream_ptr())
+        _lib.check(rc, "gs_bin_tile/fast")
         I = int(total.item())
         if I <= cap:
             _cap_hint[key] = max(int(I * 1.25) + 1024, 1024)

@@ -147,6 +147,14 @@ int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, con
                 int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
                 void *scratch, size_t scratch_bytes, void *stream);
 
+/* Tile-local binning: same (ids_sorted, tile_bins, *total_dev) contract and overflow behaviour as
+ * gs_bin_fast, built from count -> tile scan -> unordered scatter -> ONE CTA PER TILE sorting its segment by
+ * depth in shared memory (ties by Gaussian id). 5 launches; the product path uses this one. */
+size_t gs_bin_tile_scratch_bytes(int N, int64_t I_cap, int T);
+int gs_bin_tile(int N, int64_t I_cap, const float *xys, const float *depths, const int32_t *radii,
+                int tiles_x, int tiles_y, int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
+                void *scratch, size_t scratch_bytes, void *stream);
+
 /* ---- stage 3: forward compositing (App. A.4) ----------------------------------------------- */
 /* colors (N,C); opac (N); bg (C) device; out_img (H,W,C); final_T (H,W); final_idx (H,W) =
  * 1 + index into ids_sorted of the last composited Gaussian (tile range start if none). */

@@ -89,8 +89,9 @@ def test_full_size_properties(cuda_dev):
     assert bool((ks[1:] >= ks[:-1]).all())
     ref_k, ref_perm = torch.sort(keys, stable=True)      # library sort as a cross-check of OUR sort
     assert torch.equal(ks, ref_k) and torch.equal(vs, ids[ref_perm])
-    ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb)
-    assert I2 == I and torch.equal(ids2[:I], vs) and torch.equal(bins2, bins)
+    for impl in ("tile", "lsd"):
+        ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
+        assert I2 == I and torch.equal(ids2[:I], vs) and torch.equal(bins2, bins), impl
     cnt = (bins[:, 1] - bins[:, 0]).long()
     assert int(cnt.sum().item()) == I
     # linearity of compositing in the colours (same geometry): render(c1 + c2) = render(c1) + render(c2), bg = 0

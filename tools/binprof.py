@@ -1,0 +1,24 @@
+"""Diagnostic: run both binning implementations on the 1 M-Gaussian bench scene (for ncu launch lists)."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from gaussctrl_exp_b200 import project_gaussians, scene  # noqa: E402
+from gaussctrl_exp_b200 import utils as U  # noqa: E402
+from gaussctrl_exp_b200.model import camera_matrices  # noqa: E402
+
+dev = torch.device("cuda:0")
+p = scene.make_scene(1_000_000, 0, device=dev)
+cam = scene.make_cameras(1, 0)[0]
+V, P, _, _, tb = camera_matrices(cam.c2w, cam.fx, cam.fy, cam.W, cam.H)
+with torch.no_grad():
+    xys, depths, radii, conics, hit, _ = project_gaussians(
+        p["means"], p["scales"].exp(), 1, p["quats"] / p["quats"].norm(dim=-1, keepdim=True), V[:3].to(dev),
+        (P @ V).to(dev), cam.fx, cam.fy, cam.cx, cam.cy, cam.H, cam.W, tb)
+for rep in range(3):
+    for impl in ("lsd", "tile"):
+        ids, bins, I = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
+torch.cuda.synchronize()
+print("I", I, "max tile", int((bins[:, 1] - bins[:, 0]).max()))
