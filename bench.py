@@ -477,7 +477,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n-gaussians", type=int, default=N_GAUSS)
-    ap.add_argument("--cpu-views", type=int, default=8)
+    ap.add_argument("--cpu-views", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--render-streams", type=int, default=2)
