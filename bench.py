@@ -282,11 +282,23 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    gather_mode = world > 1 and model.fused and args.reduce == "gather"
+    gather_mode = world > 1 and model.fused and args.reduce in ("gather", "peer")
     model.view_state.defer_leaf_grads = gather_mode
+    peer = None
+    if gather_mode and args.reduce == "peer":
+        try:
+            peer = gdist.PeerViewExchange(model)      # NVLink symmetric memory; falls back to the NCCL all-gather
+        except Exception as e:                         # (e.g. no P2P between the visible devices)
+            if rank == 0:
+                print(f"bench.py: peer-memory exchange unavailable ({type(e).__name__}: {e}); using NCCL all-gather",
+                      file=sys.stderr)
+            args.reduce = "gather"
 
     def reduce_grads():
         if world == 1:
+            return
+        if peer is not None:
+            peer.reduce(model)                     # peers' view blocks read in place over NVLink inside the kernel
             return
         if gather_mode:
             gdist.reduce_view_grads(model)        # all-gather 36 B/Gaussian, replay the leaf backward per view
@@ -482,9 +494,11 @@ def main():
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--render-streams", type=int, default=2)
     ap.add_argument("--render-reps", type=int, default=3)
-    ap.add_argument("--reduce", default="gather", choices=["gather", "allreduce"],
-                    help="N>1 gradient exchange: gather = all-gather compositor-level grads (36 B/Gaussian) + replayed "
-                         "leaf backward; allreduce = NCCL all-reduce of the 236 B/Gaussian leaf grads")
+    ap.add_argument("--reduce", default="peer", choices=["gather", "peer", "allreduce"],
+                    help="N>1 gradient exchange: peer = each rank's multi-view leaf backward reads the peers' "
+                         "compositor-level grads (36 B/Gaussian) in place over NVLink (symmetric memory, collective fused "
+                         "into the kernel); gather = same payload through one NCCL all-gather; allreduce = NCCL "
+                         "all-reduce of the 236 B/Gaussian leaf grads")
     ap.add_argument("--path", default="fused", choices=["fused", "api"],
                     help="fused: one autograd node / 5 kernels per view (render.py); api: the literal "
                          "gsplat-0.1.2 three-operator sequence of gc_model.py")

@@ -34,6 +34,8 @@ SIGNATURES = {
     "gs_finish_view_block": (_i, [_i, _i, _vp, _vp, _vp, _vp]),
     "gs_preprocess_bwd_multi": (_i, [_i, _i, _vp, _i64, _f, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp,
                                      _vp, _vp]),
+    "gs_preprocess_bwd_multi_peer": (_i, [_i, _i, _vp, _i64, _f, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp,
+                                          _vp, _vp]),
     "gs_sh_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "gs_sh_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "gs_scan_scratch_bytes": (_sz, [_i]),

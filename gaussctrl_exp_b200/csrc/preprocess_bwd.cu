@@ -137,15 +137,28 @@ extern "C" int gs_preprocess_bwd(int N, const float *means, const float *log_sca
 // ==========================================================================================
 namespace {
 
+constexpr int PB_MAX_VIEWS = 16;
+
+struct ViewGrad {   // the 9 compositor-level gradients of one Gaussian in one view
+    float2 xy;
+    float a, b, c, u0, u1, u2, o;
+};
+
+// `views` != nullptr: V blocks `stride` floats apart in local memory (all-gathered by NCCL).
+// `peer_ptrs` != nullptr: V base pointers (one per rank, symmetric-memory mapping of the PEERS' buffers) +
+// `peer_off` floats: the blocks are read in place over NVLink — compute and collective in one kernel, no
+// gathered staging copy. Loads of view v+1 are issued before view v is processed (NVLink latency ~2 us).
 __global__ void __launch_bounds__(PB_TPB)
-preprocess_bwd_multi_kernel(int N, int Np, int V, const float *__restrict__ views, size_t stride, float scale,
+preprocess_bwd_multi_kernel(int N, int Np, int V, const float *__restrict__ views, size_t stride,
+                            const unsigned long long *__restrict__ peer_ptrs, size_t peer_off, float scale,
                             const float *__restrict__ means, const float *__restrict__ log_scales,
                             const float4 *__restrict__ quats, const float *__restrict__ opac_logits, int use_sh,
                             int deg, float *__restrict__ v_means, float *__restrict__ v_log_scales,
                             float4 *__restrict__ v_quats, float *__restrict__ v_opac_logits,
                             float *__restrict__ v_dc, float *__restrict__ v_rest) {
     __shared__ __align__(128) float rest_s[PB_TPB * PB_REST];
-    __shared__ GsCamera cam_s;
+    __shared__ GsCamera cam_s[PB_MAX_VIEWS];
+    __shared__ const float *blk_s[PB_MAX_VIEWS];
     const int tid = threadIdx.x;
     const int g0 = blockIdx.x * PB_TPB;
     const int rows = min(PB_TPB, N - g0);
@@ -153,6 +166,12 @@ preprocess_bwd_multi_kernel(int N, int Np, int V, const float *__restrict__ view
     float *row = rest_s + tid * PB_REST;
 #pragma unroll
     for (int k = 0; k < PB_REST; ++k) row[k] = 0.f;
+    if (tid < V)
+        blk_s[tid] = peer_ptrs ? reinterpret_cast<const float *>(peer_ptrs[tid]) + peer_off : views + (size_t)tid * stride;
+    __syncthreads();
+    constexpr int CAMF = (int)(sizeof(GsCamera) / 4);
+    for (int k = tid; k < V * CAMF; k += PB_TPB)      // all cameras up front: one remote round trip, no per-view barrier
+        reinterpret_cast<float *>(cam_s)[k] = blk_s[k / CAMF][(size_t)9 * Np + k % CAMF];
 
     float vm[3] = {0.f, 0.f, 0.f}, vls[3] = {0.f, 0.f, 0.f}, vd[3] = {0.f, 0.f, 0.f};
     float4 vq = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -167,46 +186,54 @@ preprocess_bwd_multi_kernel(int N, int Np, int V, const float *__restrict__ view
         q = make_float4(qr.x * iq, qr.y * iq, qr.z * iq, qr.w * iq);
         o = 1.0f / (1.0f + expf(-opac_logits[i]));
     }
-    for (int v = 0; v < V; ++v) {
-        const float *blk = views + (size_t)v * stride;
-        __syncthreads();
-        if (tid < (int)(sizeof(GsCamera) / 4)) reinterpret_cast<float *>(&cam_s)[tid] = blk[(size_t)9 * Np + tid];
-        __syncthreads();
-        if (i >= N) continue;
-        const float2 vxy = reinterpret_cast<const float2 *>(blk)[i];
+    auto load_view = [&](int v) {
+        ViewGrad g;
+        const float *blk = blk_s[v];
+        g.xy = reinterpret_cast<const float2 *>(blk)[i];
         const float *vc = blk + (size_t)2 * Np + 3 * (size_t)i;
         const float *vr = blk + (size_t)5 * Np + 3 * (size_t)i;
-        const float vA = vc[0], vB = vc[1], vC = vc[2];
-        const float u0 = vr[0], u1 = vr[1], u2 = vr[2];
-        const float vo = blk[(size_t)8 * Np + i];
-        if (vxy.x == 0.f && vxy.y == 0.f && vA == 0.f && vB == 0.f && vC == 0.f && u0 == 0.f && u1 == 0.f &&
-            u2 == 0.f && vo == 0.f)
-            continue;
-        ProjGrad g;
-        gs_project_one_bwd(cam_s.viewmat, cam_s.projmat, p0, p1, p2, s0, s1, s2, cam_s.glob_scale, q, cam_s.fx,
-                           cam_s.fy, cam_s.H, cam_s.W, vxy, 0.0f, vA, vB, vC, g);
-        vm[0] += g.vp[0]; vm[1] += g.vp[1]; vm[2] += g.vp[2];
-        vls[0] += g.vs[0]; vls[1] += g.vs[1]; vls[2] += g.vs[2];
-        vq.x += g.vq.x; vq.y += g.vq.y; vq.z += g.vq.z; vq.w += g.vq.w;
-        vop += vo;
-        if (use_sh) {
-            float dx = p0 - cam_s.cam_pos[0], dy = p1 - cam_s.cam_pos[1], dz = p2 - cam_s.cam_pos[2];
-            const float vn = sqrtf(dx * dx + dy * dy + dz * dz);
-            dx = dx / vn; dy = dy / vn; dz = dz / vn;
-            float Y[16];
-            sh_basis<3>(deg, dx, dy, dz, Y);
-            const int nb = sh_num_bases(deg);
-            vd[0] += Y[0] * u0; vd[1] += Y[0] * u1; vd[2] += Y[0] * u2;
-#pragma unroll
-            for (int k = 1; k < 16; ++k)
-                if (k < nb) {
-                    row[3 * (k - 1)] += Y[k] * u0; row[3 * (k - 1) + 1] += Y[k] * u1; row[3 * (k - 1) + 2] += Y[k] * u2;
-                }
-        } else {
-            vd[0] += u0; vd[1] += u1; vd[2] += u2;     // sender already applied d sigmoid
-        }
-    }
+        g.a = vc[0]; g.b = vc[1]; g.c = vc[2];
+        g.u0 = vr[0]; g.u1 = vr[1]; g.u2 = vr[2];
+        g.o = blk[(size_t)8 * Np + i];
+        return g;
+    };
+    __syncthreads();   // cameras staged
     if (i < N) {
+        ViewGrad cur = load_view(0);
+        for (int v = 0; v < V; ++v) {
+            ViewGrad nxt = cur;
+            if (v + 1 < V) nxt = load_view(v + 1);
+            const ViewGrad w = cur;
+            cur = nxt;
+            if (w.xy.x == 0.f && w.xy.y == 0.f && w.a == 0.f && w.b == 0.f && w.c == 0.f && w.u0 == 0.f && w.u1 == 0.f &&
+                w.u2 == 0.f && w.o == 0.f)
+                continue;
+            const GsCamera &cam = cam_s[v];
+            ProjGrad g;
+            gs_project_one_bwd(cam.viewmat, cam.projmat, p0, p1, p2, s0, s1, s2, cam.glob_scale, q, cam.fx, cam.fy,
+                               cam.H, cam.W, w.xy, 0.0f, w.a, w.b, w.c, g);
+            vm[0] += g.vp[0]; vm[1] += g.vp[1]; vm[2] += g.vp[2];
+            vls[0] += g.vs[0]; vls[1] += g.vs[1]; vls[2] += g.vs[2];
+            vq.x += g.vq.x; vq.y += g.vq.y; vq.z += g.vq.z; vq.w += g.vq.w;
+            vop += w.o;
+            if (use_sh) {
+                float dx = p0 - cam.cam_pos[0], dy = p1 - cam.cam_pos[1], dz = p2 - cam.cam_pos[2];
+                const float vn = sqrtf(dx * dx + dy * dy + dz * dz);
+                dx = dx / vn; dy = dy / vn; dz = dz / vn;
+                float Y[16];
+                sh_basis<3>(deg, dx, dy, dz, Y);
+                const int nb = sh_num_bases(deg);
+                vd[0] += Y[0] * w.u0; vd[1] += Y[0] * w.u1; vd[2] += Y[0] * w.u2;
+#pragma unroll
+                for (int k = 1; k < 16; ++k)
+                    if (k < nb) {
+                        row[3 * (k - 1)] += Y[k] * w.u0; row[3 * (k - 1) + 1] += Y[k] * w.u1;
+                        row[3 * (k - 1) + 2] += Y[k] * w.u2;
+                    }
+            } else {
+                vd[0] += w.u0; vd[1] += w.u1; vd[2] += w.u2;     // sender already applied d sigmoid
+            }
+        }
         v_means[3 * i] = vm[0] * scale; v_means[3 * i + 1] = vm[1] * scale; v_means[3 * i + 2] = vm[2] * scale;
         v_log_scales[3 * i] = vls[0] * s0 * scale; v_log_scales[3 * i + 1] = vls[1] * s1 * scale;
         v_log_scales[3 * i + 2] = vls[2] * s2 * scale;
@@ -260,27 +287,46 @@ extern "C" int gs_finish_view_block(int N, int use_sh, const GsCamera *cam_host,
     return 0;
 }
 
-extern "C" int gs_preprocess_bwd_multi(int N, int V, const float *views, int64_t stride_floats, float scale,
-                                       const float *means, const float *log_scales, const float *quats,
-                                       const float *opac_logits, int use_sh, int sh_deg, float *v_means,
-                                       float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
-                                       float *v_feat_rest, void *stream) {
-    if (N < 0 || V <= 0 || !views) return GS_ERR_BAD_ARG;
+static int launch_bwd_multi(int N, int V, const float *views, int64_t stride_floats,
+                            const unsigned long long *peer_ptrs, int64_t peer_off, float scale, const float *means,
+                            const float *log_scales, const float *quats, const float *opac_logits, int use_sh,
+                            int sh_deg, float *v_means, float *v_log_scales, float *v_quats, float *v_opac_logits,
+                            float *v_feat_dc, float *v_feat_rest, void *stream) {
+    if (N < 0 || V <= 0 || V > PB_MAX_VIEWS || (!views && !peer_ptrs)) return GS_ERR_BAD_ARG;
     if (sh_deg < 0 || sh_deg > 3) return GS_ERR_UNSUPPORTED;
     if (N == 0) return 0;
     if (!means || !log_scales || !quats || !opac_logits || !v_means || !v_log_scales || !v_quats || !v_opac_logits ||
         !v_feat_dc || !v_feat_rest)
         return GS_ERR_BAD_ARG;
-    if (!gs_aligned16(quats) || !gs_aligned16(v_quats) || !gs_aligned16(v_feat_rest) || !gs_aligned16(views) ||
-        (stride_floats & 3))
+    if (!gs_aligned16(quats) || !gs_aligned16(v_quats) || !gs_aligned16(v_feat_rest) || (views && !gs_aligned16(views)) ||
+        (stride_floats & 3) || (peer_off & 3))
         return GS_ERR_MISALIGNED;
     const int Np = (N + 3) / 4 * 4;
-    if (stride_floats < 9 * (int64_t)Np + 64) return GS_ERR_BAD_ARG;
+    if (views && stride_floats < 9 * (int64_t)Np + 64) return GS_ERR_BAD_ARG;
     const int blocks = (N + PB_TPB - 1) / PB_TPB;
     preprocess_bwd_multi_kernel<<<blocks, PB_TPB, 0, (cudaStream_t)stream>>>(
-        N, Np, V, views, (size_t)stride_floats, scale, means, log_scales, reinterpret_cast<const float4 *>(quats),
-        opac_logits, use_sh, sh_deg, v_means, v_log_scales, reinterpret_cast<float4 *>(v_quats), v_opac_logits,
-        v_feat_dc, v_feat_rest);
+        N, Np, V, views, (size_t)stride_floats, peer_ptrs, (size_t)peer_off, scale, means, log_scales,
+        reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, v_means, v_log_scales,
+        reinterpret_cast<float4 *>(v_quats), v_opac_logits, v_feat_dc, v_feat_rest);
     GS_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int gs_preprocess_bwd_multi(int N, int V, const float *views, int64_t stride_floats, float scale,
+                                       const float *means, const float *log_scales, const float *quats,
+                                       const float *opac_logits, int use_sh, int sh_deg, float *v_means,
+                                       float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
+                                       float *v_feat_rest, void *stream) {
+    return launch_bwd_multi(N, V, views, stride_floats, nullptr, 0, scale, means, log_scales, quats, opac_logits, use_sh,
+                            sh_deg, v_means, v_log_scales, v_quats, v_opac_logits, v_feat_dc, v_feat_rest, stream);
+}
+
+extern "C" int gs_preprocess_bwd_multi_peer(int N, int V, const uint64_t *peer_base_ptrs_dev, int64_t offset_floats,
+                                            float scale, const float *means, const float *log_scales,
+                                            const float *quats, const float *opac_logits, int use_sh, int sh_deg,
+                                            float *v_means, float *v_log_scales, float *v_quats,
+                                            float *v_opac_logits, float *v_feat_dc, float *v_feat_rest, void *stream) {
+    return launch_bwd_multi(N, V, nullptr, 0, reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev),
+                            offset_floats, scale, means, log_scales, quats, opac_logits, use_sh, sh_deg, v_means,
+                            v_log_scales, v_quats, v_opac_logits, v_feat_dc, v_feat_rest, stream);
 }

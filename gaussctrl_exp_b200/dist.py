@@ -115,3 +115,44 @@ def reduce_view_grads(model, average: bool = True) -> None:
     for k in GRAD_PARAMS:
         getattr(model, k).grad = grads[k]
     st.flat_grads = flat
+
+
+class PeerViewExchange:
+    """reduce_view_grads with the collective fused into the kernel (NVLink peer memory, no NCCL on the data
+    path): each rank accumulates its view block straight into a symmetric-memory buffer; after one
+    device-side barrier every rank's multi-view backward kernel reads all peers' blocks in place
+    (gs_preprocess_bwd_multi_peer). Two buffers alternate so that a rank may start writing step s+1 while
+    slower peers still read step s (the barrier of step s+1 orders the reuse at step s+2)."""
+
+    def __init__(self, model):
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import _lib
+        assert dist.is_initialized()
+        self.world = dist.get_world_size()
+        self.stride = _lib.lib().gs_view_block_floats(model.num_points)
+        self.buf = symm_mem.empty(2 * self.stride, dtype=torch.float32, device=model.device)
+        self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD)
+        self.step = 0
+        self.begin(model)
+
+    def begin(self, model) -> None:
+        """Point the next backward at this step's buffer."""
+        k = self.step % 2
+        model.view_state.defer_leaf_grads = True
+        model.view_state.view_block_buffer = self.buf[k * self.stride:(k + 1) * self.stride]
+
+    def reduce(self, model, average: bool = True) -> None:
+        from . import render
+        st = model.view_state
+        assert st.view_block is not None
+        use_sh, deg, _ = st.view_meta
+        self.hdl.barrier(channel=0)                 # every rank's block of this step is complete
+        params = {k: getattr(model, k) for k in GRAD_PARAMS}
+        flat, grads = render.leaf_grads_from_view_blocks(
+            params, None, self.world, bool(use_sh), deg, 1.0 / self.world if average else 1.0,
+            peer_ptrs_dev=self.hdl.buffer_ptrs_dev, peer_offset=(self.step % 2) * self.stride)
+        for k in GRAD_PARAMS:
+            getattr(model, k).grad = grads[k]
+        st.flat_grads = flat
+        self.step += 1
+        self.begin(model)

@@ -123,7 +123,7 @@ def _check_pending(pending):
 class ViewState:
     """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii)."""
     __slots__ = ("xys", "radii", "depths", "num_intersects", "xys_grad", "flat_grads", "defer_leaf_grads",
-                 "view_block", "view_meta")
+                 "view_block", "view_meta", "view_block_buffer")
 
     def __init__(self):
         self.xys = self.radii = self.depths = self.xys_grad = self.flat_grads = None
@@ -133,6 +133,8 @@ class ViewState:
         self.defer_leaf_grads = False
         self.view_block = None
         self.view_meta = None
+        # optional caller-owned buffer (e.g. NVLink symmetric memory) the view block is accumulated into
+        self.view_block_buffer = None
 
 
 def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, strict=True,
@@ -259,7 +261,13 @@ class _RenderView(Function):
         Np = (N + 3) // 4 * 4
         with torch.cuda.device(dev):
             st = _lib.stream_ptr()
-            g = torch.zeros(9 * Np + 64, device=dev, dtype=torch.float32)    # accumulated into by atomics
+            ext = ctx.state.view_block_buffer if (ctx.state is not None and ctx.state.defer_leaf_grads) else None
+            if ext is not None:
+                assert ext.numel() == 9 * Np + 64 and ext.is_contiguous() and ext.dtype == torch.float32
+                g = ext
+                g.zero_()
+            else:
+                g = torch.zeros(9 * Np + 64, device=dev, dtype=torch.float32)    # accumulated into by atomics
             v_xys = g[0:2 * N].view(N, 2)
             v_conics = g[2 * Np:2 * Np + 3 * N].view(N, 3)
             v_rgbs = g[5 * Np:5 * Np + 3 * N].view(N, 3)
@@ -342,22 +350,34 @@ def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: T
     return out
 
 
-def leaf_grads_from_view_blocks(params, blocks: Tensor, num_views: int, use_sh: bool, deg: int, scale: float = 1.0):
-    """gs_preprocess_bwd_multi: `blocks` = num_views view blocks back to back (as all-gathered). Returns
-    (flat, dict of the six leaf gradients as views of flat), gradients = scale * sum over the views."""
+def leaf_grads_from_view_blocks(params, blocks, num_views: int, use_sh: bool, deg: int, scale: float = 1.0,
+                                peer_ptrs_dev: Optional[int] = None, peer_offset: int = 0):
+    """gs_preprocess_bwd_multi: `blocks` = num_views view blocks back to back (as all-gathered), or — with
+    peer_ptrs_dev (device array of per-rank base pointers, symmetric memory) — the peers' blocks read in place
+    over NVLink (gs_preprocess_bwd_multi_peer). Returns (flat, dict of the six leaf gradients as views of flat),
+    gradients = scale * sum over the views."""
     means, scales, quats, opacities = params["means"], params["scales"], params["quats"], params["opacities"]
     dev = means.device
     N = means.shape[0]
     Np = (N + 3) // 4 * 4
     L = _lib.lib()
     stride = L.gs_view_block_floats(N)
-    assert blocks.numel() == num_views * stride and blocks.is_contiguous()
+    if peer_ptrs_dev is None:
+        assert blocks.numel() == num_views * stride and blocks.is_contiguous()
     flat = torch.empty(59 * Np, device=dev, dtype=torch.float32)
     out = {"means": flat[0:3 * N].view(N, 3), "scales": flat[3 * Np:3 * Np + 3 * N].view(N, 3),
            "quats": flat[6 * Np:6 * Np + 4 * N].view(N, 4), "opacities": flat[10 * Np:10 * Np + N].view(opacities.shape),
            "features_dc": flat[11 * Np:11 * Np + 3 * N].view(N, 3),
            "features_rest": flat[14 * Np:14 * Np + 45 * N].view(N, 15, 3)}
     with torch.cuda.device(dev):
+        if peer_ptrs_dev is not None:
+            rc = L.gs_preprocess_bwd_multi_peer(
+                N, int(num_views), int(peer_ptrs_dev), int(peer_offset), float(scale), means.detach().data_ptr(),
+                scales.detach().data_ptr(), quats.detach().data_ptr(), opacities.detach().data_ptr(), int(use_sh), int(deg),
+                out["means"].data_ptr(), out["scales"].data_ptr(), out["quats"].data_ptr(), out["opacities"].data_ptr(),
+                out["features_dc"].data_ptr(), out["features_rest"].data_ptr(), _lib.stream_ptr())
+            _lib.check(rc, "gs_preprocess_bwd_multi_peer")
+            return flat, out
         rc = L.gs_preprocess_bwd_multi(
             N, int(num_views), blocks.data_ptr(), stride, float(scale), means.detach().data_ptr(),
             scales.detach().data_ptr(), quats.detach().data_ptr(), opacities.detach().data_ptr(), int(use_sh), int(deg),

@@ -119,6 +119,17 @@ int gs_preprocess_bwd_multi(int N, int V, const float *views, int64_t stride_flo
                             float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
                             float *v_feat_rest, void *stream);
 
+/* Same, with the collective fused into the kernel: peer_base_ptrs_dev = DEVICE array of V pointers, entry r =
+ * this process's mapping of rank r's symmetric-memory buffer (NVLink peer memory); rank r's view block starts
+ * offset_floats into it. The kernel reads the peers' blocks in place (software-prefetched peer loads), so no
+ * gathered copy exists and the transfer overlaps the arithmetic. The caller provides the cross-rank barrier
+ * between the writers (gs_raster_bwd + gs_finish_view_block) and this call. V <= 16. */
+int gs_preprocess_bwd_multi_peer(int N, int V, const uint64_t *peer_base_ptrs_dev, int64_t offset_floats,
+                                 float scale, const float *means, const float *log_scales,
+                                 const float *quats, const float *opac_logits, int use_sh, int sh_deg,
+                                 float *v_means, float *v_log_scales, float *v_quats,
+                                 float *v_opac_logits, float *v_feat_dc, float *v_feat_rest, void *stream);
+
 /* ---- stage 2: tile binning (inside rasterize_gaussians; App. A.3) -------------------------- */
 size_t gs_scan_scratch_bytes(int N);
 /* inclusive int32 scan of tiles_hit -> cum; the total is also written to *total_dev
