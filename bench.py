@@ -287,7 +287,7 @@ def run_ours(args):
     peer = None
     if gather_mode and args.reduce == "peer":
         try:
-            peer = gdist.PeerViewExchange(model)      # NVLink symmetric memory; falls back to the NCCL all-gather
+            peer = gdist.PeerViewExchange(model, sparse=not args.dense_exchange)   # NVLink symmetric memory
         except Exception as e:                         # (e.g. no P2P between the visible devices)
             if rank == 0:
                 print(f"bench.py: peer-memory exchange unavailable ({type(e).__name__}: {e}); using NCCL all-gather",
@@ -499,6 +499,7 @@ def main():
                          "compositor-level grads (36 B/Gaussian) in place over NVLink (symmetric memory, collective fused "
                          "into the kernel); gather = same payload through one NCCL all-gather; allreduce = NCCL "
                          "all-reduce of the 236 B/Gaussian leaf grads")
+    ap.add_argument("--dense-exchange", action="store_true", help="peer exchange without compaction")
     ap.add_argument("--path", default="fused", choices=["fused", "api"],
                     help="fused: one autograd node / 5 kernels per view (render.py); api: the literal "
                          "gsplat-0.1.2 three-operator sequence of gc_model.py")

@@ -190,6 +190,20 @@ extern "C" int gs_bin_scan(int N, const int32_t *tiles_hit, int32_t *cum, int32_
     return 0;
 }
 
+// internal (not part of the ABI): exclusive int32 scan used by view_exchange.cu
+int gs_internal_exclusive_scan(int n, const int32_t *in, int32_t *out, int32_t *total_dev, void *scratch,
+                               size_t scratch_bytes, cudaStream_t st) {
+    if (n <= 0) return 0;
+    const size_t need = gs_scan_scratch_bytes(n);
+    if (scratch_bytes < need) return GS_ERR_SCRATCH_SMALL;
+    GS_CUDA(cudaMemsetAsync(scratch, 0, need, st));
+    ScanCtl *ctl = reinterpret_cast<ScanCtl *>(scratch);
+    unsigned long long *status = reinterpret_cast<unsigned long long *>(ctl + 1);
+    scan_kernel<<<(n + SCAN_TILE - 1) / SCAN_TILE, SCAN_TPB, 0, st>>>(n, in, nullptr, 1, out, total_dev, ctl, status);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int gs_bin_emit(int N, const float *xys, const float *depths, const int32_t *radii,
                            const int32_t *cum, int tiles_x, int tiles_y, int64_t *keys, int32_t *ids,
                            void *stream) {

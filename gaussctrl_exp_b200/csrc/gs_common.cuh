@@ -57,3 +57,7 @@ __device__ __forceinline__ float4 gs_ldg_stream4(const float4 *p) {
                  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
     return r;
 }
+
+// internal helpers shared between translation units (not exported through the C ABI header)
+int gs_internal_exclusive_scan(int n, const int32_t *in, int32_t *out, int32_t *total_dev, void *scratch,
+                               size_t scratch_bytes, cudaStream_t st);

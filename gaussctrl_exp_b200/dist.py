@@ -119,40 +119,56 @@ def reduce_view_grads(model, average: bool = True) -> None:
 
 class PeerViewExchange:
     """reduce_view_grads with the collective fused into the kernel (NVLink peer memory, no NCCL on the data
-    path): each rank accumulates its view block straight into a symmetric-memory buffer; after one
-    device-side barrier every rank's multi-view backward kernel reads all peers' blocks in place
-    (gs_preprocess_bwd_multi_peer). Two buffers alternate so that a rank may start writing step s+1 while
-    slower peers still read step s (the barrier of step s+1 orders the reuse at step s+2)."""
+    path). Each rank publishes its view block in a symmetric-memory buffer; after one device-side barrier
+    every rank's multi-view backward kernel reads all peers' blocks in place.
 
-    def __init__(self, model):
+    sparse=True (default): the block is compacted first (bitmap + word prefix + packed values of the ~1/5 of
+    Gaussians with a non-zero gradient, gs_pack_view_block) and receivers index it with bitmap/popcount
+    (gs_preprocess_bwd_multi_peer_sparse): ~4x fewer NVLink bytes. sparse=False: the dense block is
+    accumulated straight into symmetric memory and read as is.
+    Two buffers alternate so that a rank may start writing step s+1 while slower peers still read step s
+    (the barrier of step s+1 orders the reuse at step s+2)."""
+
+    def __init__(self, model, sparse: bool = True):
         import torch.distributed._symmetric_memory as symm_mem
         from . import _lib
         assert dist.is_initialized()
+        L = _lib.lib()
         self.world = dist.get_world_size()
-        self.stride = _lib.lib().gs_view_block_floats(model.num_points)
+        self.sparse = sparse
+        N = model.num_points
+        self.stride = L.gs_view_xbuf_floats(N) if sparse else L.gs_view_block_floats(N)
         self.buf = symm_mem.empty(2 * self.stride, dtype=torch.float32, device=model.device)
         self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD)
+        self.scratch = torch.empty(L.gs_view_pack_scratch_bytes(N), dtype=torch.uint8, device=model.device) if sparse else None
         self.step = 0
         self.begin(model)
 
     def begin(self, model) -> None:
-        """Point the next backward at this step's buffer."""
+        """Point the next backward at this step's buffer (dense mode) / at a private dense block (sparse mode)."""
         k = self.step % 2
         model.view_state.defer_leaf_grads = True
-        model.view_state.view_block_buffer = self.buf[k * self.stride:(k + 1) * self.stride]
+        model.view_state.view_block_buffer = None if self.sparse else self.buf[k * self.stride:(k + 1) * self.stride]
 
     def reduce(self, model, average: bool = True) -> None:
-        from . import render
+        from . import _lib, render
         st = model.view_state
         assert st.view_block is not None
         use_sh, deg, _ = st.view_meta
+        k = self.step % 2
+        if self.sparse:
+            xbuf = self.buf[k * self.stride:(k + 1) * self.stride]
+            with torch.cuda.device(xbuf.device):
+                rc = _lib.lib().gs_pack_view_block(model.num_points, st.view_block.data_ptr(), xbuf.data_ptr(),
+                                                   self.scratch.data_ptr(), self.scratch.numel(), _lib.stream_ptr())
+            _lib.check(rc, "gs_pack_view_block")
         self.hdl.barrier(channel=0)                 # every rank's block of this step is complete
-        params = {k: getattr(model, k) for k in GRAD_PARAMS}
+        params = {n: getattr(model, n) for n in GRAD_PARAMS}
         flat, grads = render.leaf_grads_from_view_blocks(
             params, None, self.world, bool(use_sh), deg, 1.0 / self.world if average else 1.0,
-            peer_ptrs_dev=self.hdl.buffer_ptrs_dev, peer_offset=(self.step % 2) * self.stride)
-        for k in GRAD_PARAMS:
-            getattr(model, k).grad = grads[k]
+            peer_ptrs_dev=self.hdl.buffer_ptrs_dev, peer_offset=k * self.stride, sparse=self.sparse)
+        for n in GRAD_PARAMS:
+            getattr(model, n).grad = grads[n]
         st.flat_grads = flat
         self.step += 1
         self.begin(model)

@@ -351,7 +351,7 @@ def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: T
 
 
 def leaf_grads_from_view_blocks(params, blocks, num_views: int, use_sh: bool, deg: int, scale: float = 1.0,
-                                peer_ptrs_dev: Optional[int] = None, peer_offset: int = 0):
+                                peer_ptrs_dev: Optional[int] = None, peer_offset: int = 0, sparse: bool = False):
     """gs_preprocess_bwd_multi: `blocks` = num_views view blocks back to back (as all-gathered), or — with
     peer_ptrs_dev (device array of per-rank base pointers, symmetric memory) — the peers' blocks read in place
     over NVLink (gs_preprocess_bwd_multi_peer). Returns (flat, dict of the six leaf gradients as views of flat),
@@ -371,7 +371,8 @@ def leaf_grads_from_view_blocks(params, blocks, num_views: int, use_sh: bool, de
            "features_rest": flat[14 * Np:14 * Np + 45 * N].view(N, 15, 3)}
     with torch.cuda.device(dev):
         if peer_ptrs_dev is not None:
-            rc = L.gs_preprocess_bwd_multi_peer(
+            fn = L.gs_preprocess_bwd_multi_peer_sparse if sparse else L.gs_preprocess_bwd_multi_peer
+            rc = fn(
                 N, int(num_views), int(peer_ptrs_dev), int(peer_offset), float(scale), means.detach().data_ptr(),
                 scales.detach().data_ptr(), quats.detach().data_ptr(), opacities.detach().data_ptr(), int(use_sh), int(deg),
                 out["means"].data_ptr(), out["scales"].data_ptr(), out["quats"].data_ptr(), out["opacities"].data_ptr(),

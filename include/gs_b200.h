@@ -130,6 +130,20 @@ int gs_preprocess_bwd_multi_peer(int N, int V, const uint64_t *peer_base_ptrs_de
                                  float *v_means, float *v_log_scales, float *v_quats,
                                  float *v_opac_logits, float *v_feat_dc, float *v_feat_rest, void *stream);
 
+/* Sparse form of the same exchange: only ~1/5 of the Gaussians get a non-zero gradient from one view, so the
+ * sender compacts its finished dense view block into an exchange buffer
+ *   [{bitmap word, prefix} x W | camera 64 | packed v_xy 2Np | v_conic 3Np | v_rgb 3Np | v_opacity Np]   (floats/words)
+ * (gs_view_xbuf_floats(N) floats, W = ceil(N/32) rounded up to 4) and the receivers index it with
+ * bitmap + popcount. offset_floats = start of the rank's buffer inside its symmetric allocation. */
+int gs_view_xbuf_floats(int N);
+size_t gs_view_pack_scratch_bytes(int N);
+int gs_pack_view_block(int N, const float *block, float *xbuf, void *scratch, size_t scratch_bytes, void *stream);
+int gs_preprocess_bwd_multi_peer_sparse(int N, int V, const uint64_t *peer_base_ptrs_dev, int64_t offset_floats,
+                                        float scale, const float *means, const float *log_scales,
+                                        const float *quats, const float *opac_logits, int use_sh, int sh_deg,
+                                        float *v_means, float *v_log_scales, float *v_quats,
+                                        float *v_opac_logits, float *v_feat_dc, float *v_feat_rest, void *stream);
+
 /* ---- stage 2: tile binning (inside rasterize_gaussians; App. A.3) -------------------------- */
 size_t gs_scan_scratch_bytes(int N);
 /* inclusive int32 scan of tiles_hit -> cum; the total is also written to *total_dev

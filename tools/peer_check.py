@@ -12,31 +12,45 @@ from gaussctrl_exp_b200.model import GaussianModel  # noqa: E402
 
 rank, local, world = gd.init_from_env("nccl")
 dev = torch.device("cuda", local)
-m = GaussianModel(scene.make_scene(200000, 0, s0=0.006), background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
+m = GaussianModel(scene.make_scene(1000000, 0), background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
 m.train()
 cams = scene.make_cameras(16, 0)
 v = torch.randn(512, 512, 3, generator=torch.Generator().manual_seed(1)).to(dev) / (512 * 512)
 m.view_state.defer_leaf_grads = True
+for q in m.parameters():
+    q.grad = None
+out = m(cams[rank])
+(out["rgb"] * v).sum().backward()           # ONE backward: every exchange below consumes the same view block
+block = m.view_state.view_block.clone()
 res = {}
-peer = None
-for mode in ("gather", "peer", "peer"):
-    if mode == "peer" and peer is None:
-        peer = gd.PeerViewExchange(m)
-    for q in m.parameters():
-        q.grad = None
-    out = m(cams[rank])
-    (out["rgb"] * v).sum().backward()
-    if mode == "gather":
-        m.view_state.view_block_buffer = None
-        gd.reduce_view_grads(m)
-    else:
-        peer.reduce(m)
-    torch.cuda.synchronize()
+gd.reduce_view_grads(m)
+res["gather"] = {k: getattr(m, k).grad.clone() for k in gd.GRAD_PARAMS}
+for mode in ("peer", "sparse"):
+    px = gd.PeerViewExchange(m, sparse=(mode == "sparse"))
+    for rep in range(2):                     # twice: exercises the double buffering
+        if mode == "peer":
+            m.view_state.view_block_buffer.copy_(block)
+            m.view_state.view_block = m.view_state.view_block_buffer
+        else:
+            m.view_state.view_block = block
+        px.reduce(m)
+        torch.cuda.synchronize()
     res[mode] = {k: getattr(m, k).grad.clone() for k in gd.GRAD_PARAMS}
-# the compositor's float atomics make two runs differ at the 1e-7 relative level: compare with a tolerance
-rel = max(((res["gather"][k] - res["peer"][k]).abs().max() / res["gather"][k].abs().max().clamp_min(1e-30)).item()
-          for k in gd.GRAD_PARAMS)
-print(f"rank {rank}: peer vs gather max rel diff {rel:.3e} -> {'OK' if rel < 1e-5 else 'MISMATCH'}", flush=True)
-assert rel < 1e-5
+    same = all(torch.equal(res["gather"][k], res[mode][k]) for k in gd.GRAD_PARAMS)
+    rel = {k: ((res["gather"][k] - res[mode][k]).abs().max() / res["gather"][k].abs().max().clamp_min(1e-30)).item()
+           for k in gd.GRAD_PARAMS}
+    nbad = {k: int(((res["gather"][k] - res[mode][k]).abs() > 1e-6 * res["gather"][k].abs().max()).sum().item())
+            for k in gd.GRAD_PARAMS}
+    print(f"rank {rank}: {mode} vs NCCL all-gather on the SAME view blocks: bit-identical={same} "
+          f"max rel diff={max(rel.values()):.2e} {rel} elements off by >1e-6: {nbad}", flush=True)
+    # the dense kernel is the same code path -> bit-identical; the sparse kernel is a separate translation
+    # unit (FMA contraction may differ) -> tolerance
+    assert same if mode == "peer" else max(rel.values()) < 2e-6
+blk = m.view_state.view_block
+Np = (m.num_points + 3) // 4 * 4
+nz = (blk[:2 * Np].view(-1, 2).abs().sum(1)[:m.num_points] != 0) | (blk[8 * Np:9 * Np][:m.num_points] != 0) | \
+     (blk[5 * Np:8 * Np].view(-1, 3).abs().sum(1)[:m.num_points] != 0)
+print(f"rank {rank}: Gaussians with a non-zero view gradient: {nz.float().mean().item():.3f} "
+      f"(visible {(m.view_state.radii > 0).float().mean().item():.3f})", flush=True)
 dist.barrier()
 dist.destroy_process_group()
