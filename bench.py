@@ -287,7 +287,7 @@ def run_ours(args):
     peer = None
     if gather_mode and args.reduce == "peer":
         try:
-            peer = gdist.PeerViewExchange(model, sparse=not args.dense_exchange)   # NVLink symmetric memory
+            peer = gdist.PeerViewExchange(model, mode=args.exchange)   # NVLink symmetric memory
         except Exception as e:                         # (e.g. no P2P between the visible devices)
             if rank == 0:
                 print(f"bench.py: peer-memory exchange unavailable ({type(e).__name__}: {e}); using NCCL all-gather",
@@ -409,7 +409,7 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
             "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
-            "grad_exchange": (args.reduce if world > 1 else None),
+            "grad_exchange": ((args.reduce + ("/" + args.exchange if args.reduce == "peer" else "")) if world > 1 else None),
             "eval_render": {"views_per_s": render_vps, "what": f"all-view RGB+depth+alpha render of {N_CAMS} cameras "
                             f"(gc_pipeline.py:222-228), view-sharded over {world} GPU(s), {args.render_streams} streams/GPU"},
             "host_enqueue_ms_per_step": host_enqueue_ms,
@@ -499,7 +499,8 @@ def main():
                          "compositor-level grads (36 B/Gaussian) in place over NVLink (symmetric memory, collective fused "
                          "into the kernel); gather = same payload through one NCCL all-gather; allreduce = NCCL "
                          "all-reduce of the 236 B/Gaussian leaf grads")
-    ap.add_argument("--dense-exchange", action="store_true", help="peer exchange without compaction")
+    ap.add_argument("--exchange", choices=("push", "dense", "sparse"), default="push",
+                    help="peer-memory exchange: compacted blocks pushed to the peers (default), dense pull, compacted pull")
     ap.add_argument("--path", default="fused", choices=["fused", "api"],
                     help="fused: one autograd node / 5 kernels per view (render.py); api: the literal "
                          "gsplat-0.1.2 three-operator sequence of gc_model.py")

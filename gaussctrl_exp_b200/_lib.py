@@ -39,6 +39,7 @@ SIGNATURES = {
     "gs_view_xbuf_floats": (_i, [_i]),
     "gs_view_pack_scratch_bytes": (_sz, [_i]),
     "gs_pack_view_block": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
+    "gs_pack_view_block_push": (_i, [_i, _vp, _vp, _i, _i, _vp, _i64, _vp, _sz, _vp]),
     "gs_preprocess_bwd_multi_peer_sparse": (_i, [_i, _i, _vp, _i64, _f, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp,
                                                  _vp, _vp, _vp]),
     "gs_sh_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),

@@ -10,6 +10,8 @@
 // Receivers (gs_preprocess_bwd_multi_peer_sparse) walk the Gaussians; a warp owns one bitmap word, so the
 // word and its prefix are one broadcast load each and the packed values of the warp's set lanes are
 // consecutive (coalesced peer loads). NVLink bytes per view drop from 36 N to ~0.25 N + 36 nnz.
+#include <cstdlib>
+
 #include "project_math.cuh"
 #include "sh_math.cuh"
 
@@ -46,16 +48,17 @@ vx_bitmap_kernel(int N, int Np, const float *__restrict__ blk, uint32_t *__restr
 // ---- sender 2: pack the set Gaussians ---------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 vx_pack_kernel(int N, int Np, int Wp, const float *__restrict__ blk, const uint32_t *__restrict__ bitmap,
-               const int32_t *__restrict__ prefix, uint2 *__restrict__ meta, float *__restrict__ packed) {
+               const int32_t *__restrict__ prefix, float *__restrict__ xbuf) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x < 64) xbuf[(size_t)2 * Wp + threadIdx.x] = blk[(size_t)9 * Np + threadIdx.x];
     if ((threadIdx.x & 31) == 0 && (i >> 5) < Wp)      // one 8-byte {bitmap word, prefix} record per 32 Gaussians
-        meta[i >> 5] = make_uint2(bitmap[i >> 5], (uint32_t)prefix[i >> 5]);
+        reinterpret_cast<uint2 *>(xbuf)[i >> 5] = make_uint2(bitmap[i >> 5], (uint32_t)prefix[i >> 5]);
     if (i >= N) return;
     const uint32_t word = bitmap[i >> 5];
     if (!((word >> (i & 31)) & 1u)) return;
     const int k = prefix[i >> 5] + __popc(word & gs_lanemask_lt());
-    const float2 xy = reinterpret_cast<const float2 *>(blk)[i];
-    reinterpret_cast<float2 *>(packed)[k] = xy;
+    float *packed = xbuf + (size_t)2 * Wp + 64;
+    reinterpret_cast<float2 *>(packed)[k] = reinterpret_cast<const float2 *>(blk)[i];
     const float *vc = blk + (size_t)2 * Np + 3 * (size_t)i;
     const float *vr = blk + (size_t)5 * Np + 3 * (size_t)i;
     float *pc = packed + (size_t)2 * Np + 3 * (size_t)k;
@@ -63,6 +66,38 @@ vx_pack_kernel(int N, int Np, int Wp, const float *__restrict__ blk, const uint3
     pc[0] = vc[0]; pc[1] = vc[1]; pc[2] = vc[2];
     pr[0] = vr[0]; pr[1] = vr[1]; pr[2] = vr[2];
     packed[(size_t)8 * Np + k] = blk[(size_t)8 * Np + i];
+}
+
+// ---- sender 3 (PUSH exchange): copy the compacted buffer into every peer's slot ----------------------------
+// Posted NVLink stores, 16 B per lane and 512 contiguous bytes per warp instruction; only the used part of
+// each packed array travels (the count is read from the last meta record). Scattered 4-byte peer stores
+// straight from the pack kernel were ~3x slower than pack-locally-then-copy.
+constexpr int VX_PUSH_TPB = 256;
+
+__global__ void __launch_bounds__(VX_PUSH_TPB)
+vx_push_kernel(int Np, int Wp, int D, int self, const float4 *__restrict__ src,
+               const unsigned long long *__restrict__ peer_ptrs, size_t peer_off) {
+    __shared__ float4 *dst_s[VX_MAX_VIEWS];
+    if (threadIdx.x < D) dst_s[threadIdx.x] = reinterpret_cast<float4 *>(reinterpret_cast<float *>(peer_ptrs[threadIdx.x]) + peer_off);
+    __syncthreads();
+    const uint2 last = reinterpret_cast<const uint2 *>(src)[Wp - 1];
+    const int nnz = (int)last.y + __popc(last.x);
+    const int h4 = (2 * Wp + 64) / 4, q = Np / 4;
+    const int n_xy = (2 * nnz + 3) / 4, n_c = (3 * nnz + 3) / 4, n_o = (nnz + 3) / 4;
+    const int total = h4 + n_xy + 2 * n_c + n_o;
+    for (int t = blockIdx.x * VX_PUSH_TPB + threadIdx.x; t < total; t += gridDim.x * VX_PUSH_TPB) {
+        int idx = t;                                        // float4 index inside the exchange buffer
+        if (t >= h4) {
+            int r = t - h4;
+            if (r < n_xy) idx = h4 + r;
+            else if ((r -= n_xy) < n_c) idx = h4 + 2 * q + r;
+            else if ((r -= n_c) < n_c) idx = h4 + 5 * q + r;
+            else idx = h4 + 8 * q + (r - n_c);
+        }
+        const float4 val = src[idx];
+        for (int d = 0; d < D; ++d)
+            if (d != self) dst_s[d][idx] = val;
+    }
 }
 
 struct ViewGrad {
@@ -195,6 +230,212 @@ vx_bwd_multi_sparse_kernel(int N, int Np, int Wp, int V, const unsigned long lon
     if (tid == 0 && rows4 > 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
+
+// ---- receiver v2: item-compacted multi-view leaf backward ------------------------------------------------
+// The loop-over-views kernel above runs the whole projection/SH backward for a view whenever ANY of a warp's
+// 32 Gaussians is set in it — with ~22 % density that is every warp, every view, at ~7 useful lanes. Here a
+// warp first enumerates its (Gaussian, view) ITEMS from the bitmap words, Gaussian-major, then processes them
+// 32 at a time with all lanes busy: lane j computes item j into a 31-float slot (projection vjp 10, opacity 1,
+// colour gradient 3, SH basis 16, constant 1). The slots are then folded into the 59 per-Gaussian sums with
+// the lanes TRANSPOSED over the component index (lane e owns components e and e+32 of every Gaussian): the
+// items of one Gaussian are consecutive, so each lane keeps a running sum in a register and stores it when the
+// owner changes — no shared-memory read-modify-write chain. Every Gaussian sums its views in view order:
+// deterministic, and the same on every rank.
+constexpr int VI_TPB = 128;
+constexpr int VI_HEAD = 14;      // vm3 vls3 vq4 vop1 vdc3
+constexpr int VI_HSTRIDE = 15;
+constexpr int VI_SLOT = 31;      // odd stride: per-lane slot rows stay off each other's banks; [30] holds 1.0f
+constexpr int VI_PRM = 11;
+
+struct __align__(16) ViWarp {
+    float rest[32 * VX_REST];      // contiguous: bulk-stored to v_feat_rest
+    float head[32 * VI_HSTRIDE];
+    float slot[32 * VI_SLOT];
+    float prm[32 * VI_PRM];
+    uint32_t word[VX_MAX_VIEWS];
+    uint32_t pref[VX_MAX_VIEWS];
+};
+static_assert(sizeof(ViWarp) % 16 == 0, "per-warp smem must keep 16 B alignment");
+
+// dynamic smem: 4 ViWarp | block pointers | V cameras | 4 x 32 V item records (owner | view << 8, Gaussian-major).
+// 56 KB at V = 8: four CTAs per SM.
+__host__ __device__ inline size_t vi_smem_bytes(int V) {
+    return 4 * sizeof(ViWarp) + VX_MAX_VIEWS * sizeof(const float *) + (size_t)V * sizeof(GsCamera) +
+           4 * 32 * (size_t)V * sizeof(uint16_t);
+}
+
+__global__ void __launch_bounds__(VI_TPB)
+vx_bwd_items_kernel(int N, int Np, int Wp, int V, const unsigned long long *__restrict__ peer_ptrs, size_t peer_off,
+                    float scale, const float *__restrict__ means, const float *__restrict__ log_scales,
+                    const float4 *__restrict__ quats, const float *__restrict__ opac_logits, int use_sh, int deg,
+                    float *__restrict__ v_means, float *__restrict__ v_log_scales, float4 *__restrict__ v_quats,
+                    float *__restrict__ v_opac_logits, float *__restrict__ v_dc, float *__restrict__ v_rest) {
+    extern __shared__ __align__(16) unsigned char vi_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    ViWarp &ws = reinterpret_cast<ViWarp *>(vi_smem)[warp];
+    const float **blk_s = reinterpret_cast<const float **>(vi_smem + 4 * sizeof(ViWarp));
+    GsCamera *cam_s = reinterpret_cast<GsCamera *>(blk_s + VX_MAX_VIEWS);
+    uint16_t *items = reinterpret_cast<uint16_t *>(cam_s + V) + warp * 32 * V;
+    const int i = blockIdx.x * VI_TPB + tid;
+    const int w = i >> 5;
+    if (tid < V) blk_s[tid] = reinterpret_cast<const float *>(peer_ptrs[tid]) + peer_off;
+    __syncthreads();
+    constexpr int CAMF = (int)(sizeof(GsCamera) / 4);
+    for (int k = tid; k < V * CAMF; k += VI_TPB)
+        reinterpret_cast<float *>(cam_s)[k] = blk_s[k / CAMF][(size_t)2 * Wp + k % CAMF];
+    // this warp's bitmap word + packed-array prefix of every view (lane v fetches view v)
+    uint2 m = make_uint2(0u, 0u);
+    if (lane < V) m = reinterpret_cast<const uint2 *>(blk_s[lane])[w];
+    if (lane < VX_MAX_VIEWS) { ws.word[lane] = m.x; ws.pref[lane] = m.y; }
+
+    float s0 = 1.f, s1 = 1.f, s2 = 1.f, iq = 1.f, o = 0.f;
+    float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+    if (i < N) {
+        const float p0 = means[3 * i], p1 = means[3 * i + 1], p2 = means[3 * i + 2];
+        s0 = expf(log_scales[3 * i]); s1 = expf(log_scales[3 * i + 1]); s2 = expf(log_scales[3 * i + 2]);
+        const float4 qr = quats[i];
+        iq = 1.0f / sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
+        q = make_float4(qr.x * iq, qr.y * iq, qr.z * iq, qr.w * iq);
+        o = 1.0f / (1.0f + expf(-opac_logits[i]));
+        float *pr = ws.prm + lane * VI_PRM;
+        pr[0] = p0; pr[1] = p1; pr[2] = p2; pr[3] = s0; pr[4] = s1; pr[5] = s2;
+        pr[6] = q.x; pr[7] = q.y; pr[8] = q.z; pr[9] = q.w;
+    }
+    ws.slot[lane * VI_SLOT + 30] = 1.0f;
+    __syncwarp();
+    // item list: lane = Gaussian; its set views in ascending order, Gaussians in index order
+    uint32_t vmask = 0;
+#pragma unroll
+    for (int v = 0; v < VX_MAX_VIEWS; ++v) vmask |= ((ws.word[v] >> lane) & 1u) << v;
+    int incl = __popc(vmask);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    const int T = __shfl_sync(0xffffffffu, incl, 31);
+    {
+        int pos = incl - __popc(vmask);
+        for (uint32_t mk = vmask; mk; mk &= mk - 1) items[pos++] = (uint16_t)(lane | ((__ffs(mk) - 1) << 8));
+    }
+    // Gaussians without any item keep zero sums (the fold below only ever writes rows that have items)
+    const uint32_t empty = __ballot_sync(0xffffffffu, vmask == 0);
+    if (__popc(empty) > 10) {
+        for (int e = lane; e < 32 * VX_REST; e += 32) ws.rest[e] = 0.f;
+        for (int e = lane; e < 32 * VI_HSTRIDE; e += 32) ws.head[e] = 0.f;
+    } else {
+        for (uint32_t em = empty; em; em &= em - 1) {
+            const int row = __ffs(em) - 1;
+            ws.rest[row * VX_REST + lane] = 0.f;
+            if (lane < VX_REST - 32) ws.rest[row * VX_REST + 32 + lane] = 0.f;
+            if (lane < VI_HSTRIDE) ws.head[row * VI_HSTRIDE + lane] = 0.f;
+        }
+    }
+    __syncwarp();
+    __syncthreads();   // cameras + per-warp tables staged
+
+    // fold: this lane owns components e1 = lane and e2 = lane + 32 (of 59) of every Gaussian.
+    //   component e < 11: slot[e] * slot[30] (= 1);  e >= 11: slot[14 + (e-11)/3] * slot[11 + (e-11)%3]
+    const int e1 = lane, e2 = lane + 32;
+    const bool e2_ok = e2 < VI_HEAD + VX_REST;
+    const int a1 = e1 < 11 ? e1 : 14 + (e1 - 11) / 3, b1 = e1 < 11 ? 30 : 11 + (e1 - 11) % 3;
+    const int a2 = e2_ok ? 14 + (e2 - 11) / 3 : 30, b2 = e2_ok ? 11 + (e2 - 11) % 3 : 30;
+    const int nb = use_sh ? sh_num_bases(deg) : 1;
+    // running sums of the current owner; stored after EVERY item (last store of an owner = its full sum), which
+    // keeps the loop free of branches: the items of one Gaussian are consecutive
+    int cur = -1;
+    float sum1 = 0.f, sum2 = 0.f;
+    float *dst1 = e1 < VI_HEAD ? ws.head + e1 : ws.rest + (e1 - VI_HEAD);
+    const int stride1 = e1 < VI_HEAD ? VI_HSTRIDE : VX_REST;
+    float *dst2 = e2_ok ? ws.rest + (e2 - VI_HEAD) : ws.prm + lane * VI_PRM + 10;     // lanes 27..31: an unused word
+    const int stride2 = e2_ok ? VX_REST : 0;
+
+    for (int r0 = 0; r0 < T; r0 += 32) {
+        const int j = r0 + lane;
+        if (j < T) {
+            const int it = items[j];
+            const int ow = it & 31, v = it >> 8;
+            const int k = (int)ws.pref[v] + __popc(ws.word[v] & ((1u << ow) - 1u));
+            const float *pk = blk_s[v] + (size_t)2 * Wp + 64;
+            float2 xy = reinterpret_cast<const float2 *>(pk)[k];
+            const float *vc = pk + (size_t)2 * Np + 3 * (size_t)k;
+            const float *vr = pk + (size_t)5 * Np + 3 * (size_t)k;
+            const float ga = vc[0] * scale, gb = vc[1] * scale, gc = vc[2] * scale;
+            const float u0 = vr[0] * scale, u1 = vr[1] * scale, u2 = vr[2] * scale;
+            const float go = pk[(size_t)8 * Np + k] * scale;
+            xy.x *= scale; xy.y *= scale;
+            const float *pr = ws.prm + ow * VI_PRM;
+            const float p0 = pr[0], p1 = pr[1], p2 = pr[2];
+            const GsCamera &cam = cam_s[v];
+            ProjGrad g;
+            gs_project_one_bwd(cam.viewmat, cam.projmat, p0, p1, p2, pr[3], pr[4], pr[5], cam.glob_scale,
+                               make_float4(pr[6], pr[7], pr[8], pr[9]), cam.fx, cam.fy, cam.H, cam.W, xy, 0.0f, ga, gb,
+                               gc, g);
+            float *sl = ws.slot + lane * VI_SLOT;
+            sl[0] = g.vp[0]; sl[1] = g.vp[1]; sl[2] = g.vp[2];
+            sl[3] = g.vs[0]; sl[4] = g.vs[1]; sl[5] = g.vs[2];
+            sl[6] = g.vq.x; sl[7] = g.vq.y; sl[8] = g.vq.z; sl[9] = g.vq.w;
+            sl[10] = go; sl[11] = u0; sl[12] = u1; sl[13] = u2;
+            float Y[16];
+#pragma unroll
+            for (int b = 0; b < 16; ++b) Y[b] = 0.f;
+            if (use_sh) {
+                float dx = p0 - cam.cam_pos[0], dy = p1 - cam.cam_pos[1], dz = p2 - cam.cam_pos[2];
+                const float vn = sqrtf(dx * dx + dy * dy + dz * dz);
+                dx = dx / vn; dy = dy / vn; dz = dz / vn;
+                sh_basis<3>(deg, dx, dy, dz, Y);
+            } else {
+                Y[0] = 1.0f;
+            }
+#pragma unroll
+            for (int b = 0; b < 16; ++b) sl[14 + b] = b < nb ? Y[b] : 0.f;
+        }
+        __syncwarp();
+        const int cnt = min(32, T - r0);
+#pragma unroll 4
+        for (int jj = 0; jj < cnt; ++jj) {
+            const int ow = items[r0 + jj] & 31;
+            const float *sl = ws.slot + jj * VI_SLOT;
+            const float x1 = sl[a1], y1 = sl[b1], x2 = sl[a2], y2 = sl[b2];
+            const bool same = ow == cur;
+            cur = ow;
+            sum1 = fmaf(x1, y1, same ? sum1 : 0.f);
+            sum2 = fmaf(x2, y2, same ? sum2 : 0.f);
+            dst1[ow * stride1] = sum1;
+            dst2[ow * stride2] = sum2;
+        }
+        __syncwarp();
+    }
+    __syncwarp();
+
+    const int w0 = w << 5;                    // first Gaussian of this warp
+    const int rows = min(32, N - w0);
+    if (i < N) {
+        const float *a = ws.head + lane * VI_HSTRIDE;
+        v_means[3 * i] = a[0]; v_means[3 * i + 1] = a[1]; v_means[3 * i + 2] = a[2];
+        v_log_scales[3 * i] = a[3] * s0; v_log_scales[3 * i + 1] = a[4] * s1; v_log_scales[3 * i + 2] = a[5] * s2;
+        const float4 vq = make_float4(a[6], a[7], a[8], a[9]);
+        const float dq = vq.x * q.x + vq.y * q.y + vq.z * q.z + vq.w * q.w;
+        v_quats[i] = make_float4((vq.x - q.x * dq) * iq, (vq.y - q.y * dq) * iq, (vq.z - q.z * dq) * iq,
+                                 (vq.w - q.w * dq) * iq);
+        v_opac_logits[i] = a[10] * o * (1.0f - o);
+        v_dc[3 * i] = a[11]; v_dc[3 * i + 1] = a[12]; v_dc[3 * i + 2] = a[13];
+    }
+    if (rows == 32) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(v_rest + (size_t)w0 * VX_REST),
+                         "r"(vx_smem_u32(ws.rest)), "r"((unsigned)(32 * VX_REST * 4))
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+    } else if (rows > 0) {
+        for (int f = lane; f < rows * VX_REST; f += 32) v_rest[(size_t)w0 * VX_REST + f] = ws.rest[f];
+    }
+}
+
 }  // namespace
 
 extern "C" int gs_view_xbuf_floats(int N) {
@@ -209,28 +450,41 @@ extern "C" size_t gs_view_pack_scratch_bytes(int N) {
 // block: finished dense view block (gs_finish_view_block already applied). xbuf: gs_view_xbuf_floats(N) floats.
 extern "C" int gs_pack_view_block(int N, const float *block, float *xbuf, void *scratch, size_t scratch_bytes,
                                   void *stream) {
-    if (N < 0 || !block || !xbuf || !scratch) return GS_ERR_BAD_ARG;
+    if (N < 0 || !block || !scratch || !xbuf) return GS_ERR_BAD_ARG;
     if (scratch_bytes < gs_view_pack_scratch_bytes(N)) return GS_ERR_SCRATCH_SMALL;
-    if (!gs_aligned16(xbuf) || !gs_aligned16(scratch) || !gs_aligned16(block)) return GS_ERR_MISALIGNED;
+    if (!gs_aligned16(scratch) || !gs_aligned16(block) || !gs_aligned16(xbuf)) return GS_ERR_MISALIGNED;
     cudaStream_t st = (cudaStream_t)stream;
     const int Np = (N + 3) / 4 * 4, Wp = vx_words(N);
-    uint2 *meta = reinterpret_cast<uint2 *>(xbuf);
-    float *cam = xbuf + 2 * (size_t)Wp;
-    float *packed = cam + 64;
     unsigned char *p = reinterpret_cast<unsigned char *>(scratch);
     const size_t w4 = gs_align_up((size_t)Wp * 4, 256);
     int32_t *wcount = reinterpret_cast<int32_t *>(p);
     uint32_t *bitmap = reinterpret_cast<uint32_t *>(p + w4);
     int32_t *prefix = reinterpret_cast<int32_t *>(p + 2 * w4);
     void *scan_scratch = p + 3 * w4;
-    GS_CUDA(cudaMemcpyAsync(cam, block + (size_t)9 * Np, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
-    if (N == 0) return 0;
     const int threads_total = Wp * 32;
     vx_bitmap_kernel<<<(threads_total + 255) / 256, 256, 0, st>>>(N, Np, block, bitmap, wcount);
     GS_LAUNCH_CHECK();
     const int rc = gs_internal_exclusive_scan(Wp, wcount, prefix, nullptr, scan_scratch, scratch_bytes - 3 * w4, st);
     if (rc) return rc;
-    vx_pack_kernel<<<(threads_total + 255) / 256, 256, 0, st>>>(N, Np, Wp, block, bitmap, prefix, meta, packed);
+    vx_pack_kernel<<<(threads_total + 255) / 256, 256, 0, st>>>(N, Np, Wp, block, bitmap, prefix, xbuf);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+// PUSH: pack into the caller's own slot (xbuf_self == peer_base[self] + offset_floats, local memory), then copy
+// the used part of it into the same slot of every other peer.
+extern "C" int gs_pack_view_block_push(int N, const float *block, float *xbuf_self, int n_peers, int self,
+                                       const uint64_t *peer_base_ptrs_dev, int64_t offset_floats, void *scratch,
+                                       size_t scratch_bytes, void *stream) {
+    if (!peer_base_ptrs_dev || offset_floats < 0 || n_peers <= 0 || n_peers > VX_MAX_VIEWS || self < 0 || self >= n_peers)
+        return GS_ERR_BAD_ARG;
+    if (offset_floats & 3) return GS_ERR_MISALIGNED;
+    const int rc = gs_pack_view_block(N, block, xbuf_self, scratch, scratch_bytes, stream);
+    if (rc || n_peers == 1) return rc;
+    const int Np = (N + 3) / 4 * 4;
+    vx_push_kernel<<<148 * 4, VX_PUSH_TPB, 0, (cudaStream_t)stream>>>(
+        Np, vx_words(N), n_peers, self, reinterpret_cast<const float4 *>(xbuf_self),
+        reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats);
     GS_LAUNCH_CHECK();
     return 0;
 }
@@ -251,6 +505,17 @@ extern "C" int gs_preprocess_bwd_multi_peer_sparse(int N, int V, const uint64_t 
     if (!gs_aligned16(quats) || !gs_aligned16(v_quats) || !gs_aligned16(v_feat_rest) || (offset_floats & 3))
         return GS_ERR_MISALIGNED;
     const int Np = (N + 3) / 4 * 4;
+    static const bool loop_kernel = getenv("GS_VX_LOOP") != nullptr;    // A/B switch: the loop-over-views receiver
+    if (!loop_kernel) {
+        GS_CUDA(cudaFuncSetAttribute(vx_bwd_items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)vi_smem_bytes(VX_MAX_VIEWS)));
+        vx_bwd_items_kernel<<<(N + VI_TPB - 1) / VI_TPB, VI_TPB, vi_smem_bytes(V), (cudaStream_t)stream>>>(
+            N, Np, vx_words(N), V, reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats,
+            scale, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, v_means,
+            v_log_scales, reinterpret_cast<float4 *>(v_quats), v_opac_logits, v_feat_dc, v_feat_rest);
+        GS_LAUNCH_CHECK();
+        return 0;
+    }
     vx_bwd_multi_sparse_kernel<<<(N + VX_TPB - 1) / VX_TPB, VX_TPB, 0, (cudaStream_t)stream>>>(
         N, Np, vx_words(N), V, reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats,
         scale, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, v_means,

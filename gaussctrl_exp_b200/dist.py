@@ -118,55 +118,83 @@ def reduce_view_grads(model, average: bool = True) -> None:
 
 
 class PeerViewExchange:
-    """reduce_view_grads with the collective fused into the kernel (NVLink peer memory, no NCCL on the data
-    path). Each rank publishes its view block in a symmetric-memory buffer; after one device-side barrier
-    every rank's multi-view backward kernel reads all peers' blocks in place.
+    """reduce_view_grads with the collective fused into the kernels (NVLink peer memory, no NCCL on the data
+    path). Three modes:
 
-    sparse=True (default): the block is compacted first (bitmap + word prefix + packed values of the ~1/5 of
-    Gaussians with a non-zero gradient, gs_pack_view_block) and receivers index it with bitmap/popcount
-    (gs_preprocess_bwd_multi_peer_sparse): ~4x fewer NVLink bytes. sparse=False: the dense block is
-    accumulated straight into symmetric memory and read as is.
+    "push" (default): the sender compacts its view block (bitmap + word prefix + packed values of the ~1/5 of
+        Gaussians with a non-zero gradient) and the pack kernel stores it straight into EVERY peer's
+        symmetric-memory slot (gs_pack_view_block_push: posted NVLink stores, ~8 MB per peer instead of 36 MB);
+        after one device-side barrier each rank's multi-view backward reads its LOCAL slots only.
+    "dense": every rank accumulates its dense block in symmetric memory; after the barrier the multi-view
+        backward kernel PULLS all peers' blocks in place (NVLink-ingress bound: 36 MB x (world-1) per step).
+    "sparse": compacted like push but pulled by the receivers (dependent remote loads: latency bound).
     Two buffers alternate so that a rank may start writing step s+1 while slower peers still read step s
     (the barrier of step s+1 orders the reuse at step s+2)."""
 
-    def __init__(self, model, sparse: bool = True):
+    def __init__(self, model, sparse: bool | None = None, mode: str | None = None):
         import torch.distributed._symmetric_memory as symm_mem
         from . import _lib
         assert dist.is_initialized()
         L = _lib.lib()
+        if mode is None:
+            mode = "push" if sparse is None else ("sparse" if sparse else "dense")
+        assert mode in ("push", "dense", "sparse")
+        self.mode = mode
         self.world = dist.get_world_size()
-        self.sparse = sparse
+        self.rank = dist.get_rank()
+        self.sparse = mode != "dense"
         N = model.num_points
-        self.stride = L.gs_view_xbuf_floats(N) if sparse else L.gs_view_block_floats(N)
-        self.buf = symm_mem.empty(2 * self.stride, dtype=torch.float32, device=model.device)
+        self.stride = L.gs_view_xbuf_floats(N) if self.sparse else L.gs_view_block_floats(N)
+        self.slots = self.world if mode == "push" else 1
+        self.buf = symm_mem.empty(2 * self.slots * self.stride, dtype=torch.float32, device=model.device)
         self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD)
-        self.scratch = torch.empty(L.gs_view_pack_scratch_bytes(N), dtype=torch.uint8, device=model.device) if sparse else None
+        self.scratch = (torch.empty(L.gs_view_pack_scratch_bytes(N), dtype=torch.uint8, device=model.device)
+                        if self.sparse else None)
+        if mode == "push":
+            base = self.buf.data_ptr()
+            self.local_ptrs = torch.tensor([base + v * self.stride * 4 for v in range(self.world)],
+                                           dtype=torch.int64).to(model.device)
         self.step = 0
         self.begin(model)
 
     def begin(self, model) -> None:
-        """Point the next backward at this step's buffer (dense mode) / at a private dense block (sparse mode)."""
+        """Point the next backward at this step's buffer (dense mode) / at a private dense block (sparse modes)."""
         k = self.step % 2
         model.view_state.defer_leaf_grads = True
         model.view_state.view_block_buffer = None if self.sparse else self.buf[k * self.stride:(k + 1) * self.stride]
 
-    def reduce(self, model, average: bool = True) -> None:
+    def reduce(self, model, average: bool = True, on_barrier=None) -> None:
         from . import _lib, render
         st = model.view_state
         assert st.view_block is not None
         use_sh, deg, _ = st.view_meta
         k = self.step % 2
-        if self.sparse:
+        L = _lib.lib()
+        if self.mode == "sparse":
             xbuf = self.buf[k * self.stride:(k + 1) * self.stride]
             with torch.cuda.device(xbuf.device):
-                rc = _lib.lib().gs_pack_view_block(model.num_points, st.view_block.data_ptr(), xbuf.data_ptr(),
-                                                   self.scratch.data_ptr(), self.scratch.numel(), _lib.stream_ptr())
+                rc = L.gs_pack_view_block(model.num_points, st.view_block.data_ptr(), xbuf.data_ptr(),
+                                          self.scratch.data_ptr(), self.scratch.numel(), _lib.stream_ptr())
             _lib.check(rc, "gs_pack_view_block")
-        self.hdl.barrier(channel=0)                 # every rank's block of this step is complete
+        elif self.mode == "push":
+            with torch.cuda.device(self.buf.device):
+                off = (k * self.world + self.rank) * self.stride
+                rc = L.gs_pack_view_block_push(model.num_points, st.view_block.data_ptr(),
+                                               self.buf.data_ptr() + 4 * off, self.world, self.rank,
+                                               self.hdl.buffer_ptrs_dev, off, self.scratch.data_ptr(),
+                                               self.scratch.numel(), _lib.stream_ptr())
+            _lib.check(rc, "gs_pack_view_block_push")
+        self.hdl.barrier(channel=0)                 # every rank's block of this step is complete and visible
+        if on_barrier is not None:                  # profiling hook (tools/dp_profile.py)
+            on_barrier()
         params = {n: getattr(model, n) for n in GRAD_PARAMS}
+        if self.mode == "push":
+            ptrs, off = self.local_ptrs.data_ptr(), k * self.world * self.stride
+        else:
+            ptrs, off = self.hdl.buffer_ptrs_dev, k * self.stride
         flat, grads = render.leaf_grads_from_view_blocks(
             params, None, self.world, bool(use_sh), deg, 1.0 / self.world if average else 1.0,
-            peer_ptrs_dev=self.hdl.buffer_ptrs_dev, peer_offset=k * self.stride, sparse=self.sparse)
+            peer_ptrs_dev=ptrs, peer_offset=off, sparse=self.sparse)
         for n in GRAD_PARAMS:
             getattr(model, n).grad = grads[n]
         st.flat_grads = flat

@@ -138,6 +138,13 @@ int gs_preprocess_bwd_multi_peer(int N, int V, const uint64_t *peer_base_ptrs_de
 int gs_view_xbuf_floats(int N);
 size_t gs_view_pack_scratch_bytes(int N);
 int gs_pack_view_block(int N, const float *block, float *xbuf, void *scratch, size_t scratch_bytes, void *stream);
+/* PUSH form: the block is compacted into the caller's own slot xbuf_self (== peer_base_ptrs[self] +
+ * offset_floats, local memory) and the used part of it is then copied into the same slot of every other peer
+ * (posted NVLink stores, 16 B per lane). After the device barrier each rank runs
+ * gs_preprocess_bwd_multi_peer_sparse over its LOCAL slots (pointer array of local addresses). */
+int gs_pack_view_block_push(int N, const float *block, float *xbuf_self, int n_peers, int self,
+                            const uint64_t *peer_base_ptrs_dev, int64_t offset_floats, void *scratch,
+                            size_t scratch_bytes, void *stream);
 int gs_preprocess_bwd_multi_peer_sparse(int N, int V, const uint64_t *peer_base_ptrs_dev, int64_t offset_floats,
                                         float scale, const float *means, const float *log_scales,
                                         const float *quats, const float *opac_logits, int use_sh, int sh_deg,

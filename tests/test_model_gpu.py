@@ -176,6 +176,72 @@ def test_view_block_replay_equals_summed_leaf_grads(cuda_dev):
         m.view_state.defer_leaf_grads = False
 
 
+@pytest.mark.parametrize("N,V,deg", [(20000, 2, 3), (20000, 5, 3), (20000, 16, 0), (4999, 3, 2), (97, 1, 3)])
+def test_compacted_view_exchange_equals_dense(cuda_dev, N, V, deg):
+    """gs_pack_view_block / gs_pack_view_block_push + gs_preprocess_bwd_multi_peer_sparse (both receiver
+    kernels) against the dense gs_preprocess_bwd_multi on the same V view blocks; the 'peers' are V slots of
+    one local buffer (the pointer array is what symmetric memory hands out on a real multi-GPU run, and what
+    dist.PeerViewExchange builds for its local slots in push mode)."""
+    from gaussctrl_exp_b200 import _lib, render, scene
+    from gaussctrl_exp_b200 import dist as gd
+    from gaussctrl_exp_b200.model import GaussianModel
+    dev = cuda_dev
+    L = _lib.lib()
+    p = scene.make_scene(N, 11, s0=0.02, device=dev)
+    v = torch.randn(128, 160, 3, generator=torch.Generator().manual_seed(2)).to(dev) / (128 * 160)
+    m = GaussianModel(p, sh_degree=deg, background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
+    m.train()
+    m.view_state.defer_leaf_grads = True
+    blocks = []
+    for c in range(V):
+        (m(small_cam(160, 128, 20 + c))["rgb"] * v).sum().backward()
+        blocks.append(m.view_state.view_block.clone())
+    use_sh, d, _ = m.view_state.view_meta
+    params = {k: getattr(m, k) for k in gd.GRAD_PARAMS}
+    scale = 1.0 / 4                                            # power of two: scaling commutes with the sums
+    _, want = render.leaf_grads_from_view_blocks(params, torch.cat(blocks), V, bool(use_sh), d, scale)
+    assert want["means"].abs().max() > 0
+    xs = L.gs_view_xbuf_floats(N)
+    assert xs % 4 == 0
+    scratch = torch.empty(L.gs_view_pack_scratch_bytes(N), dtype=torch.uint8, device=dev)
+    xa = torch.full((V * xs,), float("nan"), device=dev)        # filled by V local packs
+    xb = torch.full((V * V * xs,), float("nan"), device=dev)    # V 'ranks' x V slots, filled by V pushes
+    rank_bases = torch.tensor([xb.data_ptr() + r * V * xs * 4 for r in range(V)], dtype=torch.int64).to(dev)
+    for c in range(V):
+        _lib.check(L.gs_pack_view_block(N, blocks[c].data_ptr(), xa.data_ptr() + c * xs * 4, scratch.data_ptr(),
+                                        scratch.numel(), _lib.stream_ptr()), "pack")
+        self_rank = c % V                                       # 'rank' self_rank owns view c here
+        _lib.check(L.gs_pack_view_block_push(N, blocks[c].data_ptr(), xb.data_ptr() + (self_rank * V + c) * xs * 4, V,
+                                             self_rank, rank_bases.data_ptr(), c * xs, scratch.data_ptr(),
+                                             scratch.numel(), _lib.stream_ptr()), "push")
+    torch.cuda.synchronize()
+    Wp = ((N + 31) // 32 + 3) // 4 * 4
+    bits = np.arange(32, dtype=np.uint32)
+    nnz = [int(((xa[c * xs:c * xs + 2 * Wp].view(torch.int32)[0::2].cpu().numpy().astype(np.uint32)[:, None] >> bits) & 1).sum())
+           for c in range(V)]
+    for r in range(V):                                          # every 'rank' received the same V blocks
+        for c in range(V):
+            a = xa[c * xs:(c + 1) * xs].view(torch.int32)
+            b = xb[(r * V + c) * xs:(r * V + c + 1) * xs].view(torch.int32)
+            head = 2 * Wp + 41                                   # meta + camera (41 floats used)
+            assert torch.equal(a[:head], b[:head])
+            Np = (N + 3) // 4 * 4
+            for off, w in ((0, 2), (2 * Np, 3), (5 * Np, 3), (8 * Np, 1)):
+                lo = 2 * Wp + 64 + off
+                assert torch.equal(a[lo:lo + w * nnz[c]], b[lo:lo + w * nnz[c]])
+    for ptrs in (torch.tensor([xa.data_ptr() + c * xs * 4 for c in range(V)], dtype=torch.int64).to(dev),
+                 torch.tensor([xb.data_ptr() + ((V - 1) * V + c) * xs * 4 for c in range(V)], dtype=torch.int64).to(dev)):
+        _, got = render.leaf_grads_from_view_blocks(params, None, V, bool(use_sh), d, scale,
+                                                    peer_ptrs_dev=ptrs.data_ptr(), peer_offset=0, sparse=True)
+        for k in gd.GRAD_PARAMS:
+            den = want[k].abs().max().item()
+            if den == 0:
+                assert got[k].abs().max().item() == 0, k
+            else:
+                assert (got[k] - want[k]).abs().max().item() / den < 2e-6, k
+    m.view_state.defer_leaf_grads = False
+
+
 def test_render_views_matches_single_view_calls(oracle, cuda_dev):
     """The view-sharded, multi-stream all-view loop (gc_pipeline.py:222-228) returns exactly what
     per-camera get_outputs_for_camera returns; the fused RGB-D pass equals the reference's two passes."""

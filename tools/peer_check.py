@@ -25,8 +25,8 @@ block = m.view_state.view_block.clone()
 res = {}
 gd.reduce_view_grads(m)
 res["gather"] = {k: getattr(m, k).grad.clone() for k in gd.GRAD_PARAMS}
-for mode in ("peer", "sparse"):
-    px = gd.PeerViewExchange(m, sparse=(mode == "sparse"))
+for mode in ("peer", "sparse", "push"):
+    px = gd.PeerViewExchange(m, mode="dense" if mode == "peer" else mode)
     for rep in range(2):                     # twice: exercises the double buffering
         if mode == "peer":
             m.view_state.view_block_buffer.copy_(block)
