@@ -19,7 +19,7 @@ namespace gsradix {
 
 constexpr int TPB = 256;
 constexpr int WARPS = TPB / 32;
-constexpr int IPT = 8;
+constexpr int IPT = 16;
 constexpr int SUB = TPB * IPT;  // keys per CTA
 
 // element count: host value, or (n_dev != nullptr) the device value clamped by the capacity;
@@ -212,7 +212,14 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
         const int li = woff + i * 32 + lane;
         // out-of-range items get digit RADIX-1 and sort behind every valid key of the chunk
         dig[i] = li < valid ? ((uint32_t)(key[i] >> shift) & mask) : (uint32_t)(RADIX - 1);
-        peers[i] = __match_any_sync(0xffffffffu, dig[i]);
+        // match-any by ballots: `bits` ballot+select steps whatever the digit mix (the hardware match.any
+        // serialises over the DISTINCT values in the warp: ~2x slower on uniformly random digits)
+        unsigned pm = 0xffffffffu;
+        for (int b = 0; b < bits; ++b) {
+            const unsigned bal = __ballot_sync(0xffffffffu, (dig[i] >> b) & 1u);
+            pm &= ((dig[i] >> b) & 1u) ? bal : ~bal;
+        }
+        peers[i] = pm;
     }
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
