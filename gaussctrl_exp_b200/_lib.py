@@ -59,6 +59,8 @@ SIGNATURES = {
     "gs_tile_order": (_i, [_i, _vp, _i, _vp, _vp]),
     "gs_raster_fwd_ordered": (_i, [_i, _i, _i, _i] + [_vp] * 15),
     "gs_raster_bwd_ordered": (_i, [_i, _i, _i, _i] + [_vp] * 17),
+    "gs_raster_fwd_ordered_post": (_i, [_i, _i, _i, _i] + [_vp] * 17),
+    "gs_raster_bwd_ordered_post": (_i, [_i, _i, _i, _i] + [_vp] * 18),
     "gs_raster_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                            _vp, _vp, _vp, _vp, _vp]),
 }

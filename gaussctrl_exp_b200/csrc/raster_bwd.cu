@@ -64,7 +64,8 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                    const float *__restrict__ final_T, const int32_t *__restrict__ final_idx,
                    const float *__restrict__ v_out, const float *__restrict__ v_out_alpha,
                    float *__restrict__ v_xys, float *__restrict__ v_conics, float *__restrict__ v_colors,
-                   float *__restrict__ v_opac, const int32_t *__restrict__ tile_order) {
+                   float *__restrict__ v_opac, const int32_t *__restrict__ tile_order,
+                   const float *__restrict__ clamp_ref) {
     __shared__ float4 sa[RB_BATCH];  // x, y, opac, qa   (q* = pre-scaled conic, raster_common.cuh)
     __shared__ float4 sb[RB_BATCH];  // qb, qc, r, g
     __shared__ float sc[RB_BATCH];   // b
@@ -93,6 +94,11 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     float vo0 = 0.f, vo1 = 0.f, vo2 = 0.f, voa = 0.f;
     if (inside) {
         vo0 = v_out[3 * pix]; vo1 = v_out[3 * pix + 1]; vo2 = v_out[3 * pix + 2];
+        if (clamp_ref) {       // v_out is w.r.t. clamp(out, max=1): no gradient where the raw output exceeds 1
+            if (clamp_ref[3 * pix] > 1.0f) vo0 = 0.f;
+            if (clamp_ref[3 * pix + 1] > 1.0f) vo1 = 0.f;
+            if (clamp_ref[3 * pix + 2] > 1.0f) vo2 = 0.f;
+        }
         if (v_out_alpha) voa = v_out_alpha[pix];
     }
     // d out / d alpha_k through the background and the alpha output: Tf/(1-a) * (voa - bg.vo)
@@ -346,11 +352,30 @@ extern "C" int gs_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y,
     if (C == 3)
         raster_bwd3_kernel<<<tiles, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg,
                                                   final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics,
-                                                  v_colors, v_opac, nullptr);
+                                                  v_colors, v_opac, nullptr, nullptr);
     else
         raster_bwdN_kernel<<<tiles, 256, 0, st>>>(C, H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac,
                                                   bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics,
                                                   v_colors, v_opac);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int gs_raster_bwd_ordered_post(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                                     const int32_t *tile_bins, const float *xys, const float *conics,
+                                     const float *colors, const float *opac, const float *bg, const float *final_T,
+                                     const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
+                                     float *v_xys, float *v_conics, float *v_colors, float *v_opac,
+                                     const int32_t *tile_order, const float *clamp_ref, void *stream) {
+    if (H <= 0 || W <= 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (!tile_bins || !xys || !conics || !colors || !opac || !bg || !final_T || !final_idx || !v_out || !v_xys ||
+        !v_conics || !v_colors || !v_opac)
+        return GS_ERR_BAD_ARG;
+    if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
+    raster_bwd3_kernel<<<tiles_x * tiles_y, 256, 0, (cudaStream_t)stream>>>(
+        H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys),
+        conics, colors, opac, bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order,
+        clamp_ref);
     GS_LAUNCH_CHECK();
     return 0;
 }
@@ -361,14 +386,7 @@ extern "C" int gs_raster_bwd_ordered(int H, int W, int tiles_x, int tiles_y, con
                                      const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
                                      float *v_xys, float *v_conics, float *v_colors, float *v_opac,
                                      const int32_t *tile_order, void *stream) {
-    if (H <= 0 || W <= 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
-    if (!tile_bins || !xys || !conics || !colors || !opac || !bg || !final_T || !final_idx || !v_out || !v_xys ||
-        !v_conics || !v_colors || !v_opac)
-        return GS_ERR_BAD_ARG;
-    if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
-    raster_bwd3_kernel<<<tiles_x * tiles_y, 256, 0, (cudaStream_t)stream>>>(
-        H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys),
-        conics, colors, opac, bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order);
-    GS_LAUNCH_CHECK();
-    return 0;
+    return gs_raster_bwd_ordered_post(H, W, tiles_x, tiles_y, ids_sorted, tile_bins, xys, conics, colors, opac, bg,
+                                      final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac,
+                                      tile_order, nullptr, stream);
 }

@@ -32,7 +32,8 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                    const float *__restrict__ opac, const float *__restrict__ depths,
                    const float *__restrict__ bg, float *__restrict__ out_img, float *__restrict__ out_depth,
                    float *__restrict__ final_T, int32_t *__restrict__ final_idx,
-                   const int32_t *__restrict__ tile_order, int32_t *__restrict__ tile_work) {
+                   const int32_t *__restrict__ tile_order, int32_t *__restrict__ tile_work,
+                   float *__restrict__ out_clamped, float *__restrict__ out_alpha) {
     __shared__ StageRGB st[2];
     __shared__ unsigned char wlist[8][RF_BATCH];   // per-warp compacted survivors of the current batch
     __shared__ int s_work;
@@ -127,9 +128,16 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     }
     if (inside) {
         const size_t pix = (size_t)py * W + px;
-        out_img[3 * pix] = r + T * bg[0];
-        out_img[3 * pix + 1] = g + T * bg[1];
-        out_img[3 * pix + 2] = b + T * bg[2];
+        const float c0 = r + T * bg[0], c1 = g + T * bg[1], c2 = b + T * bg[2];
+        out_img[3 * pix] = c0;
+        out_img[3 * pix + 1] = c1;
+        out_img[3 * pix + 2] = c2;
+        if (out_clamped) {     // the caller's clamp(rgb, max=1) (gc_model.py:222), NaN-propagating like torch
+            out_clamped[3 * pix] = c0 > 1.0f ? 1.0f : c0;
+            out_clamped[3 * pix + 1] = c1 > 1.0f ? 1.0f : c1;
+            out_clamped[3 * pix + 2] = c2 > 1.0f ? 1.0f : c2;
+        }
+        if (out_alpha) out_alpha[pix] = 1.0f - T;
         if (WITH_DEPTH) out_depth[pix] = dacc;
         final_T[pix] = T;
         final_idx[pix] = last;
@@ -236,7 +244,7 @@ extern "C" int gs_raster_fwd(int C, int H, int W, int tiles_x, int tiles_y,
 #define GS_FWD_ARGS H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg, out_img, final_T, final_idx
     if (C == 3)
         raster_fwd3_kernel<false><<<tiles, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, nullptr,
-                                                         bg, out_img, nullptr, final_T, final_idx, nullptr, nullptr);
+                                                         bg, out_img, nullptr, final_T, final_idx, nullptr, nullptr, nullptr, nullptr);
     else if (C <= 4) raster_fwdN_kernel<4><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
     else if (C <= 8) raster_fwdN_kernel<8><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
     else if (C <= 16) raster_fwdN_kernel<16><<<tiles, 256, 0, st>>>(C, GS_FWD_ARGS);
@@ -258,7 +266,7 @@ extern "C" int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
     if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
     raster_fwd3_kernel<true><<<tiles_x * tiles_y, 256, 0, (cudaStream_t)stream>>>(
         H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys),
-        conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx, nullptr, nullptr);
+        conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx, nullptr, nullptr, nullptr, nullptr);
     GS_LAUNCH_CHECK();
     return 0;
 }
@@ -293,11 +301,12 @@ extern "C" int gs_tile_order(int T, const int32_t *work, int work_is_range, int3
     return 0;
 }
 
-extern "C" int gs_raster_fwd_ordered(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+extern "C" int gs_raster_fwd_ordered_post(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
                                      const int32_t *tile_bins, const float *xys, const float *conics,
                                      const float *colors, const float *opac, const float *depths, const float *bg,
                                      float *out_img, float *out_depth, float *final_T, int32_t *final_idx,
-                                     const int32_t *tile_order, int32_t *tile_work, void *stream) {
+                                     const int32_t *tile_order, int32_t *tile_work, float *out_clamped, float *out_alpha,
+                                     void *stream) {
     if (H <= 0 || W <= 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
     if (!tile_bins || !xys || !conics || !colors || !opac || !bg || !out_img || !final_T || !final_idx)
         return GS_ERR_BAD_ARG;
@@ -309,11 +318,21 @@ extern "C" int gs_raster_fwd_ordered(int H, int W, int tiles_x, int tiles_y, con
     if (depths)
         raster_fwd3_kernel<true><<<tiles_x * tiles_y, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors,
                                                                     opac, depths, bg, out_img, out_depth, final_T,
-                                                                    final_idx, tile_order, tile_work);
+                                                                    final_idx, tile_order, tile_work, out_clamped, out_alpha);
     else
         raster_fwd3_kernel<false><<<tiles_x * tiles_y, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors,
                                                                      opac, nullptr, bg, out_img, nullptr, final_T,
-                                                                     final_idx, tile_order, tile_work);
+                                                                     final_idx, tile_order, tile_work, out_clamped, out_alpha);
     GS_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int gs_raster_fwd_ordered(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                                     const int32_t *tile_bins, const float *xys, const float *conics,
+                                     const float *colors, const float *opac, const float *depths, const float *bg,
+                                     float *out_img, float *out_depth, float *final_T, int32_t *final_idx,
+                                     const int32_t *tile_order, int32_t *tile_work, void *stream) {
+    return gs_raster_fwd_ordered_post(H, W, tiles_x, tiles_y, ids_sorted, tile_bins, xys, conics, colors, opac, depths,
+                                      bg, out_img, out_depth, final_T, final_idx, tile_order, tile_work, nullptr, nullptr,
+                                      stream);
 }

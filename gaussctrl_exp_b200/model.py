@@ -153,22 +153,23 @@ class GaussianModel(nn.Module):
         if torch.is_grad_enabled() and self.training:
             rgb, alpha, depths, radii, hit = _render.render_view(
                 self.means, self.scales, self.quats, self.opacities, self.features_dc, self.features_rest, camera,
-                n, use_sh, background, self.view_state)
+                n, use_sh, background, self.view_state, clamp_rgb=True)       # gc_model.py:222 inside the kernels
             self.xys, self.radii = self.view_state.xys, radii
             viewmat0, projmat0 = self._caller_matrices(camera)
-            return {"rgb": torch.clamp(rgb, max=1.0), "depth": None, "accumulation": alpha[..., None],
+            return {"rgb": rgb, "depth": None, "accumulation": alpha[..., None],
                     "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
         with torch.no_grad(), torch.cuda.device(dev):
             bg = background.to(dev).float().contiguous()
             want_depth = not self.training
+            post = {}
             res = _render._forward_impl(
                 self.means.detach(), self.scales.detach(), self.quats.detach(), self.opacities.detach(),
                 self.features_dc.detach(), self.features_rest.detach(), cam, use_sh, n, bg, strict=True,
-                with_depth=want_depth)
-            xys, radii, out, fT, depth_acc = res[0], res[5], res[9], res[10], res[13]
+                with_depth=want_depth, post=post)
+            xys, radii, depth_acc = res[0], res[5], res[13]
             self.xys, self.radii = xys, radii
-            alpha = (1.0 - fT)[..., None]
-            rgb = torch.clamp(out, max=1.0)
+            alpha = post["alpha"][..., None]
+            rgb = post["rgb_clamped"]                                 # gc_model.py:222, written by the kernel
             depth_im = None
             if want_depth:                                            # gc_model.py:224-238 in the same pass
                 depth_im = depth_acc[..., None]

@@ -138,10 +138,12 @@ class ViewState:
 
 
 def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, strict=True,
-                  with_depth=False):
+                  with_depth=False, post=None):
     """strict=True: the host confirms the tile-list capacity before returning (one 4-byte read, overlapped
     with the compositing kernel; overflow -> redo). strict=False: nothing is read; the caller must run
-    _check_pending(result[-1]) before trusting the view (render_view does it at the end of backward)."""
+    _check_pending(result[-1]) before trusting the view (render_view does it at the end of backward).
+    post: optional dict; the compositing kernel then also writes the caller's per-pixel post-ops
+    (gc_model.py:221-222) and the dict receives "rgb_clamped" = clamp(out, max=1) and "alpha" = 1 - final_T."""
     L = _lib.lib()
     dev = means.device
     N = means.shape[0]
@@ -174,6 +176,11 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
     out_depth = torch.empty((H, W), device=dev, dtype=torch.float32) if with_depth else None
     order_f = torch.empty((T,), device=dev, dtype=torch.int32)
     tile_work = torch.empty((T,), device=dev, dtype=torch.int32)
+    out_c = alpha = None
+    if post is not None:
+        out_c = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
+        alpha = torch.empty((H, W), device=dev, dtype=torch.float32)
+        post["rgb_clamped"], post["alpha"] = out_c, alpha
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
         if BIN_IMPL == "tile":
@@ -195,11 +202,12 @@ def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, c
         # each tile's true depth of composition, which orders the backward
         rc = L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), st)
         _lib.check(rc, "gs_tile_order")
-        rc = L.gs_raster_fwd_ordered(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                     conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(),
-                                     depths.data_ptr() if with_depth else None, bg.data_ptr(), out.data_ptr(),
-                                     out_depth.data_ptr() if with_depth else None, fT.data_ptr(), fidx.data_ptr(),
-                                     order_f.data_ptr(), tile_work.data_ptr(), st)
+        rc = L.gs_raster_fwd_ordered_post(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                          conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(),
+                                          depths.data_ptr() if with_depth else None, bg.data_ptr(), out.data_ptr(),
+                                          out_depth.data_ptr() if with_depth else None, fT.data_ptr(),
+                                          fidx.data_ptr(), order_f.data_ptr(), tile_work.data_ptr(),
+                                          _lib.ptr(out_c), _lib.ptr(alpha), st)
         _lib.check(rc, "gs_raster_fwd")
         if not strict:
             return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, None,
@@ -222,7 +230,8 @@ def _ctypes_addr(struct):
 
 class _RenderView(Function):
     @staticmethod
-    def forward(ctx, means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, state):
+    def forward(ctx, means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, state,
+                clamp_rgb=False):
         for t, shape in ((means, 3), (scales, 3), (quats, 4), (features_dc, 3)):
             if t.ndim != 2 or t.shape[1] != shape or t.shape[0] != means.shape[0]:
                 raise ValueError("means/scales (N,3), quats (N,4), features_dc (N,3) expected")
@@ -232,27 +241,33 @@ class _RenderView(Function):
             raise ValueError("features_rest must have dimensions (N, 15, 3)")
         args = [t.detach().float().contiguous() for t in (means, scales, quats, opacities, features_dc, features_rest)]
         bg = bg.detach().to(means.device).float().contiguous()
+        post = {}
         with torch.cuda.device(means.device):
             (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, pending,
-             tile_work) = _forward_impl(*args, cam, use_sh, deg, bg, strict=not SPECULATE)
+             tile_work) = _forward_impl(*args, cam, use_sh, deg, bg, strict=not SPECULATE, post=post)
         ctx.pending = pending
-        ctx.save_for_backward(*args, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT, fidx, tile_work)
+        # clamp_rgb: the returned colour is clamp(out, max=1) (written by the compositing kernel) and the raw
+        # colour is kept so that the backward kernel can mask the incoming gradient like torch.clamp's backward
+        ctx.save_for_backward(*args, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT, fidx, tile_work,
+                              out if clamp_rgb else None)
         ctx.cam, ctx.use_sh, ctx.deg, ctx.state = cam, use_sh, deg, state
         if state is not None:
             state.xys, state.radii, state.depths, state.num_intersects = xys, radii, depths, I
-        alpha = 1.0 - fT
         ctx.mark_non_differentiable(depths, radii, hit)
-        return out, alpha, depths, radii, hit
+        ctx.set_materialize_grads(False)      # unused outputs arrive as None instead of freshly filled zeros
+        return (post["rgb_clamped"] if clamp_rgb else out), post["alpha"], depths, radii, hit
 
     @staticmethod
     def backward(ctx, v_out, v_alpha, *_unused):
         (means, scales, quats, opacities, fdc, frest, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT,
-         fidx, tile_work) = ctx.saved_tensors
+         fidx, tile_work, clamp_ref) = ctx.saved_tensors
         cam = ctx.cam
         L = _lib.lib()
         dev = means.device
         N = means.shape[0]
         H, W, tx, ty = cam.H, cam.W, cam.tiles_x, cam.tiles_y
+        if v_out is None:                       # only alpha was used downstream
+            v_out = torch.zeros((H, W, 3), device=dev, dtype=torch.float32)
         v_out = v_out.float().contiguous()
         va_ptr = None
         if v_alpha is not None:
@@ -275,11 +290,11 @@ class _RenderView(Function):
             order_b = torch.empty_like(tile_work)
             rc = L.gs_tile_order(tx * ty, tile_work.data_ptr(), 0, order_b.data_ptr(), st)
             _lib.check(rc, "gs_tile_order")
-            rc = L.gs_raster_bwd_ordered(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                         conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(),
-                                         fT.data_ptr(), fidx.data_ptr(), v_out.data_ptr(), va_ptr, v_xys.data_ptr(),
-                                         v_conics.data_ptr(), v_rgbs.data_ptr(), v_opac.data_ptr(), order_b.data_ptr(),
-                                         st)
+            rc = L.gs_raster_bwd_ordered_post(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
+                                              conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(),
+                                              fT.data_ptr(), fidx.data_ptr(), v_out.data_ptr(), va_ptr,
+                                              v_xys.data_ptr(), v_conics.data_ptr(), v_rgbs.data_ptr(),
+                                              v_opac.data_ptr(), order_b.data_ptr(), _lib.ptr(clamp_ref), st)
             _lib.check(rc, "gs_raster_bwd")
             if ctx.state is not None and ctx.state.defer_leaf_grads:
                 rc = L.gs_finish_view_block(N, int(ctx.use_sh), _ctypes_addr(cam), rgbs.data_ptr(), g.data_ptr(), st)
@@ -289,7 +304,7 @@ class _RenderView(Function):
                 ctx.state.xys_grad = v_xys
                 ctx.state.view_block = g
                 ctx.state.view_meta = (int(ctx.use_sh), int(ctx.deg), tuple(opacities.shape))
-                return (None,) * 11
+                return (None,) * 12
             # the six leaf gradients live in ONE flat buffer (59 floats / Gaussian) so that the
             # data-parallel step can all-reduce them with a single NCCL call
             flat = torch.empty(59 * Np, device=dev, dtype=torch.float32)
@@ -312,21 +327,22 @@ class _RenderView(Function):
         if ctx.state is not None:
             ctx.state.xys_grad = v_xys       # what gc_model.py:193-194 keeps via xys.retain_grad()
             ctx.state.flat_grads = flat
-        return v_means, v_scales, v_quats, v_opl, v_dc, v_rest, None, None, None, None, None
+        return v_means, v_scales, v_quats, v_opl, v_dc, v_rest, None, None, None, None, None, None
 
 
 def render_view(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, features_dc: Tensor,
                 features_rest: Tensor, camera: Camera, sh_degree_to_use: int, use_sh: bool = True,
-                background: Optional[Tensor] = None, state: Optional[ViewState] = None
+                background: Optional[Tensor] = None, state: Optional[ViewState] = None, clamp_rgb: bool = False
                 ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
     """RAW splatfacto leaves (log-scales, un-normalised wxyz quats, opacity logits (N,1),
     features_dc (N,3), features_rest (N,15,3)) + one camera -> (rgb (H,W,3) before the caller's
-    clamp(max=1), alpha (H,W), depths (N), radii (N) i32, num_tiles_hit (N) i32)."""
+    clamp(max=1) — or after it with clamp_rgb=True: the clamp and its backward are then done inside the
+    compositing kernels —, alpha (H,W), depths (N), radii (N) i32, num_tiles_hit (N) i32)."""
     if background is None:
         background = torch.ones(3, dtype=torch.float32, device=means.device)
     cam = gs_camera(camera)
     return _RenderView.apply(means, scales, quats, opacities, features_dc, features_rest, cam, bool(use_sh),
-                             int(sh_degree_to_use), background, state)
+                             int(sh_degree_to_use), background, state, bool(clamp_rgb))
 
 
 def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: Tensor) -> Tensor:

@@ -224,6 +224,23 @@ int gs_raster_bwd_ordered(int H, int W, int tiles_x, int tiles_y, const int32_t 
                           float *v_xys, float *v_conics, float *v_colors, float *v_opac,
                           const int32_t *tile_order, void *stream);
 
+/* The same two passes with the caller's per-pixel post-ops folded in (gc_model.py:221-222: alpha = 1 - T and
+ * rgb = clamp(rgb, max=1)): out_clamped (H,W,3) and out_alpha (H,W) are extra outputs (either may be NULL;
+ * out_img keeps the raw colour); clamp_ref = the raw out_img of the forward: v_out is then taken as the
+ * gradient w.r.t. the CLAMPED colour, i.e. zeroed where clamp_ref > 1 (torch.clamp's backward). */
+int gs_raster_fwd_ordered_post(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                               const int32_t *tile_bins, const float *xys, const float *conics,
+                               const float *colors, const float *opac, const float *depths, const float *bg,
+                               float *out_img, float *out_depth, float *final_T, int32_t *final_idx,
+                               const int32_t *tile_order, int32_t *tile_work, float *out_clamped,
+                               float *out_alpha, void *stream);
+int gs_raster_bwd_ordered_post(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                               const int32_t *tile_bins, const float *xys, const float *conics,
+                               const float *colors, const float *opac, const float *bg, const float *final_T,
+                               const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
+                               float *v_xys, float *v_conics, float *v_colors, float *v_opac,
+                               const int32_t *tile_order, const float *clamp_ref, void *stream);
+
 /* ---- stage 4: backward compositing (App. A.5) ---------------------------------------------- */
 /* v_out (H,W,C); v_out_alpha (H,W) or NULL. Outputs are ACCUMULATED INTO: caller zero-fills
  * v_xys (N,2), v_conics (N,3), v_colors (N,C), v_opac (N). */
