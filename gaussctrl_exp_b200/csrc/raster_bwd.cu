@@ -113,8 +113,12 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
 #pragma unroll
     for (int w = 0; w < 8; ++w) bmax = max(bmax, s_wmax[w]);
 
-    float *my_acc = acc[warp];
     unsigned char *mylist = wlist[warp];
+    const unsigned sa_a = gs_smem_addr(sa), sb_a = gs_smem_addr(sb), sc_a = gs_smem_addr(sc);
+    const unsigned list_a = gs_smem_addr(mylist);
+    // this lane's accumulator column: lanes 0,4,..,28 own moments 0..7, lane 1 owns the ninth
+    const unsigned acc_a = gs_smem_addr(acc[warp]) + (lane == 1 ? 8u : (unsigned)(lane >> 2)) * 4u;
+    const bool acc_lane = (lane & 3) == 0 || lane == 1;
     for (int hi = bmax; hi > range.x; hi -= RB_BATCH) {
         const int lo = max(range.x, hi - RB_BATCH);
         const int cnt = hi - lo;
@@ -153,22 +157,22 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
         // them and are assembled once per (tile, Gaussian) in the flush. S.vo (colour accumulated behind,
         // dotted with the upstream gradient) is carried as ONE running scalar.
         for (int t = nl - 1; t >= 0; --t) {
-            const int j = mylist[t];
-            const float4 A = sa[j];
-            const float4 B = sb[j];
+            const unsigned j = gs_lds8(list_a + t);
+            const float4 A = gs_lds128(sa_a + j * 16u);
+            const float4 B = gs_lds128(sb_a + j * 16u);
             GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};
             float dx, dy, vis, alpha;
             bool hit = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
-            hit = hit && (lo + j < my_end);
+            hit = hit && (lo + (int)j < my_end);
             if (!__any_sync(0xffffffffu, hit)) continue;
             float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             float v8 = 0.f;
             if (hit) {
-                const float ra = 1.0f / (1.0f - alpha);
+                const float ra = gs_rcp(1.0f - alpha);
                 T *= ra;
                 const float fac = alpha * T;
                 v[6] = fac * vo0; v[7] = fac * vo1; v8 = fac * vo2;
-                const float cvo = B.z * vo0 + B.w * vo1 + sc[j] * vo2;
+                const float cvo = B.z * vo0 + B.w * vo1 + gs_lds32(sc_a + j * 4u) * vo2;
                 const float v_alpha = T * cvo - ra * (Svo - tail);
                 Svo += fac * cvo;
                 if (A.z * vis <= GS_ALPHA_MAX) {
@@ -181,8 +185,10 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             }
             const float r8 = warp_reduce8(v, lane);
             const float r9 = warp_sum(v8);
-            if ((lane & 3) == 0) my_acc[j * RB_NV + (lane >> 2)] += r8;
-            if (lane == 1) my_acc[j * RB_NV + 8] += r9;
+            if (acc_lane) {
+                const unsigned a = acc_a + j * (RB_NV * 4u);
+                gs_sts32(a, gs_lds32(a) + (lane == 1 ? r9 : r8));
+            }
         }
         __syncthreads();
         // flush: one thread per Gaussian sums the 8 warp rows, turns the moments into gradients
@@ -280,7 +286,7 @@ raster_bwdN_kernel(int C, int H, int W, int tiles_x, const int32_t *__restrict__
             GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};
             float dx, dy, vis, alpha;
             bool hit = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
-            hit = hit && (lo + j < my_end);
+            hit = hit && (lo + (int)j < my_end);
             if (!__any_sync(0xffffffffu, hit)) continue;
             const int id = sid[j];
             const float *col = colors + (size_t)id * C;

@@ -64,3 +64,40 @@ __device__ __forceinline__ void gs_warp_rect(int tile_x, int tile_y, float &x0, 
     x0 = (float)(tile_x * GS_TILE + (warp & 1) * 8) + GS_PIX_CENTER;
     y0 = (float)(tile_y * GS_TILE + (warp >> 1) * 4) + GS_PIX_CENTER;
 }
+
+// Shared-memory access through 32-bit shared-window addresses held in ordinary registers. With plain C++
+// indexing the compiler re-derives the window base (S2UR SR_CgaCtaId / ULEA ...) inside the hot replay loops:
+// ~9 of ~137 issue slots per (warp, Gaussian) iteration of the backward (ncu source view, profiles/r01h).
+__device__ __forceinline__ unsigned gs_smem_addr(const void *p) {
+    unsigned a = (unsigned)__cvta_generic_to_shared(p);
+    asm volatile("" : "+r"(a));       // opaque: keeps the compiler from re-materialising the conversion per use
+    return a;
+}
+__device__ __forceinline__ float2 gs_lds64(unsigned a) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float4 gs_lds128(unsigned a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float gs_lds32(unsigned a) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ unsigned gs_lds8(unsigned a) {
+    unsigned v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void gs_sts32(unsigned a, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+}
+__device__ __forceinline__ float gs_rcp(float x) {     // 1 ulp-class reciprocal, no range fix-up (x in [1e-3, 1])
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}

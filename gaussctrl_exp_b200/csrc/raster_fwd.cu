@@ -103,10 +103,12 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
         }
         __syncwarp();
         // ---- front-to-back compositing over the survivors ----
+        const unsigned sa_a = gs_smem_addr(s.a), sb_a = gs_smem_addr(s.b), sc_a = gs_smem_addr(s.c);
+        const unsigned list_a = gs_smem_addr(mylist);
         for (int t = 0; t < nl; ++t) {
-            const int j = mylist[t];
-            const float4 A = s.a[j];
-            const float4 B = s.b[j];
+            const unsigned j = gs_lds8(list_a + t);
+            const float4 A = gs_lds128(sa_a + j * 16u);
+            const float4 B = gs_lds128(sb_a + j * 16u);
             GsSplat sp = {A.x, A.y, A.z, A.w, B.x, B.y};
             float dx, dy, vis, alpha;
             const bool ok = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
@@ -116,11 +118,11 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                     done = true;
                 } else {
                     const float w = alpha * T;
-                    const float2 Cc = s.c[j];
+                    const float2 Cc = gs_lds64(sc_a + j * 8u);
                     r += w * B.z; g += w * B.w; b += w * Cc.x;
                     if (WITH_DEPTH) dacc += w * Cc.y;
                     T = Tn;
-                    last = kbase + j + 1;
+                    last = kbase + (int)j + 1;
                 }
             }
             if (__all_sync(0xffffffffu, done)) break;
@@ -211,7 +213,7 @@ raster_fwdN_kernel(int C, int H, int W, int tiles_x, const int32_t *__restrict__
                 for (int c = 0; c < CPAD; ++c)
                     if (c < C) acc[c] += w * col[c];
                 T = Tn;
-                last = kbase + j + 1;
+                last = kbase + (int)j + 1;
             }
         }
     }
