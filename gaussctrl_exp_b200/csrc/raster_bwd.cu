@@ -165,24 +165,25 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             bool hit = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
             hit = hit && (lo + (int)j < my_end);
             if (!__any_sync(0xffffffffu, hit)) continue;
-            float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            float v8 = 0.f;
-            if (hit) {
-                const float ra = gs_rcp(1.0f - alpha);
-                T *= ra;
-                const float fac = alpha * T;
-                v[6] = fac * vo0; v[7] = fac * vo1; v8 = fac * vo2;
-                const float cvo = B.z * vo0 + B.w * vo1 + gs_lds32(sc_a + j * 4u) * vo2;
-                const float v_alpha = T * cvo - ra * (Svo - tail);
-                Svo += fac * cvo;
-                if (A.z * vis <= GS_ALPHA_MAX) {
-                    const float v_sigma = -A.z * vis * v_alpha;
-                    const float mx = v_sigma * dx, my = v_sigma * dy;
-                    v[0] = mx; v[1] = my;
-                    v[2] = mx * dx; v[3] = mx * dy; v[4] = my * dy;
-                    v[5] = vis * v_alpha;
-                }
-            }
+            // branch-free: a lane that does not hit runs the same arithmetic with alpha = 0 (T, Svo unchanged,
+            // all nine contributions exactly zero)
+            const float al = hit ? alpha : 0.0f;
+            const float ra = gs_rcp(1.0f - al);
+            T *= ra;
+            const float fac = al * T;
+            const float cvo = B.z * vo0 + B.w * vo1 + gs_lds32(sc_a + j * 4u) * vo2;
+            const float v_alpha = T * cvo - ra * (Svo - tail);
+            Svo += fac * cvo;
+            const bool live = hit && (A.z * vis <= GS_ALPHA_MAX);      // not clamped at 0.999: d alpha / d sigma != 0
+            const float visl = live ? vis : 0.0f;
+            const float v_sigma = -A.z * visl * v_alpha;
+            const float mx = v_sigma * dx, my = v_sigma * dy;
+            float v[8];
+            v[0] = mx; v[1] = my;
+            v[2] = mx * dx; v[3] = mx * dy; v[4] = my * dy;
+            v[5] = visl * v_alpha;
+            v[6] = fac * vo0; v[7] = fac * vo1;
+            const float v8 = fac * vo2;
             const float r8 = warp_reduce8(v, lane);
             const float r9 = warp_sum(v8);
             if (acc_lane) {
