@@ -27,6 +27,7 @@ scan_kernel(int N, const int32_t *__restrict__ in, const uint32_t *__restrict__ 
     __shared__ int s_warp[SCAN_TPB / 32];
     __shared__ int s_prefix;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    gs_pdl_sync();
     if (tid == 0) s_tile = atomicAdd(&ctl->ticket, 1u);
     __syncthreads();
     const int tile = (int)s_tile;
@@ -287,6 +288,7 @@ __global__ void __launch_bounds__(256)
 depth_keys_kernel(int N, const float *__restrict__ depths, const int32_t *__restrict__ radii,
                   uint32_t *__restrict__ keys) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    gs_pdl_sync();
     if (i < N) keys[i] = radii[i] > 0 ? __float_as_uint(depths[i]) : 0xFFFFFFFFu;   // culled: to the end
 }
 
@@ -295,6 +297,7 @@ emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, 
                    const int32_t *__restrict__ start, const float2 *__restrict__ xys,
                    const int32_t *__restrict__ radii, int tiles_x, int tiles_y, uint32_t *__restrict__ tkey,
                    uint32_t *__restrict__ tval) {
+    gs_pdl_sync();
     if ((int64_t)*total_dev > I_cap) return;   // capacity too small: write nothing, the host retries
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
@@ -335,6 +338,7 @@ emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, 
 __global__ void __launch_bounds__(256)
 edges32_kernel(int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ tk,
                int32_t *__restrict__ bins) {
+    gs_pdl_sync();
     const int64_t I = *total_dev;
     if (I > I_cap) return;
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -408,9 +412,11 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
     const int nblk = (N + 255) / 256;
     int rc;
 
+    // the scan's look-back state is cleared up front so that the kernel chain below is uninterrupted (every launch
+    // is a programmatic dependent launch: the next kernel is resident before the previous one drains)
+    GS_CUDA(cudaMemsetAsync(ctl, 0, gs_scan_scratch_bytes(N), st));
     // 1. depth sort: A -> B -> A -> B -> A (values start as the element index)
-    depth_keys_kernel<<<nblk, 256, 0, st>>>(N, depths, radii, keyA);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(depth_keys_kernel, nblk, 256, 0, st, N, depths, radii, keyA);
     if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyA, nullptr, keyB, valB, 0, 8, mat, st))) return rc;
     if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyB, valB, keyA, valA, 8, 8, mat, st))) return rc;
     if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyA, valA, keyB, valB, 16, 8, mat, st))) return rc;
@@ -418,15 +424,13 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
     const uint32_t *order = valA;
 
     // 2. exclusive scan of tiles_hit in depth order; total -> total_dev
-    GS_CUDA(cudaMemsetAsync(ctl, 0, gs_scan_scratch_bytes(N), st));
-    scan_kernel<<<(N + SCAN_TILE - 1) / SCAN_TILE, SCAN_TPB, 0, st>>>(N, tiles_hit, order, 1, start, total_dev, ctl, status);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(scan_kernel, (N + SCAN_TILE - 1) / SCAN_TILE, SCAN_TPB, 0, st, N, tiles_hit, order, 1, start, total_dev,
+                  ctl, status);
     if (I_cap == 0) return 0;
 
     // 3. emission in depth order
-    emit_sorted_kernel<<<nblk, 256, 0, st>>>(N, I_cap, total_dev, order, start, reinterpret_cast<const float2 *>(xys),
-                                             radii, tiles_x, tiles_y, tkey, tval);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(emit_sorted_kernel, nblk, 256, 0, st, N, I_cap, (const int32_t *)total_dev, order,
+                  (const int32_t *)start, reinterpret_cast<const float2 *>(xys), radii, tiles_x, tiles_y, tkey, tval);
 
     // 4. stable partition by tile id
     uint32_t *ids_out = reinterpret_cast<uint32_t *>(ids_sorted);

@@ -28,6 +28,33 @@ extern int64_t g_gs_launches;  // defined in abi.cu
         if (_e != cudaSuccess) return (int)_e;               \
     } while (0)
 
+// Programmatic dependent launch (sm_90+): a kernel launched with GS_PDL_LAUNCH may be made resident while the
+// previous kernel of the stream drains; it must call gs_pdl_sync() before touching ANY global memory (the wait
+// returns once the previous grid has completed and flushed; it is a no-op for a normal launch). Used for the
+// chains of short kernels (binning: 23 launches), where the ~1.2 us launch gaps added up to ~27 us per view.
+__device__ __forceinline__ void gs_pdl_sync() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+bool gs_pdl_enabled();   // abi.cu: false when GS_NO_PDL is set in the environment (A/B switch)
+
+#define GS_PDL_LAUNCH(kernel, grid, block, smem, st, ...)                                      \
+    do {                                                                                       \
+        cudaLaunchConfig_t _c = {};                                                            \
+        _c.gridDim = dim3(grid);                                                               \
+        _c.blockDim = dim3(block);                                                             \
+        _c.dynamicSmemBytes = (smem);                                                          \
+        _c.stream = (st);                                                                      \
+        cudaLaunchAttribute _a[1];                                                             \
+        _a[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                         \
+        _a[0].val.programmaticStreamSerializationAllowed = 1;                                  \
+        _c.attrs = _a;                                                                         \
+        _c.numAttrs = gs_pdl_enabled() ? 1 : 0;                                                \
+        cudaError_t _e = cudaLaunchKernelEx(&_c, kernel, __VA_ARGS__);                         \
+        if (_e != cudaSuccess) return (int)_e;                                                 \
+        ++g_gs_launches;                                                                       \
+    } while (0)
+
 static inline bool gs_aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 static inline int gs_ceil_log2(int v) { int b = 0; while ((1 << b) < v) ++b; return b; }
 static inline size_t gs_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

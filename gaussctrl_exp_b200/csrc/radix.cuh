@@ -65,6 +65,7 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
             uint32_t *__restrict__ mat, int pitch) {
     constexpr int RADIX = 1 << BITS;
     __shared__ uint32_t hist[RADIX];
+    gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
     const int64_t base = (int64_t)blockIdx.x * SUB;
     if (n < 0 || base >= n) return;
@@ -90,6 +91,7 @@ __global__ void __launch_bounds__(TPB)
 colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat, int pitch,
                uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T) {
     constexpr int RADIX = 1 << BITS;
+    gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
     if (n < 0) return;
     const int nb = (int)((n + SUB - 1) / SUB);
@@ -131,6 +133,7 @@ digit_base_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const uint32
     constexpr int RADIX = 1 << BITS;
     constexpr int DPT = (RADIX + TPB - 1) / TPB;
     __shared__ uint32_t tmp[64];
+    gs_pdl_sync();
     if (resolve_n(n_cap, n_dev) < 0) return;
     uint32_t tot[DPT], sum = 0;
 #pragma unroll
@@ -175,6 +178,7 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
     constexpr int DPT = (RADIX + TPB - 1) / TPB;  // digits per thread (contiguous)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     ScatterSmem<KeyT, BITS> &s = *reinterpret_cast<ScatterSmem<KeyT, BITS> *>(smem_raw);
+    gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
     const int64_t base = (int64_t)blockIdx.x * SUB;
     if (n < 0 || base >= n) return;
@@ -305,15 +309,13 @@ inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, con
         }
         attr_set = true;
     }
-    hist_kernel<KeyT, BITS><<<nb, TPB, 0, st>>>(n_cap, n_dev, kin, shift, bits, mat, nb);
-    GS_LAUNCH_CHECK();
-    colscan_kernel<BITS><<<(RADIX + WARPS - 1) / WARPS, TPB, 0, st>>>(n_cap, n_dev, mat, nb, totals, nullptr, 0);
-    GS_LAUNCH_CHECK();
-    digit_base_kernel<BITS><<<1, TPB, 0, st>>>(n_cap, n_dev, totals, digit_base, bins_out, bins_T);
-    GS_LAUNCH_CHECK();
-    scatter_kernel<KeyT, BITS><<<nb, TPB, smem, st>>>(n_cap, n_dev, kin, vin, kout, vout, shift, bits, mat, nb,
-                                                      digit_base);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH((hist_kernel<KeyT, BITS>), nb, TPB, 0, st, n_cap, n_dev, kin, shift, bits, mat, nb);
+    GS_PDL_LAUNCH((colscan_kernel<BITS>), (RADIX + WARPS - 1) / WARPS, TPB, 0, st, n_cap, n_dev, mat, nb, totals,
+                  (int32_t *)nullptr, 0);
+    GS_PDL_LAUNCH((digit_base_kernel<BITS>), 1, TPB, 0, st, n_cap, n_dev, (const uint32_t *)totals, digit_base, bins_out,
+                  bins_T);
+    GS_PDL_LAUNCH((scatter_kernel<KeyT, BITS>), nb, TPB, smem, st, n_cap, n_dev, kin, vin, kout, vout, shift, bits,
+                  (const uint32_t *)mat, nb, (const uint32_t *)digit_base);
     return 0;
 }
 
