@@ -31,6 +31,7 @@ preprocess_bwd_kernel(int N, const float *__restrict__ means, const float *__res
     const int g0 = blockIdx.x * PB_TPB;
     const int rows = min(PB_TPB, N - g0);
     const int i = g0 + tid;
+    gs_pdl_sync();
 
     if (i < N) {
         float vm[3] = {0.f, 0.f, 0.f}, vls[3] = {0.f, 0.f, 0.f};
@@ -116,11 +117,10 @@ extern "C" int gs_preprocess_bwd(int N, const float *means, const float *log_sca
         (reinterpret_cast<uintptr_t>(v_xys) & 7u))
         return GS_ERR_MISALIGNED;
     const int blocks = (N + PB_TPB - 1) / PB_TPB;
-    preprocess_bwd_kernel<<<blocks, PB_TPB, 0, (cudaStream_t)stream>>>(
-        N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, *cam_host, radii,
-        rgbs, reinterpret_cast<const float2 *>(v_xys), v_conics, v_rgbs, v_opac, v_means, v_log_scales,
-        reinterpret_cast<float4 *>(v_quats), v_opac_logits, v_feat_dc, v_feat_rest);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(preprocess_bwd_kernel, blocks, PB_TPB, 0, (cudaStream_t)stream, N, means, log_scales,
+                  reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, *cam_host, radii, rgbs,
+                  reinterpret_cast<const float2 *>(v_xys), v_conics, v_rgbs, v_opac, v_means, v_log_scales,
+                  reinterpret_cast<float4 *>(v_quats), v_opac_logits, v_feat_dc, v_feat_rest);
     return 0;
 }
 
@@ -264,6 +264,7 @@ __global__ void __launch_bounds__(256)
 finish_view_block_kernel(int N, int use_sh, const float *__restrict__ rgbs, float *__restrict__ v_rgbs,
                          const __grid_constant__ GsCamera cam, float *__restrict__ cam_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    gs_pdl_sync();
     if (blockIdx.x == 0 && threadIdx.x < (int)(sizeof(GsCamera) / 4))
         cam_out[threadIdx.x] = reinterpret_cast<const float *>(&cam)[threadIdx.x];
     if (i >= 3 * N) return;
@@ -281,9 +282,8 @@ extern "C" int gs_finish_view_block(int N, int use_sh, const GsCamera *cam_host,
     static_assert(sizeof(GsCamera) <= 64 * 4, "camera must fit the 64-float tail of a view block");
     const int Np = (N + 3) / 4 * 4;
     const int blocks = (3 * N + 255) / 256;
-    finish_view_block_kernel<<<blocks > 0 ? blocks : 1, 256, 0, (cudaStream_t)stream>>>(
-        N, use_sh, rgbs, block + (size_t)5 * Np, *cam_host, block + (size_t)9 * Np);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(finish_view_block_kernel, blocks > 0 ? blocks : 1, 256, 0, (cudaStream_t)stream, N, use_sh, rgbs,
+                  block + (size_t)5 * Np, *cam_host, block + (size_t)9 * Np);
     return 0;
 }
 

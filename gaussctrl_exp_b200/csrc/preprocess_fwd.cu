@@ -28,6 +28,7 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
                       const __grid_constant__ GsCamera cam, float2 *__restrict__ xys, float *__restrict__ depths,
                       int32_t *__restrict__ radii, float *__restrict__ conics, int32_t *__restrict__ tiles_hit,
                       float *__restrict__ rgbs, float *__restrict__ opac) {
+    gs_pdl_sync();   // lets the first binning kernel become resident while this one drains
     __shared__ __align__(128) float rest_s[PP_TPB * PP_REST];
     __shared__ __align__(8) unsigned long long mbar;
     const int tid = threadIdx.x;

@@ -75,6 +75,7 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     __shared__ unsigned char wlist[8][RB_BATCH];
     __shared__ int s_wmax[8];
 
+    gs_pdl_sync();
     const int tile = tile_order ? tile_order[blockIdx.x] : blockIdx.x;   // heaviest tiles first
     const int tile_x = tile % tiles_x, tile_y = tile / tiles_x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -379,11 +380,9 @@ extern "C" int gs_raster_bwd_ordered_post(int H, int W, int tiles_x, int tiles_y
         !v_conics || !v_colors || !v_opac)
         return GS_ERR_BAD_ARG;
     if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
-    raster_bwd3_kernel<<<tiles_x * tiles_y, 256, 0, (cudaStream_t)stream>>>(
-        H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys),
-        conics, colors, opac, bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order,
-        clamp_ref);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(raster_bwd3_kernel, tiles_x * tiles_y, 256, 0, (cudaStream_t)stream, H, W, tiles_x, ids_sorted,
+                  reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys), conics, colors, opac,
+                  bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref);
     return 0;
 }
 

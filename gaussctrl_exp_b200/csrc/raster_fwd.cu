@@ -37,6 +37,7 @@ raster_fwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     __shared__ StageRGB st[2];
     __shared__ unsigned char wlist[8][RF_BATCH];   // per-warp compacted survivors of the current batch
     __shared__ int s_work;
+    gs_pdl_sync();
     // heaviest tiles first (LPT): CTAs are dispatched in blockIdx order, so a descending-work permutation
     // keeps the long tiles out of the tail of the launch
     const int tile = tile_order ? tile_order[blockIdx.x] : blockIdx.x;
@@ -282,6 +283,7 @@ tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, in
     // one warp per tile: rank = number of tiles with more work (ties: lower tile id first)
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
+    gs_pdl_sync();
     if (t >= T) return;
     auto load = [&](int u) { return work_is_range ? work[2 * u + 1] - work[2 * u] : work[u]; };
     const int mine = load(t);
@@ -298,8 +300,7 @@ tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, in
 
 extern "C" int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream) {
     if (T <= 0 || !work || !order) return GS_ERR_BAD_ARG;
-    tile_order_kernel<<<(T * 32 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(T, work, work_is_range, order);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(tile_order_kernel, (T * 32 + 255) / 256, 256, 0, (cudaStream_t)stream, T, work, work_is_range, order);
     return 0;
 }
 
@@ -318,14 +319,13 @@ extern "C" int gs_raster_fwd_ordered_post(int H, int W, int tiles_x, int tiles_y
     const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
     const float2 *xy2 = reinterpret_cast<const float2 *>(xys);
     if (depths)
-        raster_fwd3_kernel<true><<<tiles_x * tiles_y, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors,
-                                                                    opac, depths, bg, out_img, out_depth, final_T,
-                                                                    final_idx, tile_order, tile_work, out_clamped, out_alpha);
+        GS_PDL_LAUNCH((raster_fwd3_kernel<true>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
+                      conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx, tile_order, tile_work,
+                      out_clamped, out_alpha);
     else
-        raster_fwd3_kernel<false><<<tiles_x * tiles_y, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors,
-                                                                     opac, nullptr, bg, out_img, nullptr, final_T,
-                                                                     final_idx, tile_order, tile_work, out_clamped, out_alpha);
-    GS_LAUNCH_CHECK();
+        GS_PDL_LAUNCH((raster_fwd3_kernel<false>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
+                      conics, colors, opac, (const float *)nullptr, bg, out_img, (float *)nullptr, final_T, final_idx,
+                      tile_order, tile_work, out_clamped, out_alpha);
     return 0;
 }
 

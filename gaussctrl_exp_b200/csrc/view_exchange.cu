@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(256)
 vx_bitmap_kernel(int N, int Np, const float *__restrict__ blk, uint32_t *__restrict__ bitmap,
                  int32_t *__restrict__ wcount) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    gs_pdl_sync();
     bool nz = false;
     if (i < N) {
         const float2 xy = reinterpret_cast<const float2 *>(blk)[i];
@@ -50,6 +51,7 @@ __global__ void __launch_bounds__(256)
 vx_pack_kernel(int N, int Np, int Wp, const float *__restrict__ blk, const uint32_t *__restrict__ bitmap,
                const int32_t *__restrict__ prefix, float *__restrict__ xbuf) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    gs_pdl_sync();
     if (blockIdx.x == 0 && threadIdx.x < 64) xbuf[(size_t)2 * Wp + threadIdx.x] = blk[(size_t)9 * Np + threadIdx.x];
     if ((threadIdx.x & 31) == 0 && (i >> 5) < Wp)      // one 8-byte {bitmap word, prefix} record per 32 Gaussians
         reinterpret_cast<uint2 *>(xbuf)[i >> 5] = make_uint2(bitmap[i >> 5], (uint32_t)prefix[i >> 5]);
@@ -78,6 +80,7 @@ __global__ void __launch_bounds__(VX_PUSH_TPB)
 vx_push_kernel(int Np, int Wp, int D, int self, const float4 *__restrict__ src,
                const unsigned long long *__restrict__ peer_ptrs, size_t peer_off) {
     __shared__ float4 *dst_s[VX_MAX_VIEWS];
+    gs_pdl_sync();
     if (threadIdx.x < D) dst_s[threadIdx.x] = reinterpret_cast<float4 *>(reinterpret_cast<float *>(peer_ptrs[threadIdx.x]) + peer_off);
     __syncthreads();
     const uint2 last = reinterpret_cast<const uint2 *>(src)[Wp - 1];
@@ -462,12 +465,11 @@ extern "C" int gs_pack_view_block(int N, const float *block, float *xbuf, void *
     int32_t *prefix = reinterpret_cast<int32_t *>(p + 2 * w4);
     void *scan_scratch = p + 3 * w4;
     const int threads_total = Wp * 32;
-    vx_bitmap_kernel<<<(threads_total + 255) / 256, 256, 0, st>>>(N, Np, block, bitmap, wcount);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(vx_bitmap_kernel, (threads_total + 255) / 256, 256, 0, st, N, Np, block, bitmap, wcount);
     const int rc = gs_internal_exclusive_scan(Wp, wcount, prefix, nullptr, scan_scratch, scratch_bytes - 3 * w4, st);
     if (rc) return rc;
-    vx_pack_kernel<<<(threads_total + 255) / 256, 256, 0, st>>>(N, Np, Wp, block, bitmap, prefix, xbuf);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(vx_pack_kernel, (threads_total + 255) / 256, 256, 0, st, N, Np, Wp, block, (const uint32_t *)bitmap,
+                  (const int32_t *)prefix, xbuf);
     return 0;
 }
 
@@ -482,10 +484,9 @@ extern "C" int gs_pack_view_block_push(int N, const float *block, float *xbuf_se
     const int rc = gs_pack_view_block(N, block, xbuf_self, scratch, scratch_bytes, stream);
     if (rc || n_peers == 1) return rc;
     const int Np = (N + 3) / 4 * 4;
-    vx_push_kernel<<<148 * 4, VX_PUSH_TPB, 0, (cudaStream_t)stream>>>(
-        Np, vx_words(N), n_peers, self, reinterpret_cast<const float4 *>(xbuf_self),
-        reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats);
-    GS_LAUNCH_CHECK();
+    GS_PDL_LAUNCH(vx_push_kernel, 148 * 4, VX_PUSH_TPB, 0, (cudaStream_t)stream, Np, vx_words(N), n_peers, self,
+                  reinterpret_cast<const float4 *>(xbuf_self),
+                  reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats);
     return 0;
 }
 
