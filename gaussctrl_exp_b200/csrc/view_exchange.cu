@@ -465,7 +465,8 @@ extern "C" int gs_pack_view_block(int N, const float *block, float *xbuf, void *
     int32_t *prefix = reinterpret_cast<int32_t *>(p + 2 * w4);
     void *scan_scratch = p + 3 * w4;
     const int threads_total = Wp * 32;
-    GS_PDL_LAUNCH(vx_bitmap_kernel, (threads_total + 255) / 256, 256, 0, st, N, Np, block, bitmap, wcount);
+    vx_bitmap_kernel<<<(threads_total + 255) / 256, 256, 0, st>>>(N, Np, block, bitmap, wcount);
+    GS_LAUNCH_CHECK();
     const int rc = gs_internal_exclusive_scan(Wp, wcount, prefix, nullptr, scan_scratch, scratch_bytes - 3 * w4, st);
     if (rc) return rc;
     GS_PDL_LAUNCH(vx_pack_kernel, (threads_total + 255) / 256, 256, 0, st, N, Np, Wp, block, (const uint32_t *)bitmap,
