@@ -28,6 +28,8 @@ SIGNATURES = {
     "gs_project_bwd": (_i, [_i, _vp, _vp, _f, _vp, _vp, _vp, _f, _f, _i, _i, _vp, _vp, _vp, _vp,
                             _vp, _vp, _vp, _vp]),
     "gs_preprocess_fwd": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_preprocess_fwd_part": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                    _vp, _vp]),
     "gs_preprocess_bwd": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                _vp, _vp, _vp, _vp, _vp]),
     "gs_view_block_floats": (_i, [_i]),

@@ -21,6 +21,10 @@ constexpr int PP_REST = 45;  // floats of features_rest per Gaussian (15 bases x
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
+// PART 0: everything. PART 1: geometry only (projection + opacity; the binning chain depends on nothing else).
+// PART 2: colour only (reads the radii PART 1 wrote) — the host runs it on a second stream underneath the
+// latency-bound binning kernels, which takes the 216 B/Gaussian SH traffic off the critical path.
+template <int PART>
 __global__ void __launch_bounds__(PP_TPB)
 preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__restrict__ log_scales,
                       const float4 *__restrict__ quats, const float *__restrict__ opac_logits,
@@ -34,7 +38,7 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
     const int tid = threadIdx.x;
     const int g0 = blockIdx.x * PP_TPB;
     const int rows = min(PP_TPB, N - g0);
-    const bool need_rest = use_sh && deg >= 1;
+    const bool need_rest = PART != 1 && use_sh && deg >= 1;
 
     if (need_rest) {
         const int rows4 = rows & ~3;                      // 4 rows = 720 B: keeps the bulk size a multiple of 16
@@ -59,7 +63,12 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
     float p0 = 0.f, p1 = 0.f, p2 = 0.f;
     ProjOut o;
     o.radius = 0;
-    if (i < N) {
+    if (PART == 2) {
+        if (i < N) {
+            p0 = means[3 * i]; p1 = means[3 * i + 1]; p2 = means[3 * i + 2];
+            o.radius = radii[i];
+        }
+    } else if (i < N) {
         p0 = means[3 * i]; p1 = means[3 * i + 1]; p2 = means[3 * i + 2];
         const float s0 = expf(log_scales[3 * i]), s1 = expf(log_scales[3 * i + 1]), s2 = expf(log_scales[3 * i + 2]);
         float4 q = quats[i];
@@ -85,7 +94,7 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
                 : "r"(smem_u32(&mbar))
                 : "memory");
     }
-    if (i >= N) return;
+    if (i >= N || PART == 1) return;
 
     float r = 0.f, g = 0.f, b = 0.f;
     if (o.radius > 0) {      // culled Gaussians never reach the compositor: colour left at 0
@@ -117,6 +126,23 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
 
 }  // namespace
 
+static int launch_preprocess_fwd(int part, int N, const float *means, const float *log_scales, const float *quats,
+                                 const float *opac_logits, const float *feat_dc, const float *feat_rest, int use_sh,
+                                 int sh_deg, const GsCamera *cam_host, float *xys, float *depths, int32_t *radii,
+                                 float *conics, int32_t *tiles_hit, float *rgbs, float *opac, void *stream) {
+    const int blocks = (N + PP_TPB - 1) / PP_TPB;
+    cudaStream_t st = (cudaStream_t)stream;
+#define GS_PP_ARGS                                                                                                       \
+    N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, feat_dc, feat_rest, use_sh, sh_deg,       \
+        *cam_host, reinterpret_cast<float2 *>(xys), depths, radii, conics, tiles_hit, rgbs, opac
+    if (part == 0) preprocess_fwd_kernel<0><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
+    else if (part == 1) preprocess_fwd_kernel<1><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
+    else preprocess_fwd_kernel<2><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
+#undef GS_PP_ARGS
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int gs_preprocess_fwd(int N, const float *means, const float *log_scales, const float *quats,
                                  const float *opac_logits, const float *feat_dc, const float *feat_rest,
                                  int use_sh, int sh_deg, const GsCamera *cam_host,
@@ -132,10 +158,28 @@ extern "C" int gs_preprocess_fwd(int N, const float *means, const float *log_sca
     if (use_sh && sh_deg >= 1 && !feat_rest) return GS_ERR_BAD_ARG;
     if (!gs_aligned16(quats) || !gs_aligned16(feat_rest) || (reinterpret_cast<uintptr_t>(xys) & 7u))
         return GS_ERR_MISALIGNED;
-    const int blocks = (N + PP_TPB - 1) / PP_TPB;
-    preprocess_fwd_kernel<<<blocks, PP_TPB, 0, (cudaStream_t)stream>>>(
-        N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
-        *cam_host, reinterpret_cast<float2 *>(xys), depths, radii, conics, tiles_hit, rgbs, opac);
-    GS_LAUNCH_CHECK();
-    return 0;
+    return launch_preprocess_fwd(0, N, means, log_scales, quats, opac_logits, feat_dc, feat_rest, use_sh, sh_deg, cam_host,
+                                 xys, depths, radii, conics, tiles_hit, rgbs, opac, stream);
+}
+
+extern "C" int gs_preprocess_fwd_part(int part, int N, const float *means, const float *log_scales, const float *quats,
+                                      const float *opac_logits, const float *feat_dc, const float *feat_rest,
+                                      int use_sh, int sh_deg, const GsCamera *cam_host, float *xys, float *depths,
+                                      int32_t *radii, float *conics, int32_t *tiles_hit, float *rgbs, float *opac,
+                                      void *stream) {
+    if (part != 1 && part != 2) return GS_ERR_BAD_ARG;
+    if (N < 0 || !cam_host) return GS_ERR_BAD_ARG;
+    if (sh_deg < 0 || sh_deg > 3) return GS_ERR_UNSUPPORTED;
+    if (cam_host->H <= 0 || cam_host->W <= 0 || cam_host->tiles_x <= 0 || cam_host->tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (N == 0) return 0;
+    if (part == 1 && (!means || !log_scales || !quats || !opac_logits || !xys || !depths || !radii || !conics ||
+                      !tiles_hit || !opac))
+        return GS_ERR_BAD_ARG;
+    if (part == 2 && (!means || !feat_dc || !radii || !rgbs || (use_sh && sh_deg >= 1 && !feat_rest)))
+        return GS_ERR_BAD_ARG;
+    if ((part == 1 && (!gs_aligned16(quats) || (reinterpret_cast<uintptr_t>(xys) & 7u))) ||
+        (part == 2 && !gs_aligned16(feat_rest)))
+        return GS_ERR_MISALIGNED;
+    return launch_preprocess_fwd(part, N, means, log_scales, quats, opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
+                                 cam_host, xys, depths, radii, conics, tiles_hit, rgbs, opac, stream);
 }

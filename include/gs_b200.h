@@ -95,6 +95,14 @@ int gs_preprocess_fwd(int N, const float *means, const float *log_scales, const 
                       int use_sh, int sh_deg, const GsCamera *cam_host,
                       float *xys, float *depths, int32_t *radii, float *conics, int32_t *tiles_hit,
                       float *rgbs, float *opac, void *stream);
+/* The same kernel in two parts: part 1 = geometry (projection + opacity: xys, depths, radii, conics, tiles_hit,
+ * opac — all the binning needs), part 2 = colour (rgbs; reads the radii part 1 wrote). Results are bit-identical to
+ * gs_preprocess_fwd. The host enqueues part 2 on a second stream so that its 216 B/Gaussian of SH traffic runs
+ * underneath the latency-bound binning chain. Pointers a part does not use may be NULL. */
+int gs_preprocess_fwd_part(int part, int N, const float *means, const float *log_scales, const float *quats,
+                           const float *opac_logits, const float *feat_dc, const float *feat_rest, int use_sh,
+                           int sh_deg, const GsCamera *cam_host, float *xys, float *depths, int32_t *radii,
+                           float *conics, int32_t *tiles_hit, float *rgbs, float *opac, void *stream);
 /* exact vjp of gs_preprocess_fwd: compositor gradients -> the six leaf gradients (all fully
  * written; culled Gaussians get zeros). rgbs = the forward's colour output (activation masks). */
 int gs_preprocess_bwd(int N, const float *means, const float *log_scales, const float *quats,

@@ -290,6 +290,20 @@ def test_fused_preprocess_matches_operator_chain(oracle, cuda_dev, N, W, H, deg,
         assert rel_linf(o[k].cpu().numpy()[m], ref.detach().cpu().numpy()[m]) < 1e-5, k
     assert rel_linf(o["rgbs"].cpu().numpy()[m], rgbs.detach().cpu().numpy()[m]) < 2e-5
     assert (o["rgbs"][~(o["radii"] > 0)] == 0).all()
+    # the two-part form of the same kernel (geometry, then colour from the stored radii) is bit-identical
+    o2 = {k: torch.full_like(v, 7) for k, v in o.items()}
+    for part in (1, 2):
+        rc = L.gs_preprocess_fwd_part(part, N, p["means"].data_ptr(), p["scales"].data_ptr(), p["quats"].data_ptr(),
+                                      p["opacities"].data_ptr(), p["features_dc"].data_ptr(),
+                                      p["features_rest"].data_ptr(), int(use_sh), deg, ctypes.addressof(gc),
+                                      o2["xys"].data_ptr(), o2["depths"].data_ptr(), o2["radii"].data_ptr(),
+                                      o2["conics"].data_ptr(), o2["hit"].data_ptr(), o2["rgbs"].data_ptr(),
+                                      o2["opac"].data_ptr(), _lib.stream_ptr())
+        assert rc == 0
+        if part == 1:
+            assert (o2["rgbs"] == 7).all()
+    for k in o:
+        assert torch.equal(o[k], o2[k]), k
 
     g = torch.Generator().manual_seed(3)
     v_xys = torch.randn(N, 2, generator=g).to(dev) * vis[:, None]
