@@ -54,6 +54,7 @@ SIGNATURES = {
     "gs_bin_edges": (_i, [_i64, _i, _vp, _vp, _vp]),
     "gs_bin_fast_scratch_bytes": (_sz, [_i, _i64, _i]),
     "gs_bin_fast": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gs_set_depth_sort_passes": (_i, [_i]),
     "gs_bin_tile_scratch_bytes": (_sz, [_i, _i64, _i]),
     "gs_bin_tile": (_i, [_i, _i64, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gs_raster_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -2,6 +2,7 @@
 // before compositing (torch.cumsum + map_gaussian_to_intersects + torch.sort +
 // get_tile_bin_edges), reached from /root/reference/gaussctrl/gc_model.py:208 and :225.
 // Integer work, bit-exact against the oracle. HBM/L2-bound.
+#include <stdlib.h>
 #include "radix.cuh"
 
 namespace {
@@ -273,7 +274,7 @@ extern "C" int gs_bin_edges(int64_t I, int T, const int64_t *keys_sorted, int32_
 // ==========================================================================================
 // Traffic-lean binning (gs_bin_fast): same ids_sorted / tile_bins as scan + emit + 64-bit sort +
 // edges, without ever materialising 64-bit keys (SURVEY.md §7 "sort bandwidth"):
-//   1. stable radix sort of the N Gaussians by depth bits (32-bit keys, passes over N, not I)
+//   1. stable radix sort of the N Gaussians by depth bits (32-bit keys, three passes over N, not I)
 //   2. exclusive scan of tiles_hit in that order (single-pass look-back, gathered input)
 //   3. emission of (tile id, Gaussian id) in that order
 //   4. ONE stable partition by tile id (<= 2048 tiles: a single pass over I)
@@ -283,14 +284,6 @@ extern "C" int gs_bin_edges(int64_t I, int T, const int64_t *keys_sorted, int32_
 // leaves the device: steps 3-5 read it from total_dev and are launched for the capacity.
 // ==========================================================================================
 namespace {
-
-__global__ void __launch_bounds__(256)
-depth_keys_kernel(int N, const float *__restrict__ depths, const int32_t *__restrict__ radii,
-                  uint32_t *__restrict__ keys) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    gs_pdl_sync();
-    if (i < N) keys[i] = radii[i] > 0 ? __float_as_uint(depths[i]) : 0xFFFFFFFFu;   // culled: to the end
-}
 
 __global__ void __launch_bounds__(256)
 emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ order,
@@ -359,11 +352,22 @@ FastLayout fast_layout(int N, int64_t I_cap) {
     const size_t n4 = (size_t)(N > 0 ? N : 1) * 4, i4 = (size_t)(I_cap > 0 ? I_cap : 1) * 4;
     L.keyA = take(n4); L.valA = take(n4); L.keyB = take(n4); L.valB = take(n4); L.start = take(n4);
     L.tkey = take(i4); L.tval = take(i4); L.tkey2 = take(i4); L.tval2 = take(i4);
-    const size_t m = gsradix::mat_entries(N, 256), mi = gsradix::mat_entries(I_cap, 2048);
+    const size_t m = gsradix::mat_entries(N, 2048), mi = gsradix::mat_entries(I_cap, 2048);
     L.mat = take((m > mi ? m : mi) * 4);
     L.ctl = take(gs_scan_scratch_bytes(N));
     L.total = at;
     return L;
+}
+
+// number of LSD passes of the depth sort (4 = 8-bit digits, default; 3 = 11/11/10-bit digits, measured slower:
+// 191 vs 169 us for the chain at 1 M Gaussians — 80 KB of shared memory per scatter CTA); initial value from the
+// environment (GS_DEPTH_SORT_PASSES), changed at run time by gs_set_depth_sort_passes (tests compare both)
+int &depth_sort_passes() {
+    static int passes = [] {
+        const char *e = getenv("GS_DEPTH_SORT_PASSES");
+        return (e && e[0] == '3') ? 3 : 4;
+    }();
+    return passes;
 }
 
 template <int BITS>
@@ -374,6 +378,12 @@ int partition_pass(int64_t I_cap, const int32_t *total_dev, const uint32_t *kin,
 }
 
 }  // namespace
+
+extern "C" int gs_set_depth_sort_passes(int passes) {
+    const int prev = depth_sort_passes();
+    if (passes == 3 || passes == 4) depth_sort_passes() = passes;
+    return prev;
+}
 
 extern "C" size_t gs_bin_fast_scratch_bytes(int N, int64_t I_cap, int T) {
     (void)T;
@@ -415,13 +425,28 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
     // the scan's look-back state is cleared up front so that the kernel chain below is uninterrupted (every launch
     // is a programmatic dependent launch: the next kernel is resident before the previous one drains)
     GS_CUDA(cudaMemsetAsync(ctl, 0, gs_scan_scratch_bytes(N), st));
-    // 1. depth sort: A -> B -> A -> B -> A (values start as the element index)
-    GS_PDL_LAUNCH(depth_keys_kernel, nblk, 256, 0, st, N, depths, radii, keyA);
-    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyA, nullptr, keyB, valB, 0, 8, mat, st))) return rc;
-    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyB, valB, keyA, valA, 8, 8, mat, st))) return rc;
-    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyA, valA, keyB, valB, 16, 8, mat, st))) return rc;
-    if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyB, valB, keyA, valA, 24, 8, mat, st))) return rc;
-    const uint32_t *order = valA;
+    // 1. depth sort (values start as the element index; the first pass forms its keys from depths/radii on the fly,
+    //    so there is no key-building kernel). Default: four passes of 8-bit digits; gs_set_depth_sort_passes(3) /
+    //    GS_DEPTH_SORT_PASSES=3 selects three passes of 11/11/10-bit digits (fewer launches, but measured slower).
+    //    Any split of the 32 bits into stable LSD passes yields the same order.
+    const uint32_t *dkeys = reinterpret_cast<const uint32_t *>(depths);
+    const uint32_t *order;
+    if (depth_sort_passes() == 4) {
+        if ((rc = gsradix::launch_pass<uint32_t, 8, true>(N, nullptr, dkeys, nullptr, keyB, valB, 0, 8, mat, st, nullptr, 0,
+                                                         radii))) return rc;
+        if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyB, valB, keyA, valA, 8, 8, mat, st))) return rc;
+        if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyA, valA, keyB, valB, 16, 8, mat, st))) return rc;
+        if ((rc = gsradix::launch_pass<uint32_t, 8>(N, nullptr, keyB, valB, (uint32_t *)nullptr, valA, 24, 8, mat, st)))
+            return rc;
+        order = valA;
+    } else {
+        if ((rc = gsradix::launch_pass<uint32_t, 11, true>(N, nullptr, dkeys, nullptr, keyB, valB, 0, 11, mat, st, nullptr,
+                                                          0, radii))) return rc;
+        if ((rc = gsradix::launch_pass<uint32_t, 11>(N, nullptr, keyB, valB, keyA, valA, 11, 11, mat, st))) return rc;
+        if ((rc = gsradix::launch_pass<uint32_t, 11>(N, nullptr, keyA, valA, (uint32_t *)nullptr, valB, 22, 10, mat, st)))
+            return rc;
+        order = valB;
+    }
 
     // 2. exclusive scan of tiles_hit in depth order; total -> total_dev
     GS_PDL_LAUNCH(scan_kernel, (N + SCAN_TILE - 1) / SCAN_TILE, SCAN_TPB, 0, st, N, tiles_hit, order, 1, start, total_dev,

@@ -1,8 +1,10 @@
 // Stable LSD radix-sort building blocks (keys + 32-bit values), one pass = three small kernels:
-//     hist    : CTA b histograms its 2048-key chunk                  -> mat[digit][b]
-//     colscan : one warp per digit scans its column over the CTAs    -> mat (exclusive), totals[digit]
-//     scatter : CTA b ranks its chunk (warp match-any, stable), stages it in shared memory in
-//               digit order and writes coalesced runs at  digit_base + mat[b][digit] + local rank
+//     hist    : CTA b histograms its 4096-key chunk                  -> mat[digit][b]
+//     colscan : one warp per digit scans its row over the CTAs       -> mat (exclusive), totals[digit]
+//     scatter : CTA b scans the digit totals itself (digit base), ranks its chunk (ballot matching,
+//               stable), stages it in shared memory in digit order and writes coalesced runs at
+//               digit_base + mat[digit][b] + local rank
+// FROM_DEPTH passes read their keys straight from (depths, radii): key = bits(depth), culled -> 0xFFFFFFFF.
 //
 // Design for B200: at the sizes of this path (N ~ 1 M Gaussians, I ~ 3 M intersections) the whole
 // working set sits in the 126 MB L2, so a pass is bound by latency and launch count, not HBM.
@@ -28,6 +30,18 @@ __device__ __forceinline__ int64_t resolve_n(int64_t n_cap, const int32_t *n_dev
     if (!n_dev) return n_cap;
     const int64_t v = *n_dev;
     return v > n_cap ? -1 : v;
+}
+
+// key of element `at`: the key array, or (FROM_DEPTH) the depth bits of a visible Gaussian / 0xFFFFFFFF for a
+// culled one (sorts behind every visible Gaussian), so that no separate key-building kernel is needed
+template <typename KeyT, bool FROM_DEPTH>
+__device__ __forceinline__ KeyT load_key(const KeyT *__restrict__ kin, const int32_t *__restrict__ radii, int64_t at) {
+    const KeyT k = kin[at];
+    if (FROM_DEPTH) {   // both loads unconditional (a load behind the radius test would serialise two round trips per key)
+        const int32_t r = radii[at];
+        return r > 0 ? k : (KeyT) ~(KeyT)0;
+    }
+    return k;
 }
 
 // block-wide exclusive scan of one value per thread (TPB threads). tmp: >= 64 uint32.
@@ -59,10 +73,10 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, u
 }
 
 // ---------------------------------------------------------------------------------------------
-template <typename KeyT, int BITS>
+template <typename KeyT, int BITS, bool FROM_DEPTH>
 __global__ void __launch_bounds__(TPB)
-hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin, int shift, int bits,
-            uint32_t *__restrict__ mat, int pitch) {
+hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
+            const int32_t *__restrict__ radii, int shift, int bits, uint32_t *__restrict__ mat, int pitch) {
     constexpr int RADIX = 1 << BITS;
     __shared__ uint32_t hist[RADIX];
     gs_pdl_sync();
@@ -76,7 +90,7 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
         const int64_t at = base + i * TPB + threadIdx.x;
-        key[i] = at < n ? kin[at] : (KeyT)0;
+        key[i] = at < n ? load_key<KeyT, FROM_DEPTH>(kin, radii, at) : (KeyT)0;
     }
 #pragma unroll
     for (int i = 0; i < IPT; ++i)
@@ -89,7 +103,7 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
 template <int BITS>
 __global__ void __launch_bounds__(TPB)
 colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat, int pitch,
-               uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T) {
+               uint32_t *__restrict__ totals) {
     constexpr int RADIX = 1 << BITS;
     gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
@@ -121,40 +135,6 @@ colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__res
         }
     }
     if (lane == 0) totals[d] = carry;
-    (void)bins_out; (void)bins_T;
-}
-
-// Exclusive scan of the digit totals -> digit_base[RADIX]; when the digit IS the tile id (single-pass
-// partition) the tile ranges fall out for free: bins[t] = [base, base + total) (0,0 for empty tiles).
-template <int BITS>
-__global__ void __launch_bounds__(TPB)
-digit_base_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const uint32_t *__restrict__ totals,
-                  uint32_t *__restrict__ digit_base, int32_t *__restrict__ bins_out, int bins_T) {
-    constexpr int RADIX = 1 << BITS;
-    constexpr int DPT = (RADIX + TPB - 1) / TPB;
-    __shared__ uint32_t tmp[64];
-    gs_pdl_sync();
-    if (resolve_n(n_cap, n_dev) < 0) return;
-    uint32_t tot[DPT], sum = 0;
-#pragma unroll
-    for (int j = 0; j < DPT; ++j) {
-        const int d = threadIdx.x * DPT + j;
-        tot[j] = d < RADIX ? totals[d] : 0u;
-        sum += tot[j];
-    }
-    uint32_t run = block_excl_scan(sum, tmp, nullptr);
-#pragma unroll
-    for (int j = 0; j < DPT; ++j) {
-        const int d = threadIdx.x * DPT + j;
-        if (d < RADIX) {
-            digit_base[d] = run;
-            if (bins_out && d < bins_T) {
-                bins_out[2 * d] = tot[j] ? (int32_t)run : 0;
-                bins_out[2 * d + 1] = tot[j] ? (int32_t)(run + tot[j]) : 0;
-            }
-        }
-        run += tot[j];
-    }
 }
 
 template <typename KeyT, int BITS>
@@ -169,11 +149,16 @@ struct ScatterSmem {
 };
 
 // vin == nullptr: value = element index. kout == nullptr: keys dropped.
-template <typename KeyT, int BITS>
+// Every CTA scans the RADIX digit totals itself (<= 8 KB out of L2 + one block scan) instead of waiting for a
+// one-CTA digit-base kernel between colscan and scatter: one launch less per pass. When the digit IS the tile id
+// (single-pass partition, bins_out != nullptr) the tile ranges fall out of the same scan: CTA 0 writes
+// bins[t] = [base, base + total) (0,0 for empty tiles).
+template <typename KeyT, int BITS, bool FROM_DEPTH>
 __global__ void __launch_bounds__(TPB)
 scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
-               const uint32_t *__restrict__ vin, KeyT *__restrict__ kout, uint32_t *__restrict__ vout, int shift,
-               int bits, const uint32_t *__restrict__ mat, int pitch, const uint32_t *__restrict__ digit_base) {
+               const int32_t *__restrict__ radii, const uint32_t *__restrict__ vin, KeyT *__restrict__ kout,
+               uint32_t *__restrict__ vout, int shift, int bits, const uint32_t *__restrict__ mat, int pitch,
+               const uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T) {
     constexpr int RADIX = 1 << BITS;
     constexpr int DPT = (RADIX + TPB - 1) / TPB;  // digits per thread (contiguous)
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -194,17 +179,33 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
         const int li = woff + i * 32 + lane;
-        key[i] = li < valid ? kin[base + li] : (KeyT) ~(KeyT)0;
+        key[i] = li < valid ? load_key<KeyT, FROM_DEPTH>(kin, radii, base + li) : (KeyT) ~(KeyT)0;
         val[i] = li < valid ? (vin ? vin[base + li] : (uint32_t)(base + li)) : 0u;
     }
-    // global cursors of this CTA: digit base + keys of the same digit in the CTAs below (mat is exclusive)
+    // global cursors of this CTA: digit base (exclusive scan of the digit totals) + keys of the same digit in the
+    // CTAs below (mat is exclusive)
     uint32_t cursor[DPT];
+    {
+        uint32_t tot[DPT], sum = 0;
 #pragma unroll
-    for (int j = 0; j < DPT; ++j) {
-        const int d = tid * DPT + j;
-        cursor[j] = d < RADIX ? digit_base[d] + mat[(size_t)d * pitch + blockIdx.x] : 0u;
+        for (int j = 0; j < DPT; ++j) {
+            const int d = tid * DPT + j;
+            tot[j] = d < RADIX ? totals[d] : 0u;
+            cursor[j] = d < RADIX ? mat[(size_t)d * pitch + blockIdx.x] : 0u;
+            sum += tot[j];
+        }
+        uint32_t run = block_excl_scan(sum, s.scan_tmp, nullptr);   // ends with a barrier: wc is zeroed after it
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) {
+            const int d = tid * DPT + j;
+            cursor[j] += run;
+            if (bins_out && blockIdx.x == 0 && d < bins_T) {
+                bins_out[2 * d] = tot[j] ? (int32_t)run : 0;
+                bins_out[2 * d + 1] = tot[j] ? (int32_t)(run + tot[j]) : 0;
+            }
+            run += tot[j];
+        }
     }
-    __syncthreads();   // wc zeroed
 
     // stable ranking inside each warp: the 8 match.any are independent and issue back to back; only the
     // counter read-modify-write chain is sequential
@@ -288,34 +289,32 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
     }
 }
 
-// host-side launcher of one pass. mat: RADIX * pitch + 2 * RADIX uint32 (pitch = ceil(n_cap/SUB); the tail
-// holds totals[RADIX] and digit_base[RADIX]). bins_out != nullptr: the digit is the tile id -> write tile ranges.
-template <typename KeyT, int BITS>
+// host-side launcher of one pass. mat: RADIX * pitch + RADIX uint32 (pitch = ceil(n_cap/SUB); the tail holds
+// totals[RADIX]). bins_out != nullptr: the digit is the tile id -> write tile ranges.
+// radii != nullptr (uint32 keys only): kin is the float depth array and the keys are formed on the fly.
+template <typename KeyT, int BITS, bool FROM_DEPTH = false>
 inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, const uint32_t *vin, KeyT *kout,
                        uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st,
-                       int32_t *bins_out = nullptr, int bins_T = 0) {
+                       int32_t *bins_out = nullptr, int bins_T = 0, const int32_t *radii = nullptr) {
     constexpr int RADIX = 1 << BITS;
     if (n_cap <= 0) return 0;
+    if (bits > BITS || (FROM_DEPTH && !radii)) return GS_ERR_BAD_ARG;
     const int nb = (int)((n_cap + SUB - 1) / SUB);
     uint32_t *totals = mat + (size_t)nb * RADIX;
-    uint32_t *digit_base = totals + RADIX;
     const size_t smem = sizeof(ScatterSmem<KeyT, BITS>);
     static bool attr_set = false;   // one per template instantiation
     if (!attr_set) {
         if (smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute((const void *)scatter_kernel<KeyT, BITS>,
+            cudaError_t e = cudaFuncSetAttribute((const void *)scatter_kernel<KeyT, BITS, FROM_DEPTH>,
                                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (e != cudaSuccess) return (int)e;
         }
         attr_set = true;
     }
-    GS_PDL_LAUNCH((hist_kernel<KeyT, BITS>), nb, TPB, 0, st, n_cap, n_dev, kin, shift, bits, mat, nb);
-    GS_PDL_LAUNCH((colscan_kernel<BITS>), (RADIX + WARPS - 1) / WARPS, TPB, 0, st, n_cap, n_dev, mat, nb, totals,
-                  (int32_t *)nullptr, 0);
-    GS_PDL_LAUNCH((digit_base_kernel<BITS>), 1, TPB, 0, st, n_cap, n_dev, (const uint32_t *)totals, digit_base, bins_out,
-                  bins_T);
-    GS_PDL_LAUNCH((scatter_kernel<KeyT, BITS>), nb, TPB, smem, st, n_cap, n_dev, kin, vin, kout, vout, shift, bits,
-                  (const uint32_t *)mat, nb, (const uint32_t *)digit_base);
+    GS_PDL_LAUNCH((hist_kernel<KeyT, BITS, FROM_DEPTH>), nb, TPB, 0, st, n_cap, n_dev, kin, radii, shift, bits, mat, nb);
+    GS_PDL_LAUNCH((colscan_kernel<BITS>), (RADIX + WARPS - 1) / WARPS, TPB, 0, st, n_cap, n_dev, mat, nb, totals);
+    GS_PDL_LAUNCH((scatter_kernel<KeyT, BITS, FROM_DEPTH>), nb, TPB, smem, st, n_cap, n_dev, kin, radii, vin, kout, vout,
+                  shift, bits, (const uint32_t *)mat, nb, (const uint32_t *)totals, bins_out, bins_T);
     return 0;
 }
 

@@ -278,14 +278,32 @@ extern "C" int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
 // Tile scheduling: rank tiles by descending work (ties by tile id). All-pairs counting in shared
 // memory: T <= a few thousand, so this is a few microseconds.
 namespace {
+constexpr int TO_SMEM_TILES = 8192;   // works staged in shared memory up to this many tiles (1080p: 8 160)
+
+// one warp per tile: rank = number of tiles with more work (ties: lower tile id first). Every CTA first stages
+// the whole work array in shared memory with independent, coalesced loads — ranking straight from global memory was a
+// serial chain of T/32 dependent L2 round trips per warp (7-8 us at T = 1024 for a few KB of data).
 __global__ void __launch_bounds__(256)
 tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, int32_t *__restrict__ order) {
-    // one warp per tile: rank = number of tiles with more work (ties: lower tile id first)
+    extern __shared__ int s_work[];
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     gs_pdl_sync();
+    const bool staged = T <= TO_SMEM_TILES;
+    if (staged) {
+        if (work_is_range) {
+            const int2 *r = reinterpret_cast<const int2 *>(work);
+            for (int u = threadIdx.x; u < T; u += 256) {
+                const int2 v = r[u];
+                s_work[u] = v.y - v.x;
+            }
+        } else {
+            for (int u = threadIdx.x; u < T; u += 256) s_work[u] = work[u];
+        }
+        __syncthreads();
+    }
     if (t >= T) return;
-    auto load = [&](int u) { return work_is_range ? work[2 * u + 1] - work[2 * u] : work[u]; };
+    auto load = [&](int u) { return staged ? s_work[u] : (work_is_range ? work[2 * u + 1] - work[2 * u] : work[u]); };
     const int mine = load(t);
     int rank = 0;
     for (int u = lane; u < T; u += 32) {
@@ -300,7 +318,8 @@ tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, in
 
 extern "C" int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream) {
     if (T <= 0 || !work || !order) return GS_ERR_BAD_ARG;
-    GS_PDL_LAUNCH(tile_order_kernel, (T * 32 + 255) / 256, 256, 0, (cudaStream_t)stream, T, work, work_is_range, order);
+    const size_t smem = T <= TO_SMEM_TILES ? (size_t)T * sizeof(int) : 0;
+    GS_PDL_LAUNCH(tile_order_kernel, (T * 32 + 255) / 256, 256, smem, (cudaStream_t)stream, T, work, work_is_range, order);
     return 0;
 }
 

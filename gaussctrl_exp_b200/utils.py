@@ -139,11 +139,16 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
                 rc = L.gs_bin_tile(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), tx, ty,
                                    _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
                                    scratch.numel(), _lib.stream_ptr())
-            else:                   # global depth sort + partition (gs_bin_fast)
-                scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")
-                rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
-                                   _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
-                                   scratch.numel(), _lib.stream_ptr())
+            else:                   # global depth sort + partition (gs_bin_fast); "lsd3": three 11/11/10-bit depth passes
+                prev = L.gs_set_depth_sort_passes(3) if impl == "lsd3" else None
+                try:
+                    scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")
+                    rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
+                                       _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
+                                       scratch.numel(), _lib.stream_ptr())
+                finally:
+                    if prev is not None:
+                        L.gs_set_depth_sort_passes(prev)
         _lib.check(rc, "gs_bin_tile/fast")
         I = int(total.item())
         if I <= cap:

@@ -186,10 +186,14 @@ int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, con
                 const int32_t *tiles_hit, int tiles_x, int tiles_y,
                 int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
                 void *scratch, size_t scratch_bytes, void *stream);
+/* Tuning knob of gs_bin_fast's depth sort: 4 (default; 8-bit digits, 12 launches) or 3 (11/11/10-bit digits, 9
+ * launches; measured slower) stable LSD passes — identical output. Returns the previous setting; other values only query.
+ * Initial value: environment variable GS_DEPTH_SORT_PASSES. */
+int gs_set_depth_sort_passes(int passes);
 
 /* Tile-local binning: same (ids_sorted, tile_bins, *total_dev) contract and overflow behaviour as
  * gs_bin_fast, built from count -> tile scan -> unordered scatter -> ONE CTA PER TILE sorting its segment by
- * depth in shared memory (ties by Gaussian id). 5 launches; the product path uses this one. */
+ * depth in shared memory (ties by Gaussian id). 5 launches; measured slower than gs_bin_fast, opt-in. */
 size_t gs_bin_tile_scratch_bytes(int N, int64_t I_cap, int T);
 int gs_bin_tile(int N, int64_t I_cap, const float *xys, const float *depths, const int32_t *radii,
                 int tiles_x, int tiles_y, int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,

@@ -92,7 +92,7 @@ def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
     assert np.array_equal(vs.cpu().numpy(), b.ids_sorted)
     assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
     # product paths: identical ids_sorted and tile ranges without 64-bit keys
-    for impl in ("tile", "lsd"):
+    for impl in ("tile", "lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         assert I2 == b.I, impl
         assert np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted), impl
@@ -117,7 +117,7 @@ def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
     b = oracle.bin_and_sort(xys, depths, radii, hit, tb)
     assert b.I == int(hit.sum()) and (b.tile_bins[:, 1] - b.tile_bins[:, 0]).max() > 50000
     t = [_t(a, cuda_dev) for a in (xys, depths, radii, hit)]
-    for impl in ("tile", "lsd"):
+    for impl in ("tile", "lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(*t, tb, impl=impl)
         assert I2 == b.I
         assert np.array_equal(bins2.cpu().numpy(), b.tile_bins), impl

@@ -4,12 +4,13 @@ import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__
 from gaussctrl_exp_b200 import scene
 from gaussctrl_exp_b200.model import GaussianModel
 dev=torch.device('cuda:0')
-m=GaussianModel(scene.make_scene(1000000,0),background_color=torch.tensor([0.1,0.2,0.3])).to(dev); m.train()
+NG=int(os.environ.get('NG','1000000'))
+m=GaussianModel(scene.make_scene(NG,0),background_color=torch.tensor([0.1,0.2,0.3])).to(dev); m.train()
 cams=scene.make_cameras(40,0); v=torch.randn(512,512,3,device=dev)/(512*512)
 params=list(m.parameters())
 def step(i):
     for p in params: p.grad=None
-    out=m(cams[i%40]); (out['rgb']*v).sum().backward()
+    out=m(cams[i%40]); out['rgb'].backward(v)
 for i in range(20): step(i)
 torch.cuda.synchronize()
 t=time.perf_counter()
