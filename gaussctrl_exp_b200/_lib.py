@@ -64,6 +64,8 @@ SIGNATURES = {
     "gs_raster_bwd_ordered": (_i, [_i, _i, _i, _i] + [_vp] * 17),
     "gs_raster_fwd_ordered_post": (_i, [_i, _i, _i, _i] + [_vp] * 17),
     "gs_raster_bwd_ordered_post": (_i, [_i, _i, _i, _i] + [_vp] * 18),
+    "gs_noise_mask_scratch_bytes": (_sz, [_i, _i]),
+    "gs_noise_mask": (_i, [_i, _vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _f, _vp, _sz, _vp, _vp]),
     "gs_raster_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                            _vp, _vp, _vp, _vp, _vp]),
 }

@@ -263,6 +263,19 @@ int gs_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y,
                   const float *v_out, const float *v_out_alpha,
                   float *v_xys, float *v_conics, float *v_colors, float *v_opac, void *stream);
 
+/* ---- multi-view noise mask ------------------------------------------------------------------
+ * Replaces MultiVeiwNoiseRenderer.render_noise_SS (/root/reference/gaussctrl/ad_render.py:273-333) and its GLSL
+ * shaders (:384-479): P instances (points (P,3), device) of a triangle mesh (verts (V,3) float, tris (F,3) int32,
+ * device; V <= 128) drawn with the row-major 4x4 `view` and `proj` matrices (HOST pointers, 16 floats each);
+ * a fragment is kept iff 0 <= depth[r][c] - |view-space fragment position| <= threshold (depth (H,W) device, clipped
+ * to [0, 1000]); no depth test, the last primitive in draw order wins; colour = (world position + 1) / 2.
+ * out_rgba (H,W,4) uint8 device = the image the reference returns (after its fliplr/flipud); untouched pixels are
+ * (0,0,0,0). scratch: gs_noise_mask_scratch_bytes(H, W) bytes, 8-byte aligned. Headless: no GL context or window. */
+size_t gs_noise_mask_scratch_bytes(int H, int W);
+int gs_noise_mask(int P, const float *points, int V, const float *verts, int F, const int32_t *tris,
+                  const float *view16_host, const float *proj16_host, int H, int W, const float *depth,
+                  float threshold, void *scratch, size_t scratch_bytes, uint8_t *out_rgba, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

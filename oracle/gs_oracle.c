@@ -584,3 +584,119 @@ void orc_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y, int N,
     }
     free(G);
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Multi-view noise mask — CPU restatement of /root/reference/gaussctrl/ad_render.py:273-333
+ * (render_noise_SS) and the GLSL shaders at :384-479, drawn in order on the CPU: instances in
+ * buffer order, triangles in index order, later fragments overwrite earlier ones (the reference
+ * never enables GL_DEPTH_TEST or blending). Coverage: pixel centres, window coordinates snapped
+ * to 1/256 px, exact integer edge functions, left/top tie rule. Everything else fp32 in the
+ * order written here (the build uses -ffp-contract=off). PARITY UNPINNED against a real GL
+ * implementation (no graphics stack on this box); see gs_oracle.h.
+ * view / proj: row-major 4x4. out_rgba (H,W,4) = the image render_noise_SS returns (after its
+ * fliplr / flipud); depth (H,W) is the image handed to depth_np2texture (:104-123).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+    int ix, iy, ok;
+    float invw, vx, vy, vz, cr, cg, cb;
+} orc_nm_vert;
+
+static unsigned orc_nm_u8(float c) {
+    c = fminf(fmaxf(c, 0.0f), 1.0f);
+    return (unsigned)floorf(c * 255.0f + 0.5f);
+}
+
+static int orc_nm_edge_in(long long e, int dx, int dy) {
+    return e > 0 || (e == 0 && (dy < 0 || (dy == 0 && dx < 0)));
+}
+
+static int orc_floor_div256(int v) { return v >= 0 ? v / 256 : -((-v + 255) / 256); }
+
+void orc_noise_mask(int P, const float *points, int V, const float *verts, int F, const int32_t *tris,
+                    const float *Vm, const float *Pm, int H, int W, const float *depth, float threshold,
+                    uint8_t *out_rgba) {
+    memset(out_rgba, 0, (size_t)H * W * 4);
+    orc_nm_vert *vs = (orc_nm_vert *)malloc(sizeof(orc_nm_vert) * (size_t)V);
+    for (int inst = 0; inst < P; ++inst) {
+        const float ox = points[3 * inst], oy = points[3 * inst + 1], oz = points[3 * inst + 2];
+        for (int k = 0; k < V; ++k) {
+            const float wx = verts[3 * k] + ox, wy = verts[3 * k + 1] + oy, wz = verts[3 * k + 2] + oz;
+            orc_nm_vert o;
+            o.vx = Vm[0] * wx + Vm[1] * wy + Vm[2] * wz + Vm[3];
+            o.vy = Vm[4] * wx + Vm[5] * wy + Vm[6] * wz + Vm[7];
+            o.vz = Vm[8] * wx + Vm[9] * wy + Vm[10] * wz + Vm[11];
+            const float cx = Pm[0] * o.vx + Pm[1] * o.vy + Pm[2] * o.vz + Pm[3];
+            const float cy = Pm[4] * o.vx + Pm[5] * o.vy + Pm[6] * o.vz + Pm[7];
+            const float cw = Pm[12] * o.vx + Pm[13] * o.vy + Pm[14] * o.vz + Pm[15];
+            o.cr = (wx + 1.0f) / 2.0f; o.cg = (wy + 1.0f) / 2.0f; o.cb = (wz + 1.0f) / 2.0f;
+            o.ok = 0; o.ix = o.iy = 0; o.invw = 0.f;
+            if (cw > 0.0f) {
+                o.invw = 1.0f / cw;
+                const float sx = (cx * o.invw * 0.5f + 0.5f) * (float)W;
+                const float sy = (cy * o.invw * 0.5f + 0.5f) * (float)H;
+                if (fabsf(sx) < 1.0e5f && fabsf(sy) < 1.0e5f) {
+                    o.ix = (int)floorf(sx * 256.0f + 0.5f);
+                    o.iy = (int)floorf(sy * 256.0f + 0.5f);
+                    o.ok = 1;
+                }
+            }
+            vs[k] = o;
+        }
+        for (int f = 0; f < F; ++f) {
+            int ia = tris[3 * f], ib = tris[3 * f + 1], ic = tris[3 * f + 2];
+            if (ia < 0 || ia >= V || ib < 0 || ib >= V || ic < 0 || ic >= V) continue;
+            if (!(vs[ia].ok && vs[ib].ok && vs[ic].ok)) continue;
+            long long area2 = (long long)(vs[ib].ix - vs[ia].ix) * (vs[ic].iy - vs[ia].iy) -
+                              (long long)(vs[ib].iy - vs[ia].iy) * (vs[ic].ix - vs[ia].ix);
+            if (area2 == 0) continue;
+            if (area2 < 0) { int t = ib; ib = ic; ic = t; area2 = -area2; }
+            const orc_nm_vert a = vs[ia], b = vs[ib], c = vs[ic];
+            int minx = a.ix < b.ix ? a.ix : b.ix, maxx = a.ix > b.ix ? a.ix : b.ix;
+            int miny = a.iy < b.iy ? a.iy : b.iy, maxy = a.iy > b.iy ? a.iy : b.iy;
+            if (c.ix < minx) minx = c.ix;
+            if (c.ix > maxx) maxx = c.ix;
+            if (c.iy < miny) miny = c.iy;
+            if (c.iy > maxy) maxy = c.iy;
+            int x0 = orc_floor_div256(minx - 128 + 255), x1 = orc_floor_div256(maxx - 128);
+            int y0 = orc_floor_div256(miny - 128 + 255), y1 = orc_floor_div256(maxy - 128);
+            if (x0 < 0) x0 = 0;
+            if (y0 < 0) y0 = 0;
+            if (x1 > W - 1) x1 = W - 1;
+            if (y1 > H - 1) y1 = H - 1;
+            const float farea = (float)area2;
+            for (int y = y0; y <= y1; ++y) {
+                const int py = y * 256 + 128;
+                for (int x = x0; x <= x1; ++x) {
+                    const int px = x * 256 + 128;
+                    const long long e_bc = (long long)(c.ix - b.ix) * (py - b.iy) - (long long)(c.iy - b.iy) * (px - b.ix);
+                    const long long e_ca = (long long)(a.ix - c.ix) * (py - c.iy) - (long long)(a.iy - c.iy) * (px - c.ix);
+                    const long long e_ab = (long long)(b.ix - a.ix) * (py - a.iy) - (long long)(b.iy - a.iy) * (px - a.ix);
+                    if (!orc_nm_edge_in(e_bc, c.ix - b.ix, c.iy - b.iy) || !orc_nm_edge_in(e_ca, a.ix - c.ix, a.iy - c.iy) ||
+                        !orc_nm_edge_in(e_ab, b.ix - a.ix, b.iy - a.iy))
+                        continue;
+                    const float la = ((float)e_bc / farea) * a.invw, lb = ((float)e_ca / farea) * b.invw,
+                                lc = ((float)e_ab / farea) * c.invw;
+                    const float ls = la + lb + lc;
+                    const float wa = la / ls, wb = lb / ls, wc = lc / ls;
+                    const float qx = wa * a.vx + wb * b.vx + wc * c.vx;
+                    const float qy = wa * a.vy + wb * b.vy + wc * c.vy;
+                    const float qz = wa * a.vz + wb * b.vz + wc * c.vz;
+                    const float zc = Pm[8] * qx + Pm[9] * qy + Pm[10] * qz + Pm[11];
+                    const float wc4 = Pm[12] * qx + Pm[13] * qy + Pm[14] * qz + Pm[15];
+                    if (zc < -wc4 || zc > wc4) continue;
+                    const float dfrag = sqrtf(qx * qx + qy * qy + qz * qz);
+                    const int r = H - 1 - y, cc = W - 1 - x;
+                    const float dtex = fminf(fmaxf(depth[(size_t)r * W + cc], 0.0f), 1000.0f);
+                    const float diff = dtex - dfrag;
+                    if (diff < 0.0f || diff > threshold) continue;
+                    uint8_t *o = out_rgba + ((size_t)r * W + cc) * 4;
+                    o[0] = (uint8_t)orc_nm_u8(wa * a.cr + wb * b.cr + wc * c.cr);
+                    o[1] = (uint8_t)orc_nm_u8(wa * a.cg + wb * b.cg + wc * c.cg);
+                    o[2] = (uint8_t)orc_nm_u8(wa * a.cb + wb * b.cb + wc * c.cb);
+                    o[3] = 255;
+                }
+            }
+        }
+    }
+    free(vs);
+}

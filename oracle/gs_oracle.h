@@ -75,6 +75,11 @@ void orc_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y, int N,
                     const float *v_out, const float *v_out_alpha /* may be NULL */,
                     float *v_xys, float *v_conics, float *v_colors, float *v_opac);
 
+/* Multi-view noise mask (ad_render.py:273-333 + shaders :384-479), drawn in order on the CPU. */
+void orc_noise_mask(int P, const float *points, int V, const float *verts, int F, const int32_t *tris,
+                    const float *view16, const float *proj16, int H, int W, const float *depth, float threshold,
+                    uint8_t *out_rgba /*H*W*4*/);
+
 int orc_num_threads(void);
 void orc_set_num_threads(int n);
 

@@ -295,3 +295,18 @@ def render_view_backward(params, ctx, v_rgb, v_alpha=None):
     vq64 = vq.astype(np.float64)
     g["quats"] = ((vq64 - qn * (qn * vq64).sum(-1, keepdims=True)) / nq).astype(np.float32)
     return g
+
+
+def noise_mask(points, verts, tris, view, proj, depth, threshold):
+    """orc_noise_mask: CPU restatement of ad_render.py:273-333 + shaders :384-479 (sequential draw order).
+    points (P,3), verts (V,3), tris (F,3) int32, view / proj 4x4 row-major, depth (H,W) -> (H,W,4) uint8."""
+    points, verts, depth = _f(points).reshape(-1, 3), _f(verts).reshape(-1, 3), _f(depth)
+    tris = np.ascontiguousarray(tris, np.int32).reshape(-1, 3)
+    Vm, Pm = _f(view).reshape(-1), _f(proj).reshape(-1)
+    assert Vm.size == 16 and Pm.size == 16 and depth.ndim == 2
+    H, W = depth.shape
+    out = np.zeros((H, W, 4), np.uint8)
+    lib().orc_noise_mask(C.c_int(points.shape[0]), _p(points), C.c_int(verts.shape[0]), _p(verts),
+                         C.c_int(tris.shape[0]), _p(tris), _p(Vm), _p(Pm), C.c_int(H), C.c_int(W), _p(depth),
+                         C.c_float(threshold), _p(out))
+    return out

@@ -7,6 +7,7 @@ only sees the committed .npz files.
    projection_matrix, projection_matrix_ogl) and executed unmodified. These are the only pieces of
    the hot path whose code is in the reference tree; they pin the caller-side
    matrix conventions.
+   (3. reference_postops.npz and 4. reference_noise_helpers.npz: see main().)
 2. oracle_small_scene.npz — a small seeded scene pushed through the CPU oracle (NOT
    reference-derived: gsplat is absent). It freezes the oracle's behaviour so later edits to the
    oracle or to the scene generator cannot drift silently.
@@ -75,6 +76,26 @@ def main():
     disp = env_p["depth2disparity_torch"](None, depth[:, :, 0][None])
     np.savez(os.path.join(HERE, "reference_postops.npz"), depth=depth.numpy(), mat_view=mat_view.numpy(), rays=rays,
              pts_world=pts.numpy(), disparity=disp.numpy(), rays_rect=env_p["compute_ray_directions"](resolution=(20, 12)))
+
+    # 4. reference_noise_helpers.npz — the numpy-only helpers of the noise-mask renderer, executed unmodified:
+    #    ad_noise.py:5-24 (create_sphere), :53-66 (generate_uniform_points_in_cube), ad_render.py:164-205
+    #    (extract_camera_parameters, compute_view_matrix_ogl). The GL draw itself cannot run here.
+    env_n = extract(os.path.join(REF, "ad_noise.py"), {"create_sphere", "generate_uniform_points_in_cube"}, {"np": np})
+    env_v = extract(os.path.join(REF, "ad_render.py"), {"extract_camera_parameters", "compute_view_matrix_ogl"}, {"np": np})
+    sv, si = env_n["create_sphere"](0.015, 8, 8)
+    sv2, si2 = env_n["create_sphere"](0.3, 5, 7)
+    cube = env_n["generate_uniform_points_in_cube"](2.0, 6)
+    gq = torch.Generator().manual_seed(11)
+    c2ws, views = [], []
+    for _ in range(3):
+        m = np.eye(4)
+        m[:3, :3] = torch.linalg.qr(torch.randn(3, 3, generator=gq))[0].numpy()
+        m[:3, 3] = torch.randn(3, generator=gq).numpy()
+        pos, up, fw = env_v["extract_camera_parameters"](m)
+        c2ws.append(m)
+        views.append(env_v["compute_view_matrix_ogl"](pos, up, fw))
+    np.savez(os.path.join(HERE, "reference_noise_helpers.npz"), sphere_v=sv, sphere_i=si, sphere2_v=sv2, sphere2_i=si2,
+             cube=cube, c2ws=np.stack(c2ws), views=np.stack(views))
 
     from oracle import oracle as orc
     from util import np_params, small_cam
