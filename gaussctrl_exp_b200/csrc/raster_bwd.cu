@@ -8,10 +8,12 @@
 //   (1) skipped outright when the splat's alpha >= 1/255 box misses the warp's 8x4 pixel rect
 //       (per-warp compacted survivor lists) or no lane of the warp hit it (warp ballot),
 //   (2) reduced across the warp with a halving butterfly (9 + 5 shuffles instead of 45),
-//   (3) accumulated, conflict- and atomic-free, into per-warp shared-memory rows,
-//   (4) summed over the 8 warps and flushed with ONE red.global.add per (tile, Gaussian,
-//       component) after the batch.
+//   (3) accumulated in shared memory — one row set per tile that the warps add into with shared-memory atomics
+//       (default), or eight private per-warp row sets summed at flush time (earlier variant, kept for A/B),
+//   (4) flushed with ONE red.global.add per (tile, Gaussian, component) after the batch.
 // Bound: SM issue rate + shuffle throughput; global atomics drop from 9*P to <= 9*I.
+#include <stdlib.h>
+
 #include "raster_common.cuh"
 
 namespace {
@@ -56,6 +58,11 @@ __device__ __forceinline__ int warp_max(int x) {
     return x;
 }
 
+// RB_B: Gaussians staged per batch. ATOMIC_ACC: the per-(tile, Gaussian) moment sums live in ONE shared row set that
+// the warps add into with shared-memory atomics (a CAS loop on this architecture: LDS + FADD + ATOMS.CAST) instead of
+// eight private per-warp row sets — 8x less shared memory for the sums (so a batch can be 256 Gaussians: half the
+// barriers per Gaussian) and a flush that reads 9 instead of 72 values per Gaussian.
+template <int RB_B, bool ATOMIC_ACC>
 __global__ void __launch_bounds__(256)
 raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_sorted,
                    const int2 *__restrict__ tile_bins, const float2 *__restrict__ xys,
@@ -66,13 +73,13 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
                    float *__restrict__ v_xys, float *__restrict__ v_conics, float *__restrict__ v_colors,
                    float *__restrict__ v_opac, const int32_t *__restrict__ tile_order,
                    const float *__restrict__ clamp_ref) {
-    __shared__ float4 sa[RB_BATCH];  // x, y, opac, qa   (q* = pre-scaled conic, raster_common.cuh)
-    __shared__ float4 sb[RB_BATCH];  // qb, qc, r, g
-    __shared__ float sc[RB_BATCH];   // b
-    __shared__ float2 se[RB_BATCH];  // alpha >= 1/255 half-extents
-    __shared__ int sid[RB_BATCH];
-    __shared__ float acc[8][RB_BATCH * RB_NV];
-    __shared__ unsigned char wlist[8][RB_BATCH];
+    __shared__ float4 sa[RB_B];  // x, y, opac, qa   (q* = pre-scaled conic, raster_common.cuh)
+    __shared__ float4 sb[RB_B];  // qb, qc, r, g
+    __shared__ float sc[RB_B];   // b
+    __shared__ float2 se[RB_B];  // alpha >= 1/255 half-extents
+    __shared__ int sid[RB_B];
+    __shared__ float acc[ATOMIC_ACC ? 1 : 8][RB_B * RB_NV];
+    __shared__ unsigned char wlist[8][RB_B];
     __shared__ int s_wmax[8];
 
     gs_pdl_sync();
@@ -108,7 +115,7 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
 
     const int wmax = warp_max(my_end);
     if (lane == 0) s_wmax[warp] = wmax;
-    for (int i = tid; i < 8 * RB_BATCH * RB_NV; i += 256) (&acc[0][0])[i] = 0.f;
+    for (int i = tid; i < (ATOMIC_ACC ? 1 : 8) * RB_B * RB_NV; i += 256) (&acc[0][0])[i] = 0.f;
     __syncthreads();
     int bmax = range.x;
 #pragma unroll
@@ -118,10 +125,11 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
     const unsigned sa_a = gs_smem_addr(sa), sb_a = gs_smem_addr(sb), sc_a = gs_smem_addr(sc);
     const unsigned list_a = gs_smem_addr(mylist);
     // this lane's accumulator column: lanes 0,4,..,28 own moments 0..7, lane 1 owns the ninth
-    const unsigned acc_a = gs_smem_addr(acc[warp]) + (lane == 1 ? 8u : (unsigned)(lane >> 2)) * 4u;
+    const int acc_col = lane == 1 ? 8 : (lane >> 2);
+    const unsigned acc_a = gs_smem_addr(acc[ATOMIC_ACC ? 0 : warp]) + (unsigned)acc_col * 4u;
     const bool acc_lane = (lane & 3) == 0 || lane == 1;
-    for (int hi = bmax; hi > range.x; hi -= RB_BATCH) {
-        const int lo = max(range.x, hi - RB_BATCH);
+    for (int hi = bmax; hi > range.x; hi -= RB_B) {
+        const int lo = max(range.x, hi - RB_B);
         const int cnt = hi - lo;
         if (tid < cnt) {
             const int id = ids_sorted[lo + tid];
@@ -188,8 +196,13 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             const float r8 = warp_reduce8(v, lane);
             const float r9 = warp_sum(v8);
             if (acc_lane) {
-                const unsigned a = acc_a + j * (RB_NV * 4u);
-                gs_sts32(a, gs_lds32(a) + (lane == 1 ? r9 : r8));
+                const float add = lane == 1 ? r9 : r8;
+                if (ATOMIC_ACC) {
+                    if (add != 0.0f) atomicAdd(&acc[0][j * RB_NV + acc_col], add);
+                } else {
+                    const unsigned a = acc_a + j * (RB_NV * 4u);
+                    gs_sts32(a, gs_lds32(a) + add);
+                }
             }
         }
         __syncthreads();
@@ -202,7 +215,7 @@ raster_bwd3_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_so
             for (int c = 0; c < RB_NV; ++c) {
                 float sum = 0.f;
 #pragma unroll
-                for (int w = 0; w < 8; ++w) {
+                for (int w = 0; w < (ATOMIC_ACC ? 1 : 8); ++w) {
                     sum += acc[w][tid * RB_NV + c];
                     acc[w][tid * RB_NV + c] = 0.f;
                 }
@@ -358,7 +371,7 @@ extern "C" int gs_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y,
     const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
     const float2 *xy2 = reinterpret_cast<const float2 *>(xys);
     if (C == 3)
-        raster_bwd3_kernel<<<tiles, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg,
+        raster_bwd3_kernel<256, true><<<tiles, 256, 0, st>>>(H, W, tiles_x, ids_sorted, bins, xy2, conics, colors, opac, bg,
                                                   final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics,
                                                   v_colors, v_opac, nullptr, nullptr);
     else
@@ -380,9 +393,18 @@ extern "C" int gs_raster_bwd_ordered_post(int H, int W, int tiles_x, int tiles_y
         !v_conics || !v_colors || !v_opac)
         return GS_ERR_BAD_ARG;
     if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
-    GS_PDL_LAUNCH(raster_bwd3_kernel, tiles_x * tiles_y, 256, 0, (cudaStream_t)stream, H, W, tiles_x, ids_sorted,
-                  reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys), conics, colors, opac,
-                  bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref);
+#define GS_RB_LAUNCH(B, A)                                                                                              \
+    GS_PDL_LAUNCH((raster_bwd3_kernel<B, A>), tiles_x * tiles_y, 256, 0, (cudaStream_t)stream, H, W, tiles_x, ids_sorted,  \
+                  reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys), conics, colors, opac,  \
+                  bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref)
+    // default: 256-Gaussian batches with shared-atomic sums (0.715 ms/step); GS_RB_VARIANT=0 selects the earlier
+    // 128-Gaussian batches with per-warp rows (0.727), =1 128-Gaussian batches with atomic sums (0.721). Same gradients
+    // up to the order of fp32 additions inside a tile.
+    static const int variant = [] { const char *e = getenv("GS_RB_VARIANT"); return e ? atoi(e) : 2; }();
+    if (variant == 0) GS_RB_LAUNCH(128, false);
+    else if (variant == 1) GS_RB_LAUNCH(128, true);
+    else GS_RB_LAUNCH(256, true);
+#undef GS_RB_LAUNCH
     return 0;
 }
 
