@@ -480,7 +480,7 @@ def run_ours(args):
             # `roofline` is the dominant HBM-bound kernel of the step, in the schema's units.
             step_hbm = {k: stages[k] for k in ("preprocess_fwd", "preprocess_bwd") if k in stages}
             top = max(step_hbm, key=lambda k: step_hbm[k]["us"])
-            ncu_traffic = {"preprocess_bwd": 275.0e6, "preprocess_fwd": 268.0e6}   # dram rd+wr per launch (ncu --set full; profiles/README.md r01b, r01l)
+            ncu_traffic = {"preprocess_bwd": 273.8e6, "preprocess_fwd": 268.6e6}   # dram rd+wr per launch (ncu --set full; profiles/README.md r01k)
             line["roofline"] = {"bound": "hbm", "kernel": top + "_kernel", "achieved": step_hbm[top]["GBps"],
                                 "peak": hbm_peak, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)",
                                 "unit": "GB/s", "frac": step_hbm[top]["frac_hbm"],
