@@ -11,7 +11,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libgs_b200.so")
+SO_PATH = os.environ.get("GS_B200_LIB") or os.path.join(_HERE, "libgs_b200.so")   # GS_B200_LIB: A/B builds
 CSRC = os.path.join(_HERE, "csrc")
 
 _lib = None

@@ -3,6 +3,7 @@
 // get_tile_bin_edges), reached from /root/reference/gaussctrl/gc_model.py:208 and :225.
 // Integer work, bit-exact against the oracle. HBM/L2-bound.
 #include <stdlib.h>
+#define GS_PDL_GROUP 1
 #include "radix.cuh"
 
 namespace {

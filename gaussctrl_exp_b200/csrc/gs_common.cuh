@@ -32,13 +32,20 @@ extern int64_t g_gs_launches;  // defined in abi.cu
 // previous kernel of the stream drains; it must call gs_pdl_sync() before touching ANY global memory (the wait
 // returns once the previous grid has completed and flushed; it is a no-op for a normal launch). Used for the
 // chains of short kernels (binning: 23 launches), where the ~1.2 us launch gaps added up to ~27 us per view.
+__device__ __forceinline__ void gs_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void gs_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void gs_pdl_sync() {
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    gs_pdl_wait();
+    gs_pdl_trigger();
 }
-bool gs_pdl_enabled();   // abi.cu: false when GS_NO_PDL is set in the environment (A/B switch)
+// abi.cu: false when GS_NO_PDL is set in the environment, or when GS_NO_PDL_GROUPS lists the calling file's group
+// (1 = binning chain, 2 = compositing + tile order, 3 = preprocess, 4 = view exchange): A/B switches
+bool gs_pdl_enabled(int group);
+#ifndef GS_PDL_GROUP
+#define GS_PDL_GROUP 0
+#endif
 
-#define GS_PDL_LAUNCH(kernel, grid, block, smem, st, ...)                                      \
+#define GS_PDL_LAUNCH_IF(cond, kernel, grid, block, smem, st, ...)                            \
     do {                                                                                       \
         cudaLaunchConfig_t _c = {};                                                            \
         _c.gridDim = dim3(grid);                                                               \
@@ -49,11 +56,13 @@ bool gs_pdl_enabled();   // abi.cu: false when GS_NO_PDL is set in the environme
         _a[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                         \
         _a[0].val.programmaticStreamSerializationAllowed = 1;                                  \
         _c.attrs = _a;                                                                         \
-        _c.numAttrs = gs_pdl_enabled() ? 1 : 0;                                                \
+        _c.numAttrs = ((cond) && gs_pdl_enabled(GS_PDL_GROUP)) ? 1 : 0;                                               \
         cudaError_t _e = cudaLaunchKernelEx(&_c, kernel, __VA_ARGS__);                         \
         if (_e != cudaSuccess) return (int)_e;                                                 \
         ++g_gs_launches;                                                                       \
     } while (0)
+
+#define GS_PDL_LAUNCH(kernel, grid, block, smem, st, ...) GS_PDL_LAUNCH_IF(true, kernel, grid, block, smem, st, __VA_ARGS__)
 
 static inline bool gs_aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 static inline int gs_ceil_log2(int v) { int b = 0; while ((1 << b) < v) ++b; return b; }

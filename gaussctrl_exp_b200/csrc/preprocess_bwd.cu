@@ -7,6 +7,7 @@
 //
 // The (N,15,3) v_features_rest block of a 128-Gaussian CTA is built in shared memory (rows of
 // 45 floats: odd pitch, conflict-free) and leaves with ONE TMA bulk store.
+#define GS_PDL_GROUP 3
 #include "project_math.cuh"
 #include "sh_math.cuh"
 

@@ -11,6 +11,7 @@
 // projection arithmetic; rows are 45 floats (odd) so per-thread row reads are bank-conflict free.
 //
 // COMPILED WITH -fmad=false (shares the bit-exact projection math with project_fwd.cu).
+#define GS_PDL_GROUP 3
 #include "project_math.cuh"
 #include "sh_math.cuh"
 

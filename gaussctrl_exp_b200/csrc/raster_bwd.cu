@@ -14,6 +14,7 @@
 // Bound: SM issue rate + shuffle throughput; global atomics drop from 9*P to <= 9*I.
 #include <stdlib.h>
 
+#define GS_PDL_GROUP 2
 #include "raster_common.cuh"
 
 namespace {
@@ -394,7 +395,7 @@ extern "C" int gs_raster_bwd_ordered_post(int H, int W, int tiles_x, int tiles_y
         return GS_ERR_BAD_ARG;
     if (tiles_x * GS_TILE < W || tiles_y * GS_TILE < H) return GS_ERR_BAD_ARG;
 #define GS_RB_LAUNCH(B, A)                                                                                              \
-    GS_PDL_LAUNCH((raster_bwd3_kernel<B, A>), tiles_x * tiles_y, 256, 0, (cudaStream_t)stream, H, W, tiles_x, ids_sorted,  \
+    GS_PDL_LAUNCH_IF(tiles_x * tiles_y <= GS_RASTER_PDL_MAX_TILES, (raster_bwd3_kernel<B, A>), tiles_x * tiles_y, 256, 0, (cudaStream_t)stream, H, W, tiles_x, ids_sorted,  \
                   reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float2 *>(xys), conics, colors, opac,  \
                   bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref)
     // default: 256-Gaussian batches with shared-atomic sums (0.715 ms/step); GS_RB_VARIANT=0 selects the earlier

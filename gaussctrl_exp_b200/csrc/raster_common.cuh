@@ -3,6 +3,12 @@
 #pragma once
 #include "gs_common.cuh"
 
+// The compositing kernels and the tile-order kernel are programmatic dependent launches only for images of up to this
+// many tiles. Measured: at 512x512 (1 024 tiles, ~1 wave of CTAs) the early launch is worth 2 % of a training step
+// (0.714 vs 0.729 ms); at 1920x1080 (8 160 tiles, 9 waves) it COSTS 15 % (5 M Gaussians: 272 vs 319 training views/s,
+// 476 vs 560 eval views/s) — the dependent grid's CTAs take over SM slots while the many-wave grid is still running.
+#define GS_RASTER_PDL_MAX_TILES 2048
+
 // A 16x16 tile is covered by 8 warps of 8x4 pixels: compact warp footprints mean more
 // warp-uniform early termination than the row-major 16x2 footprint.
 __device__ __forceinline__ void gs_pixel_of_thread(int tile_x, int tile_y, int &px, int &py) {

@@ -8,6 +8,7 @@
 // behind the arithmetic; one barrier per batch (__syncthreads_count) both publishes the
 // stage and retires the tile as soon as every pixel has saturated.
 // Bound: SM issue rate (FP32 + MUFU.EX2) and shared-memory broadcast reads, not HBM.
+#define GS_PDL_GROUP 2
 #include "raster_common.cuh"
 
 namespace {
@@ -319,7 +320,7 @@ tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, in
 extern "C" int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream) {
     if (T <= 0 || !work || !order) return GS_ERR_BAD_ARG;
     const size_t smem = T <= TO_SMEM_TILES ? (size_t)T * sizeof(int) : 0;
-    GS_PDL_LAUNCH(tile_order_kernel, (T * 32 + 255) / 256, 256, smem, (cudaStream_t)stream, T, work, work_is_range, order);
+    GS_PDL_LAUNCH_IF(T <= GS_RASTER_PDL_MAX_TILES, tile_order_kernel, (T * 32 + 255) / 256, 256, smem, (cudaStream_t)stream, T, work, work_is_range, order);
     return 0;
 }
 
@@ -338,11 +339,11 @@ extern "C" int gs_raster_fwd_ordered_post(int H, int W, int tiles_x, int tiles_y
     const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
     const float2 *xy2 = reinterpret_cast<const float2 *>(xys);
     if (depths)
-        GS_PDL_LAUNCH((raster_fwd3_kernel<true>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
+        GS_PDL_LAUNCH_IF(tiles_x * tiles_y <= GS_RASTER_PDL_MAX_TILES, (raster_fwd3_kernel<true>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
                       conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx, tile_order, tile_work,
                       out_clamped, out_alpha);
     else
-        GS_PDL_LAUNCH((raster_fwd3_kernel<false>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
+        GS_PDL_LAUNCH_IF(tiles_x * tiles_y <= GS_RASTER_PDL_MAX_TILES, (raster_fwd3_kernel<false>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
                       conics, colors, opac, (const float *)nullptr, bg, out_img, (float *)nullptr, final_T, final_idx,
                       tile_order, tile_work, out_clamped, out_alpha);
     return 0;

@@ -12,6 +12,7 @@
 // consecutive (coalesced peer loads). NVLink bytes per view drop from 36 N to ~0.25 N + 36 nnz.
 #include <cstdlib>
 
+#define GS_PDL_GROUP 4
 #include "project_math.cuh"
 #include "sh_math.cuh"
 
