@@ -158,6 +158,16 @@ class GaussianModel(nn.Module):
             viewmat0, projmat0 = self._caller_matrices(camera)
             return {"rgb": rgb, "depth": None, "accumulation": alpha[..., None],
                     "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
+        if self.num_points == 0:               # empty model: background, zero accumulation, depth 1000 (gc_model.py:238)
+            with torch.no_grad():
+                rgb = torch.clamp(background.to(dev).float().expand(H, W, 3).clone(), max=1.0)
+                alpha = torch.zeros((H, W, 1), device=dev)
+                depth_im = None if self.training else torch.full((H, W, 1), 1000.0, device=dev)
+            self.xys = torch.zeros((0, 2), device=dev)
+            self.radii = torch.zeros((0,), device=dev, dtype=torch.int32)
+            viewmat0, projmat0 = self._caller_matrices(camera)
+            return {"rgb": rgb, "depth": depth_im, "accumulation": alpha,
+                    "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
         with torch.no_grad(), torch.cuda.device(dev):
             bg = background.to(dev).float().contiguous()
             want_depth = not self.training

@@ -71,6 +71,14 @@ def rasterize_gaussians(
     if not xys.is_cuda:
         raise ValueError("rasterize_gaussians needs CUDA tensors (no CPU fallback)")
     H, W = int(img_height), int(img_width)
+    if xys.shape[0] == 0:
+        # empty Gaussian set: nothing to bin or composite (gsplat returns the background when there are no
+        # intersections; the caller's own early-out is gc_model.py:189-190). Kept on the autograd graph of the inputs.
+        zero = xys.sum() + colors.sum()
+        out_img = background.to(xys.device).float().expand(H, W, colors.shape[-1]) + zero
+        if return_alpha:
+            return out_img, torch.zeros((H, W), device=xys.device, dtype=torch.float32) + zero
+        return out_img
     with torch.no_grad():
         (ids_sorted, tile_bins, num_intersects), tb = _binning(xys, depths, radii, num_tiles_hit, H, W)
     return _RasterizeGaussians.apply(xys, conics, colors, opacity, background, ids_sorted, tile_bins,

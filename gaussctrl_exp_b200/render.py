@@ -381,6 +381,21 @@ def render_view(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor,
     if background is None:
         background = torch.ones(3, dtype=torch.float32, device=means.device)
     cam = gs_camera(camera)
+    if means.shape[0] == 0:
+        # empty model: background image, zero alpha, empty per-Gaussian outputs; stays on the autograd graph so that
+        # backward hands (empty) gradients to the six leaves
+        dev = means.device
+        zero = (means.sum() + scales.sum() + quats.sum() + opacities.sum() + features_dc.sum() + features_rest.sum())
+        rgb = background.to(dev).float().expand(cam.H, cam.W, 3) + zero
+        if clamp_rgb:
+            rgb = torch.clamp(rgb, max=1.0)
+        if state is not None:
+            state.xys = torch.zeros((0, 2), device=dev)
+            state.radii = torch.zeros((0,), device=dev, dtype=torch.int32)
+            state.depths = torch.zeros((0,), device=dev)
+            state.num_intersects = 0
+        return (rgb, torch.zeros((cam.H, cam.W), device=dev) + zero, torch.zeros((0,), device=dev),
+                torch.zeros((0,), device=dev, dtype=torch.int32), torch.zeros((0,), device=dev, dtype=torch.int32))
     return _RenderView.apply(means, scales, quats, opacities, features_dc, features_rest, cam, bool(use_sh),
                              int(sh_degree_to_use), background, state, bool(clamp_rgb))
 

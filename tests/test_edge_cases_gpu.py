@@ -1,0 +1,100 @@
+"""Edge cases the reference's callers can produce (empty / fully culled Gaussian sets, ragged image sizes, uint8
+colours, default background), through the gsplat-compatible operators and the fused model."""
+import numpy as np
+import pytest
+import torch
+
+from gaussctrl_exp_b200 import project_gaussians, rasterize_gaussians, scene, spherical_harmonics
+from gaussctrl_exp_b200.model import GaussianModel, camera_matrices
+from util import np_params, small_cam
+
+pytestmark = pytest.mark.gpu
+
+
+def _cam_mats(cam, dev):
+    V, P, _, _, tb = camera_matrices(cam.c2w, cam.fx, cam.fy, cam.W, cam.H)
+    return V[:3].contiguous().to(dev), (P @ V).to(dev), tb
+
+
+def test_empty_gaussian_set_operators(cuda_dev):
+    dev = cuda_dev
+    cam = small_cam(50, 37, 0)
+    Vd, PVd, tb = _cam_mats(cam, dev)
+    e = lambda *s, dt=torch.float32: torch.zeros(s, device=dev, dtype=dt)
+    means = e(0, 3).requires_grad_()
+    xys, depths, radii, conics, hit, cov3d = project_gaussians(means, e(0, 3), 1, e(0, 4), Vd, PVd, cam.fx, cam.fy, cam.cx,
+                                                               cam.cy, cam.H, cam.W, tb)
+    assert xys.shape == (0, 2) and radii.dtype == torch.int32 and hit.shape == (0,) and cov3d.shape == (0, 6)
+    cols = spherical_harmonics(3, e(0, 3), e(0, 16, 3))
+    assert cols.shape == (0, 3)
+    bg = torch.tensor([0.2, 0.4, 0.6], device=dev)
+    out, alpha = rasterize_gaussians(xys, depths, radii, conics, hit, cols, e(0, 1), cam.H, cam.W, background=bg,
+                                     return_alpha=True)
+    assert out.shape == (cam.H, cam.W, 3) and torch.allclose(out, bg.expand(cam.H, cam.W, 3)) and (alpha == 0).all()
+    out.sum().backward()
+    assert means.grad is None or means.grad.shape == (0, 3)
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_empty_and_fully_culled_model(cuda_dev, fused):
+    dev = cuda_dev
+    cam = small_cam(64, 48, 1)
+    bg = torch.tensor([0.1, 0.2, 0.3])
+    p = {k: v[:0] for k, v in scene.make_scene(8, 0).items()}
+    if fused:                                     # literal path: the caller's own early-out covers the empty set
+        m = GaussianModel(p, sh_degree=3, background_color=bg, fused=True).to(dev)
+        m.train()
+        out = m(cam)
+        assert out["rgb"].shape == (48, 64, 3) and torch.allclose(out["rgb"], bg.to(dev).expand(48, 64, 3))
+        assert (out["accumulation"] == 0).all()
+        out["rgb"].sum().backward()
+        ev = m.get_outputs_for_camera(cam)
+        assert torch.allclose(ev["rgb"], bg.to(dev).expand(48, 64, 3)) and (ev["depth"] == 1000).all()
+    # every Gaussian behind the camera: culled by the clip threshold -> background, zero gradients, depth 1000
+    q = scene.make_scene(500, 2, s0=0.02)
+    q["means"] = q["means"] * 0.05 + cam.c2w[:3, 3] * 2.0            # twice as far from the origin as the camera, behind it
+    m = GaussianModel(q, sh_degree=3, background_color=bg, fused=fused).to(dev)
+    m.train()
+    out = m(cam)
+    assert torch.allclose(out["rgb"], bg.to(dev).expand(48, 64, 3))
+    if fused:
+        out["rgb"].sum().backward()
+        assert all(float(getattr(m, n).grad.abs().max()) == 0.0 for n in ("means", "scales", "quats", "opacities"))
+        ev = m.get_outputs_for_camera(cam)
+        assert (ev["accumulation"] == 0).all() and (ev["depth"] == 1000).all()
+
+
+@pytest.mark.parametrize("W,H", [(1, 1), (17, 9), (16, 16), (33, 16), (250, 3)])
+def test_ragged_image_sizes(oracle, cuda_dev, W, H):
+    """Image sizes that are not multiples of the 16-pixel tile, down to a single pixel."""
+    N = 400
+    p = np_params(N, seed=3, s0=0.08)
+    cam = small_cam(W, H, 3, f=max(40.0, 1.2 * max(W, H)))
+    ref, _ = oracle.render_view(p, cam.as_dict(), 2, training=False)
+    m = GaussianModel({k: torch.from_numpy(v) for k, v in p.items()}, sh_degree=2, background_color=torch.tensor([0.1, 0.2, 0.3]),
+                      step=30000).to(cuda_dev)
+    out = m.get_outputs_for_camera(cam)
+    assert out["rgb"].shape == (H, W, 3)
+    err = np.abs(out["rgb"].cpu().numpy() - ref["rgb"]).max(-1)
+    assert err.max() < 1.5 / 255                                   # at most one alpha quantum (an __expf-vs-expf flip)
+    assert (err > 1e-4).sum() <= max(1, int(2e-3 * H * W))
+    assert np.abs(out["accumulation"].cpu().numpy() - ref["accumulation"]).max() < 2e-3
+
+
+def test_uint8_colors_and_default_background(oracle, cuda_dev):
+    dev = cuda_dev
+    from util import projected
+    d = projected(oracle, N=3000, W=96, H=64, seed=4, s0=0.04)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    rng = np.random.default_rng(0)
+    c8 = rng.integers(0, 256, (d["N"], 3), dtype=np.uint8)
+    args = (t(d["xys"]), t(d["depths"]), t(d["radii"]), t(d["conics"]), t(d["hit"]))
+    opac = t(d["opac"].reshape(-1, 1))
+    a = rasterize_gaussians(*args, t(c8), opac, d["H"], d["W"])                       # uint8 -> /255, background ones
+    b = rasterize_gaussians(*args, t(c8.astype(np.float32) / 255), opac, d["H"], d["W"], background=torch.ones(3, device=dev))
+    assert torch.allclose(a, b, atol=2e-6, rtol=0)      # torch divides by 255 as a multiplication by 1/255 on the GPU
+    bb = oracle.bin_and_sort(d["xys"], d["depths"], d["radii"], d["hit"], d["tb"])
+    ref = oracle.raster_fwd(bb, d["xys"], d["conics"], c8.astype(np.float32) / 255, d["opac"].reshape(-1), np.ones(3, np.float32),
+                            d["H"], d["W"], d["tb"])[0]
+    err = np.abs(a.cpu().numpy() - ref).max(-1)
+    assert err.max() < 1.5 / 255 and (err > 1e-4).mean() <= 2e-3
