@@ -279,32 +279,14 @@ extern "C" int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
 // Tile scheduling: rank tiles by descending work (ties by tile id). All-pairs counting in shared
 // memory: T <= a few thousand, so this is a few microseconds.
 namespace {
-constexpr int TO_SMEM_TILES = 8192;   // works staged in shared memory up to this many tiles (1080p: 8 160)
-
-// one warp per tile: rank = number of tiles with more work (ties: lower tile id first). Every CTA first stages
-// the whole work array in shared memory with independent, coalesced loads — ranking straight from global memory was a
-// serial chain of T/32 dependent L2 round trips per warp (7-8 us at T = 1024 for a few KB of data).
 __global__ void __launch_bounds__(256)
 tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, int32_t *__restrict__ order) {
-    extern __shared__ int s_work[];
+    // one warp per tile: rank = number of tiles with more work (ties: lower tile id first)
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     gs_pdl_sync();
-    const bool staged = T <= TO_SMEM_TILES;
-    if (staged) {
-        if (work_is_range) {
-            const int2 *r = reinterpret_cast<const int2 *>(work);
-            for (int u = threadIdx.x; u < T; u += 256) {
-                const int2 v = r[u];
-                s_work[u] = v.y - v.x;
-            }
-        } else {
-            for (int u = threadIdx.x; u < T; u += 256) s_work[u] = work[u];
-        }
-        __syncthreads();
-    }
     if (t >= T) return;
-    auto load = [&](int u) { return staged ? s_work[u] : (work_is_range ? work[2 * u + 1] - work[2 * u] : work[u]); };
+    auto load = [&](int u) { return work_is_range ? work[2 * u + 1] - work[2 * u] : work[u]; };
     const int mine = load(t);
     int rank = 0;
     for (int u = lane; u < T; u += 32) {
@@ -319,8 +301,8 @@ tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, in
 
 extern "C" int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream) {
     if (T <= 0 || !work || !order) return GS_ERR_BAD_ARG;
-    const size_t smem = T <= TO_SMEM_TILES ? (size_t)T * sizeof(int) : 0;
-    GS_PDL_LAUNCH_IF(T <= GS_RASTER_PDL_MAX_TILES, tile_order_kernel, (T * 32 + 255) / 256, 256, smem, (cudaStream_t)stream, T, work, work_is_range, order);
+    GS_PDL_LAUNCH_IF(T <= GS_RASTER_PDL_MAX_TILES, tile_order_kernel, (T * 32 + 255) / 256, 256, 0, (cudaStream_t)stream, T,
+                     work, work_is_range, order);
     return 0;
 }
 
@@ -338,14 +320,16 @@ extern "C" int gs_raster_fwd_ordered_post(int H, int W, int tiles_x, int tiles_y
     cudaStream_t st = (cudaStream_t)stream;
     const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
     const float2 *xy2 = reinterpret_cast<const float2 *>(xys);
+    const int tiles = tiles_x * tiles_y;
+    const bool pdl = tiles <= GS_RASTER_PDL_MAX_TILES;   // raster_common.cuh: the early launch hurts on many-wave grids
     if (depths)
-        GS_PDL_LAUNCH_IF(tiles_x * tiles_y <= GS_RASTER_PDL_MAX_TILES, (raster_fwd3_kernel<true>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
-                      conics, colors, opac, depths, bg, out_img, out_depth, final_T, final_idx, tile_order, tile_work,
-                      out_clamped, out_alpha);
+        GS_PDL_LAUNCH_IF(pdl, (raster_fwd3_kernel<true>), tiles, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2, conics,
+                         colors, opac, depths, bg, out_img, out_depth, final_T, final_idx, tile_order, tile_work,
+                         out_clamped, out_alpha);
     else
-        GS_PDL_LAUNCH_IF(tiles_x * tiles_y <= GS_RASTER_PDL_MAX_TILES, (raster_fwd3_kernel<false>), tiles_x * tiles_y, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2,
-                      conics, colors, opac, (const float *)nullptr, bg, out_img, (float *)nullptr, final_T, final_idx,
-                      tile_order, tile_work, out_clamped, out_alpha);
+        GS_PDL_LAUNCH_IF(pdl, (raster_fwd3_kernel<false>), tiles, 256, 0, st, H, W, tiles_x, ids_sorted, bins, xy2, conics,
+                         colors, opac, (const float *)nullptr, bg, out_img, (float *)nullptr, final_T, final_idx,
+                         tile_order, tile_work, out_clamped, out_alpha);
     return 0;
 }
 
