@@ -96,8 +96,8 @@ class CpuReference:
         from gaussctrl_exp_b200 import scene
         from oracle import oracle as orc
         orc.build()
-        if threads:
-            orc.set_num_threads(threads)
+        # torchrun exports OMP_NUM_THREADS=1 to its workers: ask for every host core explicitly
+        orc.set_num_threads(threads or os.cpu_count() or 1)
         self.orc = orc
         self.cores = orc.num_threads()
         self.p = {k: v.numpy() for k, v in scene.make_scene(n_gauss, 0).items()}
@@ -117,20 +117,23 @@ class CpuReference:
 
 
 def run_reference(args):
+    """The reference arm: the CPU restatement of the path on ALL host cores, same config as our arm at this N
+    (one step = `world` views, fwd + bwd each — the views the N ranks of our arm render in one step)."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
     ref = CpuReference(args.n_gaussians)
     ref.run(min(max(args.warmup, 0), 2))
-    _, dt = ref.run(args.steps, first=2)                  # one step = one view, fwd + bwd
+    _, dt = ref.run(args.steps * world, first=2)          # one step = `world` views
     ms = 1e3 * dt / args.steps
-    val = 1e3 / ms
-    sample = "1 view (fwd+bwd) of the same 1M-Gaussian/512^2 workload per step, C oracle + OpenMP"
+    val = world * 1e3 / ms
+    sample = (f"{world} view(s) (fwd+bwd) of the same {args.n_gaussians}-Gaussian/512^2 workload per step, "
+              f"{args.steps} steps, C oracle + OpenMP on {ref.cores} threads")
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "views/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, 1),
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
         "cpu_baseline": {"value": val, "unit": "views/s", "cores": ref.cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "gsplat 0.1.2 (the reference's implementation of this path) is not in /root/reference and not "
@@ -140,118 +143,238 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------
-def stage_breakdown(model, cams, v_out, iters=20):
-    """Per-stage device times (CUDA events on the current stream) and rooflines for one view.
-    Algorithmic bytes per SURVEY.md §8d."""
+def timed_events(fn, n=20, warm=3):
+    """Average device time of fn() in seconds: CUDA events on the current stream, sync on both sides."""
     import torch
-    from gaussctrl_exp_b200 import project_gaussians, rasterize_gaussians, spherical_harmonics
-    from gaussctrl_exp_b200 import utils as U
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n * 1e-3
+
+
+def stage_breakdown(model, cam, v_out, iters=20):
+    """Per-stage device times (CUDA events on the current stream) for one view of `cam`, kernels called through the raw
+    C ABI on device-resident inputs. Algorithmic bytes per SURVEY.md §8d (+ the 48-byte packed record where a kernel
+    reads / writes it). Returns ({stage: (seconds, alg_bytes | None)}, intersections, visible Gaussians)."""
+    import ctypes
+    import torch
+    from gaussctrl_exp_b200 import _lib, project_gaussians, render, spherical_harmonics
     from gaussctrl_exp_b200.model import camera_matrices
     dev = model.device
-    cam = cams[0]
     H, W = cam.H, cam.W
     V, P, _, _, tb = camera_matrices(cam.c2w, cam.fx, cam.fy, W, H)
     Vd, PVd = V[:3].contiguous().to(dev), (P @ V).to(dev)
     N = model.num_points
-    with torch.no_grad():
-        means, scales = model.means.detach(), model.scales.detach().exp()
-        quats = model.quats.detach() / model.quats.detach().norm(dim=-1, keepdim=True)
-        coeffs = torch.cat((model.features_dc.detach()[:, None, :], model.features_rest.detach()), 1).contiguous()
-        dirs = means - cam.c2w[:3, 3].to(dev)
-        dirs = dirs / dirs.norm(dim=-1, keepdim=True)
-        opac = torch.sigmoid(model.opacities.detach())
-    bg = torch.tensor(BG, device=dev)
-
-    def timed(fn, n=iters):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(n):
-            fn()
-        e1.record()
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / n * 1e-3
-
-    from gaussctrl_exp_b200 import _lib
+    T = tb[0] * tb[1]
     L = _lib.lib()
     st = {}
-    with torch.no_grad():
-        xys, depths, radii, conics, hit, cov3d = project_gaussians(means, scales, 1, quats, Vd, PVd, cam.fx, cam.fy,
-                                                                   cam.cx, cam.cy, H, W, tb)
-        rgbs = torch.clamp(spherical_harmonics(SH_DEG, dirs, coeffs) + 0.5, min=0.0)
-        ids_sorted, bins, I = U.bin_fast(xys, depths, radii, hit, tb)
-        T = tb[0] * tb[1]
-        st["project_fwd"] = (timed(lambda: project_gaussians(means, scales, 1, quats, Vd, PVd, cam.fx, cam.fy, cam.cx,
-                                                             cam.cy, H, W, tb)), 96 * N)
-        st["sh_fwd"] = (timed(lambda: spherical_harmonics(SH_DEG, dirs, coeffs)), 216 * N)
-        # binning through the raw ABI (no host read inside the timed loop)
-        cap = ids_sorted.numel()
-        scratch = torch.empty(L.gs_bin_fast_scratch_bytes(N, cap, T), device=dev, dtype=torch.uint8)
-        total = torch.zeros(1, device=dev, dtype=torch.int32)
-        st["bin_fast"] = (timed(lambda: L.gs_bin_fast(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(),
-                                                       hit.data_ptr(), tb[0], tb[1], ids_sorted.data_ptr(),
-                                                       bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
-                                                       scratch.numel(), _lib.stream_ptr())),
-                          8 * N + 20 * N + 12 * I + 24 * I + 8 * I + 8 * T)
-        scratch2 = torch.empty(L.gs_bin_tile_scratch_bytes(N, cap, T), device=dev, dtype=torch.uint8)
-        st["bin_tile"] = (timed(lambda: L.gs_bin_tile(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(),
-                                                       tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(),
-                                                       total.data_ptr(), scratch2.data_ptr(), scratch2.numel(),
-                                                       _lib.stream_ptr())),
-                          8 * N + 20 * N + 12 * I + 24 * I + 8 * I + 8 * T)
-        out = torch.empty((H, W, 3), device=dev)
-        fT = torch.empty((H, W), device=dev)
-        fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
-        opv = opac.view(-1).contiguous()
-        order_f = torch.empty(T, device=dev, dtype=torch.int32)
-        order_b = torch.empty(T, device=dev, dtype=torch.int32)
-        twork = torch.empty(T, device=dev, dtype=torch.int32)
-        L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), _lib.stream_ptr())
-        st["tile_order"] = (timed(lambda: L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), _lib.stream_ptr())), None)
-        fwd = lambda: L.gs_raster_fwd_ordered(H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                              conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), None, bg.data_ptr(),
-                                              out.data_ptr(), None, fT.data_ptr(), fidx.data_ptr(), order_f.data_ptr(),
-                                              twork.data_ptr(), _lib.stream_ptr())
-        st["raster_fwd"] = (timed(fwd), None)
-        g = [torch.zeros((N, k), device=dev) for k in (2, 3, 3, 1)]
-        L.gs_tile_order(T, twork.data_ptr(), 0, order_b.data_ptr(), _lib.stream_ptr())
-        bwd = lambda: L.gs_raster_bwd_ordered(H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                              conics.data_ptr(), rgbs.data_ptr(), opv.data_ptr(), bg.data_ptr(),
-                                              fT.data_ptr(), fidx.data_ptr(), v_out.data_ptr(), None, g[0].data_ptr(),
-                                              g[1].data_ptr(), g[2].data_ptr(), g[3].data_ptr(), order_b.data_ptr(),
-                                              _lib.stream_ptr())
-        st["raster_bwd"] = (timed(bwd), None)
-        vcoef = torch.empty((N, 16, 3), device=dev)
-        st["sh_bwd"] = (timed(lambda: L.gs_sh_bwd(N, 16, SH_DEG, dirs.data_ptr(), g[2].data_ptr(), vcoef.data_ptr(),
-                                                  _lib.stream_ptr())), 216 * N)
-        # fused per-view kernels (render.py path)
-        import ctypes
-        from gaussctrl_exp_b200 import render
+    timed = lambda fn: timed_events(fn, iters)
+    with torch.no_grad(), torch.cuda.device(dev):
+        sp = _lib.stream_ptr()
+        raw = [t.detach().float().contiguous() for t in (model.means, model.scales, model.quats, model.opacities,
+                                                         model.features_dc, model.features_rest)]
         gc = render.gs_camera(cam)
-        raw = [t.detach().contiguous() for t in (model.means, model.scales, model.quats, model.opacities,
-                                                 model.features_dc, model.features_rest)]
-        o_xy, o_d, o_c, o_rgb, o_op = (torch.empty_like(t) for t in (xys, depths, conics, rgbs, opv))
-        o_r, o_h = torch.empty_like(radii), torch.empty_like(hit)
+        bg = torch.tensor(BG, device=dev)
+        # the product forward once: workspace with records, tile lists, images
+        ws, im, I, _ = render.forward_views(*raw, [gc], True, SH_DEG, bg)
+        vis = int((ws.radii > 0).sum().item())
+        rec, depths, radii, hit, ids_sorted, bins = ws.rec, ws.depths, ws.radii, ws.num_tiles_hit, ws.ids_sorted, ws.tile_bins
+        cap = ws.cap
+        # ---- fused stage 1: leaves -> packed records (+ depths, radii, tiles_hit) ----
+        ws2 = render.ViewWorkspace(dev, N, 1, cap, T)
+        scratch = torch.empty(L.gs_view_scratch_bytes(N, 1, cap, T), device=dev, dtype=torch.uint8)
+        # gs_view_fwd = preprocess + binning + tile order + compositing; the pieces below are timed one by one
+        o_xy, o_c, o_rgb = torch.empty(N, 2, device=dev), torch.empty(N, 3, device=dev), torch.empty(N, 3, device=dev)
+        o_d, o_op = torch.empty(N, device=dev), torch.empty(N, device=dev)
+        o_r, o_h = torch.empty(N, device=dev, dtype=torch.int32), torch.empty(N, device=dev, dtype=torch.int32)
         st["preprocess_fwd"] = (timed(lambda: L.gs_preprocess_fwd(
             N, raw[0].data_ptr(), raw[1].data_ptr(), raw[2].data_ptr(), raw[3].data_ptr(), raw[4].data_ptr(),
             raw[5].data_ptr(), 1, SH_DEG, ctypes.addressof(gc), o_xy.data_ptr(), o_d.data_ptr(), o_r.data_ptr(),
-            o_c.data_ptr(), o_h.data_ptr(), o_rgb.data_ptr(), o_op.data_ptr(), _lib.stream_ptr())), 284 * N)
+            o_c.data_ptr(), o_h.data_ptr(), o_rgb.data_ptr(), o_op.data_ptr(), sp)), 284 * N)
+        # ---- binning through the raw ABI (no host read inside the timed loop) ----
+        total = torch.zeros(1, device=dev, dtype=torch.int32)
+        ids2, bins2 = torch.empty_like(ids_sorted), torch.empty_like(bins)
+        st["bin_fast"] = (timed(lambda: L.gs_bin_fast(N, cap, o_xy.data_ptr(), o_d.data_ptr(), o_r.data_ptr(),
+                                                       o_h.data_ptr(), tb[0], tb[1], ids2.data_ptr(), bins2.data_ptr(),
+                                                       total.data_ptr(), scratch.data_ptr(), scratch.numel(), sp)),
+                          8 * N + 20 * N + 12 * I + 24 * I + 8 * I + 8 * T)
+        order_f = torch.empty(T, device=dev, dtype=torch.int32)
+        order_b = torch.empty(T, device=dev, dtype=torch.int32)
+        twork = torch.empty(T, device=dev, dtype=torch.int32)
+        L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), sp)
+        st["tile_order"] = (timed(lambda: L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), sp)), None)
+        # ---- compositing over packed records (the product kernels) ----
+        fwd = lambda: L.gs_raster_fwd_packed(1, H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), rec.data_ptr(),
+                                             bg.data_ptr(), im.out.data_ptr(), None, im.final_T.data_ptr(),
+                                             im.final_idx.data_ptr(), order_f.data_ptr(), twork.data_ptr(),
+                                             im.out_clamped.data_ptr(), im.alpha.data_ptr(), sp)
+        st["raster_fwd"] = (timed(fwd), None)
+        Np = (N + 3) // 4 * 4
+        g = torch.zeros(9 * Np + 64, device=dev)
+        gx, gc_, gr, go = g[0:2 * N], g[2 * Np:2 * Np + 3 * N], g[5 * Np:5 * Np + 3 * N], g[8 * Np:8 * Np + N]
+        L.gs_tile_order(T, twork.data_ptr(), 0, order_b.data_ptr(), sp)
+        bwd = lambda: L.gs_raster_bwd_packed(H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), rec.data_ptr(),
+                                             bg.data_ptr(), im.final_T.data_ptr(), im.final_idx.data_ptr(), v_out.data_ptr(),
+                                             None, gx.data_ptr(), gc_.data_ptr(), gr.data_ptr(), go.data_ptr(),
+                                             order_b.data_ptr(), None, sp)
+        st["raster_bwd"] = (timed(bwd), None)
+        # ---- the un-packed compositing kernels (round-1 design: register double buffer, five arrays) for A/B ----
+        conics = ws.conics().contiguous()
+        xys_c, rgbs_c, opac_c = ws.xys.contiguous(), ws.rgbs.contiguous(), ws.opac.contiguous()
+        out_o = torch.empty((H, W, 3), device=dev)
+        fT_o, fidx_o = torch.empty((H, W), device=dev), torch.empty((H, W), device=dev, dtype=torch.int32)
+        st["raster_fwd_unpacked_r01"] = (timed(lambda: L.gs_raster_fwd_ordered(
+            H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys_c.data_ptr(), conics.data_ptr(),
+            rgbs_c.data_ptr(), opac_c.data_ptr(), None, bg.data_ptr(), out_o.data_ptr(), None, fT_o.data_ptr(),
+            fidx_o.data_ptr(), order_f.data_ptr(), twork.data_ptr(), sp)), None)
+        g2 = [torch.zeros((N, k), device=dev) for k in (2, 3, 3, 1)]
+        st["raster_bwd_unpacked_r01"] = (timed(lambda: L.gs_raster_bwd_ordered(
+            H, W, tb[0], tb[1], ids_sorted.data_ptr(), bins.data_ptr(), xys_c.data_ptr(), conics.data_ptr(),
+            rgbs_c.data_ptr(), opac_c.data_ptr(), bg.data_ptr(), fT_o.data_ptr(), fidx_o.data_ptr(), v_out.data_ptr(),
+            None, g2[0].data_ptr(), g2[1].data_ptr(), g2[2].data_ptr(), g2[3].data_ptr(), order_b.data_ptr(), sp)), None)
+        # ---- leaf backward ----
         gl = [torch.empty_like(t) for t in raw]
         st["preprocess_bwd"] = (timed(lambda: L.gs_preprocess_bwd(
             N, raw[0].data_ptr(), raw[1].data_ptr(), raw[2].data_ptr(), raw[3].data_ptr(), 1, SH_DEG,
-            ctypes.addressof(gc), o_r.data_ptr(), o_rgb.data_ptr(), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(),
-            g[3].data_ptr(), gl[0].data_ptr(), gl[1].data_ptr(), gl[2].data_ptr(), gl[3].data_ptr(), gl[4].data_ptr(),
-            gl[5].data_ptr(), _lib.stream_ptr())), 332 * N)
+            ctypes.addressof(gc), o_r.data_ptr(), o_rgb.data_ptr(), g2[0].data_ptr(), g2[1].data_ptr(), g2[2].data_ptr(),
+            g2[3].data_ptr(), gl[0].data_ptr(), gl[1].data_ptr(), gl[2].data_ptr(), gl[3].data_ptr(), gl[4].data_ptr(),
+            gl[5].data_ptr(), sp)), 332 * N)
+        # ---- whole-view C entries (what the product calls): forward, backward ----
+        pin = torch.zeros(1, dtype=torch.int32).pin_memory()
+        im2 = render.ViewImages(dev, 1, H, W, False)
+        view_fwd = lambda: L.gs_view_fwd(N, 1, raw[0].data_ptr(), raw[1].data_ptr(), raw[2].data_ptr(), raw[3].data_ptr(),
+                                         raw[4].data_ptr(), raw[5].data_ptr(), None, 1, SH_DEG, ctypes.addressof(gc),
+                                         bg.data_ptr(), cap, ws2.buf.data_ptr(), ws2.buf.numel(), scratch.data_ptr(),
+                                         scratch.numel(), im2.out.data_ptr(), im2.out_clamped.data_ptr(),
+                                         im2.alpha.data_ptr(), None, im2.final_T.data_ptr(), im2.final_idx.data_ptr(),
+                                         None, None, sp)
+        st["view_fwd_total"] = (timed(view_fwd), None)
+        flat = torch.empty(59 * Np, device=dev)
+        view_bwd = lambda: L.gs_view_bwd(N, raw[0].data_ptr(), raw[1].data_ptr(), raw[2].data_ptr(), raw[3].data_ptr(), 1,
+                                         SH_DEG, ctypes.addressof(gc), bg.data_ptr(), ws2.buf.data_ptr(), ws2.buf.numel(),
+                                         cap, im2.final_T.data_ptr(), im2.final_idx.data_ptr(), v_out.data_ptr(), None,
+                                         im2.out.data_ptr(), g.data_ptr(), flat.data_ptr(), sp)
+        st["view_bwd_total"] = (timed(view_bwd), None)
+        st["preprocess_fwd_packed"] = (timed(lambda: L.gs_preprocess_fwd_packed(
+            N, raw[0].data_ptr(), raw[1].data_ptr(), raw[2].data_ptr(), raw[3].data_ptr(), raw[4].data_ptr(),
+            raw[5].data_ptr(), None, 1, SH_DEG, ctypes.addressof(gc), ws2.rec.data_ptr(), ws2.depths.data_ptr(),
+            ws2.radii.data_ptr(), ws2.num_tiles_hit.data_ptr(), sp)), 296 * N)     # 236 in + 48 record + 12 ints/depth
+        # ---- literal operators (what the drop-in API runs): projection, SH, their backward, packing ----
+        means, scales = raw[0], raw[1].exp()
+        quats = raw[2] / raw[2].norm(dim=-1, keepdim=True)
+        coeffs = torch.cat((raw[4][:, None, :], raw[5]), 1).contiguous()
+        dirs = means - cam.c2w[:3, 3].to(dev)
+        dirs = dirs / dirs.norm(dim=-1, keepdim=True)
+        st["project_fwd"] = (timed(lambda: project_gaussians(means, scales, 1, quats, Vd, PVd, cam.fx, cam.fy, cam.cx,
+                                                             cam.cy, H, W, tb)), 96 * N)
+        st["sh_fwd"] = (timed(lambda: spherical_harmonics(SH_DEG, dirs, coeffs)), 216 * N)
+        vcoef = torch.empty((N, 16, 3), device=dev)
+        st["sh_bwd"] = (timed(lambda: L.gs_sh_bwd(N, 16, SH_DEG, dirs.data_ptr(), g2[2].data_ptr(), vcoef.data_ptr(), sp)),
+                        216 * N)
         vm, vs, vq = torch.empty_like(means), torch.empty_like(means), torch.empty_like(quats)
         vdep = torch.zeros(N, device=dev)
         st["project_bwd"] = (timed(lambda: L.gs_project_bwd(N, means.data_ptr(), scales.data_ptr(), 1.0, quats.data_ptr(),
                                                             Vd.data_ptr(), PVd.data_ptr(), cam.fx, cam.fy, H, W,
-                                                            radii.data_ptr(), g[0].data_ptr(), vdep.data_ptr(),
-                                                            g[1].data_ptr(), vm.data_ptr(), vs.data_ptr(), vq.data_ptr(),
-                                                            _lib.stream_ptr())), 144 * N)
-    return st, I, int((radii > 0).sum().item())
+                                                            o_r.data_ptr(), g2[0].data_ptr(), vdep.data_ptr(),
+                                                            g2[1].data_ptr(), vm.data_ptr(), vs.data_ptr(), vq.data_ptr(),
+                                                            sp)), 144 * N)
+        rec2 = torch.empty((N, 12), device=dev)
+        st["pack_splats"] = (timed(lambda: L.gs_pack_splats(N, xys_c.data_ptr(), conics.data_ptr(), rgbs_c.data_ptr(),
+                                                            opac_c.data_ptr(), None, rec2.data_ptr(), sp)), 84 * N)
+    return st, I, vis
+
+
+def load_ncu_profile():
+    """profiles/r02_ncu_metrics.json: per-kernel metrics extracted (tools/ncu_extract.py) from the `ncu --set full`
+    capture of THIS build that is committed next to it. bench.py measures times live; instruction counts, issue
+    utilisation and DRAM traffic can only come from a profiler run, so they are read from that file."""
+    path = os.path.join(ROOT, "profiles", "r02_ncu_metrics.json")
+    try:
+        return json.load(open(path)), os.path.relpath(path, ROOT)
+    except Exception:
+        return {}, None
+
+
+def time_model_steps(model, cams, v_out, steps, warmup, rank=0, world=1):
+    import torch
+    params = [model.means, model.scales, model.quats, model.features_dc, model.features_rest, model.opacities]
+
+    def step(i):
+        for p in params:
+            p.grad = None
+        model(cams[(i * world + rank) % len(cams)])["rgb"].backward(v_out)
+    for i in range(warmup):
+        step(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        step(warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def config1_api_500k(dev, steps=20):
+    """BASELINE.json configs[1]: 500 K Gaussians, SH deg 3, 512x512, fwd+bwd on one GPU THROUGH THE
+    gsplat-0.1.2-COMPATIBLE API (the literal operator sequence of gc_model.py:172-222: torch pre-ops +
+    project_gaussians + spherical_harmonics + rasterize_gaussians); the fused path on the same scene beside it."""
+    import torch
+    from gaussctrl_exp_b200 import scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    p = scene.make_scene(500_000, 0)
+    cams = scene.make_cameras(N_CAMS, 0)
+    g = torch.Generator().manual_seed(1234)
+    v = (torch.randn(512, 512, 3, generator=g) / (512 * 512)).to(dev)
+    out = {"workload": "synthetic 500000 Gaussians, SH deg 3, 512x512, one view fwd+bwd per step, 1 GPU"}
+    for name, fused in (("api", False), ("fused", True)):
+        m = GaussianModel(p, sh_degree=SH_DEG, background_color=torch.tensor(BG), fused=fused).to(dev)
+        m.train()
+        ms = time_model_steps(m, cams, v, steps, 5)
+        out[name + "_views_per_s"] = 1e3 / ms
+        out[name + "_ms_per_step"] = ms
+        del m
+    torch.cuda.empty_cache()
+    return out
+
+
+def config5_stress(dev, n_gauss=5_000_000, n_cams=64, batch=8):
+    """BASELINE.json configs[4]: 5 M Gaussians at 1920x1080, a 64-camera batch: eval render (batched
+    render_views), training step, and binning / compositing throughput in intersections/s."""
+    import torch
+    from gaussctrl_exp_b200 import scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    cams = scene.make_cameras(n_cams, 0, intrinsics=scene.HD_INTRINSICS)
+    H, W = cams[0].H, cams[0].W
+    v = (torch.randn(H, W, 3, generator=torch.Generator().manual_seed(1234)) / (H * W)).to(dev)
+    m = GaussianModel(scene.make_scene(n_gauss, 0), sh_degree=SH_DEG, background_color=torch.tensor(BG)).to(dev)
+    m.eval()
+    m.render_views(cams[:batch], batch=batch)                    # warm-up: capacity hints, allocator
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    m.render_views(cams, batch=batch)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_eval = e0.elapsed_time(e1) / n_cams
+    m.train()
+    ms_train = time_model_steps(m, cams, v, 16, 3)
+    st, I, vis = stage_breakdown(m, cams[0], v, iters=5)
+    out = {"workload": f"stress: {n_gauss} Gaussians, {W}x{H}, {n_cams} cameras (batches of {batch}), SH deg 3",
+           "intersections_cam0": int(I), "visible_cam0": vis, "eval_render_views_per_s": 1e3 / ms_eval,
+           "train_fwd_bwd_views_per_s": 1e3 / ms_train,
+           "bin_fast_us": st["bin_fast"][0] * 1e6, "bin_fast_Gintersections_per_s": I / st["bin_fast"][0] / 1e9,
+           "raster_fwd_us": st["raster_fwd"][0] * 1e6, "raster_fwd_Gintersections_per_s": I / st["raster_fwd"][0] / 1e9,
+           "raster_bwd_us": st["raster_bwd"][0] * 1e6, "peak_mem_GB": torch.cuda.max_memory_allocated() / 2**30}
+    del m
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_ours(args):
@@ -319,6 +442,52 @@ def run_ours(args):
         # e2e loop below has a real L1 loss against a target image copied from the host)
         out["rgb"].backward(v_out)
         reduce_grads()
+
+    # ---- N > 1: the exchange that the timed loop uses against a plain NCCL all-reduce of the leaf gradients ----
+    grad_check = None
+    allreduce_ms = None
+    if world > 1 and model.fused:
+        def grads_allreduce(i):
+            model.view_state.defer_leaf_grads = False
+            model.view_state.view_block_buffer = None
+            for p in params:
+                p.grad = None
+            model(cams[(i * world + rank) % N_CAMS])["rgb"].backward(v_out)
+            gdist.allreduce_flat(model.view_state.flat_grads)
+            flat = model.view_state.flat_grads
+            model.view_state.defer_leaf_grads = gather_mode
+            if peer is not None:
+                peer.begin(model)
+            return flat
+        step(0)
+        torch.cuda.synchronize()
+        a = model.view_state.flat_grads.clone()
+        b = grads_allreduce(0)
+        torch.cuda.synchronize()
+        den = b.abs().max().clamp_min(1e-30)
+        diff = ((a - b).abs().max() / den).reshape(1)
+        # bit pattern checksum of this rank's reduced gradients: identical on every rank?
+        chk = a.view(torch.int32).to(torch.int64).sum().reshape(1)
+        chks = [torch.zeros_like(chk) for _ in range(world)]
+        dist.all_gather(chks, chk)
+        dist.all_reduce(diff, op=dist.ReduceOp.MAX)
+        grad_check = {"exchange": args.reduce + ("/" + args.exchange if args.reduce == "peer" else ""),
+                      "against": "NCCL sum-allreduce of the 59-float leaf gradients, averaged",
+                      "max_rel_diff": float(diff.item()), "ranks_identical": bool(all(int(c.item()) == int(chks[0].item()) for c in chks)),
+                      "nonzero": bool(b.abs().max().item() > 0), "step": 0}
+        # config 4 as BASELINE.json words it: fwd+bwd + NCCL allreduce of the parameter gradients
+        for i in range(3):
+            grads_allreduce(i)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for i in range(10):
+            grads_allreduce(3 + i)
+        a1.record()
+        barrier()
+        t = torch.tensor([a0.elapsed_time(a1) / 10], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        allreduce_ms = float(t.item())
 
     loss_pinned = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
     loss_events = [torch.cuda.Event() for _ in range(2)]
@@ -390,7 +559,7 @@ def run_ours(args):
         h0 = time.perf_counter()
         for i in range(steps):
             fn(warmup + i)
-        host_ms[0] = 1e3 * (time.perf_counter() - h0) / steps     # host enqueue time per step (diagnostic)
+        host_ms[0] = 1e3 * (time.perf_counter() - h0) / steps     # host time per step (diagnostic)
         if drain:
             drain()
         e1.record()
@@ -409,7 +578,7 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
 
     # per-step distribution (median and p10/p90): the same steps, each bracketed by its own events
-    # (no host sync in between; events are read back afterwards). Diagnostic only: `value` is the loop above.
+    # (events are read back afterwards). Diagnostic only: `value` is the loop above.
     n_dist = min(args.steps, 100)
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_dist + 1)]
     barrier()
@@ -424,10 +593,9 @@ def run_ours(args):
                  "what": "per-step device time of this rank, CUDA events around each step"}
     ms_e2e, _ = timed_loop(step_e2e, max(3, args.warmup // 2), args.steps, drain=drain_losses)
 
-    # config 3: all-view eval render, RGB + depth + alpha, 40 views sharded over the ranks
-    model.eval_render = True
+    # config 3: all-view eval render, RGB + depth + alpha, 40 views sharded over the ranks, batched
     def render_all():
-        return model.render_views(cams, rank, world, num_streams=args.render_streams)
+        return model.render_views(cams, rank, world, batch=args.render_batch)
     for _ in range(2):
         render_all()
     barrier()
@@ -452,20 +620,30 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args.n_gaussians, world),
             "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
             "grad_exchange": ((args.reduce + ("/" + args.exchange if args.reduce == "peer" else "")) if world > 1 else None),
-            "eval_render": {"views_per_s": render_vps, "what": f"all-view RGB+depth+alpha render of {N_CAMS} cameras "
-                            f"(gc_pipeline.py:222-228), view-sharded over {world} GPU(s), {args.render_streams} streams/GPU"},
-            "host_enqueue_ms_per_step": host_enqueue_ms, "step_time_distribution": step_dist,
+            "grad_exchange_check": grad_check,
+            "host_ms_per_step": host_enqueue_ms, "step_time_distribution": step_dist,
             "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "views/s",
-                    "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4},
+                    "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4 + 4},
+            # BASELINE.json configs, one named key each (configs[0] is the CPU case = cpu_baseline / --impl reference)
+            "config3_all_view_render": {
+                "views_per_s": render_vps, "n_gpus": world,
+                "what": f"all-view RGB+depth+alpha render of {N_CAMS} cameras, 1M Gaussians, 512^2 (gc_pipeline.py:222-228), "
+                        f"view-sharded over {world} GPU(s), batches of {args.render_batch} cameras per call"},
         }
+        if allreduce_ms is not None:
+            line["config4_finetune_step_nccl_allreduce"] = {
+                "views_per_s": world * 1e3 / allreduce_ms, "ms_per_step": allreduce_ms, "n_gpus": world,
+                "what": "fwd+bwd + NCCL sum-allreduce of the 59-float leaf gradients (236 MB) every step — BASELINE.json "
+                        "configs[3] as worded; `value` uses the compacted peer-memory exchange instead"}
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
         hbm_peak, peak_src = (peaks.get("hbm_gbs"), "measured") if peaks.get("hbm_gbs") else (6650.0, "fallback")
+        prof, prof_path = load_ncu_profile()
         if not args.no_stages:
-            st, I, vis = stage_breakdown(model, cams, v_out)
+            st, I, vis = stage_breakdown(model, cams[0], v_out)
             stages = {}
             for k, (sec, byts) in st.items():
                 stages[k] = {"us": sec * 1e6}
@@ -474,50 +652,59 @@ def run_ours(args):
             line["stages"] = stages
             line["intersections"] = I
             line["visible"] = vis
-            # Kernels of the measured (fused) step: preprocess_fwd, binning, tile_order x2, raster_fwd, raster_bwd,
-            # preprocess_bwd. The dominant one (raster_bwd3, ~35 % of the step) is bound by SM issue rate, not
-            # HBM or tensor cores (no dense contraction anywhere on this path) -> `roofline_raster`.
-            # `roofline` is the dominant HBM-bound kernel of the step, in the schema's units.
-            step_hbm = {k: stages[k] for k in ("preprocess_fwd", "preprocess_bwd") if k in stages}
+            # `roofline` (schema object) = the dominant HBM-bound kernel of the step; the dominant kernel overall is
+            # SM-issue bound (no dense contraction anywhere on this path) -> `roofline_raster`.
+            step_hbm = {k: stages[k] for k in ("preprocess_fwd_packed", "preprocess_bwd") if k in stages}
             top = max(step_hbm, key=lambda k: step_hbm[k]["us"])
-            ncu_traffic = {"preprocess_bwd": 273.8e6, "preprocess_fwd": 268.6e6}   # dram rd+wr per launch (ncu --set full; profiles/README.md r01k)
-            line["roofline"] = {"bound": "hbm", "kernel": top + "_kernel", "achieved": step_hbm[top]["GBps"],
+            kname = {"preprocess_fwd_packed": "preprocess_fwd_kernel", "preprocess_bwd": "preprocess_bwd_kernel"}[top]
+            pk = prof.get(kname, {}) if args.n_gaussians == N_GAUSS else {}
+            line["roofline"] = {"bound": "hbm", "kernel": kname, "achieved": step_hbm[top]["GBps"],
                                 "peak": hbm_peak, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)",
                                 "unit": "GB/s", "frac": step_hbm[top]["frac_hbm"],
                                 "alg_bytes_per_launch": step_hbm[top]["alg_bytes"],
-                                "traffic": ncu_traffic.get(top) if args.n_gaussians == N_GAUSS else None,
+                                "traffic": pk.get("dram_bytes"), "traffic_source": prof_path if pk else None,
                                 "note": "dominant HBM-bound kernel of the step; the dominant kernel overall is "
-                                        "SM-issue bound, see roofline_raster; multi-kernel binning stage: stages.bin_fast"}
-            bin_key = "bin_tile" if os.environ.get("GS_BIN_IMPL", "lsd") == "tile" else "bin_fast"
-            line["roofline_binning"] = {"bound": "hbm", "kernel": "gs_" + bin_key + " (multi-kernel stage)",
-                                        "achieved": stages[bin_key]["GBps"], "peak": hbm_peak, "unit": "GB/s",
-                                        "frac": stages[bin_key]["frac_hbm"],
+                                        "SM-issue bound, see roofline_raster; multi-kernel binning stage: roofline_binning"}
+            line["roofline_binning"] = {"bound": "hbm", "kernel": "gs_bin_fast (multi-kernel stage)",
+                                        "achieved": stages["bin_fast"]["GBps"], "peak": hbm_peak, "unit": "GB/s",
+                                        "frac": stages["bin_fast"]["frac_hbm"],
+                                        "projection_plus_sort_frac": (stages["preprocess_fwd_packed"]["alg_bytes"] + stages["bin_fast"]["alg_bytes"])
+                                        / (stages["preprocess_fwd_packed"]["us"] + stages["bin_fast"]["us"]) / 1e3 / hbm_peak,
                                         "note": "L2-resident, latency-bound at this size (see DESIGN.md §4)"}
-        pairs = None
+            # dominant kernel: time measured live (CUDA events above), instruction / issue / shared-memory figures from the
+            # committed ncu capture of this build
+            f_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
+            slots = 148 * 4 * f_clk                       # warp-instruction issue slots per second
+            rr = {"bound": "sm_issue", "kernel": "raster_bwd_packed_kernel", "us": stages["raster_bwd"]["us"],
+                  "peak": slots, "unit": "warp-inst/s", "sm_mhz": f_clk / 1e6, "metrics_source": prof_path}
+            for kname2, key in (("raster_bwd_packed_kernel", "bwd"), ("raster_fwd_packed_kernel", "fwd")):
+                pk2 = prof.get(kname2) if args.n_gaussians == N_GAUSS else None
+                us = stages["raster_" + key]["us"]
+                ent = {"us": us}
+                if pk2:
+                    ent.update({"smsp__inst_executed.sum": pk2.get("inst_executed"),
+                                "smsp__issue_active.avg.pct": pk2.get("issue_active_pct"),
+                                "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum": pk2.get("smem_wavefronts"),
+                                "achieved_warp_inst_per_s": (pk2.get("inst_executed") or 0) / (us * 1e-6),
+                                "frac": (pk2.get("inst_executed") or 0) / (us * 1e-6) / slots})
+                rr[key] = ent
+            if "frac" in rr["bwd"]:
+                rr["achieved"], rr["frac"] = rr["bwd"]["achieved_warp_inst_per_s"], rr["bwd"]["frac"]
+            line["roofline_raster"] = rr
         if world == 1 and not args.no_cpu:
             ref = CpuReference(args.n_gaussians)
             out0, _ = ref.orc.render_view(ref.p, ref.cams[0].as_dict(), SH_DEG, bg=BG, training=True)
-            pairs = int(out0["pairs"])                      # (pixel, Gaussian) pairs of the reference algorithm, view 0
             vps, dt = ref.run(args.cpu_views, first=1)
             line["cpu_baseline"] = {"value": vps, "unit": "views/s", "cores": ref.cores, "kind": "port",
                                     "sample": f"{args.cpu_views} views of the same workload (fwd+bwd), C oracle + OpenMP, {dt:.1f} s"}
-        if not args.no_stages and pairs:
-            # a front-to-back compositor must evaluate P pairs at ~16 FP32-pipe instructions each
-            # (backward ~2.5x); ceiling = 148 SMs x 128 lanes x f_clk lane-instructions/s
-            f_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
-            peak_lane_ips = 148 * 128 * f_clk
-            rf = {}
-            for k, ipp in (("raster_fwd", 16.0), ("raster_bwd", 40.0)):
-                t = stages[k]["us"] * 1e-6
-                rf[k] = {"pairs_per_s": pairs / t, "lane_inst_per_s": pairs * ipp / t, "frac": pairs * ipp / t / peak_lane_ips,
-                         "us": stages[k]["us"], "model_inst_per_pair": ipp}
-            line["roofline_raster"] = {"bound": "sm_issue", "kernel": "raster_bwd3_kernel", "pairs_P": pairs,
-                                       "peak_lane_inst_per_s": peak_lane_ips, "sm_mhz": f_clk / 1e6,
-                                       "achieved": rf["raster_bwd"]["lane_inst_per_s"], "unit": "lane-inst/s",
-                                       "frac": rf["raster_bwd"]["frac"], "fwd": rf["raster_fwd"], "bwd": rf["raster_bwd"],
-                                       "note": "P = pairs the reference's per-pixel loop visits (oracle, camera 0); the "
-                                               "kernels skip pairs whose alpha-extent box misses the warp, so frac is an "
-                                               "algorithmic-work rate, not an issue-slot utilisation (ncu: profiles/)"}
+            if "roofline_raster" in line:
+                line["roofline_raster"]["pairs_P_reference_loop"] = int(out0["pairs"])
+            del ref
+        if world == 1 and not args.no_extra_configs:
+            line["config1_api_500k"] = config1_api_500k(dev)
+            del model
+            torch.cuda.empty_cache()
+            line["config5_stress"] = config5_stress(dev)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -534,7 +721,9 @@ def main():
     ap.add_argument("--cpu-views", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
-    ap.add_argument("--render-streams", type=int, default=2)
+    ap.add_argument("--no-extra-configs", action="store_true",
+                    help="skip BASELINE.json configs[1] (500 K through the operator API) and configs[4] (5 M / 1080p stress)")
+    ap.add_argument("--render-batch", type=int, default=8)
     ap.add_argument("--render-reps", type=int, default=3)
     ap.add_argument("--reduce", default="peer", choices=["gather", "peer", "allreduce"],
                     help="N>1 gradient exchange: peer = each rank's multi-view leaf backward reads the peers' "
@@ -544,7 +733,7 @@ def main():
     ap.add_argument("--exchange", choices=("push", "dense", "sparse"), default="push",
                     help="peer-memory exchange: compacted blocks pushed to the peers (default), dense pull, compacted pull")
     ap.add_argument("--path", default="fused", choices=["fused", "api"],
-                    help="fused: one autograd node / 5 kernels per view (render.py); api: the literal "
+                    help="fused: one autograd node / two C calls per view (render.py); api: the literal "
                          "gsplat-0.1.2 three-operator sequence of gc_model.py")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -55,8 +55,6 @@ SIGNATURES = {
     "gs_bin_fast_scratch_bytes": (_sz, [_i, _i64, _i]),
     "gs_bin_fast": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gs_set_depth_sort_passes": (_i, [_i]),
-    "gs_bin_tile_scratch_bytes": (_sz, [_i, _i64, _i]),
-    "gs_bin_tile": (_i, [_i, _i64, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gs_raster_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_raster_fwd_rgbd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_tile_order": (_i, [_i, _vp, _i, _vp, _vp]),
@@ -68,6 +66,16 @@ SIGNATURES = {
     "gs_noise_mask": (_i, [_i, _vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _f, _vp, _sz, _vp, _vp]),
     "gs_raster_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                            _vp, _vp, _vp, _vp, _vp]),
+    "gs_pack_splats": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_preprocess_fwd_packed": (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_raster_fwd_packed": (_i, [_i, _i, _i, _i, _i] + [_vp] * 13),
+    "gs_raster_bwd_packed": (_i, [_i, _i, _i, _i] + [_vp] * 15),
+    "gs_view_layout": (_i, [_i, _i, _i64, _i, _vp]),
+    "gs_view_scratch_bytes": (_sz, [_i, _i, _i64, _i]),
+    "gs_view_fwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _i64, _vp, _sz, _vp, _sz,
+                         _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "gs_view_bwd": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
+                         _vp, _vp]),
 }
 
 
@@ -78,6 +86,12 @@ class GsCamera(C.Structure):
                 ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
                 ("glob_scale", C.c_float), ("clip", C.c_float),
                 ("H", C.c_int32), ("W", C.c_int32), ("tiles_x", C.c_int32), ("tiles_y", C.c_int32)]
+
+
+class GsViewLayout(C.Structure):
+    """Mirror of `struct GsViewLayout`: byte offsets of the arrays inside a view workspace."""
+    _fields_ = [(n, C.c_int64) for n in ("rec", "depths", "radii", "tiles_hit", "ids_sorted", "tile_bins", "tile_work",
+                                         "order_fwd", "order_bwd", "total", "bytes")]
 
 
 _ERRORS = {-1: "GS_ERR_BAD_ARG", -2: "GS_ERR_SCRATCH_SMALL", -3: "GS_ERR_UNSUPPORTED", -4: "GS_ERR_MISALIGNED"}

@@ -288,21 +288,24 @@ namespace {
 
 __global__ void __launch_bounds__(256)
 emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ order,
-                   const int32_t *__restrict__ start, const float2 *__restrict__ xys,
-                   const int32_t *__restrict__ radii, int tiles_x, int tiles_y, uint32_t *__restrict__ tkey,
-                   uint32_t *__restrict__ tval) {
+                   const int32_t *__restrict__ start, const float *__restrict__ xy_base, int xy_stride,
+                   const int32_t *__restrict__ radii, int tiles_x, int tiles_y, int n_per_view,
+                   uint32_t *__restrict__ tkey, uint32_t *__restrict__ tval) {
     gs_pdl_sync();
     if ((int64_t)*total_dev > I_cap) return;   // capacity too small: write nothing, the host retries
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    int x0 = 0, y0 = 0, x1 = 0, y1 = 0, st = 0, g = 0;
+    // several views in one call (gs_view_fwd, views > 1): element g belongs to view g / n_per_view and its tiles
+    // live in that view's slice [view * T, (view + 1) * T) of the tile-id space
+    int x0 = 0, y0 = 0, x1 = 0, y1 = 0, st = 0, g = 0, tbase = 0;
     if (j < N) {
         g = (int)order[j];
         const int r = radii[g];
         if (r > 0) {
-            const float2 c = xys[g];
+            const float2 c = *reinterpret_cast<const float2 *>(xy_base + (size_t)g * xy_stride);
             gs_tile_bbox(c.x, c.y, (float)r, tiles_x, tiles_y, x0, y0, x1, y1);
             st = start[j];
+            tbase = (g / n_per_view) * (tiles_x * tiles_y);
         }
     }
     const int bw = x1 - x0, area = bw * (y1 - y0);
@@ -310,7 +313,7 @@ emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, 
         int at = st;
         for (int ty = y0; ty < y1; ++ty)
             for (int tx = x0; tx < x1; ++tx) {
-                tkey[at] = (uint32_t)(ty * tiles_x + tx);
+                tkey[at] = (uint32_t)(tbase + ty * tiles_x + tx);
                 tval[at] = (uint32_t)g;
                 ++at;
             }
@@ -322,8 +325,9 @@ emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, 
         const int sx0 = __shfl_sync(0xffffffffu, x0, src), sy0 = __shfl_sync(0xffffffffu, y0, src);
         const int sbw = __shfl_sync(0xffffffffu, bw, src), sarea = __shfl_sync(0xffffffffu, area, src);
         const int sst = __shfl_sync(0xffffffffu, st, src), sg = __shfl_sync(0xffffffffu, g, src);
+        const int stb = __shfl_sync(0xffffffffu, tbase, src);
         for (int k = lane; k < sarea; k += 32) {
-            tkey[sst + k] = (uint32_t)((sy0 + k / sbw) * tiles_x + sx0 + k % sbw);
+            tkey[sst + k] = (uint32_t)(stb + (sy0 + k / sbw) * tiles_x + sx0 + k % sbw);
             tval[sst + k] = (uint32_t)sg;
         }
     }
@@ -391,14 +395,17 @@ extern "C" size_t gs_bin_fast_scratch_bytes(int N, int64_t I_cap, int T) {
     return fast_layout(N, I_cap).total;
 }
 
-extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, const int32_t *radii,
-                           const int32_t *tiles_hit, int tiles_x, int tiles_y,
-                           int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
-                           void *scratch, size_t scratch_bytes, void *stream) {
-    if (N < 0 || I_cap < 0 || tiles_x <= 0 || tiles_y <= 0) return GS_ERR_BAD_ARG;
+// N = elements of ALL views (view v owns [v * n_per_view, (v + 1) * n_per_view)); xy of element g at
+// xy_base + g * xy_stride floats (2 = an (N,2) array, 12 = the packed records); tile_bins has views * T rows.
+int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int xy_stride, const float *depths,
+                   const int32_t *radii, const int32_t *tiles_hit, int tiles_x, int tiles_y, int32_t *ids_sorted,
+                   int32_t *tile_bins, int32_t *total_dev, void *scratch, size_t scratch_bytes, void *stream) {
+    if (N < 0 || I_cap < 0 || tiles_x <= 0 || tiles_y <= 0 || n_per_view <= 0 || (N % n_per_view) != 0) return GS_ERR_BAD_ARG;
     if (!tile_bins || !total_dev || !scratch) return GS_ERR_BAD_ARG;
     if (I_cap >= (1ll << 31)) return GS_ERR_UNSUPPORTED;
-    const int T = tiles_x * tiles_y;
+    const int views = N > 0 ? N / n_per_view : 1;
+    if ((int64_t)views * tiles_x * tiles_y >= (1ll << 22)) return GS_ERR_UNSUPPORTED;
+    const int T = views * tiles_x * tiles_y;
     const int tile_bits = T > 1 ? gs_ceil_log2(T) : 1;
     if (tile_bits > 22) return GS_ERR_UNSUPPORTED;
     cudaStream_t st = (cudaStream_t)stream;
@@ -456,7 +463,7 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
 
     // 3. emission in depth order
     GS_PDL_LAUNCH(emit_sorted_kernel, nblk, 256, 0, st, N, I_cap, (const int32_t *)total_dev, order,
-                  (const int32_t *)start, reinterpret_cast<const float2 *>(xys), radii, tiles_x, tiles_y, tkey, tval);
+                  (const int32_t *)start, xys, xy_stride, radii, tiles_x, tiles_y, n_per_view, tkey, tval);
 
     // 4. stable partition by tile id
     uint32_t *ids_out = reinterpret_cast<uint32_t *>(ids_sorted);
@@ -488,4 +495,12 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
         GS_LAUNCH_CHECK();
     }
     return 0;
+}
+
+extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, const int32_t *radii,
+                           const int32_t *tiles_hit, int tiles_x, int tiles_y,
+                           int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
+                           void *scratch, size_t scratch_bytes, void *stream) {
+    return gs_bin_fast_ex(N, N > 0 ? N : 1, I_cap, xys, 2, depths, radii, tiles_hit, tiles_x, tiles_y, ids_sorted, tile_bins,
+                          total_dev, scratch, scratch_bytes, stream);
 }

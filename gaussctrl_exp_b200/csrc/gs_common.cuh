@@ -97,3 +97,20 @@ __device__ __forceinline__ float4 gs_ldg_stream4(const float4 *p) {
 // internal helpers shared between translation units (not exported through the C ABI header)
 int gs_internal_exclusive_scan(int n, const int32_t *in, int32_t *out, int32_t *total_dev, void *scratch,
                                size_t scratch_bytes, cudaStream_t st);
+// binning.cu: gs_bin_fast over the elements of several views at once, xy read with a stride (packed records)
+int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int xy_stride, const float *depths,
+                   const int32_t *radii, const int32_t *tiles_hit, int tiles_x, int tiles_y, int32_t *ids_sorted,
+                   int32_t *tile_bins, int32_t *total_dev, void *scratch, size_t scratch_bytes, void *stream);
+// preprocess_fwd.cu / preprocess_bwd.cu: packed-record forms used by view.cu
+int gs_launch_preprocess_fwd_packed(int N, const float *means, const float *log_scales, const float *quats,
+                                    const float *opac_logits, const float *feat_dc, const float *feat_rest, int use_sh,
+                                    int sh_deg, const GsCamera *cam_host, const int32_t *subset, float *rec, float *depths,
+                                    int32_t *radii, int32_t *tiles_hit, cudaStream_t st);
+int gs_launch_preprocess_bwd(int N, const float *means, const float *log_scales, const float *quats,
+                             const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host,
+                             const int32_t *radii, const float *rgbs, int rgb_stride, const float *v_xys,
+                             const float *v_conics, const float *v_rgbs, const float *v_opac, float *v_means,
+                             float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
+                             float *v_feat_rest, cudaStream_t st);
+int gs_launch_finish_view_block(int N, int use_sh, const GsCamera *cam_host, const float *rgbs, int rgb_stride,
+                                float *block, cudaStream_t st);

@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(PB_TPB)
 preprocess_bwd_kernel(int N, const float *__restrict__ means, const float *__restrict__ log_scales,
                       const float4 *__restrict__ quats, const float *__restrict__ opac_logits, int use_sh, int deg,
                       const __grid_constant__ GsCamera cam, const int32_t *__restrict__ radii,
-                      const float *__restrict__ rgbs, const float2 *__restrict__ v_xys,
+                      const float *__restrict__ rgbs, int rgb_stride, const float2 *__restrict__ v_xys,
                       const float *__restrict__ v_conics, const float *__restrict__ v_rgbs,
                       const float *__restrict__ v_opac, float *__restrict__ v_means,
                       float *__restrict__ v_log_scales, float4 *__restrict__ v_quats,
@@ -60,7 +60,8 @@ preprocess_bwd_kernel(int N, const float *__restrict__ means, const float *__res
                              (g.vq.w - q.w * dq) * iq);
             const float o = 1.0f / (1.0f + expf(-opac_logits[i]));
             vol = v_opac[i] * o * (1.0f - o);                                              // d sigmoid
-            const float c0 = rgbs[3 * i], c1 = rgbs[3 * i + 1], c2 = rgbs[3 * i + 2];
+            const float *crow = rgbs + (size_t)i * rgb_stride;   // (N,3) array, or the colour quad of the packed records
+            const float c0 = crow[0], c1 = crow[1], c2 = crow[2];
             const float u0 = v_rgbs[3 * i], u1 = v_rgbs[3 * i + 1], u2 = v_rgbs[3 * i + 2];
             if (use_sh) {
                 vc0 = c0 > 0.f ? u0 : 0.f; vc1 = c1 > 0.f ? u1 : 0.f; vc2 = c2 > 0.f ? u2 : 0.f;   // d clamp(min=0)
@@ -102,12 +103,14 @@ preprocess_bwd_kernel(int N, const float *__restrict__ means, const float *__res
 
 }  // namespace
 
-extern "C" int gs_preprocess_bwd(int N, const float *means, const float *log_scales, const float *quats,
-                                 const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host,
-                                 const int32_t *radii, const float *rgbs, const float *v_xys, const float *v_conics,
-                                 const float *v_rgbs, const float *v_opac, float *v_means, float *v_log_scales,
-                                 float *v_quats, float *v_opac_logits, float *v_feat_dc, float *v_feat_rest,
-                                 void *stream) {
+// rgbs: post-activation colours, row i at rgbs + i * rgb_stride floats (3 = an (N,3) array; 12 with rgbs pointing at
+// float 8 of the packed records)
+int gs_launch_preprocess_bwd(int N, const float *means, const float *log_scales, const float *quats,
+                             const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host,
+                             const int32_t *radii, const float *rgbs, int rgb_stride, const float *v_xys,
+                             const float *v_conics, const float *v_rgbs, const float *v_opac, float *v_means,
+                             float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
+                             float *v_feat_rest, cudaStream_t st) {
     if (N < 0 || !cam_host) return GS_ERR_BAD_ARG;
     if (sh_deg < 0 || sh_deg > 3) return GS_ERR_UNSUPPORTED;
     if (N == 0) return 0;
@@ -118,11 +121,22 @@ extern "C" int gs_preprocess_bwd(int N, const float *means, const float *log_sca
         (reinterpret_cast<uintptr_t>(v_xys) & 7u))
         return GS_ERR_MISALIGNED;
     const int blocks = (N + PB_TPB - 1) / PB_TPB;
-    GS_PDL_LAUNCH(preprocess_bwd_kernel, blocks, PB_TPB, 0, (cudaStream_t)stream, N, means, log_scales,
-                  reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, *cam_host, radii, rgbs,
+    GS_PDL_LAUNCH(preprocess_bwd_kernel, blocks, PB_TPB, 0, st, N, means, log_scales,
+                  reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, *cam_host, radii, rgbs, rgb_stride,
                   reinterpret_cast<const float2 *>(v_xys), v_conics, v_rgbs, v_opac, v_means, v_log_scales,
                   reinterpret_cast<float4 *>(v_quats), v_opac_logits, v_feat_dc, v_feat_rest);
     return 0;
+}
+
+extern "C" int gs_preprocess_bwd(int N, const float *means, const float *log_scales, const float *quats,
+                                 const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host,
+                                 const int32_t *radii, const float *rgbs, const float *v_xys, const float *v_conics,
+                                 const float *v_rgbs, const float *v_opac, float *v_means, float *v_log_scales,
+                                 float *v_quats, float *v_opac_logits, float *v_feat_dc, float *v_feat_rest,
+                                 void *stream) {
+    return gs_launch_preprocess_bwd(N, means, log_scales, quats, opac_logits, use_sh, sh_deg, cam_host, radii, rgbs, 3,
+                                    v_xys, v_conics, v_rgbs, v_opac, v_means, v_log_scales, v_quats, v_opac_logits,
+                                    v_feat_dc, v_feat_rest, (cudaStream_t)stream);
 }
 
 // ==========================================================================================
@@ -262,14 +276,14 @@ preprocess_bwd_multi_kernel(int N, int Np, int V, const float *__restrict__ view
 
 // sender side: apply the colour activation's derivative to v_rgbs in place and append the camera
 __global__ void __launch_bounds__(256)
-finish_view_block_kernel(int N, int use_sh, const float *__restrict__ rgbs, float *__restrict__ v_rgbs,
+finish_view_block_kernel(int N, int use_sh, const float *__restrict__ rgbs, int rgb_stride, float *__restrict__ v_rgbs,
                          const __grid_constant__ GsCamera cam, float *__restrict__ cam_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     gs_pdl_sync();
     if (blockIdx.x == 0 && threadIdx.x < (int)(sizeof(GsCamera) / 4))
         cam_out[threadIdx.x] = reinterpret_cast<const float *>(&cam)[threadIdx.x];
     if (i >= 3 * N) return;
-    const float c = rgbs[i];
+    const float c = rgbs[(size_t)(i / 3) * rgb_stride + (i % 3)];
     v_rgbs[i] = use_sh ? (c > 0.f ? v_rgbs[i] : 0.f) : v_rgbs[i] * c * (1.0f - c);
 }
 
@@ -277,15 +291,20 @@ finish_view_block_kernel(int N, int use_sh, const float *__restrict__ rgbs, floa
 
 extern "C" int gs_view_block_floats(int N) { return 9 * ((N + 3) / 4 * 4) + 64; }
 
-extern "C" int gs_finish_view_block(int N, int use_sh, const GsCamera *cam_host, const float *rgbs, float *block,
-                                    void *stream) {
+int gs_launch_finish_view_block(int N, int use_sh, const GsCamera *cam_host, const float *rgbs, int rgb_stride,
+                                float *block, cudaStream_t st) {
     if (N < 0 || !cam_host || !block || (N > 0 && !rgbs)) return GS_ERR_BAD_ARG;
     static_assert(sizeof(GsCamera) <= 64 * 4, "camera must fit the 64-float tail of a view block");
     const int Np = (N + 3) / 4 * 4;
     const int blocks = (3 * N + 255) / 256;
-    GS_PDL_LAUNCH(finish_view_block_kernel, blocks > 0 ? blocks : 1, 256, 0, (cudaStream_t)stream, N, use_sh, rgbs,
+    GS_PDL_LAUNCH(finish_view_block_kernel, blocks > 0 ? blocks : 1, 256, 0, st, N, use_sh, rgbs, rgb_stride,
                   block + (size_t)5 * Np, *cam_host, block + (size_t)9 * Np);
     return 0;
+}
+
+extern "C" int gs_finish_view_block(int N, int use_sh, const GsCamera *cam_host, const float *rgbs, float *block,
+                                    void *stream) {
+    return gs_launch_finish_view_block(N, use_sh, cam_host, rgbs, 3, block, (cudaStream_t)stream);
 }
 
 static int launch_bwd_multi(int N, int V, const float *views, int64_t stride_floats,

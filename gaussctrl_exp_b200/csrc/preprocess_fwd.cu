@@ -14,6 +14,7 @@
 #define GS_PDL_GROUP 3
 #include "project_math.cuh"
 #include "sh_math.cuh"
+#include "raster_packed.cuh"
 
 namespace {
 
@@ -25,14 +26,20 @@ __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)_
 // PART 0: everything. PART 1: geometry only (projection + opacity; the binning chain depends on nothing else).
 // PART 2: colour only (reads the radii PART 1 wrote) — the host runs it on a second stream underneath the
 // latency-bound binning kernels, which takes the 216 B/Gaussian SH traffic off the critical path.
-template <int PART>
+// PACKED (PART 0 only): instead of the operator-shaped arrays (xys, conics, rgbs, opac) the kernel writes ONE 48-byte
+// splat record per Gaussian (raster_packed.cuh: pixel centre + alpha extents | opacity + pre-scaled conic | colour +
+// depth) — what the packed compositing kernels copy with cp.async — plus depths / radii / tiles_hit for the binning.
+// subset != nullptr: element i is Gaussian subset[i] (the eval crop box of gc_model.py:108-113, :157-170, as an index
+// list instead of six gathered copies); its SH rows are then fetched per thread, not by the bulk copy.
+template <int PART, bool PACKED>
 __global__ void __launch_bounds__(PP_TPB)
 preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__restrict__ log_scales,
                       const float4 *__restrict__ quats, const float *__restrict__ opac_logits,
                       const float *__restrict__ feat_dc, const float *__restrict__ feat_rest, int use_sh, int deg,
                       const __grid_constant__ GsCamera cam, float2 *__restrict__ xys, float *__restrict__ depths,
                       int32_t *__restrict__ radii, float *__restrict__ conics, int32_t *__restrict__ tiles_hit,
-                      float *__restrict__ rgbs, float *__restrict__ opac) {
+                      float *__restrict__ rgbs, float *__restrict__ opac, const int32_t *__restrict__ subset,
+                      float4 *__restrict__ rec) {
     gs_pdl_sync();   // lets the first binning kernel become resident while this one drains
     __shared__ __align__(128) float rest_s[PP_TPB * PP_REST];
     __shared__ __align__(8) unsigned long long mbar;
@@ -40,8 +47,12 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
     const int g0 = blockIdx.x * PP_TPB;
     const int rows = min(PP_TPB, N - g0);
     const bool need_rest = PART != 1 && use_sh && deg >= 1;
+    const int src = (g0 + tid < N) ? (subset ? subset[g0 + tid] : g0 + tid) : 0;
 
-    if (need_rest) {
+    if (need_rest && subset) {
+        if (g0 + tid < N)
+            for (int f = 0; f < PP_REST; ++f) rest_s[tid * PP_REST + f] = feat_rest[(size_t)src * PP_REST + f];
+    } else if (need_rest) {
         const int rows4 = rows & ~3;                      // 4 rows = 720 B: keeps the bulk size a multiple of 16
         const unsigned bytes = (unsigned)rows4 * PP_REST * 4u;
         if (tid == 0) {
@@ -64,28 +75,34 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
     float p0 = 0.f, p1 = 0.f, p2 = 0.f;
     ProjOut o;
     o.radius = 0;
+    float op = 0.f;
     if (PART == 2) {
         if (i < N) {
-            p0 = means[3 * i]; p1 = means[3 * i + 1]; p2 = means[3 * i + 2];
+            p0 = means[3 * src]; p1 = means[3 * src + 1]; p2 = means[3 * src + 2];
             o.radius = radii[i];
         }
     } else if (i < N) {
-        p0 = means[3 * i]; p1 = means[3 * i + 1]; p2 = means[3 * i + 2];
-        const float s0 = expf(log_scales[3 * i]), s1 = expf(log_scales[3 * i + 1]), s2 = expf(log_scales[3 * i + 2]);
-        float4 q = quats[i];
+        p0 = means[3 * src]; p1 = means[3 * src + 1]; p2 = means[3 * src + 2];
+        const float s0 = expf(log_scales[3 * src]), s1 = expf(log_scales[3 * src + 1]), s2 = expf(log_scales[3 * src + 2]);
+        float4 q = quats[src];
         const float qn = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);   // quats / quats.norm()
         q.x = q.x / qn; q.y = q.y / qn; q.z = q.z / qn; q.w = q.w / qn;
         gs_project_one(cam.viewmat, cam.projmat, p0, p1, p2, s0, s1, s2, cam.glob_scale, q, cam.fx, cam.fy, cam.cx,
                        cam.cy, cam.H, cam.W, cam.tiles_x, cam.tiles_y, cam.clip, o);
-        xys[i] = o.xy;
+        op = 1.0f / (1.0f + expf(-opac_logits[src]));
         depths[i] = o.depth;
         radii[i] = o.radius;
-        conics[3 * i] = o.ca; conics[3 * i + 1] = o.cb; conics[3 * i + 2] = o.cc;
         tiles_hit[i] = o.hit;
-        opac[i] = 1.0f / (1.0f + expf(-opac_logits[i]));
+        if (!PACKED) {
+            xys[i] = o.xy;
+            conics[3 * i] = o.ca; conics[3 * i + 1] = o.cb; conics[3 * i + 2] = o.cc;
+            opac[i] = op;
+        }
     }
 
-    if (need_rest) {
+    if (need_rest && subset) {
+        __syncthreads();
+    } else if (need_rest) {
         __syncthreads();  // mbarrier init + remainder rows visible
         unsigned done = 0;
         while (!done)
@@ -95,11 +112,11 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
                 : "r"(smem_u32(&mbar))
                 : "memory");
     }
-    if (i >= N || PART == 1) return;
+    if (!PACKED && (i >= N || PART == 1)) return;
 
     float r = 0.f, g = 0.f, b = 0.f;
-    if (o.radius > 0) {      // culled Gaussians never reach the compositor: colour left at 0
-        const float d0 = feat_dc[3 * i], d1 = feat_dc[3 * i + 1], d2 = feat_dc[3 * i + 2];
+    if (i < N && o.radius > 0) {      // culled Gaussians never reach the compositor: colour left at 0
+        const float d0 = feat_dc[3 * src], d1 = feat_dc[3 * src + 1], d2 = feat_dc[3 * src + 2];
         if (use_sh) {
             // viewdirs = normalise(means - cam_pos)  (gc_model.py:197-198); the SH routine normalises again
             float vx = p0 - cam.cam_pos[0], vy = p1 - cam.cam_pos[1], vz = p2 - cam.cam_pos[2];
@@ -122,7 +139,19 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
             r = 1.0f / (1.0f + expf(-d0)); g = 1.0f / (1.0f + expf(-d1)); b = 1.0f / (1.0f + expf(-d2));   // :203
         }
     }
-    rgbs[3 * i] = r; rgbs[3 * i + 1] = g; rgbs[3 * i + 2] = b;
+    if (!PACKED) {
+        rgbs[3 * i] = r; rgbs[3 * i + 1] = g; rgbs[3 * i + 2] = b;
+        return;
+    }
+    // PACKED: the CTA's 128 records are one dense 6 144-byte span; they are assembled in shared memory (the SH stage,
+    // free once every thread has consumed its row) and leave with fully coalesced 16-byte stores
+    float4 q0 = make_float4(0.f, 0.f, -1.f, -1.f), q1 = make_float4(0.f, 0.f, 0.f, 0.f), q2 = q1;   // culled: zero row
+    if (i < N && o.radius > 0) gs_make_record(o.xy.x, o.xy.y, o.ca, o.cb, o.cc, op, r, g, b, o.depth, q0, q1, q2);
+    __syncthreads();
+    float4 *rs = reinterpret_cast<float4 *>(rest_s);
+    rs[3 * tid] = q0; rs[3 * tid + 1] = q1; rs[3 * tid + 2] = q2;
+    __syncthreads();
+    for (int f = tid; f < 3 * rows; f += PP_TPB) rec[3 * (size_t)g0 + f] = rs[f];
 }
 
 }  // namespace
@@ -135,11 +164,27 @@ static int launch_preprocess_fwd(int part, int N, const float *means, const floa
     cudaStream_t st = (cudaStream_t)stream;
 #define GS_PP_ARGS                                                                                                       \
     N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, feat_dc, feat_rest, use_sh, sh_deg,       \
-        *cam_host, reinterpret_cast<float2 *>(xys), depths, radii, conics, tiles_hit, rgbs, opac
-    if (part == 0) preprocess_fwd_kernel<0><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
-    else if (part == 1) preprocess_fwd_kernel<1><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
-    else preprocess_fwd_kernel<2><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
+        *cam_host, reinterpret_cast<float2 *>(xys), depths, radii, conics, tiles_hit, rgbs, opac,                        \
+        (const int32_t *)nullptr, (float4 *)nullptr
+    if (part == 0) preprocess_fwd_kernel<0, false><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
+    else if (part == 1) preprocess_fwd_kernel<1, false><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
+    else preprocess_fwd_kernel<2, false><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
 #undef GS_PP_ARGS
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+// internal (view.cu): packed-record form, optional index list; N = number of elements (subset length when given)
+int gs_launch_preprocess_fwd_packed(int N, const float *means, const float *log_scales, const float *quats,
+                                    const float *opac_logits, const float *feat_dc, const float *feat_rest, int use_sh,
+                                    int sh_deg, const GsCamera *cam_host, const int32_t *subset, float *rec, float *depths,
+                                    int32_t *radii, int32_t *tiles_hit, cudaStream_t st) {
+    if (N <= 0) return 0;
+    const int blocks = (N + PP_TPB - 1) / PP_TPB;
+    preprocess_fwd_kernel<0, true><<<blocks, PP_TPB, 0, st>>>(
+        N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
+        *cam_host, (float2 *)nullptr, depths, radii, (float *)nullptr, tiles_hit, (float *)nullptr, (float *)nullptr,
+        subset, reinterpret_cast<float4 *>(rec));
     GS_LAUNCH_CHECK();
     return 0;
 }
@@ -183,4 +228,20 @@ extern "C" int gs_preprocess_fwd_part(int part, int N, const float *means, const
         return GS_ERR_MISALIGNED;
     return launch_preprocess_fwd(part, N, means, log_scales, quats, opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
                                  cam_host, xys, depths, radii, conics, tiles_hit, rgbs, opac, stream);
+}
+
+extern "C" int gs_preprocess_fwd_packed(int N, const float *means, const float *log_scales, const float *quats,
+                                        const float *opac_logits, const float *feat_dc, const float *feat_rest,
+                                        const int32_t *subset, int use_sh, int sh_deg, const GsCamera *cam_host,
+                                        float *rec, float *depths, int32_t *radii, int32_t *tiles_hit, void *stream) {
+    if (N < 0 || !cam_host) return GS_ERR_BAD_ARG;
+    if (sh_deg < 0 || sh_deg > 3) return GS_ERR_UNSUPPORTED;
+    if (cam_host->H <= 0 || cam_host->W <= 0 || cam_host->tiles_x <= 0 || cam_host->tiles_y <= 0) return GS_ERR_BAD_ARG;
+    if (N == 0) return 0;
+    if (!means || !log_scales || !quats || !opac_logits || !feat_dc || !rec || !depths || !radii || !tiles_hit)
+        return GS_ERR_BAD_ARG;
+    if (use_sh && sh_deg >= 1 && !feat_rest) return GS_ERR_BAD_ARG;
+    if (!gs_aligned16(quats) || !gs_aligned16(feat_rest) || !gs_aligned16(rec)) return GS_ERR_MISALIGNED;
+    return gs_launch_preprocess_fwd_packed(N, means, log_scales, quats, opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
+                                           cam_host, subset, rec, depths, radii, tiles_hit, (cudaStream_t)stream);
 }

@@ -302,14 +302,12 @@ inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, con
     const int nb = (int)((n_cap + SUB - 1) / SUB);
     uint32_t *totals = mat + (size_t)nb * RADIX;
     const size_t smem = sizeof(ScatterSmem<KeyT, BITS>);
-    static bool attr_set = false;   // one per template instantiation
-    if (!attr_set) {
-        if (smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute((const void *)scatter_kernel<KeyT, BITS, FROM_DEPTH>,
-                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return (int)e;
-        }
-        attr_set = true;
+    // the attribute is per DEVICE: set it on every launch (a few hundred ns) rather than once per process — a second
+    // GPU in the same process (tests, tools, set_device after first use) would otherwise launch without the opt-in
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute((const void *)scatter_kernel<KeyT, BITS, FROM_DEPTH>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
     }
     GS_PDL_LAUNCH((hist_kernel<KeyT, BITS, FROM_DEPTH>), nb, TPB, 0, st, n_cap, n_dev, kin, radii, shift, bits, mat, nb);
     GS_PDL_LAUNCH((colscan_kernel<BITS>), (RADIX + WARPS - 1) / WARPS, TPB, 0, st, n_cap, n_dev, mat, nb, totals);

@@ -6,6 +6,7 @@ Differentiable w.r.t. xys, conics, colors, opacity (exact derivative of the forw
 """
 from __future__ import annotations
 
+import weakref
 from typing import Optional
 
 import torch
@@ -30,11 +31,13 @@ def _binning(xys, depths, radii, num_tiles_hit, H, W):
     if BINNING_CACHE:
         sig = (xys._version, depths._version, radii._version, H, W)
         hit = _bin_cache.get(xys.device.index)
-        if hit is not None and hit[0] is xys and hit[1] is depths and hit[2] is radii and hit[3] == sig:
+        # weak references: the cache keeps neither the caller's tensors nor their autograd graph alive, and a
+        # recycled allocation (same address, new tensor) can never hit
+        if hit is not None and hit[0]() is xys and hit[1]() is depths and hit[2]() is radii and hit[3] == sig:
             return hit[4], tile_bounds
     res = bin_fast(xys, depths, radii, num_tiles_hit, tile_bounds)
     if BINNING_CACHE:
-        _bin_cache[xys.device.index] = (xys, depths, radii, sig, res)
+        _bin_cache[xys.device.index] = (weakref.ref(xys), weakref.ref(depths), weakref.ref(radii), sig, res)
     return res, tile_bounds
 
 
@@ -86,6 +89,12 @@ def rasterize_gaussians(
 
 
 class _RasterizeGaussians(Function):
+    """Three channels (the RGB call of gc_model.py:208 and the replicated-depth call of :225) run on the packed
+    compositing kernels: the operator's tensors are packed once per call into 48-byte splat records
+    (gs_pack_splats, one pass over N), the tiles are launched heaviest-first, and forward / backward are
+    gs_raster_fwd_packed / gs_raster_bwd_packed — the same kernels the fused path uses. Other channel counts go
+    through the generic kernels (gs_raster_fwd / gs_raster_bwd)."""
+
     @staticmethod
     def forward(ctx, xys, conics, colors, opacity, background, ids_sorted, tile_bins, H, W, tb,
                 return_alpha=False):
@@ -100,24 +109,40 @@ class _RasterizeGaussians(Function):
         out_img = torch.empty((H, W, C), device=dev, dtype=torch.float32)
         final_T = torch.empty((H, W), device=dev, dtype=torch.float32)
         final_idx = torch.empty((H, W), device=dev, dtype=torch.int32)
+        L = _lib.lib()
+        T = tb[0] * tb[1]
+        rec = order = work = None
         with torch.cuda.device(dev):
-            rc = _lib.lib().gs_raster_fwd(
-                C, H, W, tb[0], tb[1], _lib.ptr(ids_sorted), _lib.ptr(tile_bins), _lib.ptr(xys_f),
-                _lib.ptr(conics_f), _lib.ptr(colors_f), _lib.ptr(opac_f), _lib.ptr(bg), _lib.ptr(out_img),
-                _lib.ptr(final_T), _lib.ptr(final_idx), _lib.stream_ptr())
+            st = _lib.stream_ptr()
+            if C == 3:
+                rec = torch.empty((N, 12), device=dev, dtype=torch.float32)
+                order = torch.empty((T,), device=dev, dtype=torch.int32)
+                work = torch.empty((T,), device=dev, dtype=torch.int32)
+                _lib.check(L.gs_pack_splats(N, _lib.ptr(xys_f), _lib.ptr(conics_f), _lib.ptr(colors_f), _lib.ptr(opac_f),
+                                            None, _lib.ptr(rec), st), "gs_pack_splats")
+                _lib.check(L.gs_tile_order(T, _lib.ptr(tile_bins), 1, _lib.ptr(order), st), "gs_tile_order")
+                rc = L.gs_raster_fwd_packed(1, H, W, tb[0], tb[1], _lib.ptr(ids_sorted), _lib.ptr(tile_bins), _lib.ptr(rec),
+                                            _lib.ptr(bg), _lib.ptr(out_img), None, _lib.ptr(final_T), _lib.ptr(final_idx),
+                                            _lib.ptr(order), _lib.ptr(work), None, None, st)
+            else:
+                rc = L.gs_raster_fwd(
+                    C, H, W, tb[0], tb[1], _lib.ptr(ids_sorted), _lib.ptr(tile_bins), _lib.ptr(xys_f),
+                    _lib.ptr(conics_f), _lib.ptr(colors_f), _lib.ptr(opac_f), _lib.ptr(bg), _lib.ptr(out_img),
+                    _lib.ptr(final_T), _lib.ptr(final_idx), st)
         _lib.check(rc, "gs_raster_fwd")
-        ctx.save_for_backward(ids_sorted, tile_bins, xys_f, conics_f, colors_f, opac_f, bg, final_T, final_idx)
-        ctx.meta = (H, W, C, tb, tuple(opacity.shape))
+        if C == 3:
+            ctx.save_for_backward(ids_sorted, tile_bins, rec, work, bg, final_T, final_idx)
+        else:
+            ctx.save_for_backward(ids_sorted, tile_bins, xys_f, conics_f, colors_f, opac_f, bg, final_T, final_idx)
+        ctx.meta = (H, W, C, tb, tuple(opacity.shape), N)
         if return_alpha:
             return out_img, 1.0 - final_T
         return out_img
 
     @staticmethod
     def backward(ctx, v_out_img, v_out_alpha=None):
-        ids_sorted, tile_bins, xys, conics, colors, opac, bg, final_T, final_idx = ctx.saved_tensors
-        H, W, C, tb, opac_shape = ctx.meta
-        N = xys.shape[0]
-        dev = xys.device
+        H, W, C, tb, opac_shape, N = ctx.meta
+        dev = v_out_img.device
         v_out_img = v_out_img.float().contiguous()
         if v_out_alpha is not None:
             v_out_alpha = v_out_alpha.float().contiguous()
@@ -125,11 +150,23 @@ class _RasterizeGaussians(Function):
         v_conics = torch.zeros((N, 3), device=dev, dtype=torch.float32)
         v_colors = torch.zeros((N, C), device=dev, dtype=torch.float32)
         v_opac = torch.zeros((N,), device=dev, dtype=torch.float32)
+        L = _lib.lib()
         with torch.cuda.device(dev):
-            rc = _lib.lib().gs_raster_bwd(
-                C, H, W, tb[0], tb[1], _lib.ptr(ids_sorted), _lib.ptr(tile_bins), _lib.ptr(xys), _lib.ptr(conics),
-                _lib.ptr(colors), _lib.ptr(opac), _lib.ptr(bg), _lib.ptr(final_T), _lib.ptr(final_idx),
-                _lib.ptr(v_out_img), _lib.ptr(v_out_alpha), _lib.ptr(v_xys), _lib.ptr(v_conics),
-                _lib.ptr(v_colors), _lib.ptr(v_opac), _lib.stream_ptr())
+            st = _lib.stream_ptr()
+            if C == 3:
+                ids_sorted, tile_bins, rec, work, bg, final_T, final_idx = ctx.saved_tensors
+                order = torch.empty_like(work)
+                _lib.check(L.gs_tile_order(tb[0] * tb[1], _lib.ptr(work), 0, _lib.ptr(order), st), "gs_tile_order")
+                rc = L.gs_raster_bwd_packed(H, W, tb[0], tb[1], _lib.ptr(ids_sorted), _lib.ptr(tile_bins), _lib.ptr(rec),
+                                            _lib.ptr(bg), _lib.ptr(final_T), _lib.ptr(final_idx), _lib.ptr(v_out_img),
+                                            _lib.ptr(v_out_alpha), _lib.ptr(v_xys), _lib.ptr(v_conics), _lib.ptr(v_colors),
+                                            _lib.ptr(v_opac), _lib.ptr(order), None, st)
+            else:
+                ids_sorted, tile_bins, xys, conics, colors, opac, bg, final_T, final_idx = ctx.saved_tensors
+                rc = L.gs_raster_bwd(
+                    C, H, W, tb[0], tb[1], _lib.ptr(ids_sorted), _lib.ptr(tile_bins), _lib.ptr(xys), _lib.ptr(conics),
+                    _lib.ptr(colors), _lib.ptr(opac), _lib.ptr(bg), _lib.ptr(final_T), _lib.ptr(final_idx),
+                    _lib.ptr(v_out_img), _lib.ptr(v_out_alpha), _lib.ptr(v_xys), _lib.ptr(v_conics),
+                    _lib.ptr(v_colors), _lib.ptr(v_opac), st)
         _lib.check(rc, "gs_raster_bwd")
         return (v_xys, v_conics, v_colors, v_opac.view(opac_shape), None, None, None, None, None, None, None)

@@ -1,18 +1,27 @@
-"""Fused per-view render: ONE autograd node from the six splatfacto leaf tensors to (rgb, alpha).
+"""Fused per-view render: ONE autograd node from the six splatfacto leaf tensors to (rgb, alpha), and ONE C-ABI call
+per direction.
 
 Same result as the three-operator sequence of /root/reference/gaussctrl/gc_model.py:172-222
 (pre-activations -> project_gaussians -> spherical_harmonics -> rasterize_gaussians) and its
-backward (gc_trainer.py:275), but as five kernel launches per training view:
-    forward : gs_preprocess_fwd -> gs_bin_fast -> gs_raster_fwd
-    backward: gs_raster_bwd -> gs_preprocess_bwd
-with no device->host synchronisation other than one 4-byte read of the intersection count, which
-is overlapped with the compositing kernel (the tile lists are allocated speculatively; the read
-only confirms the capacity was enough, otherwise the binning is redone).
+backward (gc_trainer.py:275):
+    forward : gs_view_fwd  = preprocess (-> packed splat records) -> binning -> tile order -> compositing
+    backward: gs_view_bwd  = tile order -> compositing backward -> leaf backward
+Each is a single ctypes call that enqueues the whole kernel chain from C (csrc/view.cu). Everything a view keeps
+between forward and backward lives in ONE workspace tensor whose layout the library reports (gs_view_layout).
+
+Tile-list capacity. ids_sorted is allocated for a capacity learnt from earlier views of the same shape; the true
+intersection count is copied to a pinned host word right behind the binning. By default the host reads that word after
+it has enqueued the compositing kernel (the wait ends when the BINNING is done, while compositing still runs, so the
+device never idles) and redoes the view if the capacity was too small: a caller never sees a torn image.
+`speculate=True` skips even that wait; an overflow then shows as a NaN image (the compositing kernel poisons it) and
+as CapacityOverflow at the end of backward.
 """
 from __future__ import annotations
 
+import ctypes
 import math
-from typing import Optional, Tuple
+import os as _os
+from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -22,28 +31,22 @@ from torch.autograd import Function
 from . import _lib
 from .scene import Camera
 
-# Training views (render_view under autograd): do not read the intersection count in the forward; verify it
-# at the end of backward instead (raises CapacityOverflow, before any gradient is returned, in the unlikely
-# case the count grew by more than 50 % between consecutive views of the same shape).
-SPECULATE = True
-
-# "tile": count / scan / scatter / per-tile shared-memory sort (gs_bin_tile, 5 launches);
-# "lsd": global depth sort + stable partition by tile (gs_bin_fast). Identical outputs.
-import os as _os
-BIN_IMPL = _os.environ.get("GS_BIN_IMPL", "lsd")
+# Fully asynchronous training forward (see module docstring). Off by default: correctness first.
+SPECULATE = _os.environ.get("GS_SPECULATE") is not None
 
 _cam_cache = {}
 _cap_hint = {}
 _scratch = {}
-_pinned = {}
+_pinned_free = {}
 
 
 def gs_camera(camera: Camera, glob_scale: float = 1.0, clip: float = 0.01) -> _lib.GsCamera:
-    """Host-side matrices of gc_model.py:117-155 packed into the C struct (cached per camera)."""
-    key = id(camera)
+    """Host-side matrices of gc_model.py:117-155 packed into the C struct. Cached by VALUE (pose + intrinsics):
+    an in-place update of the camera (pose optimiser, rescale_output_resolution) can never hit a stale entry."""
+    key = (camera.signature(), float(glob_scale), float(clip))
     hit = _cam_cache.get(key)
-    if hit is not None and hit[0] is camera:
-        return hit[1]
+    if hit is not None:
+        return hit
     c2w = camera.c2w.detach().cpu().numpy().astype(np.float32)
     W, H = int(camera.W), int(camera.H)
     R = c2w[:3, :3] @ np.diag(np.array([1, -1, -1], np.float32))       # :129-130
@@ -72,7 +75,7 @@ def gs_camera(camera: Camera, glob_scale: float = 1.0, clip: float = 0.01) -> _l
     cam.tiles_x, cam.tiles_y = (W + 15) // 16, (H + 15) // 16
     if len(_cam_cache) > 4096:
         _cam_cache.clear()
-    _cam_cache[key] = (camera, cam)
+    _cam_cache[key] = cam
     return cam
 
 
@@ -87,67 +90,114 @@ def _get_scratch(dev, nbytes):
     return buf
 
 
-_side = {}
-# Opt-in (GS_SPLIT_COLOR=1): run the SH colour half of the preprocess on a side stream underneath the binning chain.
-# Measured SLOWER (0.787 vs 0.772 ms/step): the colour kernel's 7 800 CTAs flood the SMs and the short binning kernels
-# queue behind them (no stream below the default priority exists to demote it).
-SPLIT_COLOR = _os.environ.get("GS_SPLIT_COLOR") is not None
+class _Pending:
+    """One in-flight intersection count: its OWN pinned word + event (never shared between views)."""
+    __slots__ = ("pinned", "event", "cap", "key", "dev")
 
+    def __init__(self, dev):
+        free = _pinned_free.setdefault(dev.index, [])
+        if free:
+            self.pinned, self.event = free.pop()
+        else:
+            self.pinned, self.event = torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event()
+            self.event.record(torch.cuda.current_stream(dev))    # creates the cudaEvent_t the library records later
+        self.dev, self.cap, self.key = dev, 0, None
 
-def _get_side_stream(dev, cur):
-    """(side stream, geometry-done event, colour-done event) paired with the stream `cur`; the events come from a
-    small ring because several views may be in flight on one stream."""
-    key = (dev.index, cur.cuda_stream)
-    ent = _side.get(key)
-    if ent is None:
-        ent = {"stream": torch.cuda.Stream(device=dev),
-               "events": [(torch.cuda.Event(), torch.cuda.Event()) for _ in range(8)], "next": 0}
-        _side[key] = ent
-    a, b = ent["events"][ent["next"]]
-    ent["next"] = (ent["next"] + 1) % len(ent["events"])
-    return ent["stream"], a, b
-
-
-_RING = 16
-
-
-def _get_pinned(dev):
-    """Next (pinned int32[1], event) slot of a small per-device ring: several views may be in flight
-    before the host looks at their intersection counts."""
-    ring = _pinned.get(dev.index)
-    if ring is None:
-        ring = {"slots": [(torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event()) for _ in range(_RING)],
-                "next": 0}
-        _pinned[dev.index] = ring
-    slot = ring["slots"][ring["next"]]
-    ring["next"] = (ring["next"] + 1) % _RING
-    return slot
+    def wait(self) -> int:
+        """Blocks until the count has landed; returns it and recycles the slot."""
+        self.event.synchronize()
+        I = int(self.pinned[0])
+        _pinned_free[self.dev.index].append((self.pinned, self.event))
+        self.pinned = self.event = None
+        return I
 
 
 class CapacityOverflow(RuntimeError):
-    """Raised by the deferred check of a speculative (non-strict) forward: the tile lists did not fit the
-    speculative capacity, so that view's image/gradients are invalid. The capacity hint has already been
-    raised: re-running the step succeeds."""
+    """speculate=True only: the tile lists of a view did not fit the speculative capacity. The image the forward
+    returned was NaN-poisoned; no gradient is handed out. The capacity hint has been raised: re-running succeeds."""
 
 
-def _check_pending(pending):
-    pinned, ev, cap, key = pending
-    ev.synchronize()
-    I = int(pinned[0])
-    if I > cap:
-        _cap_hint[key] = int(I * 1.5) + 1024
-        raise CapacityOverflow(f"{I} intersections exceed the speculative capacity {cap}; re-run this view")
-    _cap_hint[key] = max(_cap_hint.get(key, 0), int(I * 1.5) + 1024)
-    return I
+def _raise_hint(key, I):
+    _cap_hint[key] = max(_cap_hint.get(key, 0), int(I * 1.5) + 1024)      # monotone: never shrinks
+
+
+class ViewWorkspace:
+    """Everything one forward leaves behind for the backward and for the caller (gc_model.py keeps self.xys /
+    self.radii): one uint8 tensor + typed views of it, following gs_view_layout."""
+
+    def __init__(self, dev, n: int, views: int, cap: int, T_view: int):
+        L = _lib.lib()
+        lay = _lib.GsViewLayout()
+        _lib.check(L.gs_view_layout(n, views, cap, T_view, ctypes.byref(lay)), "gs_view_layout")
+        self.n, self.views, self.cap, self.T_view, self.lay = n, views, cap, T_view, lay
+        self.buf = torch.empty(lay.bytes, device=dev, dtype=torch.uint8)
+
+    def _view(self, off, count, dtype):
+        nbytes = count * 4
+        return self.buf[off:off + nbytes].view(dtype)
+
+    @property
+    def rec(self):                      # (views*n, 12) packed splat records
+        return self._view(self.lay.rec, self.n * self.views * 12, torch.float32).view(-1, 12)
+
+    @property
+    def xys(self):                      # strided views into the records: no copies
+        return self.rec[:, 0:2]
+
+    @property
+    def opac(self):
+        return self.rec[:, 4]
+
+    @property
+    def rgbs(self):
+        return self.rec[:, 8:11]
+
+    @property
+    def depths(self):
+        return self._view(self.lay.depths, self.n * self.views, torch.float32)
+
+    @property
+    def radii(self):
+        return self._view(self.lay.radii, self.n * self.views, torch.int32)
+
+    @property
+    def num_tiles_hit(self):
+        return self._view(self.lay.tiles_hit, self.n * self.views, torch.int32)
+
+    @property
+    def ids_sorted(self):
+        return self._view(self.lay.ids_sorted, self.cap, torch.int32)
+
+    @property
+    def tile_bins(self):
+        return self._view(self.lay.tile_bins, self.T_view * self.views * 2, torch.int32).view(-1, 2)
+
+    @property
+    def tile_work(self):
+        return self._view(self.lay.tile_work, self.T_view * self.views, torch.int32)
+
+    @property
+    def total(self):
+        return self._view(self.lay.total, 1, torch.int32)
+
+    def conics(self):
+        """True conics (a, b, c) recovered from the records' pre-scaled form (diagnostics / tests)."""
+        q = self.rec[:, 5:8]
+        k = 1.0 / 1.4426950408889634
+        return torch.stack((q[:, 0] * (-2.0 * k), q[:, 1] * (-1.0 * k), q[:, 2] * (-2.0 * k)), dim=1)
 
 
 class ViewState:
     """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii)."""
     __slots__ = ("xys", "radii", "depths", "num_intersects", "xys_grad", "flat_grads", "defer_leaf_grads",
-                 "view_block", "view_meta", "view_block_buffer")
+                 "view_block", "view_meta", "view_block_buffer", "num_tiles_hit", "ids_sorted", "tile_bins",
+                 "final_idx", "final_T", "workspace")
 
     def __init__(self):
         self.xys = self.radii = self.depths = self.xys_grad = self.flat_grads = None
+        # integer by-products of the last view (what gsplat's rasterize keeps for its backward); the parity
+        # tests compare them bit for bit with the oracle
+        self.num_tiles_hit = self.ids_sorted = self.tile_bins = self.final_idx = self.final_T = self.workspace = None
         self.num_intersects = 0
         # data-parallel mode (dist.reduce_view_grads): backward stops at the compositor-level gradients,
         # leaves them (+ the camera) in view_block and returns no leaf gradients
@@ -158,120 +208,106 @@ class ViewState:
         self.view_block_buffer = None
 
 
-def _forward_impl(means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, strict=True,
-                  with_depth=False, post=None):
-    """strict=True: the host confirms the tile-list capacity before returning (one 4-byte read, overlapped
-    with the compositing kernel; overflow -> redo). strict=False: nothing is read; the caller must run
-    _check_pending(result[-1]) before trusting the view (render_view does it at the end of backward).
-    post: optional dict; the compositing kernel then also writes the caller's per-pixel post-ops
-    (gc_model.py:221-222) and the dict receives "rgb_clamped" = clamp(out, max=1) and "alpha" = 1 - final_T."""
+class ViewImages:
+    """Image-shaped outputs of one forward, carved from ONE allocation."""
+
+    def __init__(self, dev, views: int, H: int, W: int, with_depth: bool):
+        hw = views * H * W
+        self.buf = torch.empty((10 if with_depth else 9) * hw, device=dev, dtype=torch.float32)
+        b = self.buf
+        shape3 = (views, H, W, 3) if views > 1 else (H, W, 3)
+        shape1 = (views, H, W) if views > 1 else (H, W)
+        self.out = b[0:3 * hw].view(shape3)
+        self.out_clamped = b[3 * hw:6 * hw].view(shape3)
+        self.alpha = b[6 * hw:7 * hw].view(shape1)
+        self.final_T = b[7 * hw:8 * hw].view(shape1)
+        self.final_idx = b[8 * hw:9 * hw].view(torch.int32).view(shape1)
+        self.depth = b[9 * hw:10 * hw].view(shape1) if with_depth else None
+
+
+def forward_views(means, scales, quats, opacities, features_dc, features_rest, cams: Sequence[_lib.GsCamera],
+                  use_sh: bool, deg: int, bg: Tensor, with_depth: bool = False, subset: Optional[Tensor] = None,
+                  speculate: bool = False) -> Tuple[ViewWorkspace, ViewImages, Optional[int], Optional[_Pending]]:
+    """gs_view_fwd for `len(cams)` cameras of one image size over the same Gaussians (detached, contiguous fp32
+    CUDA tensors). Returns (workspace, images, intersection count | None, pending | None): with speculate=False the
+    count has been verified (the view was redone with a larger capacity if necessary); with speculate=True nothing
+    was read and the caller must call check_pending(pending) before trusting the view."""
     L = _lib.lib()
     dev = means.device
-    N = means.shape[0]
-    H, W, tx, ty = cam.H, cam.W, cam.tiles_x, cam.tiles_y
-    T = tx * ty
-    Np = (N + 3) // 4 * 4
-    fbuf = torch.empty(10 * Np, device=dev, dtype=torch.float32)
-    ibuf = torch.empty(2 * Np, device=dev, dtype=torch.int32)
-    xys = fbuf[0:2 * N].view(N, 2)
-    depths = fbuf[2 * Np:2 * Np + N]
-    conics = fbuf[3 * Np:3 * Np + 3 * N].view(N, 3)
-    rgbs = fbuf[6 * Np:6 * Np + 3 * N].view(N, 3)
-    opac = fbuf[9 * Np:9 * Np + N]
-    radii, hit = ibuf[0:N], ibuf[Np:Np + N]
-    st = _lib.stream_ptr()
-    color_done = None
-    pp_args = (N, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(),
-               features_dc.data_ptr(), features_rest.data_ptr(), int(use_sh), int(deg),
-               _ctypes_addr(cam), xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), conics.data_ptr(),
-               hit.data_ptr(), rgbs.data_ptr(), opac.data_ptr())
-    if SPLIT_COLOR:
-        # geometry on this stream (the binning chain needs nothing else); the SH colour pass — 216 of the 284 bytes
-        # per Gaussian — on a side stream, underneath the latency-bound binning kernels; joined before compositing.
-        # fbuf outlives the join, and everything later on this stream is ordered after it: no record_stream needed.
-        rc = L.gs_preprocess_fwd_part(1, *pp_args, st)
-        _lib.check(rc, "gs_preprocess_fwd_part(geometry)")
-        cur = torch.cuda.current_stream(dev)
-        side, geom_done, color_done = _get_side_stream(dev, cur)
-        geom_done.record(cur)
-        side.wait_event(geom_done)
-        rc = L.gs_preprocess_fwd_part(2, *pp_args, side.cuda_stream)
-        _lib.check(rc, "gs_preprocess_fwd_part(colour)")
-        color_done.record(side)
-    else:
-        rc = L.gs_preprocess_fwd(*pp_args, st)
-        _lib.check(rc, "gs_preprocess_fwd")
-    key = (dev.index, N, T)
+    n = int(subset.shape[0]) if subset is not None else means.shape[0]
+    views = len(cams)
+    c0 = cams[0]
+    H, W, T_view = c0.H, c0.W, c0.tiles_x * c0.tiles_y
+    cam_arr = (_lib.GsCamera * views)(*cams) if views > 1 else c0
+    key = (dev.index, n, views, T_view)
     known = key in _cap_hint
-    cap = _cap_hint.get(key, max(4 * N, 1024))
-    strict = strict or not known           # never speculate blindly on the first view of a shape
-    bins = torch.empty((T, 2), device=dev, dtype=torch.int32)
-    total = torch.empty(1, device=dev, dtype=torch.int32)
-    out = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
-    fT = torch.empty((H, W), device=dev, dtype=torch.float32)
-    fidx = torch.empty((H, W), device=dev, dtype=torch.int32)
-    out_depth = torch.empty((H, W), device=dev, dtype=torch.float32) if with_depth else None
-    order_f = torch.empty((T,), device=dev, dtype=torch.int32)
-    tile_work = torch.empty((T,), device=dev, dtype=torch.int32)
-    out_c = alpha = None
-    if post is not None:
-        out_c = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
-        alpha = torch.empty((H, W), device=dev, dtype=torch.float32)
-        post["rgb_clamped"], post["alpha"] = out_c, alpha
+    cap = _cap_hint.get(key, max(4 * n * views, 1024))
+    speculate = speculate and known           # never speculate blindly on the first view of a shape
+    st = _lib.stream_ptr()
     while True:
-        ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
-        if BIN_IMPL == "tile":
-            scratch = _get_scratch(dev, L.gs_bin_tile_scratch_bytes(N, cap, T))
-            rc = L.gs_bin_tile(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), tx, ty,
-                               ids_sorted.data_ptr(), bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
-                               scratch.numel(), st)
-        else:
-            scratch = _get_scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T))
-            rc = L.gs_bin_fast(N, cap, xys.data_ptr(), depths.data_ptr(), radii.data_ptr(), hit.data_ptr(), tx, ty,
-                               ids_sorted.data_ptr(), bins.data_ptr(), total.data_ptr(), scratch.data_ptr(),
-                               scratch.numel(), st)
-        _lib.check(rc, "gs_bin_tile/fast")
-        pinned, ev = _get_pinned(dev)
-        pinned.copy_(total, non_blocking=True)
-        ev.record()
-        # compositing is enqueued BEFORE the host looks at the count: it only reads tile_bins
-        # tiles are launched heaviest-first (list length as the forward's work proxy); the forward records
-        # each tile's true depth of composition, which orders the backward
-        rc = L.gs_tile_order(T, bins.data_ptr(), 1, order_f.data_ptr(), st)
-        _lib.check(rc, "gs_tile_order")
-        if color_done is not None:
-            torch.cuda.current_stream(dev).wait_event(color_done)
-            color_done = None
-        rc = L.gs_raster_fwd_ordered_post(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                          conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(),
-                                          depths.data_ptr() if with_depth else None, bg.data_ptr(), out.data_ptr(),
-                                          out_depth.data_ptr() if with_depth else None, fT.data_ptr(),
-                                          fidx.data_ptr(), order_f.data_ptr(), tile_work.data_ptr(),
-                                          _lib.ptr(out_c), _lib.ptr(alpha), st)
-        _lib.check(rc, "gs_raster_fwd")
-        if not strict:
-            return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, None,
-                    (pinned, ev, cap, key), tile_work)
-        ev.synchronize()
-        I = int(pinned[0])
+        ws = ViewWorkspace(dev, n, views, cap, T_view)
+        im = ViewImages(dev, views, H, W, with_depth)
+        scratch = _get_scratch(dev, L.gs_view_scratch_bytes(n, views, cap, T_view))
+        pend = _Pending(dev)
+        pend.cap, pend.key = cap, key
+        rc = L.gs_view_fwd(n, views, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(),
+                           features_dc.data_ptr(), features_rest.data_ptr(), _lib.ptr(subset), int(use_sh), int(deg),
+                           ctypes.addressof(cam_arr), bg.data_ptr(), cap, ws.buf.data_ptr(), ws.buf.numel(),
+                           scratch.data_ptr(), scratch.numel(), im.out.data_ptr(), im.out_clamped.data_ptr(),
+                           im.alpha.data_ptr(), _lib.ptr(im.depth), im.final_T.data_ptr(), im.final_idx.data_ptr(),
+                           pend.pinned.data_ptr(), pend.event.cuda_event, st)
+        _lib.check(rc, "gs_view_fwd")
+        # the library recorded the event right behind the count copy, BEFORE it enqueued the compositing kernel:
+        # waiting here ends when the binning is done, while the compositing still runs
+        if speculate:
+            return ws, im, None, pend
+        I = pend.wait()
         if I <= cap:
-            _cap_hint[key] = max(int(I * 1.5) + 1024, 1024)
-            break
-        cap = int(I * 1.5) + 1024      # capacity was too small: nothing was composited from a torn list; redo
-    if with_depth:
-        return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, out_depth, tile_work)
-    return (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, None, tile_work)
+            _raise_hint(key, I)
+            return ws, im, I, None
+        cap = int(I * 1.5) + 1024       # capacity was too small: the binning wrote nothing; redo with room
 
 
-def _ctypes_addr(struct):
-    import ctypes
-    return ctypes.addressof(struct)
+def check_pending(pend: _Pending) -> int:
+    cap, key = pend.cap, pend.key
+    I = pend.wait()
+    _raise_hint(key, I)
+    if I > cap:
+        raise CapacityOverflow(f"{I} intersections exceed the speculative capacity {cap}; re-run this view")
+    return I
+
+
+def backward_view(means, scales, quats, opacities, cam: _lib.GsCamera, use_sh: bool, deg: int, bg: Tensor,
+                  ws: ViewWorkspace, final_T: Tensor, final_idx: Tensor, v_out: Tensor, v_alpha: Optional[Tensor],
+                  clamp_ref: Optional[Tensor], gbuf: Optional[Tensor] = None, leaf_grads: bool = True):
+    """gs_view_bwd. Returns (gbuf = compositor-level gradient block, flat = 59*Np leaf-gradient buffer | None)."""
+    L = _lib.lib()
+    dev = means.device
+    n = ws.n
+    Np = (n + 3) // 4 * 4
+    if gbuf is None:
+        gbuf = torch.empty(9 * Np + 64, device=dev, dtype=torch.float32)      # zero-filled by the library
+    flat = torch.empty(59 * Np, device=dev, dtype=torch.float32) if leaf_grads else None
+    rc = L.gs_view_bwd(n, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(), int(use_sh),
+                       int(deg), ctypes.addressof(cam), bg.data_ptr(), ws.buf.data_ptr(), ws.buf.numel(), ws.cap,
+                       final_T.data_ptr(), final_idx.data_ptr(), v_out.data_ptr(), _lib.ptr(v_alpha),
+                       _lib.ptr(clamp_ref), gbuf.data_ptr(), _lib.ptr(flat), _lib.stream_ptr())
+    _lib.check(rc, "gs_view_bwd")
+    return gbuf, flat
+
+
+def split_flat_grads(flat: Tensor, n: int, opac_shape):
+    """The six leaf gradients as views of the flat 59*Np buffer (layout of gs_view_bwd)."""
+    Np = (n + 3) // 4 * 4
+    return (flat[0:3 * n].view(n, 3), flat[3 * Np:3 * Np + 3 * n].view(n, 3), flat[6 * Np:6 * Np + 4 * n].view(n, 4),
+            flat[10 * Np:10 * Np + n].view(opac_shape), flat[11 * Np:11 * Np + 3 * n].view(n, 3),
+            flat[14 * Np:14 * Np + 45 * n].view(n, 15, 3))
 
 
 class _RenderView(Function):
     @staticmethod
     def forward(ctx, means, scales, quats, opacities, features_dc, features_rest, cam, use_sh, deg, bg, state,
-                clamp_rgb=False):
+                clamp_rgb=False, speculate=False):
         for t, shape in ((means, 3), (scales, 3), (quats, 4), (features_dc, 3)):
             if t.ndim != 2 or t.shape[1] != shape or t.shape[0] != means.shape[0]:
                 raise ValueError("means/scales (N,3), quats (N,4), features_dc (N,3) expected")
@@ -281,99 +317,68 @@ class _RenderView(Function):
             raise ValueError("features_rest must have dimensions (N, 15, 3)")
         args = [t.detach().float().contiguous() for t in (means, scales, quats, opacities, features_dc, features_rest)]
         bg = bg.detach().to(means.device).float().contiguous()
-        post = {}
         with torch.cuda.device(means.device):
-            (xys, depths, conics, rgbs, opac, radii, hit, ids_sorted, bins, out, fT, fidx, I, pending,
-             tile_work) = _forward_impl(*args, cam, use_sh, deg, bg, strict=not SPECULATE, post=post)
-        ctx.pending = pending
+            ws, im, I, pend = forward_views(*args, [cam], use_sh, deg, bg, speculate=speculate)
+        ctx.pending = pend
+        ctx.ws, ctx.im = ws, im
         # clamp_rgb: the returned colour is clamp(out, max=1) (written by the compositing kernel) and the raw
         # colour is kept so that the backward kernel can mask the incoming gradient like torch.clamp's backward
-        ctx.save_for_backward(*args, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT, fidx, tile_work,
-                              out if clamp_rgb else None)
+        ctx.clamp_rgb = clamp_rgb
+        ctx.save_for_backward(*args[:4], bg)
         ctx.cam, ctx.use_sh, ctx.deg, ctx.state = cam, use_sh, deg, state
+        ctx.opac_shape = tuple(opacities.shape)
+        depths, radii, hit = ws.depths, ws.radii, ws.num_tiles_hit
         if state is not None:
-            state.xys, state.radii, state.depths, state.num_intersects = xys, radii, depths, I
+            state.xys, state.radii, state.depths, state.num_intersects = ws.xys, radii, depths, I
+            state.num_tiles_hit, state.ids_sorted, state.tile_bins = hit, ws.ids_sorted, ws.tile_bins
+            state.final_idx, state.final_T, state.workspace = im.final_idx, im.final_T, ws
         ctx.mark_non_differentiable(depths, radii, hit)
         ctx.set_materialize_grads(False)      # unused outputs arrive as None instead of freshly filled zeros
-        return (post["rgb_clamped"] if clamp_rgb else out), post["alpha"], depths, radii, hit
+        return (im.out_clamped if clamp_rgb else im.out), im.alpha, depths, radii, hit
 
     @staticmethod
     def backward(ctx, v_out, v_alpha, *_unused):
-        (means, scales, quats, opacities, fdc, frest, bg, xys, conics, rgbs, opac, radii, ids_sorted, bins, fT,
-         fidx, tile_work, clamp_ref) = ctx.saved_tensors
-        cam = ctx.cam
-        L = _lib.lib()
+        means, scales, quats, opacities, bg = ctx.saved_tensors
+        cam, ws, im = ctx.cam, ctx.ws, ctx.im
         dev = means.device
-        N = means.shape[0]
-        H, W, tx, ty = cam.H, cam.W, cam.tiles_x, cam.tiles_y
+        n = means.shape[0]
+        H, W = cam.H, cam.W
         if v_out is None:                       # only alpha was used downstream
             v_out = torch.zeros((H, W, 3), device=dev, dtype=torch.float32)
         v_out = v_out.float().contiguous()
-        va_ptr = None
         if v_alpha is not None:
             v_alpha = v_alpha.float().contiguous()
-            va_ptr = v_alpha.data_ptr()
-        Np = (N + 3) // 4 * 4
+        defer = ctx.state is not None and ctx.state.defer_leaf_grads
+        ext = ctx.state.view_block_buffer if defer else None
+        Np = (n + 3) // 4 * 4
+        if ext is not None:
+            assert ext.numel() == 9 * Np + 64 and ext.is_contiguous() and ext.dtype == torch.float32
         with torch.cuda.device(dev):
-            st = _lib.stream_ptr()
-            ext = ctx.state.view_block_buffer if (ctx.state is not None and ctx.state.defer_leaf_grads) else None
-            if ext is not None:
-                assert ext.numel() == 9 * Np + 64 and ext.is_contiguous() and ext.dtype == torch.float32
-                g = ext
-                g.zero_()
-            else:
-                g = torch.zeros(9 * Np + 64, device=dev, dtype=torch.float32)    # accumulated into by atomics
-            v_xys = g[0:2 * N].view(N, 2)
-            v_conics = g[2 * Np:2 * Np + 3 * N].view(N, 3)
-            v_rgbs = g[5 * Np:5 * Np + 3 * N].view(N, 3)
-            v_opac = g[8 * Np:8 * Np + N]
-            order_b = torch.empty_like(tile_work)
-            rc = L.gs_tile_order(tx * ty, tile_work.data_ptr(), 0, order_b.data_ptr(), st)
-            _lib.check(rc, "gs_tile_order")
-            rc = L.gs_raster_bwd_ordered_post(H, W, tx, ty, ids_sorted.data_ptr(), bins.data_ptr(), xys.data_ptr(),
-                                              conics.data_ptr(), rgbs.data_ptr(), opac.data_ptr(), bg.data_ptr(),
-                                              fT.data_ptr(), fidx.data_ptr(), v_out.data_ptr(), va_ptr,
-                                              v_xys.data_ptr(), v_conics.data_ptr(), v_rgbs.data_ptr(),
-                                              v_opac.data_ptr(), order_b.data_ptr(), _lib.ptr(clamp_ref), st)
-            _lib.check(rc, "gs_raster_bwd")
-            if ctx.state is not None and ctx.state.defer_leaf_grads:
-                rc = L.gs_finish_view_block(N, int(ctx.use_sh), _ctypes_addr(cam), rgbs.data_ptr(), g.data_ptr(), st)
-                _lib.check(rc, "gs_finish_view_block")
-                if ctx.pending is not None:
-                    ctx.state.num_intersects = _check_pending(ctx.pending)
-                ctx.state.xys_grad = v_xys
-                ctx.state.view_block = g
-                ctx.state.view_meta = (int(ctx.use_sh), int(ctx.deg), tuple(opacities.shape))
-                return (None,) * 12
-            # the six leaf gradients live in ONE flat buffer (59 floats / Gaussian) so that the
-            # data-parallel step can all-reduce them with a single NCCL call
-            flat = torch.empty(59 * Np, device=dev, dtype=torch.float32)
-            v_means = flat[0:3 * N].view(N, 3)
-            v_scales = flat[3 * Np:3 * Np + 3 * N].view(N, 3)
-            v_quats = flat[6 * Np:6 * Np + 4 * N].view(N, 4)
-            v_opl = flat[10 * Np:10 * Np + N].view(opacities.shape)
-            v_dc = flat[11 * Np:11 * Np + 3 * N].view(N, 3)
-            v_rest = flat[14 * Np:14 * Np + 45 * N].view(N, 15, 3)
-            rc = L.gs_preprocess_bwd(N, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(),
-                                     int(ctx.use_sh), int(ctx.deg), _ctypes_addr(cam), radii.data_ptr(), rgbs.data_ptr(),
-                                     v_xys.data_ptr(), v_conics.data_ptr(), v_rgbs.data_ptr(), v_opac.data_ptr(),
-                                     v_means.data_ptr(), v_scales.data_ptr(), v_quats.data_ptr(), v_opl.data_ptr(),
-                                     v_dc.data_ptr(), v_rest.data_ptr(), st)
-            _lib.check(rc, "gs_preprocess_bwd")
+            g, flat = backward_view(means, scales, quats, opacities, cam, ctx.use_sh, ctx.deg, bg, ws, im.final_T,
+                                    im.final_idx, v_out, v_alpha, im.out if ctx.clamp_rgb else None, gbuf=ext,
+                                    leaf_grads=not defer)
+        v_xys = g[0:2 * n].view(n, 2)
         if ctx.pending is not None:
-            I = _check_pending(ctx.pending)      # long since complete: does not stall the device
+            I = check_pending(ctx.pending)        # long since complete: does not stall the device
+            ctx.pending = None
             if ctx.state is not None:
                 ctx.state.num_intersects = I
         if ctx.state is not None:
-            ctx.state.xys_grad = v_xys       # what gc_model.py:193-194 keeps via xys.retain_grad()
+            ctx.state.xys_grad = v_xys            # what gc_model.py:193-194 keeps via xys.retain_grad()
+        if defer:
+            ctx.state.view_block = g
+            ctx.state.view_meta = (int(ctx.use_sh), int(ctx.deg), ctx.opac_shape)
+            return (None,) * 13
+        if ctx.state is not None:
             ctx.state.flat_grads = flat
-        return v_means, v_scales, v_quats, v_opl, v_dc, v_rest, None, None, None, None, None, None
+        v_means, v_scales, v_quats, v_opl, v_dc, v_rest = split_flat_grads(flat, n, ctx.opac_shape)
+        return v_means, v_scales, v_quats, v_opl, v_dc, v_rest, None, None, None, None, None, None, None
 
 
 def render_view(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor, features_dc: Tensor,
                 features_rest: Tensor, camera: Camera, sh_degree_to_use: int, use_sh: bool = True,
-                background: Optional[Tensor] = None, state: Optional[ViewState] = None, clamp_rgb: bool = False
-                ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
+                background: Optional[Tensor] = None, state: Optional[ViewState] = None, clamp_rgb: bool = False,
+                speculate: Optional[bool] = None) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor]:
     """RAW splatfacto leaves (log-scales, un-normalised wxyz quats, opacity logits (N,1),
     features_dc (N,3), features_rest (N,15,3)) + one camera -> (rgb (H,W,3) before the caller's
     clamp(max=1) — or after it with clamp_rgb=True: the clamp and its backward are then done inside the
@@ -397,7 +402,32 @@ def render_view(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor,
         return (rgb, torch.zeros((cam.H, cam.W), device=dev) + zero, torch.zeros((0,), device=dev),
                 torch.zeros((0,), device=dev, dtype=torch.int32), torch.zeros((0,), device=dev, dtype=torch.int32))
     return _RenderView.apply(means, scales, quats, opacities, features_dc, features_rest, cam, bool(use_sh),
-                             int(sh_degree_to_use), background, state, bool(clamp_rgb))
+                             int(sh_degree_to_use), background, state, bool(clamp_rgb),
+                             SPECULATE if speculate is None else bool(speculate))
+
+
+@torch.no_grad()
+def render_eval(means, scales, quats, opacities, features_dc, features_rest, cameras: List[Camera],
+                sh_degree_to_use: int, use_sh: bool, background: Tensor, with_depth: bool = True,
+                subset: Optional[Tensor] = None):
+    """No-grad render of a BATCH of cameras (one image size) in one call: RGB (clamped, gc_model.py:222),
+    accumulation and — with_depth — the expected depth normalised by accumulation, 1000 where nothing was hit
+    (gc_model.py:224-238), all from ONE binning and ONE compositing launch over cameras x tiles.
+    Returns (workspace, rgb (V,H,W,3), accumulation (V,H,W,1), depth (V,H,W,1) | None) — V axis dropped for one camera."""
+    dev = means.device
+    cams = [gs_camera(c) for c in cameras]
+    args = [t.detach().float().contiguous() for t in (means, scales, quats, opacities, features_dc, features_rest)]
+    bg = background.detach().to(dev).float().contiguous()
+    if subset is not None:
+        subset = subset.to(device=dev, dtype=torch.int32).contiguous()
+    with torch.cuda.device(dev):
+        ws, im, I, _ = forward_views(*args, cams, use_sh, sh_degree_to_use, bg, with_depth=with_depth, subset=subset)
+    alpha = im.alpha[..., None]
+    depth = None
+    if with_depth:
+        d = im.depth[..., None]
+        depth = torch.where(alpha > 0, d / alpha, torch.full_like(d, 1000.0))
+    return ws, im.out_clamped, alpha, depth
 
 
 def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: Tensor) -> Tensor:
@@ -409,6 +439,7 @@ def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: T
     dev = xys.device
     C = colors.shape[1]
     colors = colors.float().contiguous()
+    xys, conics, opac = xys.float().contiguous(), conics.float().contiguous(), opac.float().contiguous()
     bg = background.to(dev).float().contiguous()
     out = torch.empty((cam.H, cam.W, C), device=dev, dtype=torch.float32)
     fT = torch.empty((cam.H, cam.W), device=dev, dtype=torch.float32)

@@ -60,6 +60,38 @@ class Camera:
     def as_dict(self):
         return dict(c2w=self.c2w.numpy(), fx=self.fx, fy=self.fy, cx=self.cx, cy=self.cy, W=self.W, H=self.H)
 
+    def rescale_output_resolution(self, scaling_factor: float) -> None:
+        """nerfstudio `Cameras.rescale_output_resolution` (called at gc_model.py:115 and :206), default
+        "floor" rounding: intrinsics scale, width / height truncate. In place, like the original."""
+        self.fx, self.fy = self.fx * scaling_factor, self.fy * scaling_factor
+        self.cx, self.cy = self.cx * scaling_factor, self.cy * scaling_factor
+        self.W, self.H = int(self.W * scaling_factor), int(self.H * scaling_factor)
+
+    def signature(self):
+        """Value key for caches: an in-place pose / intrinsics update (camera optimiser, rescale) must not
+        hit a stale entry."""
+        return (self.c2w.detach().cpu().numpy().tobytes(), float(self.fx), float(self.fy), float(self.cx),
+                float(self.cy), int(self.W), int(self.H))
+
+
+@dataclass
+class OrientedBox:
+    """nerfstudio `OrientedBox` as far as gc_model.py:108-113 / :244-251 use it (`crop_box.within(means)`):
+    R (3,3) rotation, T (3,) centre, S (3,) full side lengths."""
+    R: torch.Tensor
+    T: torch.Tensor
+    S: torch.Tensor
+
+    def within(self, pts: torch.Tensor) -> torch.Tensor:
+        R, T, S = self.R.to(pts), self.T.to(pts), self.S.to(pts)
+        H = torch.eye(4, device=pts.device, dtype=pts.dtype)
+        H[:3, :3] = R
+        H[:3, 3] = T
+        H_world2bbox = torch.inverse(H)
+        ph = torch.cat((pts, torch.ones_like(pts[..., :1])), dim=-1)
+        local = torch.matmul(H_world2bbox, ph.T).T[..., :3]
+        return torch.all(torch.cat([local > -S / 2, local < S / 2], dim=-1), dim=-1)
+
 
 def look_at(pos: torch.Tensor, target: torch.Tensor, up=(0.0, 0.0, 1.0)) -> torch.Tensor:
     """c2w (3,4) of a camera at `pos` looking at `target`; columns = right, up, back."""

@@ -3,7 +3,7 @@ plus `bin_fast`, the traffic-lean path `rasterize_gaussians` uses internally.
 
 These are the steps gsplat's rasterize_gaussians performs before compositing for the calls at
 /root/reference/gaussctrl/gc_model.py:208 and :225. All integer outputs are bit-exact against the
-oracle (tests/test_binning_gpu.py).
+oracle (tests/test_parity_gpu.py, tests/test_parity_scale_gpu.py).
 """
 from __future__ import annotations
 
@@ -130,26 +130,21 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
     bins = torch.empty((T, 2), device=dev, dtype=torch.int32)
     total = torch.empty(1, device=dev, dtype=torch.int32)
     if impl is None:
-        from .render import BIN_IMPL as impl
+        impl = "lsd"
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
         with torch.cuda.device(dev):
-            if impl == "tile":      # per-tile shared-memory sort (gs_bin_tile)
-                scratch = _scratch(dev, L.gs_bin_tile_scratch_bytes(N, cap, T), "bintile")
-                rc = L.gs_bin_tile(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), tx, ty,
+            # global depth sort + partition (gs_bin_fast); "lsd3": three 11/11/10-bit depth passes
+            prev = L.gs_set_depth_sort_passes(3) if impl == "lsd3" else None
+            try:
+                scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")
+                rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
                                    _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
                                    scratch.numel(), _lib.stream_ptr())
-            else:                   # global depth sort + partition (gs_bin_fast); "lsd3": three 11/11/10-bit depth passes
-                prev = L.gs_set_depth_sort_passes(3) if impl == "lsd3" else None
-                try:
-                    scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")
-                    rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
-                                       _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
-                                       scratch.numel(), _lib.stream_ptr())
-                finally:
-                    if prev is not None:
-                        L.gs_set_depth_sort_passes(prev)
-        _lib.check(rc, "gs_bin_tile/fast")
+            finally:
+                if prev is not None:
+                    L.gs_set_depth_sort_passes(prev)
+        _lib.check(rc, "gs_bin_fast")
         I = int(total.item())
         if I <= cap:
             _cap_hint[key] = max(int(I * 1.25) + 1024, 1024)

@@ -191,14 +191,6 @@ int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, con
  * Initial value: environment variable GS_DEPTH_SORT_PASSES. */
 int gs_set_depth_sort_passes(int passes);
 
-/* Tile-local binning: same (ids_sorted, tile_bins, *total_dev) contract and overflow behaviour as
- * gs_bin_fast, built from count -> tile scan -> unordered scatter -> ONE CTA PER TILE sorting its segment by
- * depth in shared memory (ties by Gaussian id). 5 launches; measured slower than gs_bin_fast, opt-in. */
-size_t gs_bin_tile_scratch_bytes(int N, int64_t I_cap, int T);
-int gs_bin_tile(int N, int64_t I_cap, const float *xys, const float *depths, const int32_t *radii,
-                int tiles_x, int tiles_y, int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
-                void *scratch, size_t scratch_bytes, void *stream);
-
 /* ---- stage 3: forward compositing (App. A.4) ----------------------------------------------- */
 /* colors (N,C); opac (N); bg (C) device; out_img (H,W,C); final_T (H,W); final_idx (H,W) =
  * 1 + index into ids_sorted of the last composited Gaussian (tile range start if none). */
@@ -262,6 +254,71 @@ int gs_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y,
                   const float *bg, const float *final_T, const int32_t *final_idx,
                   const float *v_out, const float *v_out_alpha,
                   float *v_xys, float *v_conics, float *v_colors, float *v_opac, void *stream);
+
+/* ---- packed splat records: what the compositing kernels stage with cp.async ------------------------------------
+ * One 48-byte record per projected Gaussian per view (12 floats):
+ *   [0..3] x, y, ex, ey      pixel centre (xys), half-extents of the region where alpha can reach 1/255
+ *   [4..7] opac, qa, qb, qc  opacity; conic scaled for exp2: qa = -a/2 log2e, qb = -b log2e, qc = -c/2 log2e
+ *   [8..11] r, g, b, depth   colour handed to the compositor; view-space depth
+ * gs_pack_splats builds them from the operator-API tensors (what rasterize_gaussians receives at
+ * gc_model.py:208-220); depths may be NULL (depth field 0). rec: 12*N floats, 16-byte aligned. */
+#define GS_REC_FLOATS_PER_SPLAT 12
+int gs_pack_splats(int N, const float *xys, const float *conics, const float *colors, const float *opac,
+                   const float *depths, float *rec, void *stream);
+/* gs_preprocess_fwd writing records instead of the operator-shaped arrays: rec (N,12) + depths, radii, tiles_hit (what
+ * the binning reads). subset != NULL: N = length of the index list, element i = Gaussian subset[i] (eval crop box,
+ * gc_model.py:108-113 / :157-170). */
+int gs_preprocess_fwd_packed(int N, const float *means, const float *log_scales, const float *quats,
+                             const float *opac_logits, const float *feat_dc, const float *feat_rest,
+                             const int32_t *subset, int use_sh, int sh_deg, const GsCamera *cam_host, float *rec,
+                             float *depths, int32_t *radii, int32_t *tiles_hit, void *stream);
+/* Forward / backward compositing over records (3 channels, optional depth channel = out_depth != NULL). `views`
+ * images of H x W are composited in one launch: tile_bins has views*T rows (view-major), ids_sorted holds indices
+ * into rec, outputs are (views,H,W,..). tile_order / tile_work / out_clamped / out_alpha as in the *_ordered_post
+ * entry points (NULL = not wanted). Same results as gs_raster_fwd / gs_raster_bwd on the same inputs. */
+int gs_raster_fwd_packed(int views, int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                         const int32_t *tile_bins, const float *rec, const float *bg, float *out_img,
+                         float *out_depth, float *final_T, int32_t *final_idx, const int32_t *tile_order,
+                         int32_t *tile_work, float *out_clamped, float *out_alpha, void *stream);
+int gs_raster_bwd_packed(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                         const int32_t *tile_bins, const float *rec, const float *bg, const float *final_T,
+                         const int32_t *final_idx, const float *v_out, const float *v_out_alpha, float *v_xys,
+                         float *v_conics, float *v_colors, float *v_opac, const int32_t *tile_order,
+                         const float *clamp_ref, void *stream);
+
+/* ---- one call per rendered view / batch of views (gc_model.py:172-238; gc_pipeline.py:222-228) ------------------
+ * Workspace: ONE device buffer of gs_view_layout(...).bytes bytes holds everything a view keeps between forward
+ * and backward; the layout gives the byte offset of each array so the host can alias them (records (views*n,12) f32,
+ * depths / radii / tiles_hit (views*n), ids_sorted (I_cap) i32, tile_bins (views*T,2) i32, ...). */
+typedef struct GsViewLayout {
+    int64_t rec, depths, radii, tiles_hit, ids_sorted, tile_bins, tile_work, order_fwd, order_bwd, total, bytes;
+} GsViewLayout;
+int gs_view_layout(int n, int views, int64_t I_cap, int T_view, GsViewLayout *out);
+size_t gs_view_scratch_bytes(int n, int views, int64_t I_cap, int T_view);
+/* Forward of `views` cameras (cams_host[views], same image size) over the same n Gaussians (RAW splatfacto leaves
+ * as gs_preprocess_fwd takes them; subset != NULL: n = length of the index list, element i = Gaussian subset[i]).
+ * Outputs (views,H,W,3) out_img [+ out_clamped = clamp(out,max=1)] [+ out_alpha (views,H,W) = 1 - final_T]
+ * [+ out_depth = sum alpha T depth], final_T, final_idx. I_cap = capacity of ids_sorted; the true intersection
+ * count is left in the workspace (layout.total) and, if total_host != NULL (pinned host int32), copied there behind
+ * the binning, after which count_event (a cudaEvent_t, may be NULL) is recorded — i.e. BEFORE the compositing
+ * kernel is enqueued, so waiting on it does not wait for the compositing. count > I_cap: out_img is NaN-filled
+ * (alpha 0) and the caller must redo the call with more room. */
+int gs_view_fwd(int n, int views, const float *means, const float *log_scales, const float *quats,
+                const float *opac_logits, const float *feat_dc, const float *feat_rest, const int32_t *subset,
+                int use_sh, int sh_deg, const GsCamera *cams_host, const float *bg, int64_t I_cap, void *ws,
+                size_t ws_bytes, void *scratch, size_t scratch_bytes, float *out_img, float *out_clamped,
+                float *out_alpha, float *out_depth, float *final_T, int32_t *final_idx, int32_t *total_host,
+                void *count_event, void *stream);
+/* Backward of ONE view rendered by gs_view_fwd(views = 1, subset = NULL) from its workspace: gbuf (9*Np + 64 floats,
+ * Np = n rounded up to 4; zero-filled here) receives the compositor-level gradients (view-block layout of
+ * gs_view_block_floats); flat_leaf_grads (59*Np floats: v_means | v_log_scales at 3Np | v_quats at 6Np | v_opacity
+ * logits at 10Np | v_features_dc at 11Np | v_features_rest at 14Np) receives the six leaf gradients, or, when NULL,
+ * the view block is finished for the data-parallel exchange instead (gs_finish_view_block). clamp_ref = raw out_img
+ * when v_out is w.r.t. the clamped image, else NULL. */
+int gs_view_bwd(int n, const float *means, const float *log_scales, const float *quats, const float *opac_logits,
+                int use_sh, int sh_deg, const GsCamera *cam_host, const float *bg, void *ws, size_t ws_bytes,
+                int64_t I_cap, const float *final_T, const int32_t *final_idx, const float *v_out,
+                const float *v_out_alpha, const float *clamp_ref, float *gbuf, float *flat_leaf_grads, void *stream);
 
 /* ---- multi-view noise mask ------------------------------------------------------------------
  * Replaces MultiVeiwNoiseRenderer.render_noise_SS (/root/reference/gaussctrl/ad_render.py:273-333) and its GLSL

@@ -585,6 +585,85 @@ void orc_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y, int N,
     free(G);
 }
 
+/* ------------------------------------------------------------------------- */
+/* Test diagnostics for the parity tests at full size (tests/test_parity_scale_gpu.py).          */
+/* The forward of A.4 takes three discontinuous decisions per (pixel, Gaussian) pair:             */
+/*   alpha >= 1/255 (skip), T(1-alpha) <= 1e-4 (stop), opac*exp(-sigma) vs 0.999 (clamp: only the */
+/*   derivative is discontinuous). Two correct fp32 implementations (expf here, ex2.approx on the */
+/*   GPU, gsplat's __expf) can take a decision differently only where the quantity sits within    */
+/*   rounding distance of its threshold. orc_raster_risk returns, per pixel, the smallest RELATIVE */
+/*   distance |q/threshold - 1| over all decisions this oracle took at that pixel, so a test can   */
+/*   assert "every pixel that deviates is one where a decision was within eps of its threshold".   */
+/* ------------------------------------------------------------------------- */
+void orc_raster_risk(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                     const int32_t *tile_bins, const float *xys, const float *conics,
+                     const float *opac, float *risk_alpha, float *risk_T, float *risk_clamp) {
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int tile = 0; tile < tiles_x * tiles_y; ++tile) {
+        int tx = tile % tiles_x, ty = tile / tiles_x;
+        int s = tile_bins[2 * tile], e = tile_bins[2 * tile + 1];
+        for (int ly = 0; ly < TILE; ++ly)
+            for (int lx = 0; lx < TILE; ++lx) {
+                int i = ty * TILE + ly, j = tx * TILE + lx;
+                if (i >= H || j >= W) continue;
+                float px = (float)j + PIX_CENTER, py = (float)i + PIX_CENTER;
+                float T = 1.0f;
+                double ra = 1e30, rt = 1e30, rc = 1e30;
+                for (int k = s; k < e; ++k) {
+                    int g = ids_sorted[k];
+                    float dx = xys[2 * g] - px, dy = xys[2 * g + 1] - py;
+                    float ca = conics[3 * g], cb = conics[3 * g + 1], cc = conics[3 * g + 2];
+                    float sigma = 0.5f * (ca * dx * dx + cc * dy * dy) + cb * dx * dy;
+                    if (sigma < 0.0f) continue;
+                    double raw = (double)opac[g] * exp(-(double)sigma);
+                    double da = fabs(raw / (double)ALPHA_MIN - 1.0);
+                    if (da < ra) ra = da;
+                    float alpha = fminf(ALPHA_MAX, opac[g] * expf(-sigma));
+                    if (alpha < ALPHA_MIN) continue;
+                    double dc = fabs(raw / (double)ALPHA_MAX - 1.0);
+                    if (dc < rc) rc = dc;
+                    float Tn = T * (1.0f - alpha);
+                    double dt = fabs((double)Tn / (double)T_EPS - 1.0);
+                    if (dt < rt) rt = dt;
+                    if (Tn <= T_EPS) break;
+                    T = Tn;
+                }
+                size_t pix = (size_t)i * W + j;
+                risk_alpha[pix] = (float)ra; risk_T[pix] = (float)rt; risk_clamp[pix] = (float)rc;
+            }
+    }
+}
+
+/* touched[g] = 1 for every Gaussian that can influence (forward or backward) a pixel with mask != 0:
+ * all list entries k in [range start, upto[pix]) whose raw alpha at that pixel is at least half the
+ * 1/255 threshold. upto = per-pixel exclusive end index (max of the two implementations' final_idx). */
+void orc_mark_contributors(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                           const int32_t *tile_bins, const float *xys, const float *conics,
+                           const float *opac, const uint8_t *mask, const int32_t *upto, uint8_t *touched) {
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int tile = 0; tile < tiles_x * tiles_y; ++tile) {
+        int tx = tile % tiles_x, ty = tile / tiles_x;
+        int s = tile_bins[2 * tile], e = tile_bins[2 * tile + 1];
+        for (int ly = 0; ly < TILE; ++ly)
+            for (int lx = 0; lx < TILE; ++lx) {
+                int i = ty * TILE + ly, j = tx * TILE + lx;
+                if (i >= H || j >= W) continue;
+                size_t pix = (size_t)i * W + j;
+                if (!mask[pix]) continue;
+                float px = (float)j + PIX_CENTER, py = (float)i + PIX_CENTER;
+                int hi = upto[pix] < e ? upto[pix] : e;
+                for (int k = s; k < hi; ++k) {
+                    int g = ids_sorted[k];
+                    float dx = xys[2 * g] - px, dy = xys[2 * g + 1] - py;
+                    float ca = conics[3 * g], cb = conics[3 * g + 1], cc = conics[3 * g + 2];
+                    float sigma = 0.5f * (ca * dx * dx + cc * dy * dy) + cb * dx * dy;
+                    if (sigma < 0.0f) continue;
+                    if (opac[g] * expf(-sigma) >= 0.5f * ALPHA_MIN) touched[g] = 1;   /* benign race: all writers store 1 */
+                }
+            }
+    }
+}
+
 /* ------------------------------------------------------------------------------------------
  * Multi-view noise mask — CPU restatement of /root/reference/gaussctrl/ad_render.py:273-333
  * (render_noise_SS) and the GLSL shaders at :384-479, drawn in order on the CPU: instances in

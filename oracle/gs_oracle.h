@@ -75,6 +75,16 @@ void orc_raster_bwd(int C, int H, int W, int tiles_x, int tiles_y, int N,
                     const float *v_out, const float *v_out_alpha /* may be NULL */,
                     float *v_xys, float *v_conics, float *v_colors, float *v_opac);
 
+/* Test diagnostics (tests/test_parity_scale_gpu.py): per-pixel smallest relative distance of a forward
+ * decision to its threshold (alpha vs 1/255, T(1-alpha) vs 1e-4, raw alpha vs 0.999), and the set of
+ * Gaussians that can influence a masked pixel. */
+void orc_raster_risk(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                     const int32_t *tile_bins, const float *xys, const float *conics,
+                     const float *opac, float *risk_alpha, float *risk_T, float *risk_clamp);
+void orc_mark_contributors(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                           const int32_t *tile_bins, const float *xys, const float *conics,
+                           const float *opac, const uint8_t *mask, const int32_t *upto, uint8_t *touched);
+
 /* Multi-view noise mask (ad_render.py:273-333 + shaders :384-479), drawn in order on the CPU. */
 void orc_noise_mask(int P, const float *points, int V, const float *verts, int F, const int32_t *tris,
                     const float *view16, const float *proj16, int H, int W, const float *depth, float threshold,

@@ -178,6 +178,30 @@ def raster_bwd(b: Binning, xys, conics, colors, opac, bg, H, W, tile_bounds, fT,
     return v_xys, v_con, v_col, v_op[:, None]
 
 
+def raster_risk(b: Binning, xys, conics, opac, H, W, tile_bounds):
+    """Per-pixel smallest relative distance of a forward decision to its threshold:
+    -> (risk_alpha, risk_T, risk_clamp), each (H,W) float32 (1e30 where no decision was taken)."""
+    xys, conics, opac = _f(xys), _f(conics), _f(opac).reshape(-1)
+    ra = np.empty((H, W), np.float32)
+    rt = np.empty((H, W), np.float32)
+    rc = np.empty((H, W), np.float32)
+    lib().orc_raster_risk(C.c_int(H), C.c_int(W), C.c_int(tile_bounds[0]), C.c_int(tile_bounds[1]),
+                          _p(b.ids_sorted), _p(b.tile_bins), _p(xys), _p(conics), _p(opac), _p(ra), _p(rt), _p(rc))
+    return ra, rt, rc
+
+
+def mark_contributors(b: Binning, xys, conics, opac, H, W, tile_bounds, mask, upto):
+    """-> touched (N,) bool: Gaussians that can influence a pixel with mask != 0 (list entries before upto[pix])."""
+    xys, conics, opac = _f(xys), _f(conics), _f(opac).reshape(-1)
+    mask = np.ascontiguousarray(mask, np.uint8)
+    upto = np.ascontiguousarray(upto, np.int32)
+    touched = np.zeros((xys.shape[0],), np.uint8)
+    lib().orc_mark_contributors(C.c_int(H), C.c_int(W), C.c_int(tile_bounds[0]), C.c_int(tile_bounds[1]),
+                                _p(b.ids_sorted), _p(b.tile_bins), _p(xys), _p(conics), _p(opac), _p(mask),
+                                _p(upto), _p(touched))
+    return touched.astype(bool)
+
+
 # ----------------------------------------------------------------------------------------------
 # Caller semantics: /root/reference/gaussctrl/gc_model.py:117-241 restated in numpy.
 # ----------------------------------------------------------------------------------------------

@@ -35,6 +35,134 @@ def extract(path, names, env):
     return env
 
 
+def reference_caller_golden():
+    """5. reference_caller.npz — the reference's OWN caller, GaussCtrlModel.get_outputs / get_outputs_for_camera
+    (/root/reference/gaussctrl/gc_model.py:77-255), extracted by AST and executed UNMODIFIED on the CPU. What it needs
+    from outside the file is stubbed: nerfstudio's `Cameras` / `SplatfactoModel` attributes it reads (a10 of SURVEY.md
+    §8), `OrientedBox.within`, `renderers.BACKGROUND_COLOR_OVERRIDE`, nerfstudio's `projection_matrix` (pinned
+    separately against ad_render.py:49-67 in reference_matrices.npz), and the three gsplat operators, which here are
+    the CPU oracle's. The outputs pin every caller-side decision (background, crop, downscale, pre-activations,
+    `+0.5`/clamp, depth normalisation, early returns, returned matrices) for the host mirrors in
+    gaussctrl_exp_b200/model.py and oracle/oracle.py."""
+    import torch
+    from typing import Dict, List, Optional, Union
+    from gaussctrl_exp_b200 import scene
+    from gaussctrl_exp_b200.model import projection_matrix
+    from oracle import oracle as orc
+
+    def project_gaussians(means3d, scales, glob_scale, quats, viewmat, projmat, fx, fy, cx, cy, H, W, tile_bounds,
+                          clip_thresh=0.01):
+        r = orc.project_fwd(means3d.detach().numpy(), scales.detach().numpy(), float(glob_scale), quats.detach().numpy(),
+                            viewmat.numpy(), projmat.numpy(), fx, fy, cx, cy, H, W, tile_bounds, clip_thresh)
+        xys, depths, radii, conics, hit, cov3d = (torch.from_numpy(a) for a in r)
+        return xys.requires_grad_(), depths, radii, conics, hit, cov3d
+
+    def spherical_harmonics(n, viewdirs, coeffs):
+        return torch.from_numpy(orc.sh_fwd(int(n), viewdirs.detach().numpy(), coeffs.detach().numpy()))
+
+    def rasterize_gaussians(xys, depths, radii, conics, num_tiles_hit, colors, opacity, H, W, background=None,
+                            return_alpha=False):
+        tb = ((W + 15) // 16, (H + 15) // 16, 1)
+        b = orc.bin_and_sort(xys.detach().numpy(), depths.numpy(), radii.numpy(), num_tiles_hit.numpy(), tb)
+        bg = np.ones(colors.shape[-1], np.float32) if background is None else background.numpy()
+        img, fT, fidx, _ = orc.raster_fwd(b, xys.detach().numpy(), conics.numpy(), colors.detach().numpy(),
+                                          opacity.detach().numpy(), bg, H, W, tb)
+        if return_alpha:
+            return torch.from_numpy(img), torch.from_numpy(1.0 - fT)
+        return torch.from_numpy(img)
+
+    class Cameras:                              # the attributes gc_model.py reads (SURVEY.md §8 a10)
+        def __init__(self, cam):
+            self.camera_to_worlds = cam.c2w.clone()[None]
+            self.fx, self.fy = torch.tensor([[cam.fx]]), torch.tensor([[cam.fy]])
+            self.cx, self.cy = torch.tensor([[cam.cx]]), torch.tensor([[cam.cy]])
+            self.width, self.height = torch.tensor([[cam.W]]), torch.tensor([[cam.H]])
+            self.shape = (1,)
+
+        def rescale_output_resolution(self, s):          # nerfstudio Cameras, "floor" rounding
+            self.fx, self.fy, self.cx, self.cy = self.fx * s, self.fy * s, self.cx * s, self.cy * s
+            self.width, self.height = (self.width * s).to(torch.int64), (self.height * s).to(torch.int64)
+
+        def to(self, device):
+            return self
+
+    class Renderers:
+        BACKGROUND_COLOR_OVERRIDE = None
+
+    class Config:
+        def __init__(self, background_color):
+            self.background_color, self.sh_degree, self.sh_degree_interval = background_color, 3, 1000
+
+    env = {"torch": torch, "math": math, "Dict": Dict, "Union": Union, "List": List, "Optional": Optional,
+           "Cameras": Cameras, "renderers": Renderers, "OrientedBox": scene.OrientedBox,
+           "projection_matrix": projection_matrix, "project_gaussians": project_gaussians,
+           "spherical_harmonics": spherical_harmonics, "rasterize_gaussians": rasterize_gaussians}
+    path = os.path.join(REF, "gc_model.py")
+    tree = ast.parse(open(path).read())
+    extract(path, {"projection_matrix_ogl"}, env)
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "GaussCtrlModel")
+    methods = {}
+    for node in cls.body:
+        if isinstance(node, ast.FunctionDef) and node.name in ("get_outputs", "get_outputs_for_camera"):
+            exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), env)
+            methods[node.name] = env[node.name]
+
+    class Stub:                                  # what GaussCtrlModel inherits from SplatfactoModel, as far as it is read
+        device = torch.device("cpu")
+
+        def __init__(self, p, background_color, num_downscales=0, step=30000):
+            for k, v in p.items():
+                setattr(self, k, torch.from_numpy(v))
+            self.config = Config(background_color)
+            self.background_color = (torch.tensor([0.1490, 0.1647, 0.2157]) if background_color == "random"
+                                     else torch.tensor({"white": [1.0, 1.0, 1.0], "black": [0.0, 0.0, 0.0]}[background_color]))
+            self.training, self.crop_box, self.step = True, None, step
+            self.num_downscales, self.resolution_schedule = num_downscales, 250
+
+        def set_crop(self, box):
+            self.crop_box = box
+
+        def _get_downscale_factor(self):          # nerfstudio splatfacto
+            if self.training:
+                return 2 ** max(self.num_downscales - self.step // self.resolution_schedule, 0)
+            return 1
+    Stub.get_outputs = methods["get_outputs"]
+    Stub.get_outputs_for_camera = methods["get_outputs_for_camera"]
+
+    N, W, H = 3000, 96, 64
+    p = {k: v.numpy() for k, v in scene.make_scene(N, 31, s0=0.03).items()}
+    cam = scene.make_cameras(3, 31, intrinsics=dict(fx=110.0, fy=109.0, cx=47.7, cy=32.2, W=W, H=H))[1]
+    th = 0.3
+    box = scene.OrientedBox(R=torch.tensor([[math.cos(th), -math.sin(th), 0.0], [math.sin(th), math.cos(th), 0.0],
+                                            [0.0, 0.0, 1.0]]), T=torch.tensor([0.02, 0.03, -0.04]),
+                            S=torch.tensor([0.45, 0.5, 0.4]))
+    far = scene.OrientedBox(R=torch.eye(3), T=torch.tensor([50.0, 0.0, 0.0]), S=torch.ones(3))
+    out = {"c2w": cam.c2w.numpy(), "intr": np.array([cam.fx, cam.fy, cam.cx, cam.cy, W, H], np.float64),
+           "scene": np.array([N, 31, 0.03]), "box_R": box.R.numpy(), "box_T": box.T.numpy(), "box_S": box.S.numpy(),
+           "far_T": far.T.numpy()}
+
+    def put(tag, res):
+        for k, v in res.items():
+            if v is not None:
+                out[f"{tag}_{k}"] = v.detach().numpy() if isinstance(v, torch.Tensor) else np.asarray(v)
+        out[f"{tag}_keys"] = np.array(sorted(k for k, v in res.items() if v is not None))
+
+    m = Stub(p, "random")
+    put("eval", m.get_outputs_for_camera(Cameras(cam)))
+    assert m.training and m.xys.shape == (N, 2)
+    put("crop", m.get_outputs_for_camera(Cameras(cam), obb_box=box))
+    out["crop_count"] = np.array(m.xys.shape[0])
+    put("empty", m.get_outputs_for_camera(Cameras(cam), obb_box=far))
+    mw = Stub(p, "white", num_downscales=1, step=3100)     # training: factor 2 ** max(1 - 3100 // 250, 0) = 1 ...
+    assert mw._get_downscale_factor() == 1
+    mw.step, mw.resolution_schedule = 3100, 10000           # ... and with a long schedule, 2
+    assert mw._get_downscale_factor() == 2
+    c = Cameras(cam)
+    put("train_half", mw.get_outputs(c))
+    assert int(c.width.item()) == W and int(c.height.item()) == H     # rescaled back (gc_model.py:206)
+    np.savez_compressed(os.path.join(HERE, "reference_caller.npz"), **out)
+
+
 def main():
     import torch
     from typing import Union
@@ -96,6 +224,8 @@ def main():
         views.append(env_v["compute_view_matrix_ogl"](pos, up, fw))
     np.savez(os.path.join(HERE, "reference_noise_helpers.npz"), sphere_v=sv, sphere_i=si, sphere2_v=sv2, sphere2_i=si2,
              cube=cube, c2ws=np.stack(c2ws), views=np.stack(views))
+
+    reference_caller_golden()
 
     from oracle import oracle as orc
     from util import np_params, small_cam

@@ -89,7 +89,7 @@ def test_full_size_properties(cuda_dev):
     assert bool((ks[1:] >= ks[:-1]).all())
     ref_k, ref_perm = torch.sort(keys, stable=True)      # library sort as a cross-check of OUR sort
     assert torch.equal(ks, ref_k) and torch.equal(vs, ids[ref_perm])
-    for impl in ("tile", "lsd"):
+    for impl in ("lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         assert I2 == I and torch.equal(ids2[:I], vs) and torch.equal(bins2, bins), impl
     cnt = (bins[:, 1] - bins[:, 0]).long()
@@ -134,9 +134,11 @@ def test_config2_api_path_equals_fused_path_500k(cuda_dev):
         assert den > 0 and (g - res[1][2][k]).abs().max().item() / den < TOL, k
 
 
-def test_speculative_capacity_overflow_is_detected(cuda_dev):
-    """Training views do not read the intersection count in the forward; an undersized speculative
-    capacity must be caught (before gradients are returned) and the retry must succeed."""
+def test_capacity_overflow_heals_or_is_flagged(cuda_dev):
+    """The tile lists are allocated for a capacity learnt from earlier views. Default mode: an undersized capacity is
+    noticed inside the forward (count read behind the binning) and the view is redone — the caller never sees a torn
+    image. speculate=True (nothing read in the forward): the image is NaN-poisoned by the compositing kernel and
+    backward raises CapacityOverflow before handing out gradients; the hint is raised so that a retry succeeds."""
     from gaussctrl_exp_b200 import render, scene
     from gaussctrl_exp_b200.model import GaussianModel
     dev = cuda_dev
@@ -144,21 +146,65 @@ def test_speculative_capacity_overflow_is_detected(cuda_dev):
     cam = small_cam(160, 128, 5)
     m = GaussianModel(p, background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
     m.train()
-    ref = m(cam)["rgb"].detach().clone()          # first view of this shape: strict, sets the hint
-    key = (dev.index, 30000, 10 * 8)
+    ref = m(cam)["rgb"].detach().clone()          # first view of this shape sets the hint
+    key = (dev.index, 30000, 1, 10 * 8)
     assert key in render._cap_hint
-    I_true = render._cap_hint[key]
+    I_true = m.view_state.num_intersects
+    assert I_true > 2048
     render._cap_hint[key] = 2048                   # sabotage: far too small
-    out = m(cam)
+    out = m(cam)                                   # default: healed inside the forward
+    assert torch.equal(out["rgb"].detach(), ref) and m.view_state.num_intersects == I_true
+    assert render._cap_hint[key] >= I_true         # and the hint only ever grows
+    out["rgb"].sum().backward()
+    assert m.means.grad.abs().max() > 0
+    # fully asynchronous mode
+    render._cap_hint[key] = 2048
+    leaves = [m.means, m.scales, m.quats, m.opacities, m.features_dc, m.features_rest]
+    rgb, alpha, *_ = render.render_view(*leaves, cam, 3, True, torch.tensor([0.1, 0.2, 0.3], device=dev), m.view_state,
+                                        speculate=True)
+    assert torch.isnan(rgb).all()                  # poisoned, not a plausible background image
     with pytest.raises(render.CapacityOverflow):
-        out["rgb"].sum().backward()
-    assert render._cap_hint[key] >= I_true // 2    # hint was raised by the failed check
+        rgb.sum().backward()
+    assert render._cap_hint[key] >= I_true
     for q in m.parameters():
         q.grad = None
-    out = m(cam)                                   # retry succeeds and matches
-    out["rgb"].sum().backward()
-    assert torch.equal(out["rgb"].detach(), ref) and m.means.grad.abs().max() > 0
-    assert m.view_state.num_intersects > 2048
+    rgb, alpha, *_ = render.render_view(*leaves, cam, 3, True, torch.tensor([0.1, 0.2, 0.3], device=dev), m.view_state,
+                                        speculate=True)   # retry succeeds and matches
+    rgb.sum().backward()
+    assert torch.equal(torch.clamp(rgb.detach(), max=1.0), ref) and m.means.grad.abs().max() > 0
+    assert m.view_state.num_intersects == I_true
+
+
+def test_default_background_and_camera_updates(cuda_dev):
+    """Eval renders with the default `background_color="random"` use splatfacto's resolved grey, not black
+    (gc_model.py:102-106); an in-place pose change of a camera is seen by the next render (caches key on values)."""
+    from gaussctrl_exp_b200 import model as gm
+    from gaussctrl_exp_b200 import scene
+    dev = cuda_dev
+    p = scene.make_scene(2000, 5, s0=0.01, device=dev)
+    cam = small_cam(96, 64, 5)
+    grey = torch.tensor([0.1490, 0.1647, 0.2157], device=dev)
+    for fused in (True, False):
+        m = gm.GaussianModel(p, fused=fused).to(dev)              # background_color="random"
+        out = m.get_outputs_for_camera(cam)
+        empty = out["accumulation"][..., 0] == 0
+        assert empty.any() and torch.allclose(out["rgb"][empty], grey.expand_as(out["rgb"][empty]))
+        try:
+            gm.BACKGROUND_COLOR_OVERRIDE = torch.tensor([1.0, 0.0, 0.0])
+            out2 = m.get_outputs_for_camera(cam)
+            assert torch.allclose(out2["rgb"][empty], torch.tensor([1.0, 0.0, 0.0], device=dev).expand_as(out2["rgb"][empty]))
+        finally:
+            gm.BACKGROUND_COLOR_OVERRIDE = None
+        m.train()
+        a, b = m(cam)["rgb"].detach(), m(cam)["rgb"].detach()    # training: a fresh random colour per view
+        assert not torch.equal(a[empty], b[empty])
+        m.eval()
+        before = m.get_outputs_for_camera(cam)["rgb"].clone()
+        cam.c2w[:3, 3] += 0.05                                    # in-place pose update (camera optimiser)
+        after = m.get_outputs_for_camera(cam)["rgb"]
+        cam.c2w[:3, 3] -= 0.05
+        assert not torch.equal(before, after)
+        assert torch.equal(m.get_outputs_for_camera(cam)["rgb"], before)
 
 
 def test_view_block_replay_equals_summed_leaf_grads(cuda_dev):
@@ -271,29 +317,82 @@ def test_compacted_view_exchange_equals_dense(cuda_dev, N, V, deg):
     m.view_state.defer_leaf_grads = False
 
 
-def test_render_views_matches_single_view_calls(oracle, cuda_dev):
-    """The view-sharded, multi-stream all-view loop (gc_pipeline.py:222-228) returns exactly what
-    per-camera get_outputs_for_camera returns; the fused RGB-D pass equals the reference's two passes."""
+def test_render_views_batched(oracle, cuda_dev):
+    """The view-sharded, BATCHED all-view loop (gc_pipeline.py:222-228: several cameras per call, one binning over
+    cameras x Gaussians, one compositing launch over cameras x tiles) against the ORACLE for every camera, and
+    bit-identical to per-camera get_outputs_for_camera; the fused RGB-D pass equals the reference's two passes."""
     from gaussctrl_exp_b200 import scene
     from gaussctrl_exp_b200.model import GaussianModel
+    from util import depth_parity, forward_parity
     dev = cuda_dev
-    p = scene.make_scene(40000, 9, s0=0.01, device=dev)
+    pn = {k: v.numpy() for k, v in scene.make_scene(40000, 9, s0=0.01).items()}
+    p = {k: torch.from_numpy(v).to(dev) for k, v in pn.items()}
     cams = scene.make_cameras(7, 3, intrinsics=dict(fx=300.0, fy=299.0, cx=127.6, cy=96.3, W=256, H=192))
-    m = GaussianModel(p, background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
-    lit = GaussianModel(p, background_color=torch.tensor([0.1, 0.2, 0.3]), fused=False).to(dev)
+    bg = (0.1, 0.2, 0.3)
+    m = GaussianModel(p, background_color=torch.tensor(bg)).to(dev)
+    lit = GaussianModel(p, background_color=torch.tensor(bg), fused=False).to(dev)
     single = {v: m.get_outputs_for_camera(c) for v, c in enumerate(cams)}
     got = {}
     for rank in range(3):
-        part = m.render_views(cams, rank, 3, num_streams=2)
+        part = m.render_views(cams, rank, 3, batch=2)
         assert sorted(part) == list(range(rank, 7, 3))
         got.update(part)
+    whole = m.render_views(cams, 0, 1, batch=4)           # batches of 4 + 3
     torch.cuda.synchronize()
     for v in range(7):
         for k in ("rgb", "depth", "accumulation"):
             assert torch.equal(got[v][k], single[v][k]), (v, k)
+            assert torch.equal(whole[v][k], single[v][k]), (v, k)
+        ref, ctx = oracle.render_view(pn, cams[v].as_dict(), 3, bg=bg, training=False)
+        _, F, _ = forward_parity(oracle, ctx, whole[v]["rgb"].cpu().numpy(), ref["rgb"],
+                                 whole[v]["accumulation"].cpu().numpy(), ref["accumulation"], 192, 256)
+        depth_parity(whole[v]["depth"].cpu().numpy(), ref["depth"], ref["accumulation"], F)
     two_pass = lit.get_outputs_for_camera(cams[2])      # literal path: separate 3-channel depth pass
     assert (two_pass["rgb"] - single[2]["rgb"]).abs().max().item() < 2e-5
     assert (two_pass["accumulation"] - single[2]["accumulation"]).abs().max().item() < 2e-5
     seen = single[2]["accumulation"][..., 0] > 1e-3
     rel = ((two_pass["depth"] - single[2]["depth"]).abs() / two_pass["depth"].abs())[..., 0][seen]
     assert rel.max().item() < 1e-4
+
+
+def test_crop_box_and_downscale(oracle, cuda_dev):
+    """gc_model.py:108-113 / :157-170 (eval crop box through get_outputs_for_camera(camera, obb_box)) and
+    :114-115 / :206 (coarse-to-fine downscale while training): fused (index list into the preprocess kernel) and
+    literal (six gathers) agree with the oracle run on the cropped parameter set / the rescaled camera."""
+    from gaussctrl_exp_b200 import scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    from util import forward_parity
+    dev = cuda_dev
+    pn = {k: v.numpy() for k, v in scene.make_scene(30000, 4, s0=0.01).items()}
+    p = {k: torch.from_numpy(v).to(dev) for k, v in pn.items()}
+    cam = scene.make_cameras(3, 4, intrinsics=dict(fx=300.0, fy=299.0, cx=127.6, cy=96.3, W=256, H=192))[1]
+    bg = (0.1, 0.2, 0.3)
+    th = 0.4
+    R = torch.tensor([[np.cos(th), -np.sin(th), 0.0], [np.sin(th), np.cos(th), 0.0], [0.0, 0.0, 1.0]], dtype=torch.float32)
+    box = scene.OrientedBox(R=R, T=torch.tensor([0.05, -0.02, 0.03]), S=torch.tensor([0.5, 0.4, 0.6]))
+    inside = box.within(torch.from_numpy(pn["means"])).numpy()
+    assert 1000 < inside.sum() < 29000
+    ref, ctx = oracle.render_view({k: v[inside] for k, v in pn.items()}, cam.as_dict(), 3, bg=bg, training=False)
+    for fused in (True, False):
+        m = GaussianModel(p, background_color=torch.tensor(bg), fused=fused).to(dev)
+        out = m.get_outputs_for_camera(cam, obb_box=box)
+        assert m.radii.shape[0] == int(inside.sum()) and m.xys.shape == (int(inside.sum()), 2)
+        forward_parity(oracle, ctx, out["rgb"].cpu().numpy(), ref["rgb"], out["accumulation"].cpu().numpy(),
+                       ref["accumulation"], 192, 256)
+        full = m.get_outputs_for_camera(cam)                      # obb_box=None clears the crop (set_crop(None))
+        assert m.radii.shape[0] == 30000 and not torch.equal(full["rgb"], out["rgb"])
+        far = scene.OrientedBox(R=torch.eye(3), T=torch.tensor([50.0, 0.0, 0.0]), S=torch.ones(3))
+        none = m.get_outputs_for_camera(cam, obb_box=far)         # empty crop: background only (gc_model.py:110-111)
+        assert set(none) == {"rgb"} and none["rgb"].shape == (192, 256, 3)
+        # training with the coarse-to-fine schedule: rendered at half resolution, camera restored afterwards
+        m2 = GaussianModel(p, background_color=torch.tensor(bg), fused=fused, num_downscales=1, step=100, sh_degree_interval=10,
+                           resolution_schedule=250).to(dev)
+        m2.train()
+        out = m2(cam)
+        assert out["rgb"].shape == (96, 128, 3) and (cam.W, cam.H) == (256, 192) and m2.last_size == (96, 128)
+        half = scene.Camera(cam.c2w, cam.fx / 2, cam.fy / 2, cam.cx / 2, cam.cy / 2, 128, 96)
+        ref2, ctx2 = oracle.render_view(pn, half.as_dict(), 3, bg=bg, training=True)
+        forward_parity(oracle, ctx2, out["rgb"].detach().cpu().numpy(), ref2["rgb"],
+                       out["accumulation"].detach().cpu().numpy(), ref2["accumulation"], 96, 128)
+        out["rgb"].sum().backward()
+        assert m2.means.grad.abs().max() > 0

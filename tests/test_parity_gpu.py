@@ -92,7 +92,7 @@ def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
     assert np.array_equal(vs.cpu().numpy(), b.ids_sorted)
     assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
     # product paths: identical ids_sorted and tile ranges without 64-bit keys
-    for impl in ("tile", "lsd", "lsd3"):
+    for impl in ("lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         assert I2 == b.I, impl
         assert np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted), impl
@@ -101,8 +101,7 @@ def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
 
 
 def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
-    """Segments beyond the shared-memory capacity (global fallback of the tile sort) and exact depth ties
-    (must come out in Gaussian-id order)."""
+    """Very long tile lists (60 K entries per tile) and exact depth ties (must come out in Gaussian-id order)."""
     from gaussctrl_exp_b200 import utils as U
     rng = np.random.default_rng(5)
     N, W, H = 60000, 48, 32                      # 3 x 2 tiles, every splat covers all of them: 60 K per tile
@@ -117,17 +116,17 @@ def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
     b = oracle.bin_and_sort(xys, depths, radii, hit, tb)
     assert b.I == int(hit.sum()) and (b.tile_bins[:, 1] - b.tile_bins[:, 0]).max() > 50000
     t = [_t(a, cuda_dev) for a in (xys, depths, radii, hit)]
-    for impl in ("tile", "lsd", "lsd3"):
+    for impl in ("lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(*t, tb, impl=impl)
         assert I2 == b.I
         assert np.array_equal(bins2.cpu().numpy(), b.tile_bins), impl
         assert np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted), impl
-    # medium tiles (between the two shared-memory variants): ~9 K per tile
+    # medium tiles: ~9 K per tile
     sel = np.arange(N) < 10000
     r2 = np.where(sel, radii, 0).astype(np.int32)
     h2 = np.where(r2 > 0, 6, 0).astype(np.int32)
     b = oracle.bin_and_sort(xys, depths, r2, h2, tb)
-    ids2, bins2, I2 = U.bin_fast(t[0], t[1], _t(r2, cuda_dev), _t(h2, cuda_dev), tb, impl="tile")
+    ids2, bins2, I2 = U.bin_fast(t[0], t[1], _t(r2, cuda_dev), _t(h2, cuda_dev), tb, impl="lsd")
     assert I2 == b.I and np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted)
 
 

@@ -1,0 +1,120 @@
+"""Parity of the CUDA path against the C oracle AT THE SIZES BASELINE.json NAMES:
+
+  configs[1]  500 K Gaussians, SH deg 3, 512x512, fwd+bwd — through the gsplat-0.1.2-compatible API
+              (fused=False: the literal operator sequence of gc_model.py:172-222) and through the fused path;
+  headline    1 M Gaussians, 512x512: one training view (RGB, accumulation, six leaf gradients, xys.grad)
+              and one eval view (RGB, depth, accumulation)  — gc_model.py:174-238, gc_trainer.py:275;
+  stress      1 M Gaussians at 1920x1080 (configs[4]'s image size).
+
+Integers (radii, num_tiles_hit, ids_sorted, tile ranges; final_idx wherever no decision sat on its threshold) are
+bit-exact. Floats follow the three-part contract of tests/util.py (forward_parity / gradient_parity): every pixel
+that deviates by more than 1e-4 is a pixel where the oracle itself took an alpha >= 1/255 / T <= 1e-4 decision within
+rounding distance of the threshold, and every gradient row of a Gaussian that influences no such pixel is within 1e-4.
+The measured rates (deviating pixels, error percentiles, excluded Gaussians) are printed and written to
+gpurun_out/parity_scale_report.json; the copy under profiles/ is the one DESIGN.md quotes.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from util import TOL, depth_parity, forward_parity, gradient_parity, rel_linf, to_dev
+
+pytestmark = pytest.mark.gpu
+BG = (0.1, 0.2, 0.3)
+LEAVES = ("means", "scales", "quats", "features_dc", "features_rest", "opacities")
+_REPORT = {}
+
+
+def _scene(N, hd=False, cam_index=0):
+    from gaussctrl_exp_b200 import scene
+    p = {k: v.numpy() for k, v in scene.make_scene(N, 0).items()}
+    cams = scene.make_cameras(40, 0, intrinsics=scene.HD_INTRINSICS if hd else None)
+    return p, cams[cam_index]
+
+
+def _model(p, dev, fused):
+    from gaussctrl_exp_b200.model import GaussianModel
+    return GaussianModel(to_dev(p, dev), sh_degree=3, background_color=torch.tensor(BG), fused=fused).to(dev)
+
+
+def _save(name, rep):
+    _REPORT[name] = rep
+    print(f"\n[parity {name}] " + json.dumps(rep))
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "parity_scale_report.json"), "w") as f:
+            json.dump(_REPORT, f, indent=1)
+    except OSError:
+        pass
+
+
+def _check_integers(ctx, m, fused, rep):
+    """Bit-exact integer outputs of projection and binning."""
+    if fused:
+        st = m.view_state
+        radii, hit = st.radii.cpu().numpy(), st.num_tiles_hit.cpu().numpy()
+        ids_sorted, bins = st.ids_sorted.cpu().numpy(), st.tile_bins.cpu().numpy()
+    else:
+        from gaussctrl_exp_b200 import rasterize
+        radii = m.radii.cpu().numpy()
+        hit = None
+        cached = rasterize._bin_cache[m.device.index][4]
+        ids_sorted, bins = cached[0].cpu().numpy(), cached[1].cpu().numpy()
+    I = ctx["b"].I
+    assert np.array_equal(radii, ctx["radii"])
+    if hit is not None:
+        assert np.array_equal(hit, ctx["hit"])
+    assert np.array_equal(bins, ctx["b"].tile_bins)
+    assert np.array_equal(ids_sorted[:I], ctx["b"].ids_sorted)
+    rep["integers_bit_exact"] = {"radii": True, "num_tiles_hit": hit is not None, "ids_sorted": True,
+                                 "tile_bins": True, "I": int(I)}
+
+
+CASES = [
+    ("cfg1_500k_api_512", 500_000, False, False),
+    ("cfg1_500k_fused_512", 500_000, False, True),
+    ("headline_1m_fused_512", 1_000_000, False, True),
+    ("stress_1m_fused_1080p", 1_000_000, True, True),
+]
+
+
+@pytest.mark.parametrize("name,N,hd,fused", CASES, ids=[c[0] for c in CASES])
+def test_training_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
+    p, cam = _scene(N, hd, cam_index=1)
+    H, W = cam.H, cam.W
+    ref, ctx = oracle.render_view(p, cam.as_dict(), 3, bg=BG, training=True)
+    v = (np.random.default_rng(1234).standard_normal((H, W, 3)) / (H * W)).astype(np.float32)
+    g = oracle.render_view_backward(p, ctx, v)
+    m = _model(p, cuda_dev, fused)
+    m.train()
+    out = m(cam)
+    (out["rgb"] * torch.from_numpy(v).to(cuda_dev)).sum().backward()
+    rep = {"N": N, "image": [H, W], "path": "fused" if fused else "api", "visible": ref["visible"]}
+    _check_integers(ctx, m, fused, rep)
+    fidx = m.view_state.final_idx.cpu().numpy() if fused else None
+    rep["forward"], F, excl = forward_parity(oracle, ctx, out["rgb"].detach().cpu().numpy(), ref["rgb"],
+                                             out["accumulation"].detach().cpu().numpy(), ref["accumulation"], H, W, fidx)
+    got = {k: getattr(m, k).grad.cpu().numpy() for k in LEAVES}
+    got["xys"] = (m.view_state.xys_grad if fused else m.xys.grad).cpu().numpy()
+    refg = {k: g[k] for k in LEAVES + ("xys",)}
+    rep["gradients"] = gradient_parity(oracle, ctx, excl, got, refg, H, W)
+    _save(name + "_train", rep)
+
+
+@pytest.mark.parametrize("name,N,hd,fused", CASES, ids=[c[0] for c in CASES])
+def test_eval_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
+    p, cam = _scene(N, hd, cam_index=2)
+    H, W = cam.H, cam.W
+    ref, ctx = oracle.render_view(p, cam.as_dict(), 3, bg=BG, training=False)
+    m = _model(p, cuda_dev, fused)
+    out = m.get_outputs_for_camera(cam)
+    rgb, depth, acc = (out[k].cpu().numpy() for k in ("rgb", "depth", "accumulation"))
+    rep = {"N": N, "image": [H, W], "path": "fused" if fused else "api", "visible": ref["visible"]}
+    rep["forward"], F, _ = forward_parity(oracle, ctx, rgb, ref["rgb"], acc, ref["accumulation"], H, W)
+    rep["depth"] = depth_parity(depth, ref["depth"], ref["accumulation"], F)
+    assert (depth[ref["accumulation"] == 0] == 1000).all()
+    _save(name + "_eval", rep)
