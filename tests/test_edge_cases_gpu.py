@@ -70,15 +70,15 @@ def test_ragged_image_sizes(oracle, cuda_dev, W, H):
     N = 400
     p = np_params(N, seed=3, s0=0.08)
     cam = small_cam(W, H, 3, f=max(40.0, 1.2 * max(W, H)))
-    ref, _ = oracle.render_view(p, cam.as_dict(), 2, training=False)
+    from util import forward_parity
+    ref, ctx = oracle.render_view(p, cam.as_dict(), 2, training=False)
     m = GaussianModel({k: torch.from_numpy(v) for k, v in p.items()}, sh_degree=2, background_color=torch.tensor([0.1, 0.2, 0.3]),
                       step=30000).to(cuda_dev)
     out = m.get_outputs_for_camera(cam)
     assert out["rgb"].shape == (H, W, 3)
-    err = np.abs(out["rgb"].cpu().numpy() - ref["rgb"]).max(-1)
-    assert err.max() < 1.5 / 255                                   # at most one alpha quantum (an __expf-vs-expf flip)
-    assert (err > 1e-4).sum() <= max(1, int(2e-3 * H * W))
-    assert np.abs(out["accumulation"].cpu().numpy() - ref["accumulation"]).max() < 2e-3
+    # deviations only where the oracle's own alpha / T decision sat on its threshold, then at most one alpha quantum
+    forward_parity(oracle, ctx, out["rgb"].cpu().numpy(), ref["rgb"], out["accumulation"].cpu().numpy(),
+                   ref["accumulation"], H, W)
 
 
 def test_uint8_colors_and_default_background(oracle, cuda_dev):
@@ -94,7 +94,9 @@ def test_uint8_colors_and_default_background(oracle, cuda_dev):
     b = rasterize_gaussians(*args, t(c8.astype(np.float32) / 255), opac, d["H"], d["W"], background=torch.ones(3, device=dev))
     assert torch.allclose(a, b, atol=2e-6, rtol=0)      # torch divides by 255 as a multiplication by 1/255 on the GPU
     bb = oracle.bin_and_sort(d["xys"], d["depths"], d["radii"], d["hit"], d["tb"])
-    ref = oracle.raster_fwd(bb, d["xys"], d["conics"], c8.astype(np.float32) / 255, d["opac"].reshape(-1), np.ones(3, np.float32),
-                            d["H"], d["W"], d["tb"])[0]
-    err = np.abs(a.cpu().numpy() - ref).max(-1)
-    assert err.max() < 1.5 / 255 and (err > 1e-4).mean() <= 2e-3
+    from util import forward_parity
+    ref, fT, fidx, _ = oracle.raster_fwd(bb, d["xys"], d["conics"], c8.astype(np.float32) / 255, d["opac"].reshape(-1),
+                                         np.ones(3, np.float32), d["H"], d["W"], d["tb"])
+    ctx = {"b": bb, "xys": d["xys"], "conics": d["conics"], "opac": d["opac"], "tb": d["tb"], "fidx": fidx}
+    a2, alpha = rasterize_gaussians(*args, t(c8), opac, d["H"], d["W"], return_alpha=True)
+    forward_parity(oracle, ctx, a2.cpu().numpy(), ref, alpha.cpu().numpy(), 1 - fT, d["H"], d["W"])

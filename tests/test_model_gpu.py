@@ -20,19 +20,17 @@ def _model(p, dev, deg=3, bg=(0.1, 0.2, 0.3), fused=True):
 @pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("N,W,H,deg,s0", [(20000, 160, 128, 3, 0.02), (50000, 512, 512, 0, 0.005), (4000, 75, 50, 2, 0.05)])
 def test_eval_outputs(oracle, cuda_dev, N, W, H, deg, s0, fused):
+    from util import depth_parity, forward_parity
     p = np_params(N, seed=11, s0=s0)
     cam = small_cam(W, H, 11) if W != 512 else __import__("gaussctrl_exp_b200.scene", fromlist=["x"]).make_cameras(1, 0)[0]
-    ref, _ = oracle.render_view(p, cam.as_dict(), deg, training=False)
+    ref, ctx = oracle.render_view(p, cam.as_dict(), deg, training=False)
     m = _model(p, cuda_dev, deg, fused=fused)
     out = m.get_outputs_for_camera(cam)
     assert m.training
     rgb, depth, acc = (out[k].cpu().numpy() for k in ("rgb", "depth", "accumulation"))
     assert rgb.shape == (H, W, 3) and depth.shape == (H, W, 1) and acc.shape == (H, W, 1)
-    bad = np.abs(rgb - ref["rgb"]).max(-1) > TOL
-    assert bad.mean() <= 2e-4 and np.abs(rgb - ref["rgb"]).max() < 1.5 / 255
-    assert np.abs(acc - ref["accumulation"])[~bad].max() < TOL
-    ok = ~bad & (ref["accumulation"][..., 0] > 1e-3)
-    assert rel_linf(depth[ok], ref["depth"][ok]) < 5e-4   # depth / alpha amplifies fp32 rounding at low alpha
+    _, F, _ = forward_parity(oracle, ctx, rgb, ref["rgb"], acc, ref["accumulation"], H, W)
+    depth_parity(depth, ref["depth"], ref["accumulation"], F)
     assert (depth[acc == 0] == 1000).all()
     assert out["mat_view"].shape == (4, 4) and out["mat_proj"].shape == (4, 4) and out["mat_c2w"].shape == (3, 4)
 
@@ -40,6 +38,7 @@ def test_eval_outputs(oracle, cuda_dev, N, W, H, deg, s0, fused):
 @pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("N,W,H,deg,s0", [(20000, 160, 128, 3, 0.02), (50000, 512, 512, 0, 0.005), (3001, 70, 50, 1, 0.05)])
 def test_train_gradients(oracle, cuda_dev, N, W, H, deg, s0, fused):
+    from util import forward_parity, gradient_parity
     p = np_params(N, seed=12, s0=s0)
     from gaussctrl_exp_b200 import scene
     cam = small_cam(W, H, 12) if W != 512 else scene.make_cameras(1, 0)[0]
@@ -50,16 +49,13 @@ def test_train_gradients(oracle, cuda_dev, N, W, H, deg, s0, fused):
     m.train()
     out = m(cam)
     (out["rgb"] * torch.from_numpy(v).to(cuda_dev)).sum().backward()
-    flips = (np.abs(out["rgb"].detach().cpu().numpy() - ref["rgb"]).max(-1) > TOL).any()
-    tol = 3e-4 if flips else TOL
-    for name in ("means", "scales", "quats", "features_dc", "features_rest", "opacities"):
-        got = getattr(m, name).grad.cpu().numpy()
-        if np.abs(g[name]).max() == 0:
-            assert np.abs(got).max() == 0
-            continue
-        assert rel_linf(got, g[name]) < tol, name
-    xys_grad = m.view_state.xys_grad if fused else m.xys.grad   # kept for densification stats (gc_model.py:193-194)
-    assert rel_linf(xys_grad.cpu().numpy(), g["xys"]) < tol
+    fidx = m.view_state.final_idx.cpu().numpy() if fused else None
+    _, F, excl = forward_parity(oracle, ctx, out["rgb"].detach().cpu().numpy(), ref["rgb"],
+                                out["accumulation"].detach().cpu().numpy(), ref["accumulation"], H, W, fidx)
+    names = ("means", "scales", "quats", "features_dc", "features_rest", "opacities")
+    got = {k: getattr(m, k).grad.cpu().numpy() for k in names}
+    got["xys"] = (m.view_state.xys_grad if fused else m.xys.grad).cpu().numpy()   # kept for densification stats (gc_model.py:193-194)
+    gradient_parity(oracle, ctx, excl, got, {k: g[k] for k in names + ("xys",)}, H, W)
 
 
 def test_full_size_properties(cuda_dev):
@@ -103,35 +99,6 @@ def test_full_size_properties(cuda_dev):
     z = torch.zeros(3, device=dev)
     r = [rasterize_gaussians(xys, depths, radii, conics, hit, c, op, cam.H, cam.W, background=z) for c in (c1, c2, c1 + c2)]
     assert (r[0] + r[1] - r[2]).abs().max().item() < 1e-5
-
-
-def test_config2_api_path_equals_fused_path_500k(cuda_dev):
-    """BASELINE.json configs[1]: 500 K Gaussians, SH deg 3, 512x512, fwd+bwd through the gsplat-0.1.2-compatible
-    API (literal three-operator path of gc_model.py:172-222) — too large for the oracle, so the check is against
-    the independently written fused path on the same inputs: images and all six leaf gradients within 1e-4."""
-    from gaussctrl_exp_b200 import scene
-    from gaussctrl_exp_b200.model import GaussianModel
-    dev = cuda_dev
-    p = scene.make_scene(500_000, 0, device=dev)
-    cam = scene.make_cameras(3, 0)[1]
-    v = torch.randn(512, 512, 3, generator=torch.Generator().manual_seed(1234)).to(dev) / (512 * 512)
-    res = {}
-    for fused in (False, True):
-        m = GaussianModel(p, sh_degree=3, background_color=torch.tensor([0.1, 0.2, 0.3]), fused=fused).to(dev)
-        m.train()
-        out = m(cam)
-        (out["rgb"] * v).sum().backward()
-        res[fused] = (out["rgb"].detach(), out["accumulation"].detach(),
-                      {k: getattr(m, k).grad.clone() for k in ("means", "scales", "quats", "features_dc",
-                                                               "features_rest", "opacities")})
-    # the two paths round rgbs/conics/opacities differently in the last ulp, which can flip an alpha >= 1/255
-    # or T <= 1e-4 decision for a vanishing fraction of pixels (DESIGN.md §2): bounded by one alpha quantum
-    for a, b in ((res[0][0], res[1][0]), (res[0][1], res[1][1])):
-        d = (a - b).abs()
-        assert d.max().item() < 1.0 / 255 and (d > 1e-5).float().mean().item() < 2e-4
-    for k, g in res[0][2].items():
-        den = g.abs().max().item()
-        assert den > 0 and (g - res[1][2][k]).abs().max().item() / den < TOL, k
 
 
 def test_capacity_overflow_heals_or_is_flagged(cuda_dev):

@@ -139,11 +139,20 @@ def _raster_case(oracle, N, W, H, seed, s0, C=3):
     return d, colors, bg, b
 
 
+def _rctx(d, b, fidx):
+    """What tests/util.py's parity helpers need to know about a compositing case."""
+    return {"b": b, "xys": d["xys"], "conics": d["conics"], "opac": d["opac"], "tb": d["tb"], "fidx": fidx}
+
+
 @pytest.mark.parametrize("N,W,H,seed,s0,C", [(3000, 96, 64, 1, 0.04, 3), (50000, 512, 512, 0, 0.005, 3),
                                              (2000, 70, 45, 2, 0.05, 3), (1500, 64, 48, 3, 0.05, 1),
                                              (1500, 64, 48, 4, 0.05, 5), (800, 48, 32, 5, 0.06, 20)])
 def test_raster_fwd_bwd(oracle, cuda_dev, N, W, H, seed, s0, C):
+    """rasterize_gaussians (C = 3: pack + packed cp.async kernels; other C: generic kernels) against the oracle:
+    pixels deviate only where the oracle's own alpha / T decision sat on its threshold, gradients of Gaussians that
+    touch no such pixel are within 1e-4 (tests/util.py)."""
     from gaussctrl_exp_b200 import rasterize_gaussians
+    from util import forward_parity, gradient_parity
     dev = cuda_dev
     d, colors, bg, b = _raster_case(oracle, N, W, H, seed, s0, C)
     img, fT, fidx, pairs = oracle.raster_fwd(b, d["xys"], d["conics"], colors, d["opac"], bg, H, W, d["tb"])
@@ -154,35 +163,30 @@ def test_raster_fwd_bwd(oracle, cuda_dev, N, W, H, seed, s0, C):
     out, alpha = rasterize_gaussians(xys, _t(d["depths"], dev), _t(d["radii"], dev), conics, _t(d["hit"], dev), col,
                                      opac, H, W, background=_t(bg, dev), return_alpha=True)
     assert out.shape == (H, W, C) and alpha.shape == (H, W)
-    err = np.abs(out.detach().cpu().numpy() - img).max(-1)
-    # 1e-4 of the image range everywhere, except the (rare) pixels where __expf vs expf flips an
-    # alpha >= 1/255 or T <= 1e-4 decision: those are bounded by one alpha quantum.
-    scale = max(np.abs(img).max(), 1e-6)
-    bad = err > TOL * scale
-    assert bad.mean() <= 2e-4, f"{bad.sum()} pixels off"
-    assert err.max() <= 1.5 / 255 * max(np.abs(colors).max(), 1.0)
-    assert np.abs(alpha.detach().cpu().numpy() - (1 - fT))[~bad].max() < TOL
-
+    ctx = _rctx(d, b, fidx)
+    _, F, excl = forward_parity(oracle, ctx, out.detach().cpu().numpy(), img, alpha.detach().cpu().numpy(), 1 - fT, H, W)
     rng = np.random.default_rng(seed)
     v_out = rng.standard_normal((H, W, C)).astype(np.float32)
     v_a = rng.standard_normal((H, W)).astype(np.float32)
     ((out * _t(v_out, dev)).sum() + (alpha * _t(v_a, dev)).sum()).backward()
     g_xy, g_cn, g_co, g_op = oracle.raster_bwd(b, d["xys"], d["conics"], colors, d["opac"], bg, H, W, d["tb"], fT, fidx,
                                                v_out, v_a)
-    gtol = 2e-4 if bad.any() else TOL
-    assert rel_linf(col.grad.cpu().numpy(), g_co) < gtol
-    assert rel_linf(opac.grad.cpu().numpy(), g_op) < gtol
-    assert rel_linf(xys.grad.cpu().numpy(), g_xy) < gtol
-    assert rel_linf(conics.grad.cpu().numpy(), g_cn) < gtol
+    gradient_parity(oracle, ctx, excl, {"xys": xys.grad.cpu().numpy(), "conics": conics.grad.cpu().numpy(),
+                                        "colors": col.grad.cpu().numpy(), "opac": opac.grad.cpu().numpy()},
+                    {"xys": g_xy, "conics": g_cn, "colors": g_co, "opac": g_op}, H, W)
 
 
-def test_raster_final_idx_exact_and_no_alpha_grad(oracle, cuda_dev):
-    """final_idx (an index) is compared exactly through the raw ABI; v_out_alpha = NULL path."""
+@pytest.mark.parametrize("packed", [False, True])
+def test_raster_final_idx_exact_and_no_alpha_grad(oracle, cuda_dev, packed):
+    """Raw ABI: final_idx (an index) is bit-exact wherever no decision sat on its threshold; v_out_alpha = NULL path.
+    packed = the cp.async kernels over 48-byte records (gs_pack_splats + gs_raster_*_packed, LPT tile order),
+    otherwise the un-packed kernels (gs_raster_fwd / gs_raster_bwd)."""
     from gaussctrl_exp_b200 import _lib
-    from gaussctrl_exp_b200 import utils as U
+    from util import forward_parity, gradient_parity
     dev = cuda_dev
     d, colors, bg, b = _raster_case(oracle, 4000, 112, 80, 9, 0.03)
     H, W, tb = d["H"], d["W"], d["tb"]
+    T = tb[0] * tb[1]
     img, fT, fidx, _ = oracle.raster_fwd(b, d["xys"], d["conics"], colors, d["opac"], bg, H, W, tb)
     t = {k: _t(v, dev) for k, v in dict(xys=d["xys"], conics=d["conics"], colors=colors, opac=d["opac"][:, 0], bg=bg,
                                         ids=b.ids_sorted, bins=b.tile_bins).items()}
@@ -190,24 +194,39 @@ def test_raster_final_idx_exact_and_no_alpha_grad(oracle, cuda_dev):
     gT = torch.empty((H, W), device=dev)
     gidx = torch.empty((H, W), device=dev, dtype=torch.int32)
     L = _lib.lib()
-    rc = L.gs_raster_fwd(3, H, W, tb[0], tb[1], t["ids"].data_ptr(), t["bins"].data_ptr(), t["xys"].data_ptr(),
-                         t["conics"].data_ptr(), t["colors"].data_ptr(), t["opac"].data_ptr(), t["bg"].data_ptr(),
-                         out.data_ptr(), gT.data_ptr(), gidx.data_ptr(), _lib.stream_ptr())
-    assert rc == 0
-    mism = (gidx.cpu().numpy() != fidx)
-    assert mism.mean() <= 2e-4
+    sp = _lib.stream_ptr()
     v_out = np.random.default_rng(3).standard_normal((H, W, 3)).astype(np.float32)
     g = [torch.zeros((d["N"], k), device=dev) for k in (2, 3, 3, 1)]
     tv = _t(v_out, dev)
-    rc = L.gs_raster_bwd(3, H, W, tb[0], tb[1], t["ids"].data_ptr(), t["bins"].data_ptr(), t["xys"].data_ptr(),
-                         t["conics"].data_ptr(), t["colors"].data_ptr(), t["opac"].data_ptr(), t["bg"].data_ptr(),
-                         gT.data_ptr(), gidx.data_ptr(), tv.data_ptr(), None, g[0].data_ptr(), g[1].data_ptr(),
-                         g[2].data_ptr(), g[3].data_ptr(), _lib.stream_ptr())
-    assert rc == 0
+    if packed:
+        rec = torch.empty((d["N"], 12), device=dev)
+        order, work = torch.empty(T, device=dev, dtype=torch.int32), torch.empty(T, device=dev, dtype=torch.int32)
+        assert L.gs_pack_splats(d["N"], t["xys"].data_ptr(), t["conics"].data_ptr(), t["colors"].data_ptr(),
+                                t["opac"].data_ptr(), None, rec.data_ptr(), sp) == 0
+        assert L.gs_tile_order(T, t["bins"].data_ptr(), 1, order.data_ptr(), sp) == 0
+        assert L.gs_raster_fwd_packed(1, H, W, tb[0], tb[1], t["ids"].data_ptr(), t["bins"].data_ptr(), rec.data_ptr(),
+                                      t["bg"].data_ptr(), out.data_ptr(), None, gT.data_ptr(), gidx.data_ptr(),
+                                      order.data_ptr(), work.data_ptr(), None, None, sp) == 0
+        assert L.gs_tile_order(T, work.data_ptr(), 0, order.data_ptr(), sp) == 0
+        assert L.gs_raster_bwd_packed(H, W, tb[0], tb[1], t["ids"].data_ptr(), t["bins"].data_ptr(), rec.data_ptr(),
+                                      t["bg"].data_ptr(), gT.data_ptr(), gidx.data_ptr(), tv.data_ptr(), None,
+                                      g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(), g[3].data_ptr(), order.data_ptr(),
+                                      None, sp) == 0
+    else:
+        assert L.gs_raster_fwd(3, H, W, tb[0], tb[1], t["ids"].data_ptr(), t["bins"].data_ptr(), t["xys"].data_ptr(),
+                               t["conics"].data_ptr(), t["colors"].data_ptr(), t["opac"].data_ptr(), t["bg"].data_ptr(),
+                               out.data_ptr(), gT.data_ptr(), gidx.data_ptr(), sp) == 0
+        assert L.gs_raster_bwd(3, H, W, tb[0], tb[1], t["ids"].data_ptr(), t["bins"].data_ptr(), t["xys"].data_ptr(),
+                               t["conics"].data_ptr(), t["colors"].data_ptr(), t["opac"].data_ptr(), t["bg"].data_ptr(),
+                               gT.data_ptr(), gidx.data_ptr(), tv.data_ptr(), None, g[0].data_ptr(), g[1].data_ptr(),
+                               g[2].data_ptr(), g[3].data_ptr(), sp) == 0
+    ctx = _rctx(d, b, fidx)
+    _, F, excl = forward_parity(oracle, ctx, out.cpu().numpy(), img, (1 - gT).cpu().numpy(), 1 - fT, H, W,
+                                got_fidx=gidx.cpu().numpy())
     o_xy, o_cn, o_co, o_op = oracle.raster_bwd(b, d["xys"], d["conics"], colors, d["opac"], bg, H, W, tb, fT, fidx, v_out)
-    gt = 2e-4 if mism.any() else TOL
-    assert rel_linf(g[0].cpu().numpy(), o_xy) < gt and rel_linf(g[1].cpu().numpy(), o_cn) < gt
-    assert rel_linf(g[2].cpu().numpy(), o_co) < gt and rel_linf(g[3].cpu().numpy(), o_op) < gt
+    gradient_parity(oracle, ctx, excl, {"xys": g[0].cpu().numpy(), "conics": g[1].cpu().numpy(),
+                                        "colors": g[2].cpu().numpy(), "opac": g[3].cpu().numpy()},
+                    {"xys": o_xy, "conics": o_cn, "colors": o_co, "opac": o_op}, H, W)
 
 
 def test_zero_intersections_is_background(cuda_dev):

@@ -12,10 +12,17 @@ from gaussctrl_exp_b200.model import GaussianModel  # noqa: E402
 
 rank, local, world = gd.init_from_env("nccl")
 dev = torch.device("cuda", local)
-m = GaussianModel(scene.make_scene(1000000, 0), background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
+N_GAUSS = int(sys.argv[1]) if len(sys.argv) > 1 else 1000000
+m = GaussianModel(scene.make_scene(N_GAUSS, 0), background_color=torch.tensor([0.1, 0.2, 0.3])).to(dev)
 m.train()
 cams = scene.make_cameras(16, 0)
 v = torch.randn(512, 512, 3, generator=torch.Generator().manual_seed(1)).to(dev) / (512 * 512)
+# independent yardstick: every rank's ORDINARY leaf gradients (single-view backward), summed by a plain NCCL all-reduce
+for q in m.parameters():
+    q.grad = None
+(m(cams[rank])["rgb"] * v).sum().backward()
+gd.allreduce_flat(m.view_state.flat_grads, average=True)
+plain = {k: getattr(m, k).grad.clone() for k in gd.GRAD_PARAMS}
 m.view_state.defer_leaf_grads = True
 for q in m.parameters():
     q.grad = None
@@ -25,6 +32,11 @@ block = m.view_state.view_block.clone()
 res = {}
 gd.reduce_view_grads(m)
 res["gather"] = {k: getattr(m, k).grad.clone() for k in gd.GRAD_PARAMS}
+rel_plain = {k: ((res["gather"][k] - plain[k]).abs().max() / plain[k].abs().max().clamp_min(1e-30)).item()
+             for k in gd.GRAD_PARAMS}
+print(f"rank {rank}: view-block exchange vs NCCL all-reduce of ordinary leaf gradients: max rel diff "
+      f"{max(rel_plain.values()):.2e} {rel_plain}", flush=True)
+assert max(rel_plain.values()) < 2e-5 and all(plain[k].abs().max() > 0 for k in gd.GRAD_PARAMS)
 for mode in ("peer", "sparse", "push"):
     px = gd.PeerViewExchange(m, mode="dense" if mode == "peer" else mode)
     for rep in range(2):                     # twice: exercises the double buffering
@@ -52,5 +64,11 @@ nz = (blk[:2 * Np].view(-1, 2).abs().sum(1)[:m.num_points] != 0) | (blk[8 * Np:9
      (blk[5 * Np:8 * Np].view(-1, 3).abs().sum(1)[:m.num_points] != 0)
 print(f"rank {rank}: Gaussians with a non-zero view gradient: {nz.float().mean().item():.3f} "
       f"(visible {(m.view_state.radii > 0).float().mean().item():.3f})", flush=True)
+# every rank ended with the same gradients (bit pattern checksum)
+chk = torch.cat([res["push"][k].reshape(-1) for k in gd.GRAD_PARAMS]).view(torch.int32).to(torch.int64).sum().reshape(1)
+chks = [torch.zeros_like(chk) for _ in range(world)]
+dist.all_gather(chks, chk)
+assert all(int(c.item()) == int(chks[0].item()) for c in chks), "ranks disagree on the reduced gradients"
+print(f"rank {rank}: PEER_CHECK_OK", flush=True)
 dist.barrier()
 dist.destroy_process_group()
