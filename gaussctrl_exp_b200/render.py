@@ -117,8 +117,17 @@ class CapacityOverflow(RuntimeError):
     returned was NaN-poisoned; no gradient is handed out. The capacity hint has been raised: re-running succeeds."""
 
 
+_CAP_STEP = 1 << 20
+
+
+def _round_cap(c: int) -> int:
+    """Capacities move on a 1 Mi-entry grid: the workspace size (and with it the caching allocator's block) changes
+    rarely instead of with every new maximum."""
+    return (int(c) + _CAP_STEP - 1) // _CAP_STEP * _CAP_STEP
+
+
 def _raise_hint(key, I):
-    _cap_hint[key] = max(_cap_hint.get(key, 0), int(I * 1.5) + 1024)      # monotone: never shrinks
+    _cap_hint[key] = max(_cap_hint.get(key, 0), _round_cap(int(I * 1.5) + 1024))      # monotone: never shrinks
 
 
 class ViewWorkspace:
@@ -241,7 +250,7 @@ def forward_views(means, scales, quats, opacities, features_dc, features_rest, c
     cam_arr = (_lib.GsCamera * views)(*cams) if views > 1 else c0
     key = (dev.index, n, views, T_view)
     known = key in _cap_hint
-    cap = _cap_hint.get(key, max(4 * n * views, 1024))
+    cap = _cap_hint.get(key, _round_cap(max(4 * n * views, 1024)))
     speculate = speculate and known           # never speculate blindly on the first view of a shape
     st = _lib.stream_ptr()
     while True:
@@ -265,7 +274,7 @@ def forward_views(means, scales, quats, opacities, features_dc, features_rest, c
         if I <= cap:
             _raise_hint(key, I)
             return ws, im, I, None
-        cap = int(I * 1.5) + 1024       # capacity was too small: the binning wrote nothing; redo with room
+        cap = _round_cap(int(I * 1.5) + 1024)       # capacity was too small: the binning wrote nothing; redo with room
 
 
 def check_pending(pend: _Pending) -> int:
@@ -320,11 +329,13 @@ class _RenderView(Function):
         with torch.cuda.device(means.device):
             ws, im, I, pend = forward_views(*args, [cam], use_sh, deg, bg, speculate=speculate)
         ctx.pending = pend
-        ctx.ws, ctx.im = ws, im
+        ctx.ws = ws
         # clamp_rgb: the returned colour is clamp(out, max=1) (written by the compositing kernel) and the raw
-        # colour is kept so that the backward kernel can mask the incoming gradient like torch.clamp's backward
+        # colour is kept so that the backward kernel can mask the incoming gradient like torch.clamp's backward.
+        # NOTHING that is (or holds) a returned tensor may hang off ctx directly: output -> grad_fn -> ctx -> output
+        # is a reference cycle that only the cyclic GC breaks, i.e. ~100 MB of workspace per view would pile up.
         ctx.clamp_rgb = clamp_rgb
-        ctx.save_for_backward(*args[:4], bg)
+        ctx.save_for_backward(*args[:4], bg, im.final_T, im.final_idx, im.out if clamp_rgb else None)
         ctx.cam, ctx.use_sh, ctx.deg, ctx.state = cam, use_sh, deg, state
         ctx.opac_shape = tuple(opacities.shape)
         depths, radii, hit = ws.depths, ws.radii, ws.num_tiles_hit
@@ -338,8 +349,8 @@ class _RenderView(Function):
 
     @staticmethod
     def backward(ctx, v_out, v_alpha, *_unused):
-        means, scales, quats, opacities, bg = ctx.saved_tensors
-        cam, ws, im = ctx.cam, ctx.ws, ctx.im
+        means, scales, quats, opacities, bg, final_T, final_idx, clamp_ref = ctx.saved_tensors
+        cam, ws = ctx.cam, ctx.ws
         dev = means.device
         n = means.shape[0]
         H, W = cam.H, cam.W
@@ -354,9 +365,8 @@ class _RenderView(Function):
         if ext is not None:
             assert ext.numel() == 9 * Np + 64 and ext.is_contiguous() and ext.dtype == torch.float32
         with torch.cuda.device(dev):
-            g, flat = backward_view(means, scales, quats, opacities, cam, ctx.use_sh, ctx.deg, bg, ws, im.final_T,
-                                    im.final_idx, v_out, v_alpha, im.out if ctx.clamp_rgb else None, gbuf=ext,
-                                    leaf_grads=not defer)
+            g, flat = backward_view(means, scales, quats, opacities, cam, ctx.use_sh, ctx.deg, bg, ws, final_T,
+                                    final_idx, v_out, v_alpha, clamp_ref, gbuf=ext, leaf_grads=not defer)
         v_xys = g[0:2 * n].view(n, 2)
         if ctx.pending is not None:
             I = check_pending(ctx.pending)        # long since complete: does not stall the device
