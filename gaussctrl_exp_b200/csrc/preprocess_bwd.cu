@@ -45,7 +45,9 @@ preprocess_bwd_kernel(int N, const float *__restrict__ means, const float *__res
         float vc0 = 0.f, vc1 = 0.f, vc2 = 0.f;
         if (vis) {
             const float p0 = means[3 * i], p1 = means[3 * i + 1], p2 = means[3 * i + 2];
-            const float s0 = expf(log_scales[3 * i]), s1 = expf(log_scales[3 * i + 1]), s2 = expf(log_scales[3 * i + 2]);
+            // the forward's correctly rounded exp(scales) (preprocess_fwd.cu)
+            const float s0 = (float)exp((double)log_scales[3 * i]), s1 = (float)exp((double)log_scales[3 * i + 1]),
+                        s2 = (float)exp((double)log_scales[3 * i + 2]);
             const float4 qr = quats[i];
             const float qn = sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
             const float iq = 1.0f / qn;

@@ -83,7 +83,12 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
         }
     } else if (i < N) {
         p0 = means[3 * src]; p1 = means[3 * src + 1]; p2 = means[3 * src + 2];
-        const float s0 = expf(log_scales[3 * src]), s1 = expf(log_scales[3 * src + 1]), s2 = expf(log_scales[3 * src + 2]);
+        // exp(scales) (gc_model.py:176) correctly rounded (evaluated in double, rounded once): the integer outputs
+        // radius / num_tiles_hit depend on it through ceil(), and a 1-ulp difference between two libm's expf flips them
+        // for ~1e-6 of the Gaussians — visible at 1 M. With a correctly rounded exp the fused path's integers are
+        // reproducible on any platform (the CPU oracle does the same); 3 DP exp per Gaussian cost nothing here.
+        const float s0 = (float)exp((double)log_scales[3 * src]), s1 = (float)exp((double)log_scales[3 * src + 1]),
+                    s2 = (float)exp((double)log_scales[3 * src + 2]);
         float4 q = quats[src];
         const float qn = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);   // quats / quats.norm()
         q.x = q.x / qn; q.y = q.y / qn; q.z = q.z / qn; q.w = q.w / qn;

@@ -241,9 +241,12 @@ def _sigmoid(x):
 
 def preactivate(params, c2w, sh_degree):
     """gc_model.py:172-203 pre-ops. params: dict of numpy leaf tensors."""
-    scales = np.exp(params["scales"].astype(np.float32))
+    # exp correctly rounded (double, rounded once) and the norm as ((w*w + x*x) + y*y) + z*z in fp32: radii /
+    # num_tiles_hit are compared BIT-EXACTLY with the fused CUDA path, which evaluates the same expressions
+    scales = np.exp(params["scales"].astype(np.float64)).astype(np.float32)
     q = params["quats"].astype(np.float32)
-    quats = q / np.linalg.norm(q, axis=-1, keepdims=True)
+    nq = np.sqrt(((q[:, 0] * q[:, 0] + q[:, 1] * q[:, 1]) + q[:, 2] * q[:, 2]) + q[:, 3] * q[:, 3])
+    quats = q / nq[:, None]
     opac = _sigmoid(params["opacities"]).reshape(-1, 1)
     coeffs = np.concatenate([params["features_dc"][:, None, :], params["features_rest"]], axis=1)
     d = params["means"].astype(np.float32) - np.asarray(c2w, np.float32)[:3, 3][None]

@@ -52,26 +52,49 @@ def _save(name, rep):
         pass
 
 
-def _check_integers(ctx, m, fused, rep):
-    """Bit-exact integer outputs of projection and binning."""
-    if fused:
-        st = m.view_state
-        radii, hit = st.radii.cpu().numpy(), st.num_tiles_hit.cpu().numpy()
-        ids_sorted, bins = st.ids_sorted.cpu().numpy(), st.tile_bins.cpu().numpy()
-    else:
-        from gaussctrl_exp_b200 import rasterize
-        radii = m.radii.cpu().numpy()
-        hit = None
-        cached = rasterize._bin_cache[m.device.index][4]
-        ids_sorted, bins = cached[0].cpu().numpy(), cached[1].cpu().numpy()
+def _check_integers(ctx, m, rep):
+    """Fused path: bit-exact integer outputs of projection and binning (the kernel and the oracle evaluate the
+    pre-activations identically: correctly rounded exp, same fp32 operation order)."""
+    st = m.view_state
+    radii, hit = st.radii.cpu().numpy(), st.num_tiles_hit.cpu().numpy()
+    ids_sorted, bins = st.ids_sorted.cpu().numpy(), st.tile_bins.cpu().numpy()
     I = ctx["b"].I
     assert np.array_equal(radii, ctx["radii"])
-    if hit is not None:
-        assert np.array_equal(hit, ctx["hit"])
+    assert np.array_equal(hit, ctx["hit"])
     assert np.array_equal(bins, ctx["b"].tile_bins)
     assert np.array_equal(ids_sorted[:I], ctx["b"].ids_sorted)
-    rep["integers_bit_exact"] = {"radii": True, "num_tiles_hit": hit is not None, "ids_sorted": True,
-                                 "tile_bins": True, "I": int(I)}
+    rep["integers_bit_exact"] = {"radii": True, "num_tiles_hit": True, "ids_sorted": True, "tile_bins": True, "I": int(I)}
+
+
+def _check_integers_api(oracle, ctx, p, cam, dev, rep):
+    """Operator API: project_gaussians + the binning inside rasterize_gaussians on the ORACLE's pre-activated inputs
+    (gsplat's operators take activated tensors; the activations are the caller's torch ops): every integer output
+    bit-exact, xys / depths bit-exact, conics to 1e-6."""
+    from gaussctrl_exp_b200 import project_gaussians, rasterize, rasterize_gaussians
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    H, W = cam.H, cam.W
+    xys, depths, radii, conics, hit, cov3d = project_gaussians(
+        t(p["means"]), t(ctx["scales"]), 1, t(ctx["quats"]), t(ctx["V"][:3]), t(ctx["PV"]), cam.fx, cam.fy, cam.cx, cam.cy,
+        H, W, ctx["tb"])
+    assert np.array_equal(radii.cpu().numpy(), ctx["radii"]) and np.array_equal(hit.cpu().numpy(), ctx["hit"])
+    assert np.array_equal(xys.cpu().numpy(), ctx["xys"]) and np.array_equal(depths.cpu().numpy(), ctx["depths"])
+    assert np.abs(conics.cpu().numpy() - ctx["conics"]).max() <= 1e-6 * np.abs(ctx["conics"]).max()
+    rasterize_gaussians(xys, depths, radii, conics, hit, t(ctx["rgbs"]), t(ctx["opac"]), H, W, background=t(ctx["bg"]))
+    ids_sorted, bins, I = rasterize._bin_cache[dev.index][4]
+    assert I == ctx["b"].I and np.array_equal(bins.cpu().numpy(), ctx["b"].tile_bins)
+    assert np.array_equal(ids_sorted[:I].cpu().numpy(), ctx["b"].ids_sorted)
+    rep["integers_bit_exact"] = {"radii": True, "num_tiles_hit": True, "xys": True, "depths": True, "ids_sorted": True,
+                                 "tile_bins": True, "I": int(I), "inputs": "oracle pre-activations through the operator API"}
+
+
+def _api_radius_excuse(ctx, m, H, W, rep):
+    """Literal model path: its pre-activations are torch's; radii that moved by the one-ulp difference excuse their tiles."""
+    from util import tile_mask_of
+    radii = m.radii.cpu().numpy()
+    moved = np.nonzero(radii != ctx["radii"])[0]
+    rep["radii_moved_by_caller_side_activation_ulp"] = int(moved.size)
+    assert moved.size <= 20 and (np.abs(radii[moved] - ctx["radii"][moved]) <= 1).all()
+    return tile_mask_of(ctx, moved, radii, ctx["radii"], H, W) if moved.size else None
 
 
 CASES = [
@@ -94,10 +117,18 @@ def test_training_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
     out = m(cam)
     (out["rgb"] * torch.from_numpy(v).to(cuda_dev)).sum().backward()
     rep = {"N": N, "image": [H, W], "path": "fused" if fused else "api", "visible": ref["visible"]}
-    _check_integers(ctx, m, fused, rep)
+    extra = None
+    if fused:
+        _check_integers(ctx, m, rep)
+    else:
+        _check_integers_api(oracle, ctx, p, cam, cuda_dev, rep)
+        extra = _api_radius_excuse(ctx, m, H, W, rep)
     fidx = m.view_state.final_idx.cpu().numpy() if fused else None
     rep["forward"], F, excl = forward_parity(oracle, ctx, out["rgb"].detach().cpu().numpy(), ref["rgb"],
-                                             out["accumulation"].detach().cpu().numpy(), ref["accumulation"], H, W, fidx)
+                                             out["accumulation"].detach().cpu().numpy(), ref["accumulation"], H, W, fidx,
+                                             extra_risk=extra)
+    if extra is not None:
+        excl = excl | extra
     got = {k: getattr(m, k).grad.cpu().numpy() for k in LEAVES}
     got["xys"] = (m.view_state.xys_grad if fused else m.xys.grad).cpu().numpy()
     refg = {k: g[k] for k in LEAVES + ("xys",)}
@@ -114,7 +145,10 @@ def test_eval_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
     out = m.get_outputs_for_camera(cam)
     rgb, depth, acc = (out[k].cpu().numpy() for k in ("rgb", "depth", "accumulation"))
     rep = {"N": N, "image": [H, W], "path": "fused" if fused else "api", "visible": ref["visible"]}
-    rep["forward"], F, _ = forward_parity(oracle, ctx, rgb, ref["rgb"], acc, ref["accumulation"], H, W)
+    extra = None if fused else _api_radius_excuse(ctx, m, H, W, rep)
+    rep["forward"], F, _ = forward_parity(oracle, ctx, rgb, ref["rgb"], acc, ref["accumulation"], H, W, extra_risk=extra)
+    if extra is not None:
+        F = F | extra
     rep["depth"] = depth_parity(depth, ref["depth"], ref["accumulation"], F)
     assert (depth[ref["accumulation"] == 0] == 1000).all()
     _save(name + "_eval", rep)

@@ -63,10 +63,13 @@ def percentile(a, q):
     return float(np.quantile(a, q)) if a.size else 0.0
 
 
-def forward_parity(orc, ctx, got_rgb, ref_rgb, got_acc, ref_acc, H, W, got_fidx=None):
-    """-> (report dict, deviating-pixel mask F, gradient-exclusion pixel mask). Asserts (1) and (2)."""
+def forward_parity(orc, ctx, got_rgb, ref_rgb, got_acc, ref_acc, H, W, got_fidx=None, extra_risk=None):
+    """-> (report dict, deviating-pixel mask F, gradient-exclusion pixel mask). Asserts (1) and (2).
+    extra_risk: optional (H,W) bool mask of pixels excused for another stated reason (see tile_mask_of)."""
     ra, rt, rc = orc.raster_risk(ctx["b"], ctx["xys"], ctx["conics"], ctx["opac"], H, W, ctx["tb"])
     at_risk = (ra < EPS_ALPHA) | (rt < EPS_T)
+    if extra_risk is not None:
+        at_risk = at_risk | extra_risk
     err_rgb = np.abs(np.asarray(got_rgb, np.float64) - ref_rgb).max(-1)
     err_acc = np.abs(np.asarray(got_acc, np.float64).reshape(H, W) - ref_acc.reshape(H, W))
     F = (err_rgb > TOL) | (err_acc > TOL)
@@ -89,6 +92,22 @@ def forward_parity(orc, ctx, got_rgb, ref_rgb, got_acc, ref_acc, H, W, got_fidx=
     if got_fidx is not None:
         excl |= ~same
     return rep, F, excl
+
+
+def tile_mask_of(ctx, gaussians, radii_a, radii_b, H, W):
+    """(H,W) bool mask of the 16x16 tiles that the given Gaussians cover with either of two radii. Used for the
+    operator-API path, whose pre-activations (torch.exp / norm on the GPU, the CALLER's ops, gc_model.py:176-178) can
+    differ by one ulp from the oracle's: through ceil() that moves the integer radius of ~1e-6 of the Gaussians, i.e.
+    changes which tiles list them. Those tiles are excused — and counted in the report."""
+    mask = np.zeros((H, W), bool)
+    tb = ctx["tb"]
+    for g in gaussians:
+        x, y = ctx["xys"][g]
+        r = float(max(radii_a[g], radii_b[g]))
+        x0, x1 = max(int((x - r) / 16.0), 0), min(int((x + r) / 16.0 + 1), tb[0])
+        y0, y1 = max(int((y - r) / 16.0), 0), min(int((y + r) / 16.0 + 1), tb[1])
+        mask[16 * y0:16 * y1, 16 * x0:16 * x1] = True
+    return mask
 
 
 def gradient_parity(orc, ctx, excl_pixels, got_grads, ref_grads, H, W):
