@@ -333,6 +333,131 @@ emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, 
     }
 }
 
+// Scan + emission in ONE kernel: what scan_kernel (exclusive scan of tiles_hit in depth order) followed by
+// emit_sorted_kernel did in two, without the `start` array and without reading tiles_hit at all — a Gaussian's tile
+// count IS the area of the bbox that the emission recomputes from (xy, radius) anyway (A.1.6), so the scan's 1 M random
+// 4-byte gathers (its whole cost: profiles/README.md item 7) disappear. Each CTA takes 1 024 consecutive elements of the
+// depth order (4 per thread), scans their areas, gets its global offset by decoupled look-back (ticket order, 32-wide
+// window) and writes its (tile, id) pairs. The total is published by the last tile; writes are bounded by the capacity
+// (if the total exceeds it the consumers see that in *total_dev and do nothing).
+constexpr int SE_IPT = 4;
+constexpr int SE_TILE = SCAN_TPB * SE_IPT;
+
+__global__ void __launch_bounds__(SCAN_TPB)
+scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const float *__restrict__ xy_base, int xy_stride,
+                 const int32_t *__restrict__ radii, int tiles_x, int tiles_y, int n_per_view, uint32_t *__restrict__ tkey,
+                 uint32_t *__restrict__ tval, int32_t *__restrict__ total, ScanCtl *ctl, unsigned long long *status) {
+    __shared__ unsigned int s_tile;
+    __shared__ int s_warp[SCAN_TPB / 32];
+    __shared__ int s_prefix;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    gs_pdl_sync();
+    if (tid == 0) s_tile = atomicAdd(&ctl->ticket, 1u);
+    __syncthreads();
+    const int tile = (int)s_tile;
+    const int base = tile * SE_TILE + tid * SE_IPT;
+    int g[SE_IPT], x0[SE_IPT], y0[SE_IPT], bw[SE_IPT], area[SE_IPT], tb[SE_IPT];
+    if (base + SE_IPT <= N) {
+        const uint4 o = *reinterpret_cast<const uint4 *>(order + base);
+        g[0] = (int)o.x; g[1] = (int)o.y; g[2] = (int)o.z; g[3] = (int)o.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < SE_IPT; ++k) g[k] = base + k < N ? (int)order[base + k] : -1;
+    }
+    int rr[SE_IPT];
+#pragma unroll
+    for (int k = 0; k < SE_IPT; ++k) rr[k] = g[k] >= 0 ? radii[g[k]] : 0;       // 4 independent gathers in flight
+#pragma unroll
+    for (int k = 0; k < SE_IPT; ++k) {
+        x0[k] = y0[k] = bw[k] = area[k] = tb[k] = 0;
+        if (rr[k] > 0) {
+            const float2 c = *reinterpret_cast<const float2 *>(xy_base + (size_t)g[k] * xy_stride);
+            int x1, y1;
+            gs_tile_bbox(c.x, c.y, (float)rr[k], tiles_x, tiles_y, x0[k], y0[k], x1, y1);
+            bw[k] = x1 - x0[k];
+            area[k] = bw[k] * (y1 - y0[k]);
+            tb[k] = (g[k] / n_per_view) * (tiles_x * tiles_y);
+        }
+    }
+    int excl[SE_IPT], sum = 0;
+#pragma unroll
+    for (int k = 0; k < SE_IPT; ++k) { excl[k] = sum; sum += area[k]; }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    int warp_off = 0, block_total = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_TPB / 32; ++w) {
+        if (w < warp) warp_off += s_warp[w];
+        block_total += s_warp[w];
+    }
+    const int thread_off = warp_off + inc - sum;
+    if (warp == 0) {
+        if (lane == 0)
+            atomicExch(&status[tile], (tile == 0 ? FLAG_INC : FLAG_AGG) | (unsigned int)block_total);
+        int ex = 0;
+        int look = tile - 1;
+        while (look >= 0) {
+            const int idx = look - lane;
+            unsigned long long w;
+            do {
+                w = idx >= 0 ? *reinterpret_cast<volatile unsigned long long *>(&status[idx]) : FLAG_INC;
+            } while (__any_sync(0xffffffffu, (w >> 32) == 0));
+            const unsigned inc_mask = __ballot_sync(0xffffffffu, (w >> 32) == 2);
+            const int first = inc_mask ? __ffs(inc_mask) - 1 : 31;
+            int part = lane <= first ? (int)(unsigned int)w : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+            ex += part;
+            if (inc_mask) break;
+            look -= 32;
+        }
+        if (lane == 0) {
+            if (tile > 0) atomicExch(&status[tile], FLAG_INC | (unsigned int)(ex + block_total));
+            s_prefix = ex;
+        }
+    }
+    __syncthreads();
+    const int off = s_prefix + thread_off;
+    if (tile == (N - 1) / SE_TILE && tid == SCAN_TPB - 1) *total = s_prefix + block_total;
+    // ---- emission: row-major over the bbox (outer y, inner x), small splats by their own thread, big ones by the warp
+#pragma unroll
+    for (int k = 0; k < SE_IPT; ++k) {
+        const int st = off + excl[k];
+        if (area[k] > 0 && area[k] <= 8) {
+            int at = st;
+            for (int ty = y0[k]; ty < y0[k] + area[k] / bw[k]; ++ty)
+                for (int tx = x0[k]; tx < x0[k] + bw[k]; ++tx) {
+                    if (at < I_cap) {
+                        tkey[at] = (uint32_t)(tb[k] + ty * tiles_x + tx);
+                        tval[at] = (uint32_t)g[k];
+                    }
+                    ++at;
+                }
+        }
+        unsigned big = __ballot_sync(0xffffffffu, area[k] > 8);
+        while (big) {
+            const int src = __ffs(big) - 1;
+            big &= big - 1;
+            const int sx0 = __shfl_sync(0xffffffffu, x0[k], src), sy0 = __shfl_sync(0xffffffffu, y0[k], src);
+            const int sbw = __shfl_sync(0xffffffffu, bw[k], src), sarea = __shfl_sync(0xffffffffu, area[k], src);
+            const int sst = __shfl_sync(0xffffffffu, st, src), sg = __shfl_sync(0xffffffffu, g[k], src);
+            const int stb = __shfl_sync(0xffffffffu, tb[k], src);
+            for (int q = lane; q < sarea; q += 32) {
+                if (sst + q < I_cap) {
+                    tkey[sst + q] = (uint32_t)(stb + (sy0 + q / sbw) * tiles_x + sx0 + q % sbw);
+                    tval[sst + q] = (uint32_t)sg;
+                }
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 edges32_kernel(int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ tk,
                int32_t *__restrict__ bins) {
@@ -359,7 +484,7 @@ FastLayout fast_layout(int N, int64_t I_cap) {
     L.tkey = take(i4); L.tval = take(i4); L.tkey2 = take(i4); L.tval2 = take(i4);
     const size_t m = gsradix::mat_entries(N, 2048), mi = gsradix::mat_entries(I_cap, 2048);
     L.mat = take((m > mi ? m : mi) * 4);
-    L.ctl = take(gs_scan_scratch_bytes(N));
+    L.ctl = take(2 * gs_scan_scratch_bytes(N));      // look-back state of scan_emit_kernel (1 024-element tiles)
     L.total = at;
     return L;
 }
@@ -432,7 +557,7 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
 
     // the scan's look-back state is cleared up front so that the kernel chain below is uninterrupted (every launch
     // is a programmatic dependent launch: the next kernel is resident before the previous one drains)
-    GS_CUDA(cudaMemsetAsync(ctl, 0, gs_scan_scratch_bytes(N), st));
+    GS_CUDA(cudaMemsetAsync(ctl, 0, 2 * gs_scan_scratch_bytes(N), st));
     // 1. depth sort (values start as the element index; the first pass forms its keys from depths/radii on the fly,
     //    so there is no key-building kernel). Default: four passes of 8-bit digits; gs_set_depth_sort_passes(3) /
     //    GS_DEPTH_SORT_PASSES=3 selects three passes of 11/11/10-bit digits (fewer launches, but measured slower).
@@ -456,14 +581,21 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
         order = valB;
     }
 
-    // 2. exclusive scan of tiles_hit in depth order; total -> total_dev
-    GS_PDL_LAUNCH(scan_kernel, (N + SCAN_TILE - 1) / SCAN_TILE, SCAN_TPB, 0, st, N, tiles_hit, order, 1, start, total_dev,
-                  ctl, status);
-    if (I_cap == 0) return 0;
-
-    // 3. emission in depth order
-    GS_PDL_LAUNCH(emit_sorted_kernel, nblk, 256, 0, st, N, I_cap, (const int32_t *)total_dev, order,
-                  (const int32_t *)start, xys, xy_stride, radii, tiles_x, tiles_y, n_per_view, tkey, tval);
+    // 2 + 3. scan of the tile counts and emission, both in depth order, in one kernel (GS_BIN_SPLIT_SCAN=1: the two
+    //        separate kernels of round 1, kept for A/B). An element's count is recomputed from (xy, radius), so
+    //        tiles_hit is not read at all.
+    static const bool split_scan = getenv("GS_BIN_SPLIT_SCAN") != nullptr;
+    if (!split_scan) {
+        GS_PDL_LAUNCH(scan_emit_kernel, (N + SE_TILE - 1) / SE_TILE, SCAN_TPB, 0, st, N, I_cap, order, xys, xy_stride, radii,
+                      tiles_x, tiles_y, n_per_view, tkey, tval, total_dev, ctl, status);
+        if (I_cap == 0) return 0;
+    } else {
+        GS_PDL_LAUNCH(scan_kernel, (N + SCAN_TILE - 1) / SCAN_TILE, SCAN_TPB, 0, st, N, tiles_hit, order, 1, start, total_dev,
+                      ctl, status);
+        if (I_cap == 0) return 0;
+        GS_PDL_LAUNCH(emit_sorted_kernel, nblk, 256, 0, st, N, I_cap, (const int32_t *)total_dev, order,
+                      (const int32_t *)start, xys, xy_stride, radii, tiles_x, tiles_y, n_per_view, tkey, tval);
+    }
 
     // 4. stable partition by tile id
     uint32_t *ids_out = reinterpret_cast<uint32_t *>(ids_sorted);

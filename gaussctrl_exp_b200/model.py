@@ -129,6 +129,11 @@ class GaussianModel(nn.Module):
         # fused=True: one autograd node / two C calls per view (render.py); fused=False: the
         # reference's literal three-operator sequence through the gsplat-compatible functions.
         self.fused = fused
+        # fused training views: False (default) = the forward confirms the tile-list capacity before it returns (one
+        # host wait that ends when the BINNING is done; an overflow is healed by redoing the view); True = nothing is
+        # read in the forward (the host runs ahead of the device), an overflow NaN-poisons the image and raises
+        # render.CapacityOverflow at the end of backward — for training loops that catch it and redo the step
+        self.speculate = False
         self.view_state = _render.ViewState()
         self._mat_cache = {}
         self._streams = []
@@ -201,7 +206,8 @@ class GaussianModel(nn.Module):
         if torch.is_grad_enabled() and self.training:
             rgb, alpha, depths, radii, hit = _render.render_view(
                 self.means, self.scales, self.quats, self.opacities, self.features_dc, self.features_rest, camera,
-                n, use_sh, background, self.view_state, clamp_rgb=True)       # gc_model.py:222 inside the kernels
+                n, use_sh, background, self.view_state, clamp_rgb=True,       # gc_model.py:222 inside the kernels
+                speculate=self.speculate)
             self.xys, self.radii = self.view_state.xys, radii
             return rgb, None, alpha[..., None]
         subset = None

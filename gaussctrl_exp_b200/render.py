@@ -197,16 +197,16 @@ class ViewWorkspace:
 
 
 class ViewState:
-    """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii)."""
-    __slots__ = ("xys", "radii", "depths", "num_intersects", "xys_grad", "flat_grads", "defer_leaf_grads",
-                 "view_block", "view_meta", "view_block_buffer", "num_tiles_hit", "ids_sorted", "tile_bins",
-                 "final_idx", "final_T", "workspace")
+    """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii). The per-Gaussian and tile
+    arrays are lazy views into the last view's workspace (no tensor is created unless somebody asks)."""
+    __slots__ = ("num_intersects", "xys_grad", "flat_grads", "defer_leaf_grads", "view_block", "view_meta",
+                 "view_block_buffer", "final_idx", "final_T", "workspace", "_empty")
 
     def __init__(self):
-        self.xys = self.radii = self.depths = self.xys_grad = self.flat_grads = None
+        self.xys_grad = self.flat_grads = None
         # integer by-products of the last view (what gsplat's rasterize keeps for its backward); the parity
         # tests compare them bit for bit with the oracle
-        self.num_tiles_hit = self.ids_sorted = self.tile_bins = self.final_idx = self.final_T = self.workspace = None
+        self.final_idx = self.final_T = self.workspace = self._empty = None
         self.num_intersects = 0
         # data-parallel mode (dist.reduce_view_grads): backward stops at the compositor-level gradients,
         # leaves them (+ the camera) in view_block and returns no leaf gradients
@@ -215,6 +215,18 @@ class ViewState:
         self.view_meta = None
         # optional caller-owned buffer (e.g. NVLink symmetric memory) the view block is accumulated into
         self.view_block_buffer = None
+
+    def _ws(self, name):
+        if self.workspace is not None:
+            return getattr(self.workspace, name)
+        return None if self._empty is None else self._empty[name]
+
+    xys = property(lambda self: self._ws("xys"))
+    radii = property(lambda self: self._ws("radii"))
+    depths = property(lambda self: self._ws("depths"))
+    num_tiles_hit = property(lambda self: self._ws("num_tiles_hit"))
+    ids_sorted = property(lambda self: self._ws("ids_sorted"))
+    tile_bins = property(lambda self: self._ws("tile_bins"))
 
 
 class ViewImages:
@@ -340,9 +352,7 @@ class _RenderView(Function):
         ctx.opac_shape = tuple(opacities.shape)
         depths, radii, hit = ws.depths, ws.radii, ws.num_tiles_hit
         if state is not None:
-            state.xys, state.radii, state.depths, state.num_intersects = ws.xys, radii, depths, I
-            state.num_tiles_hit, state.ids_sorted, state.tile_bins = hit, ws.ids_sorted, ws.tile_bins
-            state.final_idx, state.final_T, state.workspace = im.final_idx, im.final_T, ws
+            state.num_intersects, state.final_idx, state.final_T, state.workspace = I, im.final_idx, im.final_T, ws
         ctx.mark_non_differentiable(depths, radii, hit)
         ctx.set_materialize_grads(False)      # unused outputs arrive as None instead of freshly filled zeros
         return (im.out_clamped if clamp_rgb else im.out), im.alpha, depths, radii, hit
@@ -405,9 +415,10 @@ def render_view(means: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor,
         if clamp_rgb:
             rgb = torch.clamp(rgb, max=1.0)
         if state is not None:
-            state.xys = torch.zeros((0, 2), device=dev)
-            state.radii = torch.zeros((0,), device=dev, dtype=torch.int32)
-            state.depths = torch.zeros((0,), device=dev)
+            state.workspace = None
+            state._empty = {"xys": torch.zeros((0, 2), device=dev), "radii": torch.zeros((0,), device=dev, dtype=torch.int32),
+                            "depths": torch.zeros((0,), device=dev), "num_tiles_hit": torch.zeros((0,), device=dev, dtype=torch.int32),
+                            "ids_sorted": torch.zeros((0,), device=dev, dtype=torch.int32), "tile_bins": None}
             state.num_intersects = 0
         return (rgb, torch.zeros((cam.H, cam.W), device=dev) + zero, torch.zeros((0,), device=dev),
                 torch.zeros((0,), device=dev, dtype=torch.int32), torch.zeros((0,), device=dev, dtype=torch.int32))

@@ -316,12 +316,11 @@ def test_render_views_batched(oracle, cuda_dev):
         _, F, _ = forward_parity(oracle, ctx, whole[v]["rgb"].cpu().numpy(), ref["rgb"],
                                  whole[v]["accumulation"].cpu().numpy(), ref["accumulation"], 192, 256)
         depth_parity(whole[v]["depth"].cpu().numpy(), ref["depth"], ref["accumulation"], F)
-    two_pass = lit.get_outputs_for_camera(cams[2])      # literal path: separate 3-channel depth pass
-    assert (two_pass["rgb"] - single[2]["rgb"]).abs().max().item() < 2e-5
-    assert (two_pass["accumulation"] - single[2]["accumulation"]).abs().max().item() < 2e-5
-    seen = single[2]["accumulation"][..., 0] > 1e-3
-    rel = ((two_pass["depth"] - single[2]["depth"]).abs() / two_pass["depth"].abs())[..., 0][seen]
-    assert rel.max().item() < 1e-4
+    two_pass = lit.get_outputs_for_camera(cams[2])      # literal path: separate 3-channel depth pass (gc_model.py:225-236)
+    ref, ctx = oracle.render_view(pn, cams[2].as_dict(), 3, bg=bg, training=False)
+    _, F, _ = forward_parity(oracle, ctx, two_pass["rgb"].cpu().numpy(), ref["rgb"],
+                             two_pass["accumulation"].cpu().numpy(), ref["accumulation"], 192, 256)
+    depth_parity(two_pass["depth"].cpu().numpy(), ref["depth"], ref["accumulation"], F)
 
 
 def test_crop_box_and_downscale(oracle, cuda_dev):

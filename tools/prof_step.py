@@ -18,10 +18,14 @@ m.train()
 cams = scene.make_cameras(40, 0)
 v = (torch.randn(512, 512, 3, generator=torch.Generator().manual_seed(1234)) / (512 * 512)).to(dev)
 for i in range(steps):
+    if i == steps - 1:                     # ncu --profile-from-start off: only the last (warm) step and the eval view
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     for q in m.parameters():
         q.grad = None
     m(cams[0])["rgb"].backward(v)          # the same camera every step: launch k of a kernel is comparable across runs
 torch.cuda.synchronize()
 m.get_outputs_for_camera(cams[0])
 torch.cuda.synchronize()
+torch.cuda.profiler.stop()
 print("prof_step ok")
