@@ -42,6 +42,9 @@ SIGNATURES = {
     "gs_view_pack_scratch_bytes": (_sz, [_i]),
     "gs_pack_view_block": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "gs_pack_view_block_push": (_i, [_i, _vp, _vp, _i, _i, _vp, _i64, _vp, _sz, _vp]),
+    "gs_view_slice_size": (_i, [_i, _i]),
+    "gs_pack_view_block_push_slices": (_i, [_i, _vp, _vp, _i, _i, _vp, _i64, _vp, _sz, _vp]),
+    "gs_leaf_bwd_slice": (_i, [_i, _i, _i, _i, _vp, _i64, _f, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_preprocess_bwd_multi_peer_sparse": (_i, [_i, _i, _vp, _i64, _f, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp,
                                                  _vp, _vp, _vp]),
     "gs_sh_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
@@ -55,6 +58,7 @@ SIGNATURES = {
     "gs_bin_fast_scratch_bytes": (_sz, [_i, _i64, _i]),
     "gs_bin_fast": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gs_set_depth_sort_passes": (_i, [_i]),
+    "gs_set_bin_impl": (_i, [_i]),
     "gs_raster_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_raster_fwd_rgbd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_tile_order": (_i, [_i, _vp, _i, _vp, _vp]),

@@ -342,6 +342,7 @@ emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, 
 // (if the total exceeds it the consumers see that in *total_dev and do nothing).
 constexpr int SE_IPT = 4;
 constexpr int SE_TILE = SCAN_TPB * SE_IPT;
+constexpr int SE_STAGE = 4096;       // pairs of one CTA staged in shared memory (a CTA's pairs are CONTIGUOUS in the output)
 
 __global__ void __launch_bounds__(SCAN_TPB)
 scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const float *__restrict__ xy_base, int xy_stride,
@@ -350,6 +351,10 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
     __shared__ unsigned int s_tile;
     __shared__ int s_warp[SCAN_TPB / 32];
     __shared__ int s_prefix;
+    // the pairs of this CTA form one contiguous run of the output: they are assembled here and stored with coalesced
+    // 128-byte rows. Written straight from the threads, every lane of a store lands in a different sector (a thread
+    // owns ~12 consecutive pairs) and the kernel is bound by the LSU's sector rate (ncu: mio_throttle, r02).
+    __shared__ uint32_t s_key[SE_STAGE], s_val[SE_STAGE];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     gs_pdl_sync();
     if (tid == 0) s_tile = atomicAdd(&ctl->ticket, 1u);
@@ -423,22 +428,27 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
         }
     }
     __syncthreads();
-    const int off = s_prefix + thread_off;
+    const int cta_off = s_prefix;
     if (tile == (N - 1) / SE_TILE && tid == SCAN_TPB - 1) *total = s_prefix + block_total;
+    const bool staged = block_total <= SE_STAGE;
+    // pair `at` (index inside this CTA's run): shared-memory stage, or straight to the output when the run is too long
+    auto put = [&](int at, uint32_t t, uint32_t id) {
+        if (staged) {
+            s_key[at] = t;
+            s_val[at] = id;
+        } else if ((int64_t)cta_off + at < I_cap) {
+            tkey[cta_off + at] = t;
+            tval[cta_off + at] = id;
+        }
+    };
     // ---- emission: row-major over the bbox (outer y, inner x), small splats by their own thread, big ones by the warp
 #pragma unroll
     for (int k = 0; k < SE_IPT; ++k) {
-        const int st = off + excl[k];
+        const int st = thread_off + excl[k];
         if (area[k] > 0 && area[k] <= 8) {
             int at = st;
             for (int ty = y0[k]; ty < y0[k] + area[k] / bw[k]; ++ty)
-                for (int tx = x0[k]; tx < x0[k] + bw[k]; ++tx) {
-                    if (at < I_cap) {
-                        tkey[at] = (uint32_t)(tb[k] + ty * tiles_x + tx);
-                        tval[at] = (uint32_t)g[k];
-                    }
-                    ++at;
-                }
+                for (int tx = x0[k]; tx < x0[k] + bw[k]; ++tx) put(at++, (uint32_t)(tb[k] + ty * tiles_x + tx), (uint32_t)g[k]);
         }
         unsigned big = __ballot_sync(0xffffffffu, area[k] > 8);
         while (big) {
@@ -448,13 +458,17 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
             const int sbw = __shfl_sync(0xffffffffu, bw[k], src), sarea = __shfl_sync(0xffffffffu, area[k], src);
             const int sst = __shfl_sync(0xffffffffu, st, src), sg = __shfl_sync(0xffffffffu, g[k], src);
             const int stb = __shfl_sync(0xffffffffu, tb[k], src);
-            for (int q = lane; q < sarea; q += 32) {
-                if (sst + q < I_cap) {
-                    tkey[sst + q] = (uint32_t)(stb + (sy0 + q / sbw) * tiles_x + sx0 + q % sbw);
-                    tval[sst + q] = (uint32_t)sg;
-                }
-            }
+            for (int q = lane; q < sarea; q += 32)
+                put(sst + q, (uint32_t)(stb + (sy0 + q / sbw) * tiles_x + sx0 + q % sbw), (uint32_t)sg);
         }
+    }
+    if (staged) {
+        __syncthreads();
+        for (int at = tid; at < block_total; at += SCAN_TPB)
+            if ((int64_t)cta_off + at < I_cap) {
+                tkey[cta_off + at] = s_key[at];
+                tval[cta_off + at] = s_val[at];
+            }
     }
 }
 
@@ -500,6 +514,15 @@ int &depth_sort_passes() {
     return passes;
 }
 
+// implementation behind gs_bin_fast: 1 = LSD pipeline (this file, default), 0 = bucket pipeline (tilebucket.cu)
+int &bin_impl() {
+    static int impl = [] {
+        const char *e = getenv("GS_BIN_IMPL");
+        return (e && (e[0] == 'b' || e[0] == '0')) ? 0 : 1;       // GS_BIN_IMPL=bucket
+    }();
+    return impl;
+}
+
 template <int BITS>
 int partition_pass(int64_t I_cap, const int32_t *total_dev, const uint32_t *kin, const uint32_t *vin, uint32_t *kout,
                    uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st, int32_t *bins = nullptr,
@@ -509,6 +532,12 @@ int partition_pass(int64_t I_cap, const int32_t *total_dev, const uint32_t *kin,
 
 }  // namespace
 
+extern "C" int gs_set_bin_impl(int impl) {
+    const int prev = bin_impl();
+    if (impl == 0 || impl == 1) bin_impl() = impl;
+    return prev;
+}
+
 extern "C" int gs_set_depth_sort_passes(int passes) {
     const int prev = depth_sort_passes();
     if (passes == 3 || passes == 4) depth_sort_passes() = passes;
@@ -516,8 +545,8 @@ extern "C" int gs_set_depth_sort_passes(int passes) {
 }
 
 extern "C" size_t gs_bin_fast_scratch_bytes(int N, int64_t I_cap, int T) {
-    (void)T;
-    return fast_layout(N, I_cap).total;
+    const size_t lsd = fast_layout(N, I_cap).total, bucket = gs_bin_bucket_scratch_bytes(I_cap, T > 0 ? T : 1);
+    return lsd > bucket ? lsd : bucket;       // either implementation can run in the same scratch buffer
 }
 
 // N = elements of ALL views (view v owns [v * n_per_view, (v + 1) * n_per_view)); xy of element g at
@@ -540,6 +569,9 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
         return 0;
     }
     if (!xys || !depths || !radii || !tiles_hit || (!ids_sorted && I_cap > 0)) return GS_ERR_BAD_ARG;
+    if (bin_impl() == 0 && gs_bin_bucket_supported(tiles_x * tiles_y, I_cap))
+        return gs_bin_bucket_ex(N, n_per_view, I_cap, xys, xy_stride, depths, radii, tiles_x, tiles_y, ids_sorted, tile_bins,
+                                total_dev, scratch, scratch_bytes, stream);
     const FastLayout L = fast_layout(N, I_cap);
     if (scratch_bytes < L.total) return GS_ERR_SCRATCH_SMALL;
     if (!gs_aligned16(scratch)) return GS_ERR_MISALIGNED;

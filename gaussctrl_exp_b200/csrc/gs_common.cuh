@@ -98,6 +98,12 @@ __device__ __forceinline__ float4 gs_ldg_stream4(const float4 *p) {
 int gs_internal_exclusive_scan(int n, const int32_t *in, int32_t *out, int32_t *total_dev, void *scratch,
                                size_t scratch_bytes, cudaStream_t st);
 // binning.cu: gs_bin_fast over the elements of several views at once, xy read with a stride (packed records)
+// bucket form of the binning (tilebucket.cu): same contract as gs_bin_fast_ex below
+size_t gs_bin_bucket_scratch_bytes(int64_t I_cap, int T);
+bool gs_bin_bucket_supported(int T_view, int64_t I_cap);
+int gs_bin_bucket_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int xy_stride, const float *depths,
+                     const int32_t *radii, int tiles_x, int tiles_y, int32_t *ids_sorted, int32_t *tile_bins,
+                     int32_t *total_dev, void *scratch, size_t scratch_bytes, void *stream);
 int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int xy_stride, const float *depths,
                    const int32_t *radii, const int32_t *tiles_hit, int tiles_x, int tiles_y, int32_t *ids_sorted,
                    int32_t *tile_bins, int32_t *total_dev, void *scratch, size_t scratch_bytes, void *stream);

@@ -224,6 +224,10 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
             const unsigned bal = __ballot_sync(0xffffffffu, (dig[i] >> b) & 1u);
             pm &= ((dig[i] >> b) & 1u) ? bal : ~bal;
         }
+        if (bits < BITS) {   // the padding digit RADIX-1 lies outside the mask: keep it apart from the valid digit `mask`
+            const unsigned bal = __ballot_sync(0xffffffffu, li < valid);
+            pm &= (li < valid) ? bal : ~bal;
+        }
         peers[i] = pm;
     }
 #pragma unroll

@@ -104,6 +104,47 @@ vx_push_kernel(int Np, int Wp, int D, int self, const float4 *__restrict__ src,
     }
 }
 
+// ---- sender 3b (SLICE exchange): peer d owns the Gaussians [d * S, (d + 1) * S) for the leaf backward, so it only needs
+// that range of this view's compacted block: its meta words, the camera, and — the packed arrays being in index
+// order — ONE contiguous run [k_lo, k_hi) of each of them (k = packed index from the meta prefix at the slice
+// boundaries). ~1/p of the block per peer instead of all of it: the bytes a rank sends per step no longer grow with p.
+// grid (blocks, D): blockIdx.y = destination. Runs are copied as float4 supersets (a few values of the neighbouring
+// slices ride along; the destination never reads them).
+__global__ void __launch_bounds__(VX_PUSH_TPB)
+vx_push_slices_kernel(int Np, int Wp, int D, int self, int slice_words, const float4 *__restrict__ src,
+                      const unsigned long long *__restrict__ peer_ptrs, size_t peer_off) {
+    gs_pdl_sync();
+    const int d = blockIdx.y;
+    if (d == self) return;
+    const int wlo = min(d * slice_words, Wp), whi = min(wlo + slice_words, Wp);
+    if (wlo >= whi) return;
+    float4 *dst = reinterpret_cast<float4 *>(reinterpret_cast<float *>(peer_ptrs[d]) + peer_off);
+    const uint2 *meta = reinterpret_cast<const uint2 *>(src);
+    const uint2 last = meta[Wp - 1];
+    const int nnz = (int)last.y + __popc(last.x);
+    const int k_lo = (int)meta[wlo].y, k_hi = whi < Wp ? (int)meta[whi].y : nnz;
+    const int h4 = (2 * Wp + 64) / 4, q = Np / 4;
+    // float4 runs: [begin, end) pairs inside the exchange buffer
+    const int m0 = wlo / 2, m1 = (whi + 1) / 2;                               // meta (2 words per float4)
+    const int c0 = (2 * Wp) / 4, c1 = h4;                                     // camera
+    const int xy0 = h4 + (2 * k_lo) / 4, xy1 = h4 + (2 * k_hi + 3) / 4;
+    const int cn0 = h4 + 2 * q + (3 * k_lo) / 4, cn1 = h4 + 2 * q + (3 * k_hi + 3) / 4;
+    const int rg0 = h4 + 5 * q + (3 * k_lo) / 4, rg1 = h4 + 5 * q + (3 * k_hi + 3) / 4;
+    const int op0 = h4 + 8 * q + k_lo / 4, op1 = h4 + 8 * q + (k_hi + 3) / 4;
+    const int n0 = m1 - m0, n1 = n0 + (c1 - c0), n2 = n1 + (xy1 - xy0), n3 = n2 + (cn1 - cn0), n4 = n3 + (rg1 - rg0);
+    const int total = n4 + (op1 - op0);
+    for (int t = blockIdx.x * VX_PUSH_TPB + threadIdx.x; t < total; t += gridDim.x * VX_PUSH_TPB) {
+        int idx;
+        if (t < n0) idx = m0 + t;
+        else if (t < n1) idx = c0 + (t - n0);
+        else if (t < n2) idx = xy0 + (t - n1);
+        else if (t < n3) idx = cn0 + (t - n2);
+        else if (t < n4) idx = rg0 + (t - n3);
+        else idx = op0 + (t - n4);
+        dst[idx] = src[idx];
+    }
+}
+
 struct ViewGrad {
     float2 xy;
     float a, b, c, u0, u1, u2, o;
@@ -268,8 +309,10 @@ __host__ __device__ inline size_t vi_smem_bytes(int V) {
            4 * 32 * (size_t)V * sizeof(uint16_t);
 }
 
+// g_first (a multiple of VI_TPB): first Gaussian of the range this launch covers; N = its end. The six output
+// pointers are those of ROW 0 (for a slice-shaped output the caller passes them pre-offset by -g_first rows).
 __global__ void __launch_bounds__(VI_TPB)
-vx_bwd_items_kernel(int N, int Np, int Wp, int V, const unsigned long long *__restrict__ peer_ptrs, size_t peer_off,
+vx_bwd_items_kernel(int g_first, int N, int Np, int Wp, int V, const unsigned long long *__restrict__ peer_ptrs, size_t peer_off,
                     float scale, const float *__restrict__ means, const float *__restrict__ log_scales,
                     const float4 *__restrict__ quats, const float *__restrict__ opac_logits, int use_sh, int deg,
                     float *__restrict__ v_means, float *__restrict__ v_log_scales, float4 *__restrict__ v_quats,
@@ -280,7 +323,7 @@ vx_bwd_items_kernel(int N, int Np, int Wp, int V, const unsigned long long *__re
     const float **blk_s = reinterpret_cast<const float **>(vi_smem + 4 * sizeof(ViWarp));
     GsCamera *cam_s = reinterpret_cast<GsCamera *>(blk_s + VX_MAX_VIEWS);
     uint16_t *items = reinterpret_cast<uint16_t *>(cam_s + V) + warp * 32 * V;
-    const int i = blockIdx.x * VI_TPB + tid;
+    const int i = g_first + blockIdx.x * VI_TPB + tid;
     const int w = i >> 5;
     if (tid < V) blk_s[tid] = reinterpret_cast<const float *>(peer_ptrs[tid]) + peer_off;
     __syncthreads();
@@ -513,7 +556,7 @@ extern "C" int gs_preprocess_bwd_multi_peer_sparse(int N, int V, const uint64_t 
         GS_CUDA(cudaFuncSetAttribute(vx_bwd_items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)vi_smem_bytes(VX_MAX_VIEWS)));
         vx_bwd_items_kernel<<<(N + VI_TPB - 1) / VI_TPB, VI_TPB, vi_smem_bytes(V), (cudaStream_t)stream>>>(
-            N, Np, vx_words(N), V, reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats,
+            0, N, Np, vx_words(N), V, reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats,
             scale, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, v_means,
             v_log_scales, reinterpret_cast<float4 *>(v_quats), v_opac_logits, v_feat_dc, v_feat_rest);
         GS_LAUNCH_CHECK();
@@ -523,6 +566,71 @@ extern "C" int gs_preprocess_bwd_multi_peer_sparse(int N, int V, const uint64_t 
         N, Np, vx_words(N), V, reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats,
         scale, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg, v_means,
         v_log_scales, reinterpret_cast<float4 *>(v_quats), v_opac_logits, v_feat_dc, v_feat_rest);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---- owner-sliced exchange (data-parallel step whose cost per rank does not grow with the number of ranks) ----------
+// Slice size in Gaussians for `world` owners: ceil(N / world) rounded up to 128 (the leaf-backward CTA), so that slice
+// boundaries are bitmap-word and float4 aligned. Owner d holds [d * S, min((d + 1) * S, N)).
+extern "C" int gs_view_slice_size(int N, int world) {
+    if (N < 0 || world <= 0) return GS_ERR_BAD_ARG;
+    const int per = (N + world - 1) / world;
+    return (per + VI_TPB - 1) / VI_TPB * VI_TPB;
+}
+
+// Like gs_pack_view_block_push, but every peer receives only the part of the compacted block that covers ITS slice.
+extern "C" int gs_pack_view_block_push_slices(int N, const float *block, float *xbuf_self, int n_peers, int self,
+                                              const uint64_t *peer_base_ptrs_dev, int64_t offset_floats, void *scratch,
+                                              size_t scratch_bytes, void *stream) {
+    if (!peer_base_ptrs_dev || offset_floats < 0 || n_peers <= 0 || n_peers > VX_MAX_VIEWS || self < 0 || self >= n_peers)
+        return GS_ERR_BAD_ARG;
+    if (offset_floats & 3) return GS_ERR_MISALIGNED;
+    const int rc = gs_pack_view_block(N, block, xbuf_self, scratch, scratch_bytes, stream);
+    if (rc || n_peers == 1 || N == 0) return rc;
+    const int Np = (N + 3) / 4 * 4;
+    const int S = gs_view_slice_size(N, n_peers);
+    cudaLaunchConfig_t c = {};
+    c.gridDim = dim3(148, n_peers);
+    c.blockDim = dim3(VX_PUSH_TPB);
+    c.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute a[1];
+    a[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    a[0].val.programmaticStreamSerializationAllowed = 1;
+    c.attrs = a;
+    c.numAttrs = gs_pdl_enabled(GS_PDL_GROUP) ? 1 : 0;
+    GS_CUDA(cudaLaunchKernelEx(&c, vx_push_slices_kernel, Np, vx_words(N), n_peers, self, S / 32,
+                               reinterpret_cast<const float4 *>(xbuf_self),
+                               reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats));
+    ++g_gs_launches;
+    return 0;
+}
+
+// Leaf backward of the Gaussians [g_lo, g_hi) over V compacted view blocks (g_lo a multiple of 128). Outputs are
+// SLICE-shaped: row 0 of every output array is Gaussian g_lo. v_feat_rest must be 16-byte aligned.
+extern "C" int gs_leaf_bwd_slice(int N, int g_lo, int g_hi, int V, const uint64_t *peer_base_ptrs_dev,
+                                 int64_t offset_floats, float scale, const float *means, const float *log_scales,
+                                 const float *quats, const float *opac_logits, int use_sh, int sh_deg, float *v_means,
+                                 float *v_log_scales, float *v_quats, float *v_opac_logits, float *v_feat_dc,
+                                 float *v_feat_rest, void *stream) {
+    if (N < 0 || V <= 0 || V > VX_MAX_VIEWS || !peer_base_ptrs_dev || g_lo < 0 || g_hi > N || (g_lo % VI_TPB) != 0)
+        return GS_ERR_BAD_ARG;
+    if (sh_deg < 0 || sh_deg > 3) return GS_ERR_UNSUPPORTED;
+    if (g_hi <= g_lo) return 0;
+    if (!means || !log_scales || !quats || !opac_logits || !v_means || !v_log_scales || !v_quats || !v_opac_logits ||
+        !v_feat_dc || !v_feat_rest)
+        return GS_ERR_BAD_ARG;
+    if (!gs_aligned16(quats) || !gs_aligned16(v_quats) || !gs_aligned16(v_feat_rest) || (offset_floats & 3))
+        return GS_ERR_MISALIGNED;
+    const int Np = (N + 3) / 4 * 4;
+    GS_CUDA(cudaFuncSetAttribute(vx_bwd_items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)vi_smem_bytes(VX_MAX_VIEWS)));
+    const size_t o = (size_t)g_lo;
+    vx_bwd_items_kernel<<<(g_hi - g_lo + VI_TPB - 1) / VI_TPB, VI_TPB, vi_smem_bytes(V), (cudaStream_t)stream>>>(
+        g_lo, g_hi, Np, vx_words(N), V, reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev),
+        (size_t)offset_floats, scale, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg,
+        v_means - 3 * o, v_log_scales - 3 * o, reinterpret_cast<float4 *>(v_quats) - o, v_opac_logits - o, v_feat_dc - 3 * o,
+        v_feat_rest - (size_t)VX_REST * o);
     GS_LAUNCH_CHECK();
     return 0;
 }

@@ -200,10 +200,13 @@ class ViewState:
     """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii). The per-Gaussian and tile
     arrays are lazy views into the last view's workspace (no tensor is created unless somebody asks)."""
     __slots__ = ("num_intersects", "xys_grad", "flat_grads", "defer_leaf_grads", "view_block", "view_meta",
-                 "view_block_buffer", "final_idx", "final_T", "workspace", "_empty")
+                 "view_block_buffer", "final_idx", "final_T", "workspace", "_empty", "sharded_grads", "shard")
 
     def __init__(self):
         self.xys_grad = self.flat_grads = None
+        # owner-sliced data-parallel mode (dist.PeerViewExchange mode="slice"): gradients of this rank's Gaussians
+        # [shard[0], shard[1]) summed over all ranks' views, slice-shaped
+        self.sharded_grads = self.shard = None
         # integer by-products of the last view (what gsplat's rasterize keeps for its backward); the parity
         # tests compare them bit for bit with the oracle
         self.final_idx = self.final_T = self.workspace = self._empty = None
@@ -471,6 +474,33 @@ def composite_extra(state_tensors, colors: Tensor, camera: Camera, background: T
                                       bg.data_ptr(), out.data_ptr(), fT.data_ptr(), fidx.data_ptr(), _lib.stream_ptr())
     _lib.check(rc, "gs_raster_fwd")
     return out
+
+
+def leaf_grads_slice(params, lo: int, hi: int, num_views: int, use_sh: bool, deg: int, scale: float, peer_ptrs_dev: int,
+                     peer_offset: int):
+    """gs_leaf_bwd_slice: leaf gradients of the Gaussians [lo, hi) summed over `num_views` compacted view blocks that sit
+    in this rank's exchange slots. Returns (flat, dict of SLICE-shaped gradients: row 0 = Gaussian lo)."""
+    means, scales, quats, opacities = params["means"], params["scales"], params["quats"], params["opacities"]
+    dev = means.device
+    N, n = means.shape[0], max(hi - lo, 0)
+    npad = (n + 3) // 4 * 4
+    L = _lib.lib()
+    flat = torch.empty(59 * npad, device=dev, dtype=torch.float32)
+    out = {"means": flat[0:3 * n].view(n, 3), "scales": flat[3 * npad:3 * npad + 3 * n].view(n, 3),
+           "quats": flat[6 * npad:6 * npad + 4 * n].view(n, 4),
+           "opacities": flat[10 * npad:10 * npad + n].view((n,) + tuple(opacities.shape[1:])),
+           "features_dc": flat[11 * npad:11 * npad + 3 * n].view(n, 3),
+           "features_rest": flat[14 * npad:14 * npad + 45 * n].view(n, 15, 3)}
+    if n == 0:
+        return flat, out
+    with torch.cuda.device(dev):
+        rc = L.gs_leaf_bwd_slice(
+            N, int(lo), int(hi), int(num_views), int(peer_ptrs_dev), int(peer_offset), float(scale), means.detach().data_ptr(),
+            scales.detach().data_ptr(), quats.detach().data_ptr(), opacities.detach().data_ptr(), int(use_sh), int(deg),
+            out["means"].data_ptr(), out["scales"].data_ptr(), out["quats"].data_ptr(), out["opacities"].data_ptr(),
+            out["features_dc"].data_ptr(), out["features_rest"].data_ptr(), _lib.stream_ptr())
+    _lib.check(rc, "gs_leaf_bwd_slice")
+    return flat, out
 
 
 def leaf_grads_from_view_blocks(params, blocks, num_views: int, use_sh: bool, deg: int, scale: float = 1.0,

@@ -134,8 +134,13 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
         with torch.cuda.device(dev):
-            # global depth sort + partition (gs_bin_fast); "lsd3": three 11/11/10-bit depth passes
+            # gs_bin_fast. "lsd" (default): global depth sort + scan/emission + stable partition by tile; "lsd3": the
+            # same with three 11/11/10-bit depth passes; "bucket": per-tile segments filled unordered, then sorted per
+            # tile in shared memory — identical output
+            if impl not in ("bucket", "lsd", "lsd3"):
+                raise ValueError(f"unknown binning implementation {impl!r}")
             prev = L.gs_set_depth_sort_passes(3) if impl == "lsd3" else None
+            prev_legacy = L.gs_set_bin_impl(0 if impl == "bucket" else 1)
             try:
                 scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")
                 rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
@@ -144,6 +149,7 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
             finally:
                 if prev is not None:
                     L.gs_set_depth_sort_passes(prev)
+                L.gs_set_bin_impl(prev_legacy)
         _lib.check(rc, "gs_bin_fast")
         I = int(total.item())
         if I <= cap:

@@ -159,6 +159,22 @@ int gs_preprocess_bwd_multi_peer_sparse(int N, int V, const uint64_t *peer_base_
                                         float *v_means, float *v_log_scales, float *v_quats,
                                         float *v_opac_logits, float *v_feat_dc, float *v_feat_rest, void *stream);
 
+/* Owner-sliced form of the exchange: rank d owns the Gaussians [d * S, min((d + 1) * S, N)), S = gs_view_slice_size(N,
+ * world) (ceil(N / world) rounded up to 128), for the leaf backward AND for the optimiser step that follows
+ * (gc_trainer.py:276-298 steps the optimisers of gc_config.py:58-87 right after backward). Every rank pushes each peer
+ * only the part of its compacted view block that covers the peer's slice (gs_pack_view_block_push_slices: ~1/world of
+ * the block per peer), and after the device barrier runs gs_leaf_bwd_slice over ITS slice and all `V` views: slice-shaped
+ * outputs (row 0 = Gaussian g_lo) holding scale * sum over the views. Work and NVLink bytes per rank are then
+ * independent of the number of ranks. */
+int gs_view_slice_size(int N, int world);
+int gs_pack_view_block_push_slices(int N, const float *block, float *xbuf_self, int n_peers, int self,
+                                   const uint64_t *peer_base_ptrs_dev, int64_t offset_floats, void *scratch,
+                                   size_t scratch_bytes, void *stream);
+int gs_leaf_bwd_slice(int N, int g_lo, int g_hi, int V, const uint64_t *peer_base_ptrs_dev, int64_t offset_floats,
+                      float scale, const float *means, const float *log_scales, const float *quats,
+                      const float *opac_logits, int use_sh, int sh_deg, float *v_means, float *v_log_scales,
+                      float *v_quats, float *v_opac_logits, float *v_feat_dc, float *v_feat_rest, void *stream);
+
 /* ---- stage 2: tile binning (inside rasterize_gaussians; App. A.3) -------------------------- */
 size_t gs_scan_scratch_bytes(int N);
 /* inclusive int32 scan of tiles_hit -> cum; the total is also written to *total_dev
@@ -190,6 +206,12 @@ int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, con
  * launches; measured slower) stable LSD passes — identical output. Returns the previous setting; other values only query.
  * Initial value: environment variable GS_DEPTH_SORT_PASSES. */
 int gs_set_depth_sort_passes(int passes);
+/* Implementation behind gs_bin_fast / gs_view_fwd: 1 (default) = LSD pipeline — depth sort of the Gaussians, scan +
+ * emission in depth order, stable partition by tile; 0 = bucket pipeline — per-tile counts, scan, unordered fill of
+ * (depth bits, id) entries into each tile's segment, one CTA per tile merge-sorts its segment in shared memory (four
+ * launches instead of sixteen, but measured slower: the per-tile sort is instruction-bound). Identical output. Returns
+ * the previous setting; other values only query. Initial value: environment variable GS_BIN_IMPL=bucket. */
+int gs_set_bin_impl(int impl);
 
 /* ---- stage 3: forward compositing (App. A.4) ----------------------------------------------- */
 /* colors (N,C); opac (N); bg (C) device; out_img (H,W,C); final_T (H,W); final_idx (H,W) =

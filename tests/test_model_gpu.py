@@ -85,7 +85,7 @@ def test_full_size_properties(cuda_dev):
     assert bool((ks[1:] >= ks[:-1]).all())
     ref_k, ref_perm = torch.sort(keys, stable=True)      # library sort as a cross-check of OUR sort
     assert torch.equal(ks, ref_k) and torch.equal(vs, ids[ref_perm])
-    for impl in ("lsd", "lsd3"):
+    for impl in ("bucket", "lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         assert I2 == I and torch.equal(ids2[:I], vs) and torch.equal(bins2, bins), impl
     cnt = (bins[:, 1] - bins[:, 0]).long()

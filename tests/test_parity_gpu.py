@@ -75,7 +75,7 @@ def test_sh(oracle, cuda_dev, K, deg):
 
 
 @pytest.mark.parametrize("N,W,H,seed,s0", [(8000, 128, 80, 1, 0.03), (50000, 512, 512, 0, 0.005), (300, 1920, 1080, 2, 0.3),
-                                           (5, 33, 17, 3, 0.05)])
+                                           (5, 33, 17, 3, 0.05), (120000, 1920, 1080, 4, 0.004), (4097, 256, 256, 6, 0.02)])
 def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
     from gaussctrl_exp_b200 import utils as U
     d = projected(oracle, N=N, W=W, H=H, seed=seed, s0=s0)
@@ -92,7 +92,7 @@ def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
     assert np.array_equal(vs.cpu().numpy(), b.ids_sorted)
     assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
     # product paths: identical ids_sorted and tile ranges without 64-bit keys
-    for impl in ("lsd", "lsd3"):
+    for impl in ("bucket", "lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         assert I2 == b.I, impl
         assert np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted), impl
@@ -116,7 +116,7 @@ def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
     b = oracle.bin_and_sort(xys, depths, radii, hit, tb)
     assert b.I == int(hit.sum()) and (b.tile_bins[:, 1] - b.tile_bins[:, 0]).max() > 50000
     t = [_t(a, cuda_dev) for a in (xys, depths, radii, hit)]
-    for impl in ("lsd", "lsd3"):
+    for impl in ("bucket", "lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(*t, tb, impl=impl)
         assert I2 == b.I
         assert np.array_equal(bins2.cpu().numpy(), b.tile_bins), impl
@@ -126,7 +126,7 @@ def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
     r2 = np.where(sel, radii, 0).astype(np.int32)
     h2 = np.where(r2 > 0, 6, 0).astype(np.int32)
     b = oracle.bin_and_sort(xys, depths, r2, h2, tb)
-    ids2, bins2, I2 = U.bin_fast(t[0], t[1], _t(r2, cuda_dev), _t(h2, cuda_dev), tb, impl="lsd")
+    ids2, bins2, I2 = U.bin_fast(t[0], t[1], _t(r2, cuda_dev), _t(h2, cuda_dev), tb, impl="bucket")
     assert I2 == b.I and np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted)
 
 

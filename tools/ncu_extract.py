@@ -1,6 +1,6 @@
 """Turns an `ncu --set full` report into the per-kernel JSON bench.py reads (profiles/rNN_ncu_metrics.json) and a
 readable table (profiles/rNN_ncu_summary.md). Run HERE on the .ncu-rep that came back in gpurun_out/:
-    python tools/ncu_extract.py gpurun_out/prof.ncu-rep profiles/r02
+    python tools/ncu_extract.py gpurun_out/prof.ncu-rep|gpurun_out/prof_raw.csv profiles/r02
 Per kernel NAME the LAST captured launch is kept (the warmest one), plus the number of launches seen."""
 import csv
 import io
@@ -48,14 +48,21 @@ def num(s):
 
 def main():
     rep, out = sys.argv[1], sys.argv[2]
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    if rep.endswith(".csv"):       # the raw page already exported on the GPU box (tools/ncu_round.sh)
+        raw = open(rep).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    raw = raw[raw.index('"ID"'):]
     rows = list(csv.reader(io.StringIO(raw)))
     head, units, body = rows[0], rows[1], rows[2:]
     col = {h: i for i, h in enumerate(head)}
     kname = col["Kernel Name"]
     kernels, order = {}, []
     for r in body:
-        name = re.sub(r"<.*", "", r[kname].split("(")[0]).strip()
+        name = r[kname].split("(")[0].replace("<unnamed>::", "").replace("void ", "").strip()
+        name = re.sub(r"^gsradix::", "", name)
+        base_name = re.sub(r"<.*", "", name)
+        name = base_name if base_name.startswith(("raster_", "preprocess_")) else name      # keep template args of the radix passes
         ent = {"launches_captured": kernels.get(name, {}).get("launches_captured", 0) + 1, "full_name": r[kname][:160]}
         for m, key in WANT.items():
             if m in col:
