@@ -468,19 +468,36 @@ def run_ours(args):
             return flat
         step(0)
         torch.cuda.synchronize()
-        a = model.view_state.flat_grads.clone()
+        sliced = peer is not None and peer.mode == "slice"
+        if sliced:
+            # owner-sliced exchange: every rank holds the reduced gradients of ITS Gaussians [lo, hi) only
+            lo, hi = model.view_state.shard
+            mine = {k: v.clone() for k, v in model.view_state.sharded_grads.items()}
+        else:
+            a = model.view_state.flat_grads.clone()
         b = grads_allreduce(0)
         torch.cuda.synchronize()
         den = b.abs().max().clamp_min(1e-30)
-        diff = ((a - b).abs().max() / den).reshape(1)
-        # bit pattern checksum of this rank's reduced gradients: identical on every rank?
-        chk = a.view(torch.int32).to(torch.int64).sum().reshape(1)
-        chks = [torch.zeros_like(chk) for _ in range(world)]
-        dist.all_gather(chks, chk)
+        if sliced:
+            full = dict(zip(gdist.GRAD_PARAMS, (lambda t: (t[0], t[1], t[2], t[4], t[5], t[3]))(
+                grender.split_flat_grads(b, args.n_gaussians, tuple(model.opacities.shape)))))
+            diff = torch.stack([(mine[k] - full[k][lo:hi]).abs().max() for k in gdist.GRAD_PARAMS]).max().div(den).reshape(1)
+            covered = torch.tensor([hi - lo], device=dev)
+            dist.all_reduce(covered)
+            identical = bool(int(covered.item()) == args.n_gaussians)       # the slices partition the Gaussians
+        else:
+            diff = ((a - b).abs().max() / den).reshape(1)
+            # bit pattern checksum of this rank's reduced gradients: identical on every rank?
+            chk = a.view(torch.int32).to(torch.int64).sum().reshape(1)
+            chks = [torch.zeros_like(chk) for _ in range(world)]
+            dist.all_gather(chks, chk)
+            identical = bool(all(int(c.item()) == int(chks[0].item()) for c in chks))
         dist.all_reduce(diff, op=dist.ReduceOp.MAX)
         grad_check = {"exchange": args.reduce + ("/" + args.exchange if args.reduce == "peer" else ""),
-                      "against": "NCCL sum-allreduce of the 59-float leaf gradients, averaged",
-                      "max_rel_diff": float(diff.item()), "ranks_identical": bool(all(int(c.item()) == int(chks[0].item()) for c in chks)),
+                      "against": "NCCL sum-allreduce of the 59-float leaf gradients, averaged" +
+                                 (" (each rank: its owner slice)" if sliced else ""),
+                      "max_rel_diff": float(diff.item()),
+                      ("slices_partition_the_gaussians" if sliced else "ranks_identical"): identical,
                       "nonzero": bool(b.abs().max().item() > 0), "step": 0}
         # config 4 as BASELINE.json words it: fwd+bwd + NCCL allreduce of the parameter gradients
         for i in range(3):
@@ -613,6 +630,55 @@ def run_ours(args):
     ms_e2e, _ = timed_loop(step_e2e, max(3, args.warmup // 2), args.steps, drain=drain_losses)
     model.speculate = False
 
+    # config 4 with the optimiser step the trainer runs right after backward (gc_trainer.py:276-298; Adam groups of
+    # gc_config.py:58-87): fwd + bwd + gradient exchange + Adam. Owner-sliced exchange: Adam over the rank's slice
+    # (1/world of the state and of the update) + all-gather of the updated rows; otherwise a replicated fused Adam.
+    # Parameters are restored afterwards so that the measurements below see the same scene.
+    def finetune_with_optimizer(n_steps=10):
+        lr = dict(means=1.6e-4, scales=5e-3, quats=1e-3, features_dc=2.5e-3, features_rest=1.25e-4, opacities=5e-2)
+        named = {k: getattr(model, k) for k in gdist.GRAD_PARAMS}
+        saved = {k: p.detach().clone() for k, p in named.items()}
+        sliced = peer is not None and peer.mode == "slice"
+        if sliced or world == 1:
+            # world == 1: the slice is the whole scene (same fused Adam kernel, nothing to exchange)
+            opt = gdist.ShardedAdam(named, rank, world, lr=lr, eps=1e-15, peer=True)
+
+            def fstep(i):
+                step(i)
+                g = model.view_state.sharded_grads if world > 1 else {k: named[k].grad for k in named}
+                opt.step(g)
+                opt.sync()
+        else:
+            opt = torch.optim.Adam([dict(params=[named[k]], lr=lr[k]) for k in named], eps=1e-15, fused=True)
+
+            def fstep(i):
+                step(i)
+                opt.step()
+        for i in range(3):
+            fstep(i)
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for i in range(n_steps):
+            fstep(3 + i)
+        f1.record()
+        barrier()
+        t = torch.tensor([f0.elapsed_time(f1) / n_steps], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        with torch.no_grad():
+            for k, p in named.items():
+                p.copy_(saved[k])
+                p.grad = None
+        del opt, saved
+        torch.cuda.empty_cache()
+        return {"ms_per_step": float(t.item()), "views_per_s": world * 1e3 / float(t.item()), "n_gpus": world,
+                "optimizer": ("gs_adam_slice over owner slices (1/%d of the rows per rank), updated rows stored into every peer's "
+                              "parameters by the same kernel (NVLink symmetric memory) + device barrier" % world)
+                if (sliced or world == 1) else "replicated torch.optim.Adam(fused=True)",
+                "what": "fwd + bwd + gradient exchange + Adam step (gc_trainer.py:276-298, lr groups of gc_config.py:58-87)"}
+    finetune_opt = finetune_with_optimizer() if model.fused else None
+
     # config 3: all-view eval render, RGB + depth + alpha, 40 views sharded over the ranks, batched
     def render_all():
         return model.render_views(cams, rank, world, batch=args.render_batch)
@@ -651,6 +717,8 @@ def run_ours(args):
                 "what": f"all-view RGB+depth+alpha render of {N_CAMS} cameras, 1M Gaussians, 512^2 (gc_pipeline.py:222-228), "
                         f"view-sharded over {world} GPU(s), batches of {args.render_batch} cameras per call"},
         }
+        if finetune_opt is not None:
+            line["config4_finetune_step_with_optimizer"] = finetune_opt
         if allreduce_ms is not None:
             line["config4_finetune_step_nccl_allreduce"] = {
                 "views_per_s": world * 1e3 / allreduce_ms, "ms_per_step": allreduce_ms, "n_gpus": world,
@@ -756,7 +824,7 @@ def main():
                          "compositor-level grads (36 B/Gaussian) in place over NVLink (symmetric memory, collective fused "
                          "into the kernel); gather = same payload through one NCCL all-gather; allreduce = NCCL "
                          "all-reduce of the 236 B/Gaussian leaf grads")
-    ap.add_argument("--exchange", choices=("push", "dense", "sparse"), default="push",
+    ap.add_argument("--exchange", choices=("slice", "push", "dense", "sparse"), default="slice",
                     help="peer-memory exchange: compacted blocks pushed to the peers (default), dense pull, compacted pull")
     ap.add_argument("--path", default="fused", choices=["fused", "api"],
                     help="fused: one autograd node / two C calls per view (render.py); api: the literal "

@@ -42,6 +42,7 @@ SIGNATURES = {
     "gs_view_pack_scratch_bytes": (_sz, [_i]),
     "gs_pack_view_block": (_i, [_i, _vp, _vp, _vp, _sz, _vp]),
     "gs_pack_view_block_push": (_i, [_i, _vp, _vp, _i, _i, _vp, _i64, _vp, _sz, _vp]),
+    "gs_adam_slice": (_i, [_i64, _vp, _vp, _vp, _vp, _f, _f, _f, _f, _f, _i, _i, _vp, _i64, _vp]),
     "gs_view_slice_size": (_i, [_i, _i]),
     "gs_pack_view_block_push_slices": (_i, [_i, _vp, _vp, _i, _i, _vp, _i64, _vp, _sz, _vp]),
     "gs_leaf_bwd_slice": (_i, [_i, _i, _i, _i, _vp, _i64, _f, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -10,6 +10,7 @@
 // Receivers (gs_preprocess_bwd_multi_peer_sparse) walk the Gaussians; a warp owns one bitmap word, so the
 // word and its prefix are one broadcast load each and the packed values of the warp's set lanes are
 // consecutive (coalesced peer loads). NVLink bytes per view drop from 36 N to ~0.25 N + 36 nnz.
+#include <algorithm>
 #include <cstdlib>
 
 #define GS_PDL_GROUP 4
@@ -631,6 +632,73 @@ extern "C" int gs_leaf_bwd_slice(int N, int g_lo, int g_hi, int V, const uint64_
         (size_t)offset_floats, scale, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, use_sh, sh_deg,
         v_means - 3 * o, v_log_scales - 3 * o, reinterpret_cast<float4 *>(v_quats) - o, v_opac_logits - o, v_feat_dc - 3 * o,
         v_feat_rest - (size_t)VX_REST * o);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---- optimiser step of the owner-sliced mode, fused with the parameter exchange ---------------------------------------
+// Adam (torch.optim.Adam's update rule; what gc_trainer.py:276-298 steps after backward, with the per-group learning
+// rates of gc_config.py:58-87) over `count` consecutive elements of ONE parameter tensor — this rank's rows — and, in the
+// same kernel, the all-gather that a replicated-parameter data-parallel step needs afterwards: every updated value is
+// stored into the same element of every peer's copy of the tensor (posted NVLink stores into symmetric memory), so the
+// transfer rides under the kernel's own HBM traffic (28 B read+written per element locally, 4 B per peer sent).
+namespace {
+__device__ __forceinline__ void adam_one(float &p, float g, float &m, float &v, float step_size, float b1, float b2, float eps,
+                                         float inv_sqrt_c2) {
+    m = b1 * m + (1.0f - b1) * g;
+    v = b2 * v + (1.0f - b2) * g * g;
+    p -= step_size * m / (sqrtf(v) * inv_sqrt_c2 + eps);
+}
+
+__global__ void __launch_bounds__(256)
+adam_slice_kernel(int64_t count, float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
+                  float *__restrict__ v, float step_size, float b1, float b2, float eps, float inv_sqrt_c2, int D, int self,
+                  const unsigned long long *__restrict__ peer_ptrs, size_t peer_off) {
+    __shared__ float *dst_s[VX_MAX_VIEWS];
+    if (threadIdx.x < D) dst_s[threadIdx.x] = peer_ptrs ? reinterpret_cast<float *>(peer_ptrs[threadIdx.x]) + peer_off : nullptr;
+    __syncthreads();
+    const int64_t n4 = count / 4;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n4; t += (int64_t)gridDim.x * blockDim.x) {
+        const float4 gg = reinterpret_cast<const float4 *>(g)[t];
+        float4 mm = reinterpret_cast<float4 *>(m)[t], vv = reinterpret_cast<float4 *>(v)[t], pp = reinterpret_cast<float4 *>(p)[t];
+        adam_one(pp.x, gg.x, mm.x, vv.x, step_size, b1, b2, eps, inv_sqrt_c2);
+        adam_one(pp.y, gg.y, mm.y, vv.y, step_size, b1, b2, eps, inv_sqrt_c2);
+        adam_one(pp.z, gg.z, mm.z, vv.z, step_size, b1, b2, eps, inv_sqrt_c2);
+        adam_one(pp.w, gg.w, mm.w, vv.w, step_size, b1, b2, eps, inv_sqrt_c2);
+        reinterpret_cast<float4 *>(m)[t] = mm;
+        reinterpret_cast<float4 *>(v)[t] = vv;
+        reinterpret_cast<float4 *>(p)[t] = pp;
+        for (int d = 0; d < D; ++d)
+            if (d != self && dst_s[d]) reinterpret_cast<float4 *>(dst_s[d])[t] = pp;
+    }
+    // tail (count not a multiple of 4)
+    for (int64_t e = n4 * 4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += (int64_t)gridDim.x * blockDim.x) {
+        float pp = p[e], mm = m[e], vv = v[e];
+        adam_one(pp, g[e], mm, vv, step_size, b1, b2, eps, inv_sqrt_c2);
+        m[e] = mm; v[e] = vv; p[e] = pp;
+        for (int d = 0; d < D; ++d)
+            if (d != self && dst_s[d]) dst_s[d][e] = pp;
+    }
+}
+}  // namespace
+
+// p, g, m, v: `count` fp32 elements each, 16-byte aligned (p = first owned element of the parameter tensor).
+// step_size = lr / (1 - b1^t), inv_sqrt_c2 = 1 / sqrt(1 - b2^t). n_peers > 1 with peer_base_ptrs_dev != NULL: p[e] is also
+// stored at peer_base[d] + offset_floats + e of every other peer d (offset_floats = position of p[0] inside the
+// symmetric buffer; a multiple of 4). The caller orders this after every peer's last read of the old parameters (the
+// exchange barrier of the step) and runs a device barrier before the next forward.
+extern "C" int gs_adam_slice(int64_t count, float *p, const float *g, float *m, float *v, float step_size, float b1, float b2,
+                             float eps, float inv_sqrt_c2, int n_peers, int self, const uint64_t *peer_base_ptrs_dev,
+                             int64_t offset_floats, void *stream) {
+    if (count < 0 || n_peers < 0 || n_peers > VX_MAX_VIEWS || (n_peers > 1 && (self < 0 || self >= n_peers))) return GS_ERR_BAD_ARG;
+    if (count == 0) return 0;
+    if (!p || !g || !m || !v) return GS_ERR_BAD_ARG;
+    if (!gs_aligned16(p) || !gs_aligned16(g) || !gs_aligned16(m) || !gs_aligned16(v) || (offset_floats & 3)) return GS_ERR_MISALIGNED;
+    const int64_t n4 = count / 4 + 1;
+    const int blocks = (int)std::min<int64_t>((n4 + 255) / 256, 148 * 8);
+    adam_slice_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+        count, p, g, m, v, step_size, b1, b2, eps, inv_sqrt_c2, peer_base_ptrs_dev ? n_peers : 0, self,
+        reinterpret_cast<const unsigned long long *>(peer_base_ptrs_dev), (size_t)offset_floats);
     GS_LAUNCH_CHECK();
     return 0;
 }

@@ -90,6 +90,118 @@ def gather_views(local: Dict[int, torch.Tensor], num_views: int, dst: int = 0):
     return out
 
 
+def slice_size(n: int, world: int) -> int:
+    """Gaussians per owner: ceil(n / world) rounded up to 128 (= gs_view_slice_size; the leaf-backward CTA and the
+    bitmap words of the exchange are aligned to it)."""
+    per = (n + world - 1) // world
+    return (per + 127) // 128 * 128
+
+
+def slice_bounds(n: int, rank: int, world: int):
+    """[lo, hi) of the Gaussians rank `rank` owns (possibly empty for the last ranks of a small scene)."""
+    s = slice_size(n, world)
+    lo = min(rank * s, n)
+    return lo, min(lo + s, n)
+
+
+class ShardedAdam:
+    """Adam over this rank's slice of the replicated Gaussian parameters, the consumer of the owner-sliced exchange
+    (PeerViewExchange mode="slice"): torch.optim.Adam's update rule (what gc_config.py:58-87 configures per parameter
+    group and gc_trainer.py:276-298 steps after backward), with the moments kept for the owned rows only (1/world of
+    the optimiser state and of the update work per rank). After `step` + `sync` every rank holds the same updated
+    parameters as a replicated Adam step on all-reduced gradients would leave.
+
+    CUDA parameters are updated by gs_adam_slice (one fused kernel per parameter tensor). peer=True (NCCL world > 1):
+    the six parameters are moved into ONE symmetric-memory buffer and the Adam kernel stores every updated value into
+    all peers' copies as it goes (NVLink, no NCCL call on the data path); `sync` is then a device-side barrier.
+    peer=False: `sync` broadcasts every owner's rows (NCCL / gloo). CPU parameters (tests under gloo): torch ops."""
+
+    def __init__(self, params: Dict[str, torch.Tensor], rank: int, world: int, lr: Dict[str, float] | float = 1e-3,
+                 betas=(0.9, 0.999), eps: float = 1e-15, peer: bool = False):
+        self.params, self.rank, self.world = params, rank, world
+        first = next(iter(params.values()))
+        n = first.shape[0]
+        self.n = n
+        self.lo, self.hi = slice_bounds(n, rank, world)
+        self.lr = {k: (lr[k] if isinstance(lr, dict) else lr) for k in params}
+        self.betas, self.eps, self.t = betas, eps, 0
+        self.m = {k: torch.zeros_like(p.data[self.lo:self.hi]) for k, p in params.items()}
+        self.v = {k: torch.zeros_like(p.data[self.lo:self.hi]) for k, p in params.items()}
+        self.cuda = first.is_cuda
+        self.peer = bool(peer) and self.cuda and world > 1 and dist.is_initialized()
+        self.hdl, self.offset = None, {}
+        if self.peer:
+            import torch.distributed._symmetric_memory as symm_mem
+            off = 0
+            for k, p in params.items():
+                self.offset[k] = off
+                off += (p.numel() + 3) // 4 * 4
+            self.buf = symm_mem.empty(off, dtype=torch.float32, device=first.device)
+            with torch.no_grad():
+                for k, p in params.items():
+                    view = self.buf[self.offset[k]:self.offset[k] + p.numel()].view(p.shape)
+                    view.copy_(p.data)
+                    p.data = view                       # the parameter now lives in symmetric memory
+            self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD)
+
+    @torch.no_grad()
+    def step(self, sharded_grads: Dict[str, torch.Tensor]) -> None:
+        self.t += 1
+        b1, b2 = self.betas
+        c1, c2 = 1.0 - b1 ** self.t, 1.0 - b2 ** self.t
+        if self.cuda:
+            from . import _lib
+            L = _lib.lib()
+            for k, p in self.params.items():
+                width = p.numel() // max(self.n, 1)
+                count = (self.hi - self.lo) * width
+                if count == 0:
+                    continue
+                g = sharded_grads[k]
+                assert g.is_contiguous() and g.numel() == count and p.data.is_contiguous()
+                with torch.cuda.device(p.device):
+                    rc = L.gs_adam_slice(count, p.data.data_ptr() + 4 * self.lo * width, g.data_ptr(), self.m[k].data_ptr(),
+                                         self.v[k].data_ptr(), self.lr[k] / c1, b1, b2, self.eps, 1.0 / c2 ** 0.5,
+                                         self.world if self.peer else 0, self.rank,
+                                         self.hdl.buffer_ptrs_dev if self.peer else None,
+                                         (self.offset[k] + self.lo * width) if self.peer else 0, _lib.stream_ptr())
+                _lib.check(rc, "gs_adam_slice")
+            return
+        names = list(self.params)
+        g = [sharded_grads[k] for k in names]
+        m, v = [self.m[k] for k in names], [self.v[k] for k in names]
+        torch._foreach_lerp_(m, g, 1.0 - b1)                          # m = b1 m + (1 - b1) g
+        torch._foreach_mul_(v, b2)
+        torch._foreach_addcmul_(v, g, g, value=1.0 - b2)              # v = b2 v + (1 - b2) g^2
+        den = torch._foreach_sqrt(v)
+        torch._foreach_div_(den, c2 ** 0.5)
+        torch._foreach_add_(den, self.eps)
+        for k, mk, dk in zip(names, m, den):
+            self.params[k].data[self.lo:self.hi].addcdiv_(mk, dk, value=-self.lr[k] / c1)
+
+    def sync(self) -> None:
+        """After this every rank sees every owner's updated rows."""
+        if self.world == 1 or not dist.is_initialized():
+            return
+        if self.peer:
+            self.hdl.barrier(channel=1)       # all pushes of this step have landed in every rank's parameters
+            return
+        self.allgather_params()
+
+    def allgather_params(self) -> None:
+        """Every owner broadcasts its updated rows (6 parameters x world owners)."""
+        if self.world == 1 or not dist.is_initialized():
+            return
+        works = []
+        for k, p in self.params.items():
+            for r in range(self.world):
+                lo, hi = slice_bounds(self.n, r, self.world)
+                if hi > lo:
+                    works.append(dist.broadcast(p.data[lo:hi], src=r, async_op=True))
+        for w in works:
+            w.wait()
+
+
 def reduce_view_grads(model, average: bool = True) -> None:
     """Data-parallel gradient step for the fused path WITHOUT a 236 B/Gaussian all-reduce.
 
@@ -128,6 +240,13 @@ class PeerViewExchange:
     "dense": every rank accumulates its dense block in symmetric memory; after the barrier the multi-view
         backward kernel PULLS all peers' blocks in place (NVLink-ingress bound: 36 MB x (world-1) per step).
     "sparse": compacted like push but pulled by the receivers (dependent remote loads: latency bound).
+    "slice": owner-sliced. Rank d owns the Gaussians [d*S, (d+1)*S) (slice_bounds) for the leaf backward and for the
+        optimiser step that follows it (ShardedAdam below). Every rank pushes each peer only the part of its compacted
+        block that covers the peer's slice (gs_pack_view_block_push_slices: ~1/world of the block per peer) and
+        runs the leaf backward over ITS slice and all views (gs_leaf_bwd_slice). NVLink bytes and leaf-backward work
+        per rank are then independent of the number of ranks (push/dense/sparse replay ALL Gaussians x ALL views on
+        every rank: an O(world) term, 209 us at 8 views against 61 us for one). Result: view_state.sharded_grads
+        (slice-shaped) + view_state.shard = (lo, hi); the parameters' .grad are left None.
     Two buffers alternate so that a rank may start writing step s+1 while slower peers still read step s
     (the barrier of step s+1 orders the reuse at step s+2)."""
 
@@ -138,19 +257,20 @@ class PeerViewExchange:
         L = _lib.lib()
         if mode is None:
             mode = "push" if sparse is None else ("sparse" if sparse else "dense")
-        assert mode in ("push", "dense", "sparse")
+        assert mode in ("push", "dense", "sparse", "slice")
         self.mode = mode
         self.world = dist.get_world_size()
         self.rank = dist.get_rank()
         self.sparse = mode != "dense"
         N = model.num_points
         self.stride = L.gs_view_xbuf_floats(N) if self.sparse else L.gs_view_block_floats(N)
-        self.slots = self.world if mode == "push" else 1
+        self.slots = self.world if mode in ("push", "slice") else 1
+        self.shard = slice_bounds(N, self.rank, self.world)
         self.buf = symm_mem.empty(2 * self.slots * self.stride, dtype=torch.float32, device=model.device)
         self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD)
         self.scratch = (torch.empty(L.gs_view_pack_scratch_bytes(N), dtype=torch.uint8, device=model.device)
                         if self.sparse else None)
-        if mode == "push":
+        if mode in ("push", "slice"):
             base = self.buf.data_ptr()
             self.local_ptrs = torch.tensor([base + v * self.stride * 4 for v in range(self.world)],
                                            dtype=torch.int64).to(model.device)
@@ -176,10 +296,11 @@ class PeerViewExchange:
                 rc = L.gs_pack_view_block(model.num_points, st.view_block.data_ptr(), xbuf.data_ptr(),
                                           self.scratch.data_ptr(), self.scratch.numel(), _lib.stream_ptr())
             _lib.check(rc, "gs_pack_view_block")
-        elif self.mode == "push":
+        elif self.mode in ("push", "slice"):
             with torch.cuda.device(self.buf.device):
                 off = (k * self.world + self.rank) * self.stride
-                rc = L.gs_pack_view_block_push(model.num_points, st.view_block.data_ptr(),
+                fn = L.gs_pack_view_block_push if self.mode == "push" else L.gs_pack_view_block_push_slices
+                rc = fn(model.num_points, st.view_block.data_ptr(),
                                                self.buf.data_ptr() + 4 * off, self.world, self.rank,
                                                self.hdl.buffer_ptrs_dev, off, self.scratch.data_ptr(),
                                                self.scratch.numel(), _lib.stream_ptr())
@@ -188,6 +309,17 @@ class PeerViewExchange:
         if on_barrier is not None:                  # profiling hook (tools/dp_profile.py)
             on_barrier()
         params = {n: getattr(model, n) for n in GRAD_PARAMS}
+        if self.mode == "slice":
+            lo, hi = self.shard
+            flat, grads = render.leaf_grads_slice(params, lo, hi, self.world, bool(use_sh), deg,
+                                                  1.0 / self.world if average else 1.0, self.local_ptrs.data_ptr(),
+                                                  k * self.world * self.stride)
+            for n in GRAD_PARAMS:
+                getattr(model, n).grad = None
+            st.flat_grads, st.sharded_grads, st.shard = flat, grads, (lo, hi)
+            self.step += 1
+            self.begin(model)
+            return
         if self.mode == "push":
             ptrs, off = self.local_ptrs.data_ptr(), k * self.world * self.stride
         else:

@@ -175,6 +175,15 @@ int gs_leaf_bwd_slice(int N, int g_lo, int g_hi, int V, const uint64_t *peer_bas
                       const float *opac_logits, int use_sh, int sh_deg, float *v_means, float *v_log_scales,
                       float *v_quats, float *v_opac_logits, float *v_feat_dc, float *v_feat_rest, void *stream);
 
+/* Optimiser step of the owner-sliced mode fused with the parameter exchange: Adam (torch.optim.Adam's rule; the step
+ * gc_trainer.py:276-298 takes after backward with the learning rates of gc_config.py:58-87) over `count` consecutive fp32
+ * elements of one parameter tensor (this rank's rows), each updated value also stored into every peer's copy of the
+ * tensor over NVLink (symmetric memory; peer_base_ptrs_dev NULL or n_peers <= 1: local only). step_size = lr / (1 - b1^t),
+ * inv_sqrt_c2 = 1 / sqrt(1 - b2^t); offset_floats = position of p[0] inside the symmetric buffer. */
+int gs_adam_slice(int64_t count, float *p, const float *g, float *m, float *v, float step_size, float b1, float b2,
+                  float eps, float inv_sqrt_c2, int n_peers, int self, const uint64_t *peer_base_ptrs_dev,
+                  int64_t offset_floats, void *stream);
+
 /* ---- stage 2: tile binning (inside rasterize_gaussians; App. A.3) -------------------------- */
 size_t gs_scan_scratch_bytes(int N);
 /* inclusive int32 scan of tiles_hit -> cum; the total is also written to *total_dev

@@ -58,6 +58,49 @@ for mode in ("peer", "sparse", "push"):
     # the dense kernel is the same code path -> bit-identical; the sparse kernel is a separate translation
     # unit (FMA contraction may differ) -> tolerance
     assert same if mode == "peer" else max(rel.values()) < 2e-6
+# owner-sliced exchange: this rank's slice of the reduced gradients, against the same two yardsticks
+px = gd.PeerViewExchange(m, mode="slice")
+for rep in range(2):
+    m.view_state.view_block = block
+    px.reduce(m)
+    torch.cuda.synchronize()
+lo, hi = m.view_state.shard
+assert (lo, hi) == gd.slice_bounds(m.num_points, rank, world) and all(getattr(m, k).grad is None for k in gd.GRAD_PARAMS)
+sg = m.view_state.sharded_grads
+rel_g = {k: ((sg[k] - res["gather"][k][lo:hi]).abs().max() / res["gather"][k].abs().max().clamp_min(1e-30)).item()
+         for k in gd.GRAD_PARAMS}
+rel_p = {k: ((sg[k] - plain[k][lo:hi]).abs().max() / plain[k].abs().max().clamp_min(1e-30)).item() for k in gd.GRAD_PARAMS}
+print(f"rank {rank}: slice [{lo}, {hi}) vs NCCL all-gather exchange: max rel diff {max(rel_g.values()):.2e}; "
+      f"vs NCCL all-reduce of ordinary leaf gradients: {max(rel_p.values()):.2e}", flush=True)
+assert max(rel_g.values()) < 2e-6 and max(rel_p.values()) < 2e-5
+# one optimiser step: sharded Adam on the slices + parameter all-gather == replicated Adam on the all-reduced gradients
+lr = dict(means=1.6e-4, scales=5e-3, quats=1e-3, features_dc=2.5e-3, features_rest=1.25e-4, opacities=5e-2)
+before = {k: getattr(m, k).detach().clone() for k in gd.GRAD_PARAMS}
+ref_p = {k: torch.nn.Parameter(before[k].clone()) for k in gd.GRAD_PARAMS}
+for k in gd.GRAD_PARAMS:
+    ref_p[k].grad = plain[k].clone()
+torch.optim.Adam([dict(params=[ref_p[k]], lr=lr[k]) for k in gd.GRAD_PARAMS], eps=1e-15).step()
+for peer_mode in (False, True):        # NCCL broadcast of the updated rows / stored into the peers by the Adam kernel
+    with torch.no_grad():
+        for k in gd.GRAD_PARAMS:
+            getattr(m, k).copy_(before[k])
+    dist.barrier()
+    opt = gd.ShardedAdam({k: getattr(m, k) for k in gd.GRAD_PARAMS}, rank, world, lr=lr, eps=1e-15, peer=peer_mode)
+    opt.step(sg)
+    opt.sync()
+    torch.cuda.synchronize()
+    far = max(((getattr(m, k).detach() - ref_p[k].detach()).abs().max() / lr[k]).item() for k in gd.GRAD_PARAMS)
+    print(f"rank {rank}: sharded Adam (peer={peer_mode}) vs replicated Adam: max |delta| / lr {far:.2e}", flush=True)
+# Adam's first step moves every touched weight by ~lr * sign(g): compare the updates, relative to lr
+upd = {k: ((getattr(m, k).detach() - ref_p[k].detach()).abs().max() / lr[k]).item() for k in gd.GRAD_PARAMS}
+# rows whose gradient is ~0 in one arithmetic and exactly 0 in the other flip sign(g): count instead of bounding those
+bad = {k: int((((getattr(m, k).detach() - ref_p[k].detach()).abs() / lr[k]) > 1e-3).sum().item()) for k in gd.GRAD_PARAMS}
+print(f"rank {rank}: sharded Adam step vs replicated Adam: max |delta| / lr {max(upd.values()):.2e}, "
+      f"weights off by > 1e-3 lr: {bad}", flush=True)
+assert sum(bad.values()) <= 1e-4 * sum(before[k].numel() for k in gd.GRAD_PARAMS)
+with torch.no_grad():
+    for k in gd.GRAD_PARAMS:
+        getattr(m, k).copy_(before[k])
 blk = m.view_state.view_block
 Np = (m.num_points + 3) // 4 * 4
 nz = (blk[:2 * Np].view(-1, 2).abs().sum(1)[:m.num_points] != 0) | (blk[8 * Np:9 * Np][:m.num_points] != 0) | \
