@@ -355,7 +355,7 @@ def config5_stress(dev, n_gauss=5_000_000, n_cams=64, batch=8):
     v = (torch.randn(H, W, 3, generator=torch.Generator().manual_seed(1234)) / (H * W)).to(dev)
     m = GaussianModel(scene.make_scene(n_gauss, 0), sh_degree=SH_DEG, background_color=torch.tensor(BG)).to(dev)
     m.eval()
-    m.render_views(cams[:batch], batch=batch)                    # warm-up: capacity hints, allocator
+    m.render_views(cams, batch=batch)                            # warm-up pass over all cameras: capacity hints, allocator
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()

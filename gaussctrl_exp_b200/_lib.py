@@ -81,6 +81,9 @@ SIGNATURES = {
                          _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_view_bwd": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
                          _vp, _vp]),
+    "gs_view_bwd_det_scratch_bytes": (_sz, [_i, _i64]),
+    "gs_view_bwd_det": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _sz, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
+                             _vp, _vp, _sz, _vp]),
 }
 
 

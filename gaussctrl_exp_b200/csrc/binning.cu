@@ -668,3 +668,96 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
     return gs_bin_fast_ex(N, N > 0 ? N : 1, I_cap, xys, 2, depths, radii, tiles_hit, tiles_x, tiles_y, ids_sorted, tile_bins,
                           total_dev, scratch, scratch_bytes, stream);
 }
+
+// ==========================================================================================
+// Deterministic per-Gaussian totals of per-intersection rows (debug switch gs_view_bwd_det): stable radix sort of the
+// list positions k by Gaussian id (ids_sorted[k]), segment bounds from the sorted ids, then ONE thread per Gaussian
+// adds its rows in list order — a fixed order of float additions, so two runs agree bit for bit.
+// ==========================================================================================
+namespace {
+
+__global__ void __launch_bounds__(256)
+segment_bounds_kernel(int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ ids_by_id,
+                      int32_t *__restrict__ seg) {
+    const int64_t I = *total_dev;
+    if (I > I_cap) return;
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= I) return;
+    const uint32_t g = ids_by_id[j];
+    if (j == 0 || ids_by_id[j - 1] != g) seg[2 * g] = (int32_t)j;
+    if (j == I - 1 || ids_by_id[j + 1] != g) seg[2 * g + 1] = (int32_t)(j + 1);
+}
+
+__global__ void __launch_bounds__(256)
+segment_sum_kernel(int n, size_t Np, const int32_t *__restrict__ seg, const uint32_t *__restrict__ pos_by_id,
+                   const float *__restrict__ rows, float *__restrict__ gbuf) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const int lo = seg[2 * g], hi = seg[2 * g + 1];
+    if (hi <= lo) return;                                   // no intersection: the zero-filled block stays
+    float a[9];
+#pragma unroll
+    for (int c = 0; c < 9; ++c) a[c] = 0.f;
+    for (int j = lo; j < hi; ++j) {
+        const float *r = rows + (size_t)pos_by_id[j] * 9;
+#pragma unroll
+        for (int c = 0; c < 9; ++c) a[c] += r[c];
+    }
+    gbuf[2 * (size_t)g] = a[0]; gbuf[2 * (size_t)g + 1] = a[1];
+    float *vc = gbuf + 2 * Np + 3 * (size_t)g, *vr = gbuf + 5 * Np + 3 * (size_t)g;
+    vc[0] = a[2]; vc[1] = a[3]; vc[2] = a[4];
+    gbuf[8 * Np + g] = a[5];
+    vr[0] = a[6]; vr[1] = a[7]; vr[2] = a[8];
+}
+
+struct SegLayout {
+    size_t keyA, valA, keyB, valB, mat, seg, total;
+};
+SegLayout seg_layout(int n, int64_t I_cap) {
+    SegLayout L;
+    size_t at = 0;
+    auto take = [&](size_t bytes) { size_t o = at; at += gs_align_up(bytes, 256); return o; };
+    const size_t i4 = (size_t)(I_cap > 0 ? I_cap : 1) * 4;
+    L.keyA = take(i4); L.valA = take(i4); L.keyB = take(i4); L.valB = take(i4);
+    L.mat = take(gsradix::mat_entries(I_cap, 256) * 4);
+    L.seg = take((size_t)(n > 0 ? n : 1) * 8);
+    L.total = at;
+    return L;
+}
+
+}  // namespace
+
+size_t gs_internal_segment_scratch_bytes(int n, int64_t I_cap) { return seg_layout(n, I_cap).total; }
+
+// rows: (I, 9) per-intersection gradients in ids_sorted order. gbuf: zero-filled compositor-gradient block
+// (v_xy | v_conic | v_rgb | v_opacity, strides of Np). total_dev: device intersection count.
+int gs_internal_segment_reduce(int n, int64_t I_cap, const int32_t *total_dev, const int32_t *ids_sorted, const float *rows,
+                               float *gbuf, void *scratch, size_t scratch_bytes, cudaStream_t st) {
+    const SegLayout L = seg_layout(n, I_cap);
+    if (scratch_bytes < L.total) return GS_ERR_SCRATCH_SMALL;
+    if (I_cap <= 0 || n <= 0) return 0;
+    unsigned char *p = reinterpret_cast<unsigned char *>(scratch);
+    uint32_t *keyA = (uint32_t *)(p + L.keyA), *valA = (uint32_t *)(p + L.valA);
+    uint32_t *keyB = (uint32_t *)(p + L.keyB), *valB = (uint32_t *)(p + L.valB);
+    uint32_t *mat = (uint32_t *)(p + L.mat);
+    int32_t *seg = (int32_t *)(p + L.seg);
+    GS_CUDA(cudaMemsetAsync(seg, 0, (size_t)n * 8, st));
+    const int bits = n > 1 ? gs_ceil_log2(n) : 1;
+    const int npass = (bits + 7) / 8;
+    const uint32_t *kin = reinterpret_cast<const uint32_t *>(ids_sorted), *vin = nullptr;      // value = list position
+    uint32_t *ko = keyA, *vo = valA;
+    for (int q = 0; q < npass; ++q) {
+        const int shift = 8 * q, b = bits - shift < 8 ? bits - shift : 8;
+        const int rc = gsradix::launch_pass<uint32_t, 8>(I_cap, total_dev, kin, vin, ko, vo, shift, b, mat, st);
+        if (rc) return rc;
+        kin = ko; vin = vo;
+        ko = ko == keyA ? keyB : keyA;
+        vo = vo == valA ? valB : valA;
+    }
+    segment_bounds_kernel<<<(int)((I_cap + 255) / 256), 256, 0, st>>>(I_cap, total_dev, kin, seg);
+    GS_LAUNCH_CHECK();
+    const size_t Np = (size_t)(n + 3) / 4 * 4;
+    segment_sum_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, Np, seg, vin, rows, gbuf);
+    GS_LAUNCH_CHECK();
+    return 0;
+}

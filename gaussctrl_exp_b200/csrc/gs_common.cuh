@@ -98,6 +98,10 @@ __device__ __forceinline__ float4 gs_ldg_stream4(const float4 *p) {
 int gs_internal_exclusive_scan(int n, const int32_t *in, int32_t *out, int32_t *total_dev, void *scratch,
                                size_t scratch_bytes, cudaStream_t st);
 // binning.cu: gs_bin_fast over the elements of several views at once, xy read with a stride (packed records)
+// deterministic per-Gaussian sums of per-intersection gradient rows (binning.cu; used by gs_view_bwd_det)
+size_t gs_internal_segment_scratch_bytes(int n, int64_t I_cap);
+int gs_internal_segment_reduce(int n, int64_t I_cap, const int32_t *total_dev, const int32_t *ids_sorted, const float *rows,
+                               float *gbuf, void *scratch, size_t scratch_bytes, cudaStream_t st);
 // bucket form of the binning (tilebucket.cu): same contract as gs_bin_fast_ex below
 size_t gs_bin_bucket_scratch_bytes(int64_t I_cap, int T);
 bool gs_bin_bucket_supported(int T_view, int64_t I_cap);

@@ -53,3 +53,7 @@ int gs_launch_raster_bwd_packed(int H, int W, int tiles_x, int tiles_y, const in
                                 const int32_t *final_idx, const float *v_out, const float *v_out_alpha, float *v_xys,
                                 float *v_conics, float *v_colors, float *v_opac, const int32_t *tile_order,
                                 const float *clamp_ref, cudaStream_t st);
+int gs_launch_raster_bwd_packed_det(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                                    const int32_t *tile_bins, const float *rec, const float *bg, const float *final_T,
+                                    const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
+                                    const int32_t *tile_order, const float *clamp_ref, float *isect, cudaStream_t st);

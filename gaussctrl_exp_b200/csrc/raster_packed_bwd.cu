@@ -59,6 +59,13 @@ __device__ __forceinline__ int warp_max(int x) {
     return x;
 }
 
+// DET (debug switch, gs_view_bwd_det): bit-reproducible gradients. The two places where the order of float additions
+// depends on scheduling are removed: (1) every warp accumulates its moments into its OWN shared-memory rows (plain
+// adds) and the flush sums the eight rows in warp order instead of shared-memory atomics; (2) the flush writes the
+// nine gradients of (tile, Gaussian) to row k of `isect` (k = position in ids_sorted, unique) instead of
+// red.global; a segmented sum in list order (binning.cu: gs_internal_segment_reduce) then forms the per-Gaussian
+// totals. 147 KB of dynamic shared memory (one CTA per SM): a debugging aid, not a fast path.
+template <bool DET>
 __global__ void __launch_bounds__(256)
 raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_sorted,
                          const int2 *__restrict__ tile_bins, const float4 *__restrict__ rec,
@@ -66,11 +73,15 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
                          const int32_t *__restrict__ final_idx, const float *__restrict__ v_out,
                          const float *__restrict__ v_out_alpha, float *__restrict__ v_xys,
                          float *__restrict__ v_conics, float *__restrict__ v_colors, float *__restrict__ v_opac,
-                         const int32_t *__restrict__ tile_order, const float *__restrict__ clamp_ref) {
+                         const int32_t *__restrict__ tile_order, const float *__restrict__ clamp_ref,
+                         float *__restrict__ isect) {
     __shared__ float4 s0[2][RPB];          // x, y, ex, ey
     __shared__ float4 s1[2][RPB];          // opac, qa, qb, qc
     __shared__ float4 s2[2][RPB];          // r, g, b, depth
-    __shared__ float acc[2][RPB * RPB_NV]; // moment sums of the batch, one row of 9 per Gaussian
+    __shared__ float acc_s[DET ? 1 : 2 * RPB * RPB_NV];   // moment sums of the batch, one row of 9 per Gaussian
+    extern __shared__ __align__(16) float acc_d[];        // DET: [2 stages][8 warps][RPB * 9]
+    float *const acc_base = DET ? acc_d : acc_s;
+    constexpr int ACC_STAGE = (DET ? 8 : 1) * RPB * RPB_NV;
     __shared__ int s_wmax[8];
 
     gs_pdl_sync();
@@ -106,7 +117,7 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
 
     const int wmax = warp_max(my_end);
     if (lane == 0) s_wmax[warp] = wmax;
-    for (int i = tid; i < 2 * RPB * RPB_NV; i += 256) (&acc[0][0])[i] = 0.f;
+    for (int i = tid; i < 2 * ACC_STAGE; i += 256) acc_base[i] = 0.f;
     __syncthreads();
     int bmax = range.x;
 #pragma unroll
@@ -129,18 +140,35 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
     // flush of one finished batch: thread t turns the 9 moment sums of ITS Gaussian into gradients
     //   v_xy = (a mx + b my, b mx + c my),  v_conic = (mxx/2, mxy, myy/2)
     // and issues one global reduction per (tile, Gaussian, component); the sums are cleared for re-use
-    auto flush = [&](int id, int stage) {
+    auto flush = [&](int id, int stage, int k) {      // k = position of this Gaussian's entry in ids_sorted
         if (id < 0) return;
         float m[RPB_NV];
-        float *row = &acc[stage][tid * RPB_NV];
+        float *row = acc_base + stage * ACC_STAGE + tid * RPB_NV;
 #pragma unroll
         for (int c = 0; c < RPB_NV; ++c) {
-            m[c] = row[c];
-            row[c] = 0.f;
+            if (DET) {
+                float sum = 0.f;
+#pragma unroll
+                for (int w = 0; w < 8; ++w) {              // fixed order: warp 0 .. 7
+                    sum += row[w * RPB * RPB_NV + c];
+                    row[w * RPB * RPB_NV + c] = 0.f;
+                }
+                m[c] = sum;
+            } else {
+                m[c] = row[c];
+                row[c] = 0.f;
+            }
         }
         const float4 Q = s1[stage][tid];
         float ca, cb, cc;
         gs_unscale_conic(Q.y, Q.z, Q.w, ca, cb, cc);
+        if (DET) {
+            float *o = isect + (size_t)k * RPB_NV;
+            o[0] = ca * m[0] + cb * m[1]; o[1] = cb * m[0] + cc * m[1];
+            o[2] = 0.5f * m[2]; o[3] = m[3]; o[4] = 0.5f * m[4];
+            o[5] = m[5]; o[6] = m[6]; o[7] = m[7]; o[8] = m[8];
+            return;
+        }
         if (m[0] != 0.f || m[1] != 0.f) {
             atomicAdd(v_xys + 2 * (size_t)id, ca * m[0] + cb * m[1]);
             atomicAdd(v_xys + 2 * (size_t)id + 1, cb * m[0] + cc * m[1]);
@@ -168,7 +196,7 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
         const int stage = b & 1;
         gs_cp_async_wait_all();
         __syncthreads();      // stage b published; every warp has finished replaying batch b-1
-        if (b > 0) flush(id_prev, stage ^ 1);
+        if (b > 0) flush(id_prev, stage ^ 1, batch_lo(b - 1) + tid);
         if (b + 1 < nb) issue(id_next, stage ^ 1);     // my own slot of the stage I just flushed from
         id_prev = id_cur;
         id_cur = id_next;
@@ -177,7 +205,7 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
         const int lo = batch_lo(b);
         const int jend = min(batch_cnt(b), wmax - lo);   // warp-uniform: nothing past this warp's last contributor
         const unsigned a0 = gs_smem_addr(s0[stage]), a1 = gs_smem_addr(s1[stage]), a2 = gs_smem_addr(s2[stage]);
-        float *accs = acc[stage];
+        float *accs = acc_base + stage * ACC_STAGE + (DET ? warp * RPB * RPB_NV : 0);
         for (int c32 = (jend - 1) & ~31; jend > 0 && c32 >= 0; c32 -= 32) {
             const int j = c32 + lane;
             bool keep = false;
@@ -219,14 +247,15 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
                 const float r9 = warp_sum(v8);
                 if (acc_lane) {
                     const float add = lane == 1 ? r9 : r8;
-                    if (add != 0.0f) atomicAdd(&accs[jj * RPB_NV + acc_col], add);
+                    if (DET) accs[jj * RPB_NV + acc_col] += add;        // this warp's own row: no other writer
+                    else if (add != 0.0f) atomicAdd(&accs[jj * RPB_NV + acc_col], add);
                 }
             }
         }
     }
     if (nb > 0) {
         __syncthreads();
-        flush(id_prev, (nb - 1) & 1);
+        flush(id_prev, (nb - 1) & 1, batch_lo(nb - 1) + tid);
     }
 }
 
@@ -238,9 +267,25 @@ int gs_launch_raster_bwd_packed(int H, int W, int tiles_x, int tiles_y, const in
                                 float *v_conics, float *v_colors, float *v_opac, const int32_t *tile_order,
                                 const float *clamp_ref, cudaStream_t st) {
     const int tiles = tiles_x * tiles_y;
-    GS_PDL_LAUNCH_IF(tiles <= GS_RASTER_PDL_MAX_TILES, raster_bwd_packed_kernel, tiles, 256, 0, st, H, W, tiles_x,
+    GS_PDL_LAUNCH_IF(tiles <= GS_RASTER_PDL_MAX_TILES, raster_bwd_packed_kernel<false>, tiles, 256, 0, st, H, W, tiles_x,
                      ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float4 *>(rec), bg,
-                     final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref);
+                     final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref,
+                     (float *)nullptr);
+    return 0;
+}
+
+// deterministic variant: per-intersection gradient rows into isect (I x 9 floats, zero-filled by the caller)
+int gs_launch_raster_bwd_packed_det(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
+                                    const int32_t *tile_bins, const float *rec, const float *bg, const float *final_T,
+                                    const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
+                                    const int32_t *tile_order, const float *clamp_ref, float *isect, cudaStream_t st) {
+    const int tiles = tiles_x * tiles_y;
+    const int smem = 2 * 8 * RPB * RPB_NV * (int)sizeof(float);
+    GS_CUDA(cudaFuncSetAttribute(raster_bwd_packed_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    raster_bwd_packed_kernel<true><<<tiles, 256, smem, st>>>(
+        H, W, tiles_x, ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float4 *>(rec), bg, final_T,
+        final_idx, v_out, v_out_alpha, nullptr, nullptr, nullptr, nullptr, tile_order, clamp_ref, isect);
+    GS_LAUNCH_CHECK();
     return 0;
 }
 

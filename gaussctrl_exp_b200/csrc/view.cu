@@ -101,11 +101,13 @@ extern "C" int gs_view_fwd(int n, int views, const float *means, const float *lo
                                        I_cap, st);
 }
 
-extern "C" int gs_view_bwd(int n, const float *means, const float *log_scales, const float *quats,
-                           const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host, const float *bg,
-                           void *ws, size_t ws_bytes, int64_t I_cap, const float *final_T, const int32_t *final_idx,
-                           const float *v_out, const float *v_out_alpha, const float *clamp_ref, float *gbuf,
-                           float *flat_leaf_grads, void *stream) {
+namespace {
+// shared body of gs_view_bwd / gs_view_bwd_det (det_scratch != nullptr: the bit-reproducible backward)
+int view_bwd_impl(int n, const float *means, const float *log_scales, const float *quats, const float *opac_logits,
+                  int use_sh, int sh_deg, const GsCamera *cam_host, const float *bg, void *ws, size_t ws_bytes, int64_t I_cap,
+                  const float *final_T, const int32_t *final_idx, const float *v_out, const float *v_out_alpha,
+                  const float *clamp_ref, float *gbuf, float *flat_leaf_grads, void *det_scratch, size_t det_scratch_bytes,
+                  void *stream) {
     if (n <= 0 || !cam_host || !ws || !bg || !final_T || !final_idx || !v_out || !gbuf) return GS_ERR_BAD_ARG;
     if (!gs_aligned16(ws) || !gs_aligned16(gbuf) || (flat_leaf_grads && !gs_aligned16(flat_leaf_grads)))
         return GS_ERR_MISALIGNED;
@@ -121,6 +123,7 @@ extern "C" int gs_view_bwd(int n, const float *means, const float *log_scales, c
     const int32_t *ids_sorted = reinterpret_cast<const int32_t *>(p + L.ids_sorted);
     const int32_t *bins = reinterpret_cast<const int32_t *>(p + L.tile_bins);
     const int32_t *tile_work = reinterpret_cast<const int32_t *>(p + L.tile_work);
+    const int32_t *total = reinterpret_cast<const int32_t *>(p + L.total);
     int32_t *order_bwd = reinterpret_cast<int32_t *>(p + L.order_bwd);
     const size_t Np = (size_t)(n + 3) / 4 * 4;
     // compositor-level gradient block (the "view block" of the data-parallel exchange): accumulated into by atomics
@@ -128,9 +131,22 @@ extern "C" int gs_view_bwd(int n, const float *means, const float *log_scales, c
     float *v_xys = gbuf, *v_conics = gbuf + 2 * Np, *v_rgbs = gbuf + 5 * Np, *v_opac = gbuf + 8 * Np;
     rc = gs_tile_order(T, tile_work, 0, order_bwd, stream);
     if (rc) return rc;
-    rc = gs_launch_raster_bwd_packed(cam_host->H, cam_host->W, cam_host->tiles_x, cam_host->tiles_y, ids_sorted, bins, rec,
-                                     bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_rgbs, v_opac, order_bwd,
-                                     clamp_ref, st);
+    if (det_scratch) {
+        if (!gs_aligned16(det_scratch)) return GS_ERR_MISALIGNED;
+        const size_t rows_bytes = up256((size_t)(I_cap > 0 ? I_cap : 1) * 9 * sizeof(float));
+        if (det_scratch_bytes < rows_bytes + gs_internal_segment_scratch_bytes(n, I_cap)) return GS_ERR_SCRATCH_SMALL;
+        float *rows = reinterpret_cast<float *>(det_scratch);
+        GS_CUDA(cudaMemsetAsync(rows, 0, rows_bytes, st));
+        rc = gs_launch_raster_bwd_packed_det(cam_host->H, cam_host->W, cam_host->tiles_x, cam_host->tiles_y, ids_sorted, bins, rec,
+                                             bg, final_T, final_idx, v_out, v_out_alpha, order_bwd, clamp_ref, rows, st);
+        if (rc) return rc;
+        rc = gs_internal_segment_reduce(n, I_cap, total, ids_sorted, rows, gbuf, reinterpret_cast<unsigned char *>(det_scratch) + rows_bytes,
+                                        det_scratch_bytes - rows_bytes, st);
+    } else {
+        rc = gs_launch_raster_bwd_packed(cam_host->H, cam_host->W, cam_host->tiles_x, cam_host->tiles_y, ids_sorted, bins, rec,
+                                         bg, final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_rgbs, v_opac, order_bwd,
+                                         clamp_ref, st);
+    }
     if (rc) return rc;
     if (!flat_leaf_grads)   // data-parallel step: stop at the compositor level, finish the view block
         return gs_launch_finish_view_block(n, use_sh, cam_host, rec + 8, GS_REC_FLOATS, gbuf, st);
@@ -139,4 +155,28 @@ extern "C" int gs_view_bwd(int n, const float *means, const float *log_scales, c
     return gs_launch_preprocess_bwd(n, means, log_scales, quats, opac_logits, use_sh, sh_deg, cam_host, radii, rec + 8,
                                     GS_REC_FLOATS, v_xys, v_conics, v_rgbs, v_opac, f, f + 3 * Np, f + 6 * Np, f + 10 * Np,
                                     f + 11 * Np, f + 14 * Np, st);
+}
+}  // namespace
+
+extern "C" int gs_view_bwd(int n, const float *means, const float *log_scales, const float *quats,
+                           const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host, const float *bg,
+                           void *ws, size_t ws_bytes, int64_t I_cap, const float *final_T, const int32_t *final_idx,
+                           const float *v_out, const float *v_out_alpha, const float *clamp_ref, float *gbuf,
+                           float *flat_leaf_grads, void *stream) {
+    return view_bwd_impl(n, means, log_scales, quats, opac_logits, use_sh, sh_deg, cam_host, bg, ws, ws_bytes, I_cap, final_T,
+                         final_idx, v_out, v_out_alpha, clamp_ref, gbuf, flat_leaf_grads, nullptr, 0, stream);
+}
+
+extern "C" size_t gs_view_bwd_det_scratch_bytes(int n, int64_t I_cap) {
+    return up256((size_t)(I_cap > 0 ? I_cap : 1) * 9 * sizeof(float)) + gs_internal_segment_scratch_bytes(n, I_cap);
+}
+
+extern "C" int gs_view_bwd_det(int n, const float *means, const float *log_scales, const float *quats,
+                               const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host, const float *bg,
+                               void *ws, size_t ws_bytes, int64_t I_cap, const float *final_T, const int32_t *final_idx,
+                               const float *v_out, const float *v_out_alpha, const float *clamp_ref, float *gbuf,
+                               float *flat_leaf_grads, void *det_scratch, size_t det_scratch_bytes, void *stream) {
+    if (!det_scratch) return GS_ERR_BAD_ARG;
+    return view_bwd_impl(n, means, log_scales, quats, opac_logits, use_sh, sh_deg, cam_host, bg, ws, ws_bytes, I_cap, final_T,
+                         final_idx, v_out, v_out_alpha, clamp_ref, gbuf, flat_leaf_grads, det_scratch, det_scratch_bytes, stream);
 }

@@ -32,6 +32,8 @@ from . import _lib
 from .scene import Camera
 
 # Fully asynchronous training forward (see module docstring). Off by default: correctness first.
+# debug switch (GS_DETERMINISTIC=1 or render.DETERMINISTIC = True): training views run the bit-reproducible backward
+DETERMINISTIC = _os.environ.get("GS_DETERMINISTIC", "") not in ("", "0")
 SPECULATE = _os.environ.get("GS_SPECULATE") is not None
 
 _cam_cache = {}
@@ -312,6 +314,15 @@ def backward_view(means, scales, quats, opacities, cam: _lib.GsCamera, use_sh: b
     if gbuf is None:
         gbuf = torch.empty(9 * Np + 64, device=dev, dtype=torch.float32)      # zero-filled by the library
     flat = torch.empty(59 * Np, device=dev, dtype=torch.float32) if leaf_grads else None
+    if DETERMINISTIC:       # debug switch: bit-reproducible gradients (gs_view_bwd_det), slower
+        det = torch.empty(L.gs_view_bwd_det_scratch_bytes(n, ws.cap), device=dev, dtype=torch.uint8)
+        rc = L.gs_view_bwd_det(n, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(), int(use_sh),
+                               int(deg), ctypes.addressof(cam), bg.data_ptr(), ws.buf.data_ptr(), ws.buf.numel(), ws.cap,
+                               final_T.data_ptr(), final_idx.data_ptr(), v_out.data_ptr(), _lib.ptr(v_alpha),
+                               _lib.ptr(clamp_ref), gbuf.data_ptr(), _lib.ptr(flat), det.data_ptr(), det.numel(),
+                               _lib.stream_ptr())
+        _lib.check(rc, "gs_view_bwd_det")
+        return gbuf, flat
     rc = L.gs_view_bwd(n, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(), int(use_sh),
                        int(deg), ctypes.addressof(cam), bg.data_ptr(), ws.buf.data_ptr(), ws.buf.numel(), ws.cap,
                        final_T.data_ptr(), final_idx.data_ptr(), v_out.data_ptr(), _lib.ptr(v_alpha),

@@ -351,6 +351,19 @@ int gs_view_bwd(int n, const float *means, const float *log_scales, const float 
                 int64_t I_cap, const float *final_T, const int32_t *final_idx, const float *v_out,
                 const float *v_out_alpha, const float *clamp_ref, float *gbuf, float *flat_leaf_grads, void *stream);
 
+/* Debug switch: the same backward with BIT-REPRODUCIBLE gradients (two runs on the same inputs agree bit for bit; the
+ * default path adds floats with shared-memory atomics and red.global, whose order depends on scheduling). The
+ * compositing kernel keeps per-warp moment rows summed in warp order and writes one 9-float row per (tile, Gaussian)
+ * intersection; a stable sort of the list positions by Gaussian id and a per-Gaussian sum in list order replace the
+ * global reductions. det_scratch: gs_view_bwd_det_scratch_bytes(n, I_cap) bytes, 16-byte aligned. Slower (one CTA per
+ * SM in the compositing, 36 B per intersection of extra traffic): for comparing runs, not for training. */
+size_t gs_view_bwd_det_scratch_bytes(int n, int64_t I_cap);
+int gs_view_bwd_det(int n, const float *means, const float *log_scales, const float *quats, const float *opac_logits,
+                    int use_sh, int sh_deg, const GsCamera *cam_host, const float *bg, void *ws, size_t ws_bytes,
+                    int64_t I_cap, const float *final_T, const int32_t *final_idx, const float *v_out,
+                    const float *v_out_alpha, const float *clamp_ref, float *gbuf, float *flat_leaf_grads,
+                    void *det_scratch, size_t det_scratch_bytes, void *stream);
+
 /* ---- multi-view noise mask ------------------------------------------------------------------
  * Replaces MultiVeiwNoiseRenderer.render_noise_SS (/root/reference/gaussctrl/ad_render.py:273-333) and its GLSL
  * shaders (:384-479): P instances (points (P,3), device) of a triangle mesh (verts (V,3) float, tris (F,3) int32,

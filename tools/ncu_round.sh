@@ -10,7 +10,11 @@ CMD="python tools/prof_step.py 4"
 MODE="${1:-full}"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
 if [ "$MODE" = "list" ]; then
-  ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
+  # the bench command itself (short form), as B200_PROFILING.md asks: its per-launch times are serialised, so it is the
+  # kernels' SHARE of the step that is compared with bench.py's live timing
+  BCMD="python bench.py --steps 4 --warmup 3 --no-cpu --no-extra-configs --no-stages"
+  $BCMD > gpurun_out/bench_plain.json 2> gpurun_out/bench_plain.err &&
+  ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none --csv --log-file gpurun_out/launches.csv $BCMD > gpurun_out/ncu_list.log 2>&1
   tail -3 gpurun_out/ncu_list.log
 elif [ "$MODE" = "source" ]; then
   ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"${NCU_KERNELS:-raster_(fwd|bwd)_packed}" -f -o gpurun_out/prof_src $CMD > gpurun_out/ncu_src.log 2>&1
