@@ -439,7 +439,20 @@ def run_ours(args):
         else:
             gdist.allreduce_grads(params)
 
+    steps_redone = [0]
+
     def step(i):
+        # model.speculate (the timed loops below set it unless --forward strict): the forward reads nothing back, so
+        # the host is never waiting for the binning when the backward has to be enqueued; a view whose tile lists
+        # overflowed their capacity raises at the end of ITS backward, before any gradient is handed out, and the
+        # step is redone — what a training loop on this mode has to do
+        try:
+            _step(i)
+        except grender.CapacityOverflow:
+            steps_redone[0] += 1
+            _step(i)
+
+    def _step(i):
         cam = cams[(i * world + rank) % N_CAMS]
         for p in params:
             p.grad = None
@@ -605,6 +618,12 @@ def run_ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), _lib.launch_count() - l0
 
+    # the same loop with the default, self-healing forward (capacity confirmed inside the forward: one host wait that
+    # ends when the binning is done); diagnostic, shorter
+    model.speculate = False
+    ms_strict, _ = timed_loop(step, max(3, args.warmup // 2), max(10, args.steps // 2))
+    ms_strict /= max(10, args.steps // 2)
+    model.speculate = args.forward == "async"
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -626,9 +645,7 @@ def run_ours(args):
     pct = lambda q: per_step[min(n_dist - 1, int(q * n_dist))]
     step_dist = {"p10_ms": pct(0.10), "median_ms": pct(0.50), "p90_ms": pct(0.90), "steps": n_dist,
                  "what": "per-step device time of this rank, CUDA events around each step"}
-    model.speculate = True
     ms_e2e, _ = timed_loop(step_e2e, max(3, args.warmup // 2), args.steps, drain=drain_losses)
-    model.speculate = False
 
     # config 4 with the optimiser step the trainer runs right after backward (gc_trainer.py:276-298; Adam groups of
     # gc_config.py:58-87): fwd + bwd + gradient exchange + Adam. Owner-sliced exchange: Adam over the rank's slice
@@ -678,6 +695,7 @@ def run_ours(args):
                 if (sliced or world == 1) else "replicated torch.optim.Adam(fused=True)",
                 "what": "fwd + bwd + gradient exchange + Adam step (gc_trainer.py:276-298, lr groups of gc_config.py:58-87)"}
     finetune_opt = finetune_with_optimizer() if model.fused else None
+    model.speculate = False
 
     # config 3: all-view eval render, RGB + depth + alpha, 40 views sharded over the ranks, batched
     def render_all():
@@ -707,10 +725,17 @@ def run_ours(args):
             "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
             "grad_exchange": ((args.reduce + ("/" + args.exchange if args.reduce == "peer" else "")) if world > 1 else None),
             "grad_exchange_check": grad_check,
+            "forward": ("asynchronous (model.speculate=True): nothing read back in the forward, an overflowed view raises "
+                        "in its backward and the step is redone" if args.forward == "async" else
+                        "strict: capacity confirmed inside the forward (host waits for the binning)"),
+            "steps_redone": steps_redone[0],
+            "strict_forward": {"views_per_s": world * 1e3 / ms_strict, "ms_per_step": ms_strict,
+                               "what": "the same loop with model.speculate=False (self-healing forward, the model's default)"},
             "host_ms_per_step": host_enqueue_ms, "step_time_distribution": step_dist,
             "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "views/s",
                     "h2d_bytes_per_step": int(tgt_host.numel() * 4 + 12 * 4 + 6 * 4), "d2h_bytes_per_step": 4 + 4,
-                    "forward": "asynchronous (model.speculate=True), overflowed steps redone", "steps_redone": e2e_retries[0]},
+                    "forward": ("asynchronous (model.speculate=True), overflowed steps redone" if args.forward == "async"
+                                else "strict"), "steps_redone": e2e_retries[0]},
             # BASELINE.json configs, one named key each (configs[0] is the CPU case = cpu_baseline / --impl reference)
             "config3_all_view_render": {
                 "views_per_s": render_vps, "n_gpus": world,
@@ -814,6 +839,9 @@ def main():
     ap.add_argument("--n-gaussians", type=int, default=N_GAUSS)
     ap.add_argument("--cpu-views", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--forward", choices=("async", "strict"), default="async",
+                    help="async (default): model.speculate=True in the timed loops, overflowed steps redone; strict: the "
+                         "model's default self-healing forward")
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--no-extra-configs", action="store_true",
                     help="skip BASELINE.json configs[1] (500 K through the operator API) and configs[4] (5 M / 1080p stress)")

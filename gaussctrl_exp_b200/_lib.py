@@ -60,6 +60,7 @@ SIGNATURES = {
     "gs_bin_fast": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gs_set_depth_sort_passes": (_i, [_i]),
     "gs_set_bin_impl": (_i, [_i]),
+    "gs_set_raster_fwd_unroll": (_i, [_i]),
     "gs_raster_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_raster_fwd_rgbd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_tile_order": (_i, [_i, _vp, _i, _vp, _vp]),

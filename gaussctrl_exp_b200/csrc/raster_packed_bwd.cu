@@ -218,6 +218,7 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
                 const unsigned jj = (unsigned)(c32 + bit);
                 const float4 A = gs_lds128(a0 + jj * 16u);
                 const float4 B = gs_lds128(a1 + jj * 16u);
+                const float4 Cc = gs_lds128(a2 + jj * 16u);      // up front: not a dependent load behind the vote
                 GsSplat sp = {A.x, A.y, B.x, B.y, B.z, B.w};
                 float dx, dy, vis, alpha;
                 bool hit = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
@@ -229,7 +230,6 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
                 const float ra = gs_rcp(1.0f - al);
                 T *= ra;
                 const float fac = al * T;
-                const float4 Cc = gs_lds128(a2 + jj * 16u);
                 const float cvo = Cc.x * vo0 + Cc.y * vo1 + Cc.z * vo2;
                 const float v_alpha = T * cvo - ra * (Svo - tail);
                 Svo += fac * cvo;

@@ -13,13 +13,14 @@
 //     the set bits front to back. Culled pairs are pairs the alpha test would skip, so no output bit changes.
 // Bound: SM issue rate (FP32 + MUFU.EX2) and shared-memory broadcast reads, not HBM.
 #define GS_PDL_GROUP 2
+#include <cstdlib>
 #include "raster_packed.cuh"
 
 namespace {
 
 constexpr int RP_BATCH = 256;
 
-template <bool WITH_DEPTH>
+template <bool WITH_DEPTH, int RP_UNROLL>
 __global__ void __launch_bounds__(256)
 raster_fwd_packed_kernel(int H, int W, int tiles_x, int T_view, const int32_t *__restrict__ ids_sorted,
                          const int2 *__restrict__ tile_bins, const float4 *__restrict__ rec,
@@ -90,25 +91,45 @@ raster_fwd_packed_kernel(int H, int W, int tiles_x, int T_view, const int32_t *_
             bool keep = false;
             if (j < cnt) keep = gs_rect_hit(gs_lds128(a0 + (unsigned)j * 16u), rx0, ry0, rx1, ry1);
             unsigned word = __ballot_sync(0xffffffffu, keep);
+            // survivors RP_UNROLL at a time, all three quads of a survivor loaded up front (the colour quad used to be
+            // loaded inside the branch that needs it: a dependent shared-memory round trip on the critical path; the
+            // loop spent ~47 % of its stall samples on fixed-latency and shared-memory dependencies,
+            // profiles/r02_raster_source_sass.csv). Measured in one process (tools/raster_ab.py): 125 us before,
+            // RP_UNROLL = 1: 116.5 us (40 registers), 2 / 3 / 4: 124 us (48 / 54 / 60 registers: one CTA per SM fewer) ->
+            // default 1. The updates are applied in list order; the saturation vote is taken once per group.
             while (word) {
-                const unsigned jj = (unsigned)c32 + (unsigned)(__ffs(word) - 1);
-                word &= word - 1;
-                const float4 A = gs_lds128(a0 + jj * 16u);
-                const float4 B = gs_lds128(a1 + jj * 16u);
-                GsSplat sp = {A.x, A.y, B.x, B.y, B.z, B.w};
-                float dx, dy, vis, alpha;
-                const bool ok = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
-                if (!done && ok) {
-                    const float Tn = T * (1.0f - alpha);
-                    if (Tn <= GS_T_EPS) {
-                        done = true;
-                    } else {
-                        const float w = alpha * T;
-                        const float4 Cc = gs_lds128(a2 + jj * 16u);
-                        r += w * Cc.x; g += w * Cc.y; b += w * Cc.z;
-                        if (WITH_DEPTH) dacc += w * Cc.w;
-                        T = Tn;
-                        last = kbase + (int)jj + 1;
+                unsigned jj[RP_UNROLL];
+                bool has[RP_UNROLL];
+#pragma unroll
+                for (int u = 0; u < RP_UNROLL; ++u) {
+                    has[u] = word != 0;
+                    jj[u] = has[u] ? (unsigned)c32 + (unsigned)(__ffs(word) - 1) : jj[0];
+                    word &= word - 1;
+                }
+                float alpha[RP_UNROLL];
+                float4 C[RP_UNROLL];
+                bool ok[RP_UNROLL];
+#pragma unroll
+                for (int u = 0; u < RP_UNROLL; ++u) {
+                    const float4 A = gs_lds128(a0 + jj[u] * 16u), B = gs_lds128(a1 + jj[u] * 16u);
+                    C[u] = gs_lds128(a2 + jj[u] * 16u);
+                    GsSplat sp = {A.x, A.y, B.x, B.y, B.z, B.w};
+                    float dx, dy, vis;
+                    ok[u] = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha[u]) && has[u];
+                }
+#pragma unroll
+                for (int u = 0; u < RP_UNROLL; ++u) {
+                    if (!done && ok[u]) {
+                        const float Tn = T * (1.0f - alpha[u]);
+                        if (Tn <= GS_T_EPS) {
+                            done = true;
+                        } else {
+                            const float w = alpha[u] * T;
+                            r += w * C[u].x; g += w * C[u].y; b += w * C[u].z;
+                            if (WITH_DEPTH) dacc += w * C[u].w;
+                            T = Tn;
+                            last = kbase + (int)jj[u] + 1;
+                        }
                     }
                 }
                 if (__all_sync(0xffffffffu, done)) { warp_done = true; break; }
@@ -160,6 +181,22 @@ pack_splats_kernel(int N, const float2 *__restrict__ xys, const float *__restric
 
 }  // namespace
 
+namespace {
+int &raster_fwd_unroll() {
+    static int u = [] {
+        const char *e = getenv("GS_RASTER_FWD_UNROLL");
+        return (e && e[0] >= '1' && e[0] <= '4') ? e[0] - '0' : 1;
+    }();
+    return u;
+}
+}  // namespace
+
+extern "C" int gs_set_raster_fwd_unroll(int u) {
+    const int prev = raster_fwd_unroll();
+    if (u >= 1 && u <= 4) raster_fwd_unroll() = u;
+    return prev;
+}
+
 int gs_launch_raster_fwd_packed(int views, int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
                                 const int32_t *tile_bins, const float *rec, const float *bg, float *out_img,
                                 float *out_depth, float *final_T, int32_t *final_idx, const int32_t *tile_order,
@@ -169,14 +206,21 @@ int gs_launch_raster_fwd_packed(int views, int H, int W, int tiles_x, int tiles_
     const int2 *bins = reinterpret_cast<const int2 *>(tile_bins);
     const float4 *rec4 = reinterpret_cast<const float4 *>(rec);
     const bool pdl = tiles <= GS_RASTER_PDL_MAX_TILES;   // raster_common.cuh: the early launch hurts on many-wave grids
-    if (out_depth)
-        GS_PDL_LAUNCH_IF(pdl, (raster_fwd_packed_kernel<true>), tiles, 256, 0, st, H, W, tiles_x, T_view, ids_sorted, bins,
-                         rec4, bg, out_img, out_depth, final_T, final_idx, tile_order, tile_work, out_clamped, out_alpha,
-                         total_dev, (int)I_cap);
-    else
-        GS_PDL_LAUNCH_IF(pdl, (raster_fwd_packed_kernel<false>), tiles, 256, 0, st, H, W, tiles_x, T_view, ids_sorted, bins,
-                         rec4, bg, out_img, (float *)nullptr, final_T, final_idx, tile_order, tile_work, out_clamped,
-                         out_alpha, total_dev, (int)I_cap);
+    // survivors composited per loop iteration (default 1, see the kernel): gs_set_raster_fwd_unroll / environment
+    // GS_RASTER_FWD_UNROLL=1..4 for A/B
+    const int unroll = raster_fwd_unroll();
+#define GS_RP_LAUNCH(D, U)                                                                                              \
+    GS_PDL_LAUNCH_IF(pdl, (raster_fwd_packed_kernel<D, U>), tiles, 256, 0, st, H, W, tiles_x, T_view, ids_sorted, bins,  \
+                     rec4, bg, out_img, out_depth, final_T, final_idx, tile_order, tile_work, out_clamped, out_alpha,   \
+                     total_dev, (int)I_cap)
+    if (out_depth) {
+        if (unroll == 1) GS_RP_LAUNCH(true, 1); else if (unroll == 2) GS_RP_LAUNCH(true, 2);
+        else if (unroll == 3) GS_RP_LAUNCH(true, 3); else GS_RP_LAUNCH(true, 4);
+    } else {
+        if (unroll == 1) GS_RP_LAUNCH(false, 1); else if (unroll == 2) GS_RP_LAUNCH(false, 2);
+        else if (unroll == 3) GS_RP_LAUNCH(false, 3); else GS_RP_LAUNCH(false, 4);
+    }
+#undef GS_RP_LAUNCH
     return 0;
 }
 

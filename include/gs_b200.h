@@ -311,6 +311,9 @@ int gs_raster_fwd_packed(int views, int H, int W, int tiles_x, int tiles_y, cons
                          const int32_t *tile_bins, const float *rec, const float *bg, float *out_img,
                          float *out_depth, float *final_T, int32_t *final_idx, const int32_t *tile_order,
                          int32_t *tile_work, float *out_clamped, float *out_alpha, void *stream);
+/* Tuning knob of the packed forward compositing kernel: survivors composited per loop iteration (1..4; default 1,
+ * environment GS_RASTER_FWD_UNROLL). Identical output. Returns the previous setting; other values only query. */
+int gs_set_raster_fwd_unroll(int u);
 int gs_raster_bwd_packed(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
                          const int32_t *tile_bins, const float *rec, const float *bg, const float *final_T,
                          const int32_t *final_idx, const float *v_out, const float *v_out_alpha, float *v_xys,

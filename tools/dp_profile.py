@@ -17,7 +17,7 @@ m = GaussianModel(scene.make_scene(1_000_000, 0), background_color=torch.tensor(
 m.train()
 cams = scene.make_cameras(40, 0)
 v = torch.randn(512, 512, 3, generator=torch.Generator().manual_seed(1)).to(dev) / (512 * 512)
-MODE = os.environ.get("GS_EXCHANGE", "push")
+MODE = os.environ.get("GS_EXCHANGE", "slice")
 px = gd.PeerViewExchange(m, mode=MODE)
 STEPS, WARM = 40, 10
 ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(STEPS)]
