@@ -202,13 +202,16 @@ class ViewState:
     """Per-view by-products a caller may want (gc_model.py keeps self.xys / self.radii). The per-Gaussian and tile
     arrays are lazy views into the last view's workspace (no tensor is created unless somebody asks)."""
     __slots__ = ("num_intersects", "xys_grad", "flat_grads", "defer_leaf_grads", "view_block", "view_meta",
-                 "view_block_buffer", "final_idx", "final_T", "workspace", "_empty", "sharded_grads", "shard")
+                 "view_block_buffer", "final_idx", "final_T", "workspace", "_empty", "sharded_grads", "shard", "verified")
 
     def __init__(self):
         self.xys_grad = self.flat_grads = None
         # owner-sliced data-parallel mode (dist.PeerViewExchange mode="slice"): gradients of this rank's Gaussians
         # [shard[0], shard[1]) summed over all ranks' views, slice-shaped
         self.sharded_grads = self.shard = None
+        # False between a speculative forward (nothing read back) and the check at the end of its backward: until
+        # then the image and everything derived from it are UNVERIFIED (an overflow NaN-poisons them)
+        self.verified = True
         # integer by-products of the last view (what gsplat's rasterize keeps for its backward); the parity
         # tests compare them bit for bit with the oracle
         self.final_idx = self.final_T = self.workspace = self._empty = None
@@ -367,6 +370,7 @@ class _RenderView(Function):
         depths, radii, hit = ws.depths, ws.radii, ws.num_tiles_hit
         if state is not None:
             state.num_intersects, state.final_idx, state.final_T, state.workspace = I, im.final_idx, im.final_T, ws
+            state.verified = pend is None
         ctx.mark_non_differentiable(depths, radii, hit)
         ctx.set_materialize_grads(False)      # unused outputs arrive as None instead of freshly filled zeros
         return (im.out_clamped if clamp_rgb else im.out), im.alpha, depths, radii, hit
@@ -397,6 +401,7 @@ class _RenderView(Function):
             ctx.pending = None
             if ctx.state is not None:
                 ctx.state.num_intersects = I
+                ctx.state.verified = True
         if ctx.state is not None:
             ctx.state.xys_grad = v_xys            # what gc_model.py:193-194 keeps via xys.retain_grad()
         if defer:

@@ -157,6 +157,7 @@ def test_capacity_overflow_heals_or_is_flagged(cuda_dev, monkeypatch):
     rgb, alpha, *_ = render.render_view(*leaves, cam, 3, True, torch.tensor([0.1, 0.2, 0.3], device=dev), m.view_state,
                                         speculate=True)
     assert torch.isnan(rgb).all()                  # poisoned, not a plausible background image
+    assert m.view_state.verified is False          # flagged as unverified until the check at the end of backward
     with pytest.raises(render.CapacityOverflow):
         rgb.sum().backward()
     assert render._cap_hint[key] >= I_true
@@ -164,7 +165,9 @@ def test_capacity_overflow_heals_or_is_flagged(cuda_dev, monkeypatch):
         q.grad = None
     rgb, alpha, *_ = render.render_view(*leaves, cam, 3, True, torch.tensor([0.1, 0.2, 0.3], device=dev), m.view_state,
                                         speculate=True)   # retry succeeds and matches
+    assert m.view_state.verified is False
     rgb.sum().backward()
+    assert m.view_state.verified is True
     assert torch.equal(torch.clamp(rgb.detach(), max=1.0), ref) and m.means.grad.abs().max() > 0
     assert m.view_state.num_intersects == I_true
 

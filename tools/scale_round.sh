@@ -1,3 +1,6 @@
+#!/bin/bash
+# Scaling on one box: tools/scale_round.sh N  (N = 2, 4 or 8 GPUs): the multi-GPU pytest, bench.py at 1, 2, .. N ranks,
+# the step anatomy at N ranks (tools/dp_profile.py). Outputs under gpurun_out/.
 mkdir -p gpurun_out
 N=${1:-4}
 timeout 600 python -m pytest tests/test_multi_gpu.py -m gpu -q -x --timeout=500 > gpurun_out/pytest_mgpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_mgpu.log
@@ -11,6 +14,8 @@ for n in 1 2 4 8; do
   fi
   echo "bench $n rc=$?"
 done
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29520 tools/dp_profile.py > gpurun_out/dp_profile_${N}gpu.log 2>&1
+grep "rank 0" gpurun_out/dp_profile_${N}gpu.log | head -2
 python - <<'PY'
 import json
 base = None
