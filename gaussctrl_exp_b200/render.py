@@ -40,6 +40,8 @@ _cam_cache = {}
 _cap_hint = {}
 _scratch = {}
 _pinned_free = {}
+_layout_cache = {}
+_scratch_bytes_cache = {}
 
 
 def gs_camera(camera: Camera, glob_scale: float = 1.0, clip: float = 0.01) -> _lib.GsCamera:
@@ -108,7 +110,7 @@ class _Pending:
     def wait(self) -> int:
         """Blocks until the count has landed; returns it and recycles the slot."""
         self.event.synchronize()
-        I = int(self.pinned[0])
+        I = ctypes.c_int32.from_address(self.pinned.data_ptr()).value
         _pinned_free[self.dev.index].append((self.pinned, self.event))
         self.pinned = self.event = None
         return I
@@ -137,9 +139,13 @@ class ViewWorkspace:
     self.radii): one uint8 tensor + typed views of it, following gs_view_layout."""
 
     def __init__(self, dev, n: int, views: int, cap: int, T_view: int):
-        L = _lib.lib()
-        lay = _lib.GsViewLayout()
-        _lib.check(L.gs_view_layout(n, views, cap, T_view, ctypes.byref(lay)), "gs_view_layout")
+        lay = _layout_cache.get((n, views, cap, T_view))
+        if lay is None:
+            lay = _lib.GsViewLayout()
+            _lib.check(_lib.lib().gs_view_layout(n, views, cap, T_view, ctypes.byref(lay)), "gs_view_layout")
+            if len(_layout_cache) > 256:
+                _layout_cache.clear()
+            _layout_cache[(n, views, cap, T_view)] = lay
         self.n, self.views, self.cap, self.T_view, self.lay = n, views, cap, T_view, lay
         self.buf = torch.empty(lay.bytes, device=dev, dtype=torch.uint8)
 
@@ -276,7 +282,10 @@ def forward_views(means, scales, quats, opacities, features_dc, features_rest, c
     while True:
         ws = ViewWorkspace(dev, n, views, cap, T_view)
         im = ViewImages(dev, views, H, W, with_depth)
-        scratch = _get_scratch(dev, L.gs_view_scratch_bytes(n, views, cap, T_view))
+        sb = _scratch_bytes_cache.get((n, views, cap, T_view))
+        if sb is None:
+            sb = _scratch_bytes_cache[(n, views, cap, T_view)] = L.gs_view_scratch_bytes(n, views, cap, T_view)
+        scratch = _get_scratch(dev, sb)
         pend = _Pending(dev)
         pend.cap, pend.key = cap, key
         rc = L.gs_view_fwd(n, views, means.data_ptr(), scales.data_ptr(), quats.data_ptr(), opacities.data_ptr(),
@@ -353,7 +362,8 @@ class _RenderView(Function):
             raise ValueError("render_view needs CUDA tensors (no CPU fallback)")
         if features_rest.shape[1:] != (15, 3):
             raise ValueError("features_rest must have dimensions (N, 15, 3)")
-        args = [t.detach().float().contiguous() for t in (means, scales, quats, opacities, features_dc, features_rest)]
+        args = [t.detach() if (t.dtype is torch.float32 and t.is_contiguous()) else t.detach().float().contiguous()
+                for t in (means, scales, quats, opacities, features_dc, features_rest)]
         bg = bg.detach().to(means.device).float().contiguous()
         with torch.cuda.device(means.device):
             ws, im, I, pend = forward_views(*args, [cam], use_sh, deg, bg, speculate=speculate)
