@@ -807,7 +807,7 @@ def run_ours(args):
                 ent = {"us": us}
                 if pk2:
                     ent.update({"smsp__inst_executed.sum": pk2.get("inst_executed"),
-                                "smsp__issue_active.avg.pct": pk2.get("issue_active_pct"),
+                                "sm__issue_active.avg.pct_of_peak_sustained_elapsed": pk2.get("issue_active_pct"),
                                 "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum": pk2.get("smem_wavefronts"),
                                 "achieved_warp_inst_per_s": (pk2.get("inst_executed") or 0) / (us * 1e-6),
                                 "frac": (pk2.get("inst_executed") or 0) / (us * 1e-6) / slots})

@@ -22,7 +22,12 @@ WANT = {
     "launch__occupancy_limit_shared_mem": "occ_limit_smem",
     "sm__warps_active.avg.pct_of_peak_sustained_active": "achieved_occupancy_pct",
     "smsp__inst_executed.sum": "inst_executed",
-    "smsp__issue_active.avg.pct": "issue_active_pct",
+    "sm__issue_active.avg.pct_of_peak_sustained_elapsed": "issue_active_pct",
+    "sm__inst_issued.avg.pct_of_peak_sustained_active": "inst_issued_pct_of_active",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active": "pipe_lsu_pct",
+    "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active": "pipe_xu_pct",
+    "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active": "pipe_fma_pct",
+    "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active": "pipe_alu_pct",
     "sm__throughput.avg.pct_of_peak_sustained_elapsed": "sm_throughput_pct",
     "gpu__compute_memory_throughput.avg.pct_of_peak_sustained_elapsed": "mem_throughput_pct",
     "dram__throughput.avg.pct_of_peak_sustained_elapsed": "dram_throughput_pct",
