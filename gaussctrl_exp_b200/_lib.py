@@ -16,7 +16,7 @@ CSRC = os.path.join(_HERE, "csrc")
 
 _lib = None
 
-_vp, _i, _f, _i64, _sz = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t
+_vp, _i, _f, _i64, _sz, _d = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_size_t, C.c_double
 
 # name -> (restype, argtypes); mirrors include/gs_b200.h line by line
 SIGNATURES = {
@@ -68,6 +68,9 @@ SIGNATURES = {
     "gs_raster_bwd_ordered": (_i, [_i, _i, _i, _i] + [_vp] * 17),
     "gs_raster_fwd_ordered_post": (_i, [_i, _i, _i, _i] + [_vp] * 17),
     "gs_raster_bwd_ordered_post": (_i, [_i, _i, _i, _i] + [_vp] * 18),
+    "gs_ray_directions": (_i, [_i, _i, _d, _d, _vp, _vp]),
+    "gs_depth_to_world": (_i, [_i, _i, _vp, _vp, _d, _d, _vp, _vp]),
+    "gs_depth_to_disparity": (_i, [_i64, _vp, _vp, _vp, _vp]),
     "gs_noise_mask_scratch_bytes": (_sz, [_i, _i]),
     "gs_noise_mask": (_i, [_i, _vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _f, _vp, _sz, _vp, _vp]),
     "gs_raster_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,

@@ -145,6 +145,22 @@ class ShardedAdam:
             self.hdl = symm_mem.rendezvous(self.buf, dist.group.WORLD)
 
     @torch.no_grad()
+    def load_reference_state(self, opt_state: Dict[str, dict]) -> None:
+        """Resume from the per-group Adam states of a reference checkpoint (postops.load_splatfacto_checkpoint(...,
+        with_optimizers=True); gc_trainer.py:158-168 saves them, :74 restores them): this rank keeps its slice of the
+        moments, and the step count, learning rates, betas and eps of the file replace the constructor's."""
+        steps = {int(s["step"]) for s in opt_state.values()}
+        if len(steps) > 1:
+            raise ValueError(f"parameter groups at different Adam steps: {sorted(steps)}")
+        for k, s in opt_state.items():
+            self.m[k].copy_(s["exp_avg"][self.lo:self.hi].to(self.m[k].device))
+            self.v[k].copy_(s["exp_avg_sq"][self.lo:self.hi].to(self.v[k].device))
+            self.lr[k] = float(s["lr"])
+            self.betas, self.eps = tuple(s["betas"]), float(s["eps"])
+        if steps:
+            self.t = steps.pop()
+
+    @torch.no_grad()
     def step(self, sharded_grads: Dict[str, torch.Tensor]) -> None:
         self.t += 1
         b1, b2 = self.betas

@@ -367,6 +367,23 @@ int gs_view_bwd_det(int n, const float *means, const float *log_scales, const fl
                     const float *v_out_alpha, const float *clamp_ref, float *gbuf, float *flat_leaf_grads,
                     void *det_scratch, size_t det_scratch_bytes, void *stream);
 
+/* ---- depth post-ops between the render and the depth ControlNet ------------------------------
+ * gs_ray_directions replaces compute_ray_directions (/root/reference/gaussctrl/gc_pipeline.py:503-536, a Python double
+ * loop): out (res1, res0, 3) float device, unit ray through each pixel of a res0-wide, res1-high viewport at z = -near
+ * (the reference unpacks `width, height = resolution`; res0/res1 keep that order). Bit-identical to the numpy result.
+ * gs_depth_to_world replaces depth_map_screen_to_world (gc_pipeline.py:286-314): depth (h,w) device, mat_view = the
+ * un-flipped world->camera matrix the model returns as outputs['mat_view'] (HOST pointer, 16 floats, row-major;
+ * inverted here in double); pts_world (h,w,3) device = inverse(mat_view) * [ray * depth, 1] / w. As in the reference
+ * the rays are built for resolution=(h, w), so only square views are defined: h != w returns GS_ERR_BAD_ARG (the
+ * reference raises a broadcast error there).
+ * gs_depth_to_disparity replaces depth2disparity / depth2disparity_torch (gc_pipeline.py:439-457): depth (n) device ->
+ * disparity3 (3, n) device, three identical channels of (1 / (depth + 1e-5)) / max(1 / (depth + 1e-5));
+ * bit-identical to torch. scratch4: 4 bytes of device memory, 4-byte aligned. */
+int gs_ray_directions(int res0, int res1, double fov_y_rad, double near, float *out, void *stream);
+int gs_depth_to_world(int h, int w, const float *depth, const float *mat_view_host, double fov_y_rad, double near,
+                      float *pts_world, void *stream);
+int gs_depth_to_disparity(int64_t n, const float *depth, float *disparity3, void *scratch4, void *stream);
+
 /* ---- multi-view noise mask ------------------------------------------------------------------
  * Replaces MultiVeiwNoiseRenderer.render_noise_SS (/root/reference/gaussctrl/ad_render.py:273-333) and its GLSL
  * shaders (:384-479): P instances (points (P,3), device) of a triangle mesh (verts (V,3) float, tris (F,3) int32,

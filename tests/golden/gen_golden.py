@@ -163,6 +163,71 @@ def reference_caller_golden():
     np.savez_compressed(os.path.join(HERE, "reference_caller.npz"), **out)
 
 
+def reference_checkpoint_golden():
+    """6. reference_step-000029999.ckpt — written by the reference's OWN `GaussCtrlTrainer.save_checkpoint`
+    (/root/reference/gaussctrl/gc_trainer.py:146-174), extracted by AST and executed unmodified. What it reads from
+    nerfstudio is stubbed: `self.pipeline` is a torch Module whose `_model` carries the six splatfacto parameters under
+    the names gc_model.py:157-170 reads (plus an `ip2p.` sub-module, which the reference filters out), `self.optimizers.
+    optimizers` holds one real torch.optim.Adam per parameter group with the names, learning rates and eps of
+    gc_config.py:58-87, stepped twice so that the moments are non-trivial, `self.grad_scaler` is torch's GradScaler.
+    The file pins the checkpoint layout the loader (postops.load_splatfacto_checkpoint) has to read."""
+    import pathlib
+    import shutil
+    import tempfile
+    import torch
+    from gaussctrl_exp_b200 import scene
+
+    path = os.path.join(REF, "gc_trainer.py")
+    tree = ast.parse(open(path).read())
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "GaussCtrlTrainer")
+    node = next(n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name == "save_checkpoint")
+    env = {"torch": torch, "check_main_thread": lambda f: f}
+    exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), env)
+
+    N = 96
+    p = scene.make_scene(N, 77, s0=0.05)
+
+    class Model(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            for k, v in p.items():
+                setattr(self, k, torch.nn.Parameter(v.clone()))
+
+    class Pipeline(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self._model = Model()
+            self.ip2p = torch.nn.Linear(2, 2)            # stands for the diffusion pipeline the reference drops
+
+    pipe = Pipeline()
+    groups = {"xyz": ("means", 1.6e-4), "features_dc": ("features_dc", 0.0025), "features_rest": ("features_rest", 0.0025 / 20),
+              "opacity": ("opacities", 0.05), "scaling": ("scales", 0.005), "rotation": ("quats", 0.001)}
+    opts = {g: torch.optim.Adam([getattr(pipe._model, name)], lr=lr, eps=1e-15) for g, (name, lr) in groups.items()}
+    gen = torch.Generator().manual_seed(5)
+    for _ in range(2):
+        for g, (name, _) in groups.items():
+            prm = getattr(pipe._model, name)
+            prm.grad = torch.randn(prm.shape, generator=gen) * 1e-3
+            opts[g].step()
+
+    class Obj:
+        pass
+    tr = Obj()
+    tmp = pathlib.Path(tempfile.mkdtemp())
+    tr.checkpoint_dir = tmp / "nerfstudio_models"
+    tr.pipeline = pipe
+    tr.optimizers = Obj()
+    tr.optimizers.optimizers = opts
+    tr.grad_scaler = torch.amp.GradScaler("cpu", enabled=False)
+    tr.config = Obj()
+    tr.config.save_only_latest_checkpoint = True
+    env["save_checkpoint"](tr, 29999)
+    src = tr.checkpoint_dir / "step-000029999.ckpt"
+    assert src.exists()
+    shutil.copy(src, os.path.join(HERE, "reference_step-000029999.ckpt"))
+    shutil.rmtree(tmp)
+
+
 def main():
     import torch
     from typing import Union
@@ -226,6 +291,7 @@ def main():
              cube=cube, c2ws=np.stack(c2ws), views=np.stack(views))
 
     reference_caller_golden()
+    reference_checkpoint_golden()
 
     from oracle import oracle as orc
     from util import np_params, small_cam

@@ -233,9 +233,9 @@ def test_postops_match_reference_goldens(tmp_path):
     g = np.load(os.path.join(GOLD, "reference_postops.npz"))
     h, w, _ = g["depth"].shape
     rays = postops.compute_ray_directions((h, w)).numpy()
-    assert rays.shape == g["rays"].shape and np.abs(rays - g["rays"]).max() < 1e-6
+    assert rays.shape == g["rays"].shape and np.array_equal(rays, g["rays"])
     rr = postops.compute_ray_directions((20, 12)).numpy()
-    assert rr.shape == g["rays_rect"].shape and np.abs(rr - g["rays_rect"]).max() < 1e-6
+    assert rr.shape == g["rays_rect"].shape and np.array_equal(rr, g["rays_rect"])
     pts = postops.depth_map_screen_to_world(torch.from_numpy(g["depth"]), torch.from_numpy(g["mat_view"])).numpy()
     assert np.abs(pts - g["pts_world"]).max() < 1e-5
     disp = postops.depth2disparity(torch.from_numpy(g["depth"][:, :, 0][None])).numpy()
@@ -249,3 +249,43 @@ def test_postops_match_reference_goldens(tmp_path):
     assert step == 29999 and all(torch.equal(p[k], q[k]) for k in p)
     raw = torch.load(f, weights_only=False)
     assert set(raw) == {"step", "pipeline", "optimizers", "scalers"} and "_model.features_rest" in raw["pipeline"]
+
+
+def test_reference_written_checkpoint_loads_and_resumes():
+    """tests/golden/reference_step-000029999.ckpt was written by the reference's OWN save_checkpoint
+    (gc_trainer.py:146-174, executed unmodified by tests/golden/gen_golden.py on stub nerfstudio objects): layout,
+    filtered `ip2p.` keys, parameter names and the per-group Adam states. The loader reads it, and a ShardedAdam resumed
+    from it takes the same next step as torch.optim.Adam resumed with load_state_dict from the same file."""
+    from gaussctrl_exp_b200 import dist as gdist
+    from gaussctrl_exp_b200 import postops, scene
+    f = os.path.join(GOLD, "reference_step-000029999.ckpt")
+    raw = torch.load(f, weights_only=False)
+    assert set(raw) == {"step", "pipeline", "optimizers", "scalers"} and raw["step"] == 29999
+    assert not any("ip2p." in k for k in raw["pipeline"])
+    assert set(raw["optimizers"]) == set(postops.OPTIMIZER_GROUPS)
+    params, step, opt = postops.load_splatfacto_checkpoint(f, with_optimizers=True)
+    assert step == 29999 and set(params) == set(postops.PARAM_KEYS) and set(opt) == set(postops.PARAM_KEYS)
+    n = params["means"].shape[0]
+    assert n == 96 and params["features_rest"].shape == (n, 15, 3) and params["opacities"].shape == (n, 1)
+    start = scene.make_scene(n, 77, s0=0.05)          # what the generator started from, two Adam steps earlier
+    assert all(params[k].shape == start[k].shape and not torch.equal(params[k], start[k]) for k in params)
+    assert opt["means"]["lr"] == 1.6e-4 and opt["opacities"]["lr"] == 0.05 and opt["scales"]["eps"] == 1e-15
+    assert all(o["step"] == 2 for o in opt.values())
+
+    g = torch.Generator().manual_seed(3)
+    grads = {k: torch.randn(v.shape, generator=g) * 1e-3 for k, v in params.items()}
+    ours = {k: v.clone() for k, v in params.items()}
+    adam = gdist.ShardedAdam(ours, rank=0, world=1)
+    adam.load_reference_state(opt)
+    assert adam.t == 2
+    adam.step(grads)
+    for group, name in postops.OPTIMIZER_GROUPS.items():
+        prm = torch.nn.Parameter(params[name].clone())
+        ref = torch.optim.Adam([prm], lr=1.0)                              # every hyper-parameter comes from the file
+        osd = raw["optimizers"][group]
+        ref.load_state_dict(osd)
+        prm.grad = grads[name].reshape(prm.shape)
+        ref.step()
+        assert ref.param_groups[0]["lr"] == opt[name]["lr"]
+        err = (ours[name] - prm.data).abs().max().item()
+        assert err <= 1e-7 + 1e-6 * prm.data.abs().max().item(), (name, err)
