@@ -87,6 +87,26 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def nvlink_kib(dev):
+    """(tx KiB, rx KiB) moved over ALL NVLinks of `dev` since driver load: NVML field values
+    NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX / _RX (138 / 139, scope = all links). None where NVML cannot say."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(dev)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(f"{pr.pci_domain_id:08x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0".encode())
+        vals = pynvml.nvmlDeviceGetFieldValues(h, [(138, 0xFFFFFFFF), (139, 0xFFFFFFFF)])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                return None
+            out.append(int(v.value.ullVal))
+        return tuple(out)
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------
 class CpuReference:
     """The oracle (CPU restatement of the path, kind 'port') on the same workload, all host threads."""
@@ -637,7 +657,15 @@ def run_ours(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    nv0 = nvlink_kib(dev) if world > 1 else None
     ms_total, launches = timed_loop(step, args.warmup, args.steps)
+    nv1 = nvlink_kib(dev) if world > 1 else None
+    nvlink = None
+    if nv0 and nv1:        # rank 0's GPU; includes the warm-up steps of the same loop
+        n_st = args.steps + args.warmup
+        nvlink = {"tx_bytes_per_step": 1024.0 * (nv1[0] - nv0[0]) / n_st, "rx_bytes_per_step": 1024.0 * (nv1[1] - nv0[1]) / n_st,
+                  "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX (all links of rank 0's GPU, KiB) around warm-up + timed "
+                            "steps; includes the barrier's flag traffic and NCCL's timing all-reduce"}
     host_enqueue_ms = host_ms[0]
     clocks = sampler.stop() if rank == 0 else None
 
@@ -735,6 +763,7 @@ def run_ours(args):
             "clocks": clocks, "gpu_launches": int(launches), "path": args.path,
             "grad_exchange": ((args.reduce + ("/" + args.exchange if args.reduce == "peer" else "")) if world > 1 else None),
             "grad_exchange_check": grad_check,
+            "nvlink": nvlink,
             "forward": ("asynchronous (model.speculate=True): nothing read back in the forward, an overflowed view raises "
                         "in its backward and the step is redone" if args.forward == "async" else
                         "strict: capacity confirmed inside the forward (host waits for the binning)"),

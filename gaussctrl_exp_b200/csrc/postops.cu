@@ -20,8 +20,8 @@ __device__ __forceinline__ float3 ray_direction(int x, int y, int width, int hei
                                                 double near) {
     const double ndc_x = ((double)x + 0.5) / (double)width;
     const double ndc_y = ((double)y + 0.5) / (double)height;
-    const float rx = (float)(ndc_x * vp_w - vp_w / 2.0);
-    const float ry = (float)(ndc_y * vp_h - vp_h / 2.0);
+    const float rx = (float)__dsub_rn(__dmul_rn(ndc_x, vp_w), vp_w / 2.0);      // no DFMA contraction: numpy has none
+    const float ry = (float)__dsub_rn(__dmul_rn(ndc_y, vp_h), vp_h / 2.0);
     const float rz = (float)(-near);
     const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz));
     const float n = __fsqrt_rn(n2);
