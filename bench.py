@@ -661,11 +661,23 @@ def run_ours(args):
     ms_total, launches = timed_loop(step, args.warmup, args.steps)
     nv1 = nvlink_kib(dev) if world > 1 else None
     nvlink = None
+    if world > 1 and peer is not None and getattr(peer, "mode", "") == "slice":
+        # what the last timed step actually stored into the peers (counted from the pushed block). The hardware
+        # counters are read as well, but this pool does not expose them (NVML NOT_SUPPORTED, `nvidia-smi nvlink -gt d`:
+        # N/A; profiles/r02_nvlink_counters_unavailable.txt)
+        sent, nnz = peer.pushed_bytes_last_step(model.num_points)
+        nvlink = {"pushed_bytes_per_step_rank0": sent, "nonzero_gaussians_in_block": nnz,
+                  "dense_allreduce_bytes_per_rank": 2 * (world - 1) / world * 59 * 4 * model.num_points,
+                  "hw_counters": None,
+                  "source": "counted from the compacted view block the last timed step pushed (run arithmetic of "
+                            "vx_push_slices_kernel); dense figure = ring all-reduce of the 59-float leaf gradients"}
     if nv0 and nv1:        # rank 0's GPU; includes the warm-up steps of the same loop
         n_st = args.steps + args.warmup
-        nvlink = {"tx_bytes_per_step": 1024.0 * (nv1[0] - nv0[0]) / n_st, "rx_bytes_per_step": 1024.0 * (nv1[1] - nv0[1]) / n_st,
-                  "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX (all links of rank 0's GPU, KiB) around warm-up + timed "
-                            "steps; includes the barrier's flag traffic and NCCL's timing all-reduce"}
+        nvlink = dict(nvlink or {})
+        nvlink["hw_counters"] = {"tx_bytes_per_step": 1024.0 * (nv1[0] - nv0[0]) / n_st,
+                                 "rx_bytes_per_step": 1024.0 * (nv1[1] - nv0[1]) / n_st,
+                                 "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX (all links of rank 0's GPU, KiB) around "
+                                           "warm-up + timed steps; includes barrier flags and NCCL's timing all-reduce"}
     host_enqueue_ms = host_ms[0]
     clocks = sampler.stop() if rank == 0 else None
 

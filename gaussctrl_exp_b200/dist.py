@@ -293,6 +293,39 @@ class PeerViewExchange:
         self.step = 0
         self.begin(model)
 
+    def pushed_bytes_last_step(self, n_points: int):
+        """Bytes this rank stored into its peers' memory in the last `reduce` (mode "slice"), counted from the compacted
+        block it pushed: the same float4 run arithmetic as vx_push_slices_kernel (meta words of the peer's slice, the
+        camera slot, the run [k_lo, k_hi) of each packed array). A diagnostic (one device->host read of the meta words);
+        it stands in for NVLink hardware counters where those are not exposed. Returns (total bytes, non-zero Gaussians)."""
+        assert self.mode == "slice" and self.step > 0
+        from . import _lib
+        k = (self.step - 1) % 2
+        off = (k * self.world + self.rank) * self.stride
+        Wp = ((((n_points + 31) // 32) + 3) // 4) * 4
+        meta = self.buf[off:off + 2 * Wp].view(torch.int32).reshape(Wp, 2).cpu().numpy()
+        bitmap, prefix = meta[:, 0].view("uint32"), meta[:, 1]
+        import numpy as np
+        nnz = int(prefix[-1]) + bin(int(bitmap[-1])).count("1")
+        S = _lib.lib().gs_view_slice_size(n_points, self.world)
+        sw = S // 32
+        total = 0
+        for d in range(self.world):
+            if d == self.rank:
+                continue
+            wlo = min(d * sw, Wp)
+            whi = min(wlo + sw, Wp)
+            if wlo >= whi:
+                continue
+            k_lo = int(prefix[wlo])
+            k_hi = int(prefix[whi]) if whi < Wp else nnz
+            quads = ((whi + 1) // 2 - wlo // 2) + 16
+            quads += (2 * k_hi + 3) // 4 - (2 * k_lo) // 4
+            quads += 2 * ((3 * k_hi + 3) // 4 - (3 * k_lo) // 4)
+            quads += (k_hi + 3) // 4 - k_lo // 4
+            total += 16 * quads
+        return total, nnz
+
     def begin(self, model) -> None:
         """Point the next backward at this step's buffer (dense mode) / at a private dense block (sparse modes)."""
         k = self.step % 2

@@ -130,6 +130,67 @@ def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
     assert I2 == b.I and np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted)
 
 
+@pytest.mark.parametrize("case", ["same_depth", "wide_range", "narrow_range", "tiny", "one_visible", "all_culled",
+                                  "two_values", "peaky_1m"])
+def test_depth_sort_corner_cases(oracle, cuda_dev, case):
+    """Depth distributions that stress a depth sort's digit handling: every key equal, keys spread over 2^30 bit
+    patterns, keys that differ only in their lowest bits, fewer keys than one chunk, one / no visible Gaussian, two
+    distinct values, half of a 1 M scene on one surface. Oracle for the small ones; at 1 M the three product pipelines
+    against each other."""
+    from gaussctrl_exp_b200 import utils as U
+    rng = np.random.default_rng(17)
+    N, W, H = 30000, 64, 48
+    tb = (4, 3, 1)
+    if case == "tiny":
+        N = 37
+    elif case == "peaky_1m":
+        N = 1_000_000
+    xys = (rng.random((N, 2)) * [W, H]).astype(np.float32)
+    radii = rng.integers(1, 12, N).astype(np.int32)
+    radii[rng.random(N) < 0.1] = 0
+    depths = (rng.random(N) * 3 + 0.2).astype(np.float32)
+    if case == "same_depth":
+        depths[:] = np.float32(1.5)
+    elif case == "wide_range":
+        depths = np.exp(rng.uniform(np.log(0.011), np.log(1e30), N)).astype(np.float32)
+    elif case == "narrow_range":
+        depths = np.float32(2.0) + (rng.integers(0, 300, N) * np.float32(2.0 ** -22)).astype(np.float32)
+    elif case == "one_visible":
+        radii[:] = 0
+        radii[N // 2] = 3
+    elif case == "all_culled":
+        radii[:] = 0
+    elif case == "two_values":
+        depths = np.where(rng.random(N) < 0.5, np.float32(0.7), np.float32(4.0e10)).astype(np.float32)
+    elif case == "peaky_1m":
+        depths[: N // 2] = (1.0 + 1e-4 * rng.standard_normal(N // 2)).astype(np.float32)     # half the scene on one surface
+    # tile counts as the projection would give them
+    f16, one = np.float32(16), np.float32(1)
+    tr = radii.astype(np.float32) / f16
+    tcx, tcy = xys[:, 0] / f16, xys[:, 1] / f16
+    x0 = np.clip((tcx - tr).astype(np.int32), 0, tb[0])
+    x1 = np.clip((tcx + tr + one).astype(np.int32), 0, tb[0])
+    y0 = np.clip((tcy - tr).astype(np.int32), 0, tb[1])
+    y1 = np.clip((tcy + tr + one).astype(np.int32), 0, tb[1])
+    hit = np.where(radii > 0, (x1 - x0) * (y1 - y0), 0).astype(np.int32)
+    radii = np.where(hit > 0, radii, 0).astype(np.int32)
+    t = [_t(a, cuda_dev) for a in (xys, depths, radii, hit)]
+    ids, bins, I = U.bin_fast(*t, tb, impl="lsd")
+    assert I == int(hit.sum())
+    if case == "peaky_1m":
+        for impl in ("lsd3", "bucket"):
+            ids4, bins4, I4 = U.bin_fast(*t, tb, impl=impl)
+            assert I4 == I and torch.equal(bins, bins4) and torch.equal(ids[:I], ids4[:I]), impl
+    else:
+        b = oracle.bin_and_sort(xys, depths, radii, hit, tb)
+        assert b.I == I
+        assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
+        assert np.array_equal(ids[:I].cpu().numpy(), b.ids_sorted)
+        for impl in ("lsd3", "bucket"):
+            ids4, bins4, I4 = U.bin_fast(*t, tb, impl=impl)
+            assert I4 == I and torch.equal(bins, bins4) and torch.equal(ids[:I], ids4[:I]), impl
+
+
 def _raster_case(oracle, N, W, H, seed, s0, C=3):
     d = projected(oracle, N=N, W=W, H=H, seed=seed, s0=s0)
     rng = np.random.default_rng(seed + 100)
