@@ -61,6 +61,7 @@ SIGNATURES = {
     "gs_set_depth_sort_passes": (_i, [_i]),
     "gs_set_bin_impl": (_i, [_i]),
     "gs_set_raster_fwd_unroll": (_i, [_i]),
+    "gs_set_raster_bwd_direct": (_i, [_i]),
     "gs_raster_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_raster_fwd_rgbd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gs_tile_order": (_i, [_i, _vp, _i, _vp, _vp]),

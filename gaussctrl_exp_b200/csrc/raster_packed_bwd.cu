@@ -16,6 +16,8 @@
 // Per lane only the raw moments of v_sigma are formed; conic / xy gradients are linear in them and are assembled once
 // per (tile, Gaussian) in the flush. Bound: SM issue rate + shuffle throughput; global atomics <= 9 * I.
 #define GS_PDL_GROUP 2
+#include <cstdlib>
+
 #include "raster_packed.cuh"
 
 namespace {
@@ -259,7 +261,185 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
     }
 }
 
+
+// DIRECT variant (default): no shared-memory accumulators and no flush. Measured on the 1 M bench scene, a (tile, Gaussian)
+// pair is hit by only ~1.35 of the tile's 8 warps (the alpha >= 1/255 box of a typical splat is smaller than a warp's
+// 8x4 rect), so accumulating the warps' sums in shared memory first saved almost no global reductions (1.35 M hitting
+// (warp, Gaussian) pairs against ~1.0 M non-empty (tile, Gaussian) pairs) while costing a compare-and-swap loop per
+// warp sum, 18 KB of shared memory and a flush pass. Here the lanes that end the butterfly with a sum turn it into
+// the gradient component they own (the xy pair needs one more shuffle: v_xy = Q (mx, my) with Q the conic) and issue
+// ONE red.global each, straight into the compositor-gradient block.
+__global__ void __launch_bounds__(256)
+raster_bwd_direct_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_sorted,
+                         const int2 *__restrict__ tile_bins, const float4 *__restrict__ rec,
+                         const float *__restrict__ bg, const float *__restrict__ final_T,
+                         const int32_t *__restrict__ final_idx, const float *__restrict__ v_out,
+                         const float *__restrict__ v_out_alpha, float *__restrict__ v_xys,
+                         float *__restrict__ v_conics, float *__restrict__ v_colors, float *__restrict__ v_opac,
+                         const int32_t *__restrict__ tile_order, const float *__restrict__ clamp_ref) {
+    __shared__ float4 s0[2][RPB];          // x, y, ex, ey
+    __shared__ float4 s1[2][RPB];          // opac, qa, qb, qc
+    __shared__ float4 s2[2][RPB];          // r, g, b, depth
+    __shared__ int s_id[2][RPB];           // Gaussian of every staged record (destination of the reductions)
+    __shared__ int s_wmax[8];
+
+    gs_pdl_sync();
+    const int tile = tile_order ? tile_order[blockIdx.x] : blockIdx.x;   // heaviest tiles first
+    const int tile_x = tile % tiles_x, tile_y = tile / tiles_x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int px, py;
+    gs_pixel_of_thread(tile_x, tile_y, px, py);
+    const bool inside = px < W && py < H;
+    const float fx = (float)px + GS_PIX_CENTER, fy = (float)py + GS_PIX_CENTER;
+    float rx0, ry0;
+    gs_warp_rect(tile_x, tile_y, rx0, ry0);
+    const float rx1 = rx0 + 7.0f, ry1 = ry0 + 3.0f;
+    const int2 range = tile_bins[tile];
+    const size_t pix = inside ? (size_t)py * W + px : 0;
+
+    const int my_end = inside ? final_idx[pix] : range.x;
+    const float Tf = inside ? final_T[pix] : 0.f;
+    float T = Tf;
+    float vo0 = 0.f, vo1 = 0.f, vo2 = 0.f, voa = 0.f;
+    if (inside) {
+        vo0 = v_out[3 * pix]; vo1 = v_out[3 * pix + 1]; vo2 = v_out[3 * pix + 2];
+        if (clamp_ref) {       // v_out is w.r.t. clamp(out, max=1): no gradient where the raw output exceeds 1
+            if (clamp_ref[3 * pix] > 1.0f) vo0 = 0.f;
+            if (clamp_ref[3 * pix + 1] > 1.0f) vo1 = 0.f;
+            if (clamp_ref[3 * pix + 2] > 1.0f) vo2 = 0.f;
+        }
+        if (v_out_alpha) voa = v_out_alpha[pix];
+    }
+    const float tail = Tf * (voa - (bg[0] * vo0 + bg[1] * vo1 + bg[2] * vo2));
+    float Svo = 0.f;
+
+    int wmax = my_end;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+    if (lane == 0) s_wmax[warp] = wmax;
+    __syncthreads();
+    int bmax = range.x;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) bmax = max(bmax, s_wmax[w]);
+    const int nb = (bmax - range.x + RPB - 1) / RPB;       // batches, walked from the back of the list
+
+    auto batch_lo = [&](int b) { return max(range.x, bmax - (b + 1) * RPB); };
+    auto batch_cnt = [&](int b) { return (bmax - b * RPB) - batch_lo(b); };
+    auto load_id = [&](int b) -> int { return tid < batch_cnt(b) ? ids_sorted[batch_lo(b) + tid] : -1; };
+    auto issue = [&](int id, int stage) {
+        if (id >= 0) {
+            const float4 *src = rec + (size_t)GS_REC_QUADS * (size_t)id;
+            gs_cp_async16(gs_smem_addr(&s0[stage][tid]), src);
+            gs_cp_async16(gs_smem_addr(&s1[stage][tid]), src + 1);
+            gs_cp_async16(gs_smem_addr(&s2[stage][tid]), src + 2);
+            s_id[stage][tid] = id;
+        }
+        gs_cp_async_commit();
+    };
+
+    // what this lane does with the sum the butterfly leaves on it (value index lane >> 2; lane 1: the ninth value):
+    //   0, 1: v_xy = (a mx + b my, b mx + c my) with (a, b, c) = conic = (K2 qa, K1 qb, K2 qc)   [needs the other sum]
+    //   2, 3, 4: v_conic = (mxx / 2, mxy, myy / 2);  5: v_opacity;  6, 7, 8: v_rgb
+    const int vi = lane >> 2;
+    const bool acc_lane = (lane & 3) == 0 || lane == 1;
+    const float K1 = -1.0f / GS_LOG2E, K2 = -2.0f / GS_LOG2E;
+    float k2 = vi < 2 ? K2 : 0.f, k1 = vi < 2 ? K1 : 0.f;
+    float mulc = vi < 2 ? 0.f : ((vi == 2 || vi == 4) ? 0.5f : 1.0f);
+    float *gp;
+    unsigned gstride;
+    if (lane == 1) { gp = v_colors + 2; gstride = 3; }
+    else if (vi < 2) { gp = v_xys + vi; gstride = 2; }
+    else if (vi < 5) { gp = v_conics + (vi - 2); gstride = 3; }
+    else if (vi == 5) { gp = v_opac; gstride = 1; }
+    else { gp = v_colors + (vi - 6); gstride = 3; }
+    const bool first = vi == 0;
+    // opaque to the compiler: it otherwise re-derives these per-lane constants from the lane id inside the replay
+    // loop (8 of ~110 issue slots per hitting (warp, Gaussian) in the first build of this kernel)
+    asm volatile("" : "+f"(k1), "+f"(k2), "+f"(mulc), "+r"(gstride));
+
+    int id_cur = -1, id_next = -1;
+    if (nb > 0) {
+        id_cur = load_id(0);
+        issue(id_cur, 0);
+        if (nb > 1) id_next = load_id(1);
+    }
+    for (int b = 0; b < nb; ++b) {
+        const int stage = b & 1;
+        gs_cp_async_wait_all();
+        __syncthreads();      // stage b published; every warp has finished replaying batch b-1
+        if (b + 1 < nb) issue(id_next, stage ^ 1);
+        id_next = (b + 2 < nb) ? load_id(b + 2) : -1;
+
+        const int lo = batch_lo(b);
+        const int jend = min(batch_cnt(b), wmax - lo);   // warp-uniform: nothing past this warp's last contributor
+        const unsigned a0 = gs_smem_addr(s0[stage]), a1 = gs_smem_addr(s1[stage]), a2 = gs_smem_addr(s2[stage]);
+        const unsigned aid = gs_smem_addr(s_id[stage]);
+        for (int c32 = (jend - 1) & ~31; jend > 0 && c32 >= 0; c32 -= 32) {
+            const int j = c32 + lane;
+            bool keep = false;
+            if (j < jend) keep = gs_rect_hit(gs_lds128(a0 + (unsigned)j * 16u), rx0, ry0, rx1, ry1);
+            unsigned word = __ballot_sync(0xffffffffu, keep);
+            while (word) {
+                const int bit = 31 - __clz(word);
+                word &= ~(1u << bit);
+                const unsigned jj = (unsigned)(c32 + bit);
+                const float4 A = gs_lds128(a0 + jj * 16u);
+                const float4 B = gs_lds128(a1 + jj * 16u);
+                const float4 Cc = gs_lds128(a2 + jj * 16u);
+                GsSplat sp = {A.x, A.y, B.x, B.y, B.z, B.w};
+                float dx, dy, vis, alpha;
+                bool hit = gs_eval_alpha(sp, fx, fy, dx, dy, vis, alpha);
+                hit = hit && (lo + (int)jj < my_end);
+                if (!__any_sync(0xffffffffu, hit)) continue;
+                const int gid = __float_as_int(gs_lds32(aid + jj * 4u));
+                const float al = hit ? alpha : 0.0f;
+                const float ra = gs_rcp(1.0f - al);
+                T *= ra;
+                const float fac = al * T;
+                const float cvo = Cc.x * vo0 + Cc.y * vo1 + Cc.z * vo2;
+                const float v_alpha = T * cvo - ra * (Svo - tail);
+                Svo += fac * cvo;
+                const bool live = hit && (B.x * vis <= GS_ALPHA_MAX);
+                const float visl = live ? vis : 0.0f;
+                const float v_sigma = -B.x * visl * v_alpha;
+                const float mx = v_sigma * dx, my = v_sigma * dy;
+                float v[8];
+                v[0] = mx; v[1] = my;
+                v[2] = mx * dx; v[3] = mx * dy; v[4] = my * dy;
+                v[5] = visl * v_alpha;
+                v[6] = fac * vo0; v[7] = fac * vo1;
+                const float v8 = fac * vo2;
+                const float r8 = warp_reduce8(v, lane);
+                const float r9 = warp_sum(v8);
+                const float other = __shfl_xor_sync(0xffffffffu, r8, 4);      // lanes of sum 0 see sum 1 and vice versa
+                const float coefA = fmaf(k2, first ? B.y : B.w, mulc);
+                float add = fmaf(k1 * B.z, other, coefA * r8);
+                if (lane == 1) add = r9;
+                if (acc_lane && add != 0.0f) atomicAdd(gp + (unsigned)gid * gstride, add);   // < 2^32 floats per array
+            }
+        }
+    }
+    gs_cp_async_wait_all();
+}
+
+// 1 (default): reductions straight to global memory; 0: shared-memory accumulators + flush. GS_RASTER_BWD_DIRECT /
+// gs_set_raster_bwd_direct: A/B switch
+int g_bwd_direct = -1;
+int raster_bwd_direct() {
+    if (g_bwd_direct < 0) {
+        const char *e = getenv("GS_RASTER_BWD_DIRECT");
+        g_bwd_direct = e ? (atoi(e) != 0) : 1;
+    }
+    return g_bwd_direct;
+}
+
 }  // namespace
+
+extern "C" int gs_set_raster_bwd_direct(int on) {
+    const int prev = raster_bwd_direct();
+    g_bwd_direct = on != 0;
+    return prev;
+}
 
 int gs_launch_raster_bwd_packed(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
                                 const int32_t *tile_bins, const float *rec, const float *bg, const float *final_T,
@@ -267,6 +447,12 @@ int gs_launch_raster_bwd_packed(int H, int W, int tiles_x, int tiles_y, const in
                                 float *v_conics, float *v_colors, float *v_opac, const int32_t *tile_order,
                                 const float *clamp_ref, cudaStream_t st) {
     const int tiles = tiles_x * tiles_y;
+    if (raster_bwd_direct()) {
+        GS_PDL_LAUNCH_IF(tiles <= GS_RASTER_PDL_MAX_TILES, raster_bwd_direct_kernel, tiles, 256, 0, st, H, W, tiles_x,
+                         ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float4 *>(rec), bg,
+                         final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref);
+        return 0;
+    }
     GS_PDL_LAUNCH_IF(tiles <= GS_RASTER_PDL_MAX_TILES, raster_bwd_packed_kernel<false>, tiles, 256, 0, st, H, W, tiles_x,
                      ids_sorted, reinterpret_cast<const int2 *>(tile_bins), reinterpret_cast<const float4 *>(rec), bg,
                      final_T, final_idx, v_out, v_out_alpha, v_xys, v_conics, v_colors, v_opac, tile_order, clamp_ref,

@@ -314,6 +314,11 @@ int gs_raster_fwd_packed(int views, int H, int W, int tiles_x, int tiles_y, cons
 /* Tuning knob of the packed forward compositing kernel: survivors composited per loop iteration (1..4; default 1,
  * environment GS_RASTER_FWD_UNROLL). Identical output. Returns the previous setting; other values only query. */
 int gs_set_raster_fwd_unroll(int u);
+/* Tuning knob of the packed backward compositing kernel: 1 (default; environment GS_RASTER_BWD_DIRECT) = every warp
+ * sum goes straight to the gradient block with one red.global; 0 = sums of a tile's warps are first accumulated in
+ * shared memory and flushed once per (tile, Gaussian). Same gradients up to the order of float additions. Returns the
+ * previous setting. */
+int gs_set_raster_bwd_direct(int on);
 int gs_raster_bwd_packed(int H, int W, int tiles_x, int tiles_y, const int32_t *ids_sorted,
                          const int32_t *tile_bins, const float *rec, const float *bg, const float *final_T,
                          const int32_t *final_idx, const float *v_out, const float *v_out_alpha, float *v_xys,

@@ -127,6 +127,47 @@ def test_deterministic_backward_is_bit_reproducible(oracle, cuda_dev, monkeypatc
         assert a[k].abs().max().item() > 0
 
 
+@pytest.mark.parametrize("s0,W,H", [(None, 192, 128), (0.06, 96, 80)])
+def test_backward_reduction_modes_agree(oracle, cuda_dev, s0, W, H):
+    """gs_set_raster_bwd_direct: warp sums reduced straight into the gradient block (default) vs accumulated per tile in
+    shared memory first — the same gradients up to the order of float additions, for small splats (most pairs hit by
+    one warp) and for big ones (every warp of many tiles), and both within the contract of the oracle."""
+    from gaussctrl_exp_b200 import _lib, scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    from util import gradient_parity, forward_parity
+    L = _lib.lib()
+    N = 20_000
+    p = scene.make_scene(N, 9, s0=s0)
+    cam = small_cam(W, H, 9)
+    v_np = (np.random.default_rng(7).standard_normal((H, W, 3)) / (H * W)).astype(np.float32)
+    v = torch.from_numpy(v_np).to(cuda_dev)
+    names = ("means", "scales", "quats", "features_dc", "features_rest", "opacities")
+    got = {}
+    prev = L.gs_set_raster_bwd_direct(1)
+    try:
+        for mode in (1, 0):
+            L.gs_set_raster_bwd_direct(mode)
+            m = GaussianModel(p, sh_degree=3, background_color=torch.tensor([0.1, 0.2, 0.3])).to(cuda_dev)
+            m.train()
+            out = m(cam)
+            (out["rgb"] * v).sum().backward()
+            got[mode] = {k: getattr(m, k).grad.clone() for k in names}
+            got[mode]["xys"] = m.view_state.xys_grad.clone()
+            if mode == 1:
+                rgb, acc, fidx = out["rgb"].detach().cpu().numpy(), out["accumulation"].detach().cpu().numpy(), m.view_state.final_idx.cpu().numpy()
+    finally:
+        L.gs_set_raster_bwd_direct(prev)
+    for k in got[1]:
+        den = got[0][k].abs().max().clamp_min(1e-30)
+        assert ((got[1][k] - got[0][k]).abs().max() / den).item() < 1e-5, k
+        assert got[1][k].abs().max().item() > 0
+    p_np = {k: t.numpy() for k, t in p.items()}
+    ref, ctx = oracle.render_view(p_np, cam.as_dict(), 3, training=True)
+    g = oracle.render_view_backward(p_np, ctx, v_np)
+    _, F, excl = forward_parity(oracle, ctx, rgb, ref["rgb"], acc, ref["accumulation"], H, W, fidx)
+    gradient_parity(oracle, ctx, excl, {k: t.cpu().numpy() for k, t in got[1].items()}, {k: g[k] for k in names + ("xys",)}, H, W)
+
+
 def test_capacity_overflow_heals_or_is_flagged(cuda_dev, monkeypatch):
     """The tile lists are allocated for a capacity learnt from earlier views. Default mode: an undersized capacity is
     noticed inside the forward (count read behind the binning) and the view is redone — the caller never sees a torn
