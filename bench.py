@@ -840,9 +840,9 @@ def run_ours(args):
             # committed ncu capture of this build
             f_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
             slots = 148 * 4 * f_clk                       # warp-instruction issue slots per second
-            rr = {"bound": "sm_issue", "kernel": "raster_bwd_packed_kernel", "us": stages["raster_bwd"]["us"],
+            rr = {"bound": "sm_issue", "kernel": "raster_bwd_direct_kernel", "us": stages["raster_bwd"]["us"],
                   "peak": slots, "unit": "warp-inst/s", "sm_mhz": f_clk / 1e6, "metrics_source": prof_path}
-            for kname2, key in (("raster_bwd_packed_kernel", "bwd"), ("raster_fwd_packed_kernel", "fwd")):
+            for kname2, key in (("raster_bwd_direct_kernel", "bwd"), ("raster_fwd_packed_kernel", "fwd")):
                 pk2 = prof.get(kname2) if args.n_gaussians == N_GAUSS else None
                 us = stages["raster_" + key]["us"]
                 ent = {"us": us}

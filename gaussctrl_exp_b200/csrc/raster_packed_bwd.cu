@@ -22,6 +22,11 @@
 
 namespace {
 
+// CTAs per SM the direct kernel is compiled for: 5 = 48 registers, no spills. 6 (40 registers, two spilled) was measured
+// slower, 248 vs 240 us, although its 27 KB of shared memory would allow eight.
+#ifndef GS_BWD_MIN_CTAS
+#define GS_BWD_MIN_CTAS 5
+#endif
 constexpr int RPB = 256;   // Gaussians per batch
 constexpr int RPB_NV = 9;  // v_x, v_y, v_ca, v_cb, v_cc, v_opac, v_r, v_g, v_b (as moments)
 
@@ -269,7 +274,7 @@ raster_bwd_packed_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ 
 // warp sum, 18 KB of shared memory and a flush pass. Here the lanes that end the butterfly with a sum turn it into
 // the gradient component they own (the xy pair needs one more shuffle: v_xy = Q (mx, my) with Q the conic) and issue
 // ONE red.global each, straight into the compositor-gradient block.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, GS_BWD_MIN_CTAS)
 raster_bwd_direct_kernel(int H, int W, int tiles_x, const int32_t *__restrict__ ids_sorted,
                          const int2 *__restrict__ tile_bins, const float4 *__restrict__ rec,
                          const float *__restrict__ bg, const float *__restrict__ final_T,

@@ -17,7 +17,7 @@ if [ "$MODE" = "list" ]; then
   ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none --csv --log-file gpurun_out/launches.csv $BCMD > gpurun_out/ncu_list.log 2>&1
   tail -3 gpurun_out/ncu_list.log
 elif [ "$MODE" = "source" ]; then
-  ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"${NCU_KERNELS:-raster_(fwd|bwd)_packed}" -f -o gpurun_out/prof_src $CMD > gpurun_out/ncu_src.log 2>&1
+  ncu --set full --clock-control none --import-source on --profile-from-start off -k regex:"${NCU_KERNELS:-raster_(fwd_packed|bwd_direct)}" -f -o gpurun_out/prof_src $CMD > gpurun_out/ncu_src.log 2>&1
   tail -3 gpurun_out/ncu_src.log
   ncu -i gpurun_out/prof_src.ncu-rep --page source --csv > gpurun_out/prof_src_source.csv 2>/dev/null
   ncu -i gpurun_out/prof_src.ncu-rep --page raw --csv > gpurun_out/prof_src_raw.csv 2>/dev/null
