@@ -159,7 +159,10 @@ def test_backward_reduction_modes_agree(oracle, cuda_dev, s0, W, H):
         L.gs_set_raster_bwd_direct(prev)
     for k in got[1]:
         den = got[0][k].abs().max().clamp_min(1e-30)
-        assert ((got[1][k] - got[0][k]).abs().max() / den).item() < 1e-5, k
+        # both modes add floats with atomics in scheduling order: with big splats (thousands of addends per Gaussian)
+        # two runs differ by ~1e-5 of the largest gradient (measured 1.2e-5 on quats); the contract itself (1e-4 against
+        # the oracle) is asserted below
+        assert ((got[1][k] - got[0][k]).abs().max() / den).item() < 5e-5, k
         assert got[1][k].abs().max().item() > 0
     p_np = {k: t.numpy() for k, t in p.items()}
     ref, ctx = oracle.render_view(p_np, cam.as_dict(), 3, training=True)
