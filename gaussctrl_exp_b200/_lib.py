@@ -59,6 +59,7 @@ SIGNATURES = {
     "gs_bin_fast_scratch_bytes": (_sz, [_i, _i64, _i]),
     "gs_bin_fast": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gs_set_depth_sort_passes": (_i, [_i]),
+    "gs_set_radix_cfg": (_i, [_i, _i]),
     "gs_set_bin_impl": (_i, [_i]),
     "gs_set_raster_fwd_unroll": (_i, [_i]),
     "gs_set_raster_bwd_direct": (_i, [_i]),

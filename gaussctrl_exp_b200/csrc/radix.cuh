@@ -4,7 +4,12 @@
 //     scatter : CTA b scans the digit totals itself (digit base), ranks its chunk (ballot matching,
 //               stable), stages it in shared memory in digit order and writes coalesced runs at
 //               digit_base + mat[digit][b] + local rank
-// FROM_DEPTH passes read their keys straight from (depths, radii): key = bits(depth), culled -> 0xFFFFFFFF.
+// MODE 1 passes read their keys straight from (depths, radii): key = bits(depth), culled -> 0xFFFFFFFF.
+// MODE 2 passes ("planned" depth sort) take digit position and width from a DEVICE-side plan: the keys are the depth
+// bits of the visible elements minus their minimum (culled -> range + 1), so only R = bitlen(max - min + 1) bits are
+// live — 25 for a typical view, i.e. THREE passes of <= 9 bits instead of four of 8. Four passes are always launched;
+// the ones the plan does not need (at the FRONT of the chain, so that the result always lands in the same buffer)
+// return at once, and the first active pass forms its keys from (depths, radii).
 //
 // Design for B200: at the sizes of this path (N ~ 1 M Gaussians, I ~ 3 M intersections) the whole
 // working set sits in the 126 MB L2, so a pass is bound by latency and launch count, not HBM.
@@ -19,10 +24,18 @@
 
 namespace gsradix {
 
-constexpr int TPB = 256;
-constexpr int WARPS = TPB / 32;
-constexpr int IPT = 16;
-constexpr int SUB = TPB * IPT;  // keys per CTA
+// CTA shape of a pass: TPB threads x IPT keys per thread = SUB keys per CTA. The passes over N ~ 1 M keys are one-wave,
+// latency-bound launches and want many warps per SM (512 x 8: 16 warps per CTA); the passes over I >= 6 M pairs are
+// throughput-bound and want smaller chunks (384 x 8 / 256 x 12) — measured per size, see select_cfg below.
+template <int TPB_, int IPT_>
+struct Cfg {
+    static constexpr int TPB = TPB_, IPT = IPT_, WARPS = TPB_ / 32, SUB = TPB_ * IPT_;
+};
+using CfgDefault = Cfg<256, 16>;
+using Cfg512x8 = Cfg<512, 8>;
+using Cfg384x8 = Cfg<384, 8>;
+using Cfg256x12 = Cfg<256, 12>;
+constexpr int MIN_SUB = 2048;   // smallest chunk of any configuration: sizes the count matrix
 
 // element count: host value, or (n_dev != nullptr) the device value clamped by the capacity;
 // returns -1 when the device value exceeds the capacity (caller retries with a larger buffer).
@@ -32,19 +45,60 @@ __device__ __forceinline__ int64_t resolve_n(int64_t n_cap, const int32_t *n_dev
     return v > n_cap ? -1 : v;
 }
 
-// key of element `at`: the key array, or (FROM_DEPTH) the depth bits of a visible Gaussian / 0xFFFFFFFF for a
+// Planned depth sort (MODE 2). range[0] = max over the visible elements of ~bits(depth), range[1] = max of bits(depth)
+// (both start at 0, so one memset initialises them; view-space depths are positive floats: their bit patterns order
+// like the values). q = position of the launch in the chain of PLAN_LAUNCHES passes.
+constexpr int PLAN_LAUNCHES = 4;
+constexpr int PLAN_BITS = 9;       // widest digit of a planned pass
+struct PlanArg {
+    const uint32_t *range;
+    const uint32_t *dkeys;         // bits(depth) per element (what the first active pass reads instead of kin)
+    int q;
+};
+struct PlanPass {
+    uint32_t kmin, kcull;          // key = bits(depth) - kmin for a visible element, kcull for a culled one
+    int shift, bits;
+    bool first;                    // first active pass: keys from (dkeys, radii), values = element index
+};
+// false: launch q is not needed for this range (it sits in front of the first active pass)
+__host__ __device__ inline bool plan_resolve(uint32_t r0, uint32_t r1, int q, PlanPass &pp) {
+    uint32_t lo = ~r0, hi = r1;
+    if (hi < lo) lo = hi = 0;                      // nothing visible: every key is kcull = 1
+    pp.kmin = lo;
+    pp.kcull = hi - lo + 1u;                       // < 2^31: visible keys are bit patterns of positive floats
+    int R = 0;
+    while (R < 32 && (pp.kcull >> R)) ++R;         // live bits, >= 1
+    const int P = R <= PLAN_BITS ? 1 : R <= 2 * PLAN_BITS ? 2 : R <= 3 * PLAN_BITS ? 3 : 4;
+    const int a = q - (PLAN_LAUNCHES - P);
+    if (a < 0) return false;
+    const int base = R / P, rem = R % P;           // the first `rem` active passes take one bit more
+    pp.bits = base + (a < rem ? 1 : 0);
+    pp.shift = a * base + (a < rem ? a : rem);
+    pp.first = a == 0;
+    return true;
+}
+
+// key of element `at`: the key array, or (MODE 1) the depth bits of a visible Gaussian / 0xFFFFFFFF for a
 // culled one (sorts behind every visible Gaussian), so that no separate key-building kernel is needed
-template <typename KeyT, bool FROM_DEPTH>
+template <typename KeyT, int MODE>
 __device__ __forceinline__ KeyT load_key(const KeyT *__restrict__ kin, const int32_t *__restrict__ radii, int64_t at) {
     const KeyT k = kin[at];
-    if (FROM_DEPTH) {   // both loads unconditional (a load behind the radius test would serialise two round trips per key)
+    if (MODE == 1) {   // both loads unconditional (a load behind the radius test would serialise two round trips per key)
         const int32_t r = radii[at];
         return r > 0 ? k : (KeyT) ~(KeyT)0;
     }
     return k;
 }
+__device__ __forceinline__ uint32_t load_key_planned(const PlanArg &pa, const PlanPass &pp, const uint32_t *__restrict__ kin,
+                                                     const int32_t *__restrict__ radii, int64_t at) {
+    if (!pp.first) return kin[at];
+    const uint32_t k = pa.dkeys[at];
+    const int32_t r = radii[at];
+    return r > 0 ? k - pp.kmin : pp.kcull;
+}
 
 // block-wide exclusive scan of one value per thread (TPB threads). tmp: >= 64 uint32.
+template <int WARPS>
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, uint32_t *total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t inc = v;
@@ -58,7 +112,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, u
     if (warp == 0) {
         uint32_t w = lane < WARPS ? tmp[lane] : 0u;
 #pragma unroll
-        for (int o = 1; o < WARPS; o <<= 1) {
+        for (int o = 1; o < 32; o <<= 1) {
             const uint32_t n = __shfl_up_sync(0xffffffffu, w, o);
             if (lane >= o) w += n;
         }
@@ -73,16 +127,23 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, u
 }
 
 // ---------------------------------------------------------------------------------------------
-template <typename KeyT, int BITS, bool FROM_DEPTH>
-__global__ void __launch_bounds__(TPB)
+template <typename KeyT, int BITS, int MODE, class C>
+__global__ void __launch_bounds__(C::TPB)
 hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
-            const int32_t *__restrict__ radii, int shift, int bits, uint32_t *__restrict__ mat, int pitch) {
+            const int32_t *__restrict__ radii, int shift, int bits, uint32_t *__restrict__ mat, int pitch, PlanArg pa) {
     constexpr int RADIX = 1 << BITS;
+    constexpr int TPB = C::TPB, IPT = C::IPT, SUB = C::SUB;
     __shared__ uint32_t hist[RADIX];
     gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
     const int64_t base = (int64_t)blockIdx.x * SUB;
     if (n < 0 || base >= n) return;
+    PlanPass pp = {};
+    if (MODE == 2) {
+        if (!plan_resolve(pa.range[0], pa.range[1], pa.q, pp)) return;
+        shift = pp.shift;
+        bits = pp.bits;
+    }
     const uint32_t mask = (1u << bits) - 1u;
     for (int d = threadIdx.x; d < RADIX; d += TPB) hist[d] = 0;
     __syncthreads();
@@ -90,7 +151,8 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
         const int64_t at = base + i * TPB + threadIdx.x;
-        key[i] = at < n ? load_key<KeyT, FROM_DEPTH>(kin, radii, at) : (KeyT)0;
+        if (MODE == 2) key[i] = at < n ? (KeyT)load_key_planned(pa, pp, (const uint32_t *)kin, radii, at) : (KeyT)0;
+        else key[i] = at < n ? load_key<KeyT, MODE>(kin, radii, at) : (KeyT)0;
     }
 #pragma unroll
     for (int i = 0; i < IPT; ++i)
@@ -100,17 +162,21 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
 }
 
 // One warp per digit: exclusive prefix over the CTA rows of mat[.][d], in place; totals[d] = sum.
-template <int BITS>
-__global__ void __launch_bounds__(TPB)
+template <int BITS, int MODE, int SUB>
+__global__ void __launch_bounds__(256)
 colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat, int pitch,
-               uint32_t *__restrict__ totals) {
+               uint32_t *__restrict__ totals, PlanArg pa) {
     constexpr int RADIX = 1 << BITS;
     gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
     if (n < 0) return;
+    if (MODE == 2) {
+        PlanPass pp;
+        if (!plan_resolve(pa.range[0], pa.range[1], pa.q, pp)) return;
+    }
     const int nb = (int)((n + SUB - 1) / SUB);
     const int lane = threadIdx.x & 31;
-    const int d = blockIdx.x * WARPS + (threadIdx.x >> 5);
+    const int d = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (d >= RADIX) return;
     uint32_t *row = mat + (size_t)d * pitch;   // mat[digit][cta]: the scan walks contiguous memory
     uint32_t carry = 0;
@@ -137,9 +203,10 @@ colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__res
     if (lane == 0) totals[d] = carry;
 }
 
-template <typename KeyT, int BITS>
+template <typename KeyT, int BITS, class C>
 struct ScatterSmem {
     static constexpr int RADIX = 1 << BITS;
+    static constexpr int SUB = C::SUB, WARPS = C::WARPS;
     KeyT stage_k[SUB];
     uint32_t stage_v[SUB];
     uint32_t dstart[RADIX];         // local start of each digit inside the CTA's chunk
@@ -153,20 +220,28 @@ struct ScatterSmem {
 // one-CTA digit-base kernel between colscan and scatter: one launch less per pass. When the digit IS the tile id
 // (single-pass partition, bins_out != nullptr) the tile ranges fall out of the same scan: CTA 0 writes
 // bins[t] = [base, base + total) (0,0 for empty tiles).
-template <typename KeyT, int BITS, bool FROM_DEPTH>
-__global__ void __launch_bounds__(TPB)
+template <typename KeyT, int BITS, int MODE, class C>
+__global__ void __launch_bounds__(C::TPB)
 scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
                const int32_t *__restrict__ radii, const uint32_t *__restrict__ vin, KeyT *__restrict__ kout,
                uint32_t *__restrict__ vout, int shift, int bits, const uint32_t *__restrict__ mat, int pitch,
-               const uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T) {
+               const uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T, PlanArg pa) {
     constexpr int RADIX = 1 << BITS;
+    constexpr int TPB = C::TPB, IPT = C::IPT, SUB = C::SUB, WARPS = C::WARPS;
     constexpr int DPT = (RADIX + TPB - 1) / TPB;  // digits per thread (contiguous)
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    ScatterSmem<KeyT, BITS> &s = *reinterpret_cast<ScatterSmem<KeyT, BITS> *>(smem_raw);
+    ScatterSmem<KeyT, BITS, C> &s = *reinterpret_cast<ScatterSmem<KeyT, BITS, C> *>(smem_raw);
     gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
     const int64_t base = (int64_t)blockIdx.x * SUB;
     if (n < 0 || base >= n) return;
+    PlanPass pp = {};
+    if (MODE == 2) {
+        if (!plan_resolve(pa.range[0], pa.range[1], pa.q, pp)) return;
+        shift = pp.shift;
+        bits = pp.bits;
+        if (pp.first) vin = nullptr;             // values start as the element index
+    }
     const int valid = (int)min((int64_t)SUB, n - base);
     const uint32_t mask = (1u << bits) - 1u;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -179,7 +254,8 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
         const int li = woff + i * 32 + lane;
-        key[i] = li < valid ? load_key<KeyT, FROM_DEPTH>(kin, radii, base + li) : (KeyT) ~(KeyT)0;
+        if (MODE == 2) key[i] = li < valid ? (KeyT)load_key_planned(pa, pp, (const uint32_t *)kin, radii, base + li) : (KeyT) ~(KeyT)0;
+        else key[i] = li < valid ? load_key<KeyT, MODE>(kin, radii, base + li) : (KeyT) ~(KeyT)0;
         val[i] = li < valid ? (vin ? vin[base + li] : (uint32_t)(base + li)) : 0u;
     }
     // global cursors of this CTA: digit base (exclusive scan of the digit totals) + keys of the same digit in the
@@ -194,7 +270,7 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
             cursor[j] = d < RADIX ? mat[(size_t)d * pitch + blockIdx.x] : 0u;
             sum += tot[j];
         }
-        uint32_t run = block_excl_scan(sum, s.scan_tmp, nullptr);   // ends with a barrier: wc is zeroed after it
+        uint32_t run = block_excl_scan<WARPS>(sum, s.scan_tmp, nullptr);   // ends with a barrier: wc is zeroed after it
 #pragma unroll
         for (int j = 0; j < DPT; ++j) {
             const int d = tid * DPT + j;
@@ -261,7 +337,7 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
         }
         csum += cnt[j];
     }
-    uint32_t dstart = block_excl_scan(csum, s.scan_tmp, nullptr);
+    uint32_t dstart = block_excl_scan<WARPS>(csum, s.scan_tmp, nullptr);
 #pragma unroll
     for (int j = 0; j < DPT; ++j) {
         const int d = tid * DPT + j;
@@ -296,32 +372,68 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
 // host-side launcher of one pass. mat: RADIX * pitch + RADIX uint32 (pitch = ceil(n_cap/SUB); the tail holds
 // totals[RADIX]). bins_out != nullptr: the digit is the tile id -> write tile ranges.
 // radii != nullptr (uint32 keys only): kin is the float depth array and the keys are formed on the fly.
-template <typename KeyT, int BITS, bool FROM_DEPTH = false>
+template <typename KeyT, int BITS, int MODE = 0, class C = CfgDefault>
 inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, const uint32_t *vin, KeyT *kout,
                        uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st,
-                       int32_t *bins_out = nullptr, int bins_T = 0, const int32_t *radii = nullptr) {
+                       int32_t *bins_out = nullptr, int bins_T = 0, const int32_t *radii = nullptr,
+                       PlanArg pa = PlanArg{nullptr, nullptr, 0}) {
     constexpr int RADIX = 1 << BITS;
     if (n_cap <= 0) return 0;
-    if (bits > BITS || (FROM_DEPTH && !radii)) return GS_ERR_BAD_ARG;
+    if (bits > BITS || (MODE != 0 && !radii) || (MODE == 2 && (!pa.range || !pa.dkeys))) return GS_ERR_BAD_ARG;
+    constexpr int TPB = C::TPB, SUB = C::SUB;
     const int nb = (int)((n_cap + SUB - 1) / SUB);
     uint32_t *totals = mat + (size_t)nb * RADIX;
-    const size_t smem = sizeof(ScatterSmem<KeyT, BITS>);
+    const size_t smem = sizeof(ScatterSmem<KeyT, BITS, C>);
     // the attribute is per DEVICE: set it on every launch (a few hundred ns) rather than once per process — a second
     // GPU in the same process (tests, tools, set_device after first use) would otherwise launch without the opt-in
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute((const void *)scatter_kernel<KeyT, BITS, FROM_DEPTH>,
+        cudaError_t e = cudaFuncSetAttribute((const void *)scatter_kernel<KeyT, BITS, MODE, C>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
     }
-    GS_PDL_LAUNCH((hist_kernel<KeyT, BITS, FROM_DEPTH>), nb, TPB, 0, st, n_cap, n_dev, kin, radii, shift, bits, mat, nb);
-    GS_PDL_LAUNCH((colscan_kernel<BITS>), (RADIX + WARPS - 1) / WARPS, TPB, 0, st, n_cap, n_dev, mat, nb, totals);
-    GS_PDL_LAUNCH((scatter_kernel<KeyT, BITS, FROM_DEPTH>), nb, TPB, smem, st, n_cap, n_dev, kin, radii, vin, kout, vout,
-                  shift, bits, (const uint32_t *)mat, nb, (const uint32_t *)totals, bins_out, bins_T);
+    GS_PDL_LAUNCH((hist_kernel<KeyT, BITS, MODE, C>), nb, TPB, 0, st, n_cap, n_dev, kin, radii, shift, bits, mat, nb, pa);
+    GS_PDL_LAUNCH((colscan_kernel<BITS, MODE, SUB>), (RADIX + 7) / 8, 256, 0, st, n_cap, n_dev, mat, nb, totals, pa);
+    GS_PDL_LAUNCH((scatter_kernel<KeyT, BITS, MODE, C>), nb, TPB, smem, st, n_cap, n_dev, kin, radii, vin, kout, vout,
+                  shift, bits, (const uint32_t *)mat, nb, (const uint32_t *)totals, bins_out, bins_T, pa);
     return 0;
 }
 
 inline size_t mat_entries(int64_t n_cap, int radix) {
-    return ((size_t)((n_cap + SUB - 1) / SUB) + 2) * (size_t)radix;
+    return ((size_t)((n_cap + MIN_SUB - 1) / MIN_SUB) + 2) * (size_t)radix;
+}
+
+// launch_pass with the CTA shape chosen at run time: 0 = 256 x 16 (round 1), 1 = 512 x 8, 2 = 384 x 8, 3 = 256 x 12
+template <typename KeyT, int BITS, int MODE = 0>
+inline int launch_pass_cfg(int cfg, int64_t n_cap, const int32_t *n_dev, const KeyT *kin, const uint32_t *vin, KeyT *kout,
+                           uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st, int32_t *bins_out = nullptr,
+                           int bins_T = 0, const int32_t *radii = nullptr, PlanArg pa = PlanArg{nullptr, nullptr, 0}) {
+#define GS_RADIX_GO(CFG) \
+    return launch_pass<KeyT, BITS, MODE, CFG>(n_cap, n_dev, kin, vin, kout, vout, shift, bits, mat, st, bins_out, bins_T, radii, pa)
+    switch (cfg) {
+        case 1: GS_RADIX_GO(Cfg512x8);
+        case 2: GS_RADIX_GO(Cfg384x8);
+        case 3: GS_RADIX_GO(Cfg256x12);
+        default: GS_RADIX_GO(CfgDefault);
+    }
+#undef GS_RADIX_GO
+}
+
+// The planned depth sort: PLAN_LAUNCHES passes over N elements; result (element indices in depth order, culled ones
+// last, ties in index order) in valA whatever the number of active passes. keyA/valA/keyB/valB: N words each.
+inline int launch_depth_sort_planned(int64_t N, const uint32_t *dkeys, const int32_t *radii, const uint32_t *range,
+                                     uint32_t *keyA, uint32_t *valA, uint32_t *keyB, uint32_t *valB, uint32_t *mat,
+                                     cudaStream_t st, int cfg = 0) {
+    int rc;
+    for (int q = 0; q < PLAN_LAUNCHES; ++q) {
+        const bool to_a = ((PLAN_LAUNCHES - 1 - q) & 1) == 0;          // the last launch writes A
+        const uint32_t *kin = to_a ? keyB : keyA, *vin = to_a ? valB : valA;
+        uint32_t *kout = q == PLAN_LAUNCHES - 1 ? nullptr : (to_a ? keyA : keyB);   // nobody reads the last pass's keys
+        uint32_t *vout = to_a ? valA : valB;
+        if ((rc = launch_pass_cfg<uint32_t, PLAN_BITS, 2>(cfg, N, nullptr, kin, vin, kout, vout, 0, PLAN_BITS, mat, st, nullptr, 0,
+                                                          radii, PlanArg{range, dkeys, q})))
+            return rc;
+    }
+    return 0;
 }
 
 }  // namespace gsradix

@@ -215,6 +215,11 @@ int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, con
  * launches; measured slower) stable LSD passes — identical output. Returns the previous setting; other values only query.
  * Initial value: environment variable GS_DEPTH_SORT_PASSES. */
 int gs_set_depth_sort_passes(int passes);
+/* CTA shape of gs_bin_fast's radix passes: which = 0 (depth sort over the N elements) or 1 (partition over the I pairs);
+ * cfg = -1 (default: chosen from the problem size), 0 = 256 threads x 16 keys, 1 = 512 x 8, 2 = 384 x 8, 3 = 256 x 12.
+ * Identical output. Returns the previous setting (-1 = automatic); other values only query. Initial value: environment
+ * variables GS_RADIX_CFG_DEPTH / GS_RADIX_CFG_PART. */
+int gs_set_radix_cfg(int which, int cfg);
 /* Implementation behind gs_bin_fast / gs_view_fwd: 1 (default) = LSD pipeline — depth sort of the Gaussians, scan +
  * emission in depth order, stable partition by tile; 0 = bucket pipeline — per-tile counts, scan, unordered fill of
  * (depth bits, id) entries into each tile's segment, one CTA per tile merge-sorts its segment in shared memory (four

@@ -92,7 +92,7 @@ def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
     assert np.array_equal(vs.cpu().numpy(), b.ids_sorted)
     assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
     # product paths: identical ids_sorted and tile ranges without 64-bit keys
-    for impl in ("bucket", "lsd", "lsd3"):
+    for impl in ("bucket", "lsd", "lsd3", "lsd4"):
         ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         assert I2 == b.I, impl
         assert np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted), impl
@@ -116,7 +116,7 @@ def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
     b = oracle.bin_and_sort(xys, depths, radii, hit, tb)
     assert b.I == int(hit.sum()) and (b.tile_bins[:, 1] - b.tile_bins[:, 0]).max() > 50000
     t = [_t(a, cuda_dev) for a in (xys, depths, radii, hit)]
-    for impl in ("bucket", "lsd", "lsd3"):
+    for impl in ("bucket", "lsd", "lsd3", "lsd4"):
         ids2, bins2, I2 = U.bin_fast(*t, tb, impl=impl)
         assert I2 == b.I
         assert np.array_equal(bins2.cpu().numpy(), b.tile_bins), impl
@@ -178,7 +178,7 @@ def test_depth_sort_corner_cases(oracle, cuda_dev, case):
     ids, bins, I = U.bin_fast(*t, tb, impl="lsd")
     assert I == int(hit.sum())
     if case == "peaky_1m":
-        for impl in ("lsd3", "bucket"):
+        for impl in ("lsd3", "lsd4", "bucket"):
             ids4, bins4, I4 = U.bin_fast(*t, tb, impl=impl)
             assert I4 == I and torch.equal(bins, bins4) and torch.equal(ids[:I], ids4[:I]), impl
     else:
@@ -186,7 +186,7 @@ def test_depth_sort_corner_cases(oracle, cuda_dev, case):
         assert b.I == I
         assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
         assert np.array_equal(ids[:I].cpu().numpy(), b.ids_sorted)
-        for impl in ("lsd3", "bucket"):
+        for impl in ("lsd3", "lsd4", "bucket"):
             ids4, bins4, I4 = U.bin_fast(*t, tb, impl=impl)
             assert I4 == I and torch.equal(bins, bins4) and torch.equal(ids[:I], ids4[:I]), impl
 
