@@ -485,41 +485,8 @@ edges32_kernel(int64_t I_cap, const int32_t *__restrict__ total_dev, const uint3
     if (k == I - 1 || tk[k + 1] != t) bins[2 * t + 1] = (int32_t)(k + 1);
 }
 
-// min / max of the visible depth keys when the caller has none (operator API: gs_bin_fast): range[0] = max(~key),
-// range[1] = max(key), both zero-initialised (radix.cuh: plan_resolve). The fused path gets them from the
-// preprocess kernel for free.
-__global__ void __launch_bounds__(256)
-depth_range_kernel(int N, const uint32_t *__restrict__ dkeys, const int32_t *__restrict__ radii, uint32_t *__restrict__ range) {
-    __shared__ uint32_t s_hi[8], s_nlo[8];
-    gs_pdl_sync();
-    uint32_t hi = 0, nlo = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
-        const uint32_t k = dkeys[i];
-        if (radii[i] > 0) {
-            hi = max(hi, k);
-            nlo = max(nlo, ~k);
-        }
-    }
-    hi = __reduce_max_sync(0xffffffffu, hi);
-    nlo = __reduce_max_sync(0xffffffffu, nlo);
-    if ((threadIdx.x & 31) == 0) {
-        s_hi[threadIdx.x >> 5] = hi;
-        s_nlo[threadIdx.x >> 5] = nlo;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int w = 1; w < 8; ++w) {
-            hi = max(hi, s_hi[w]);
-            nlo = max(nlo, s_nlo[w]);
-        }
-        if (nlo) atomicMax(&range[0], nlo);
-        if (hi) atomicMax(&range[1], hi);
-    }
-}
-
 struct FastLayout {
-    size_t keyA, valA, keyB, valB, start, tkey, tval, tkey2, tval2, mat, ctl, range, total;
+    size_t keyA, valA, keyB, valB, start, tkey, tval, tkey2, tval2, mat, ctl, total;
 };
 
 FastLayout fast_layout(int N, int64_t I_cap) {
@@ -532,20 +499,17 @@ FastLayout fast_layout(int N, int64_t I_cap) {
     const size_t m = gsradix::mat_entries(N, 2048), mi = gsradix::mat_entries(I_cap, 2048);
     L.mat = take((m > mi ? m : mi) * 4);
     L.ctl = take(2 * gs_scan_scratch_bytes(N));      // look-back state of scan_emit_kernel (1 024-element tiles)
-    L.range = take(256);                             // directly behind ctl: cleared by the same memset
     L.total = at;
     return L;
 }
 
-// depth sort of gs_bin_fast: 0 (default) = planned passes over the range-reduced keys (radix.cuh MODE 2: as many <= 9-bit
-// passes as the spread of the visible depths needs — three for a typical view); 4 = four passes of 8-bit digits over the
-// raw depth bits (round 1); 3 = 11/11/10-bit digits, measured slower: 191 vs 169 us for the chain at 1 M Gaussians —
-// 80 KB of shared memory per scatter CTA. Initial value from the environment (GS_DEPTH_SORT_PASSES), changed at run
-// time by gs_set_depth_sort_passes (the tests compare all three)
+// number of LSD passes of the depth sort (4 = 8-bit digits, default; 3 = 11/11/10-bit digits, measured slower:
+// 191 vs 169 us for the chain at 1 M Gaussians — 80 KB of shared memory per scatter CTA); initial value from the
+// environment (GS_DEPTH_SORT_PASSES), changed at run time by gs_set_depth_sort_passes (tests compare both)
 int &depth_sort_passes() {
     static int passes = [] {
         const char *e = getenv("GS_DEPTH_SORT_PASSES");
-        return (e && e[0] == '3') ? 3 : (e && e[0] == '0') ? 0 : 4;
+        return (e && e[0] == '3') ? 3 : 4;
     }();
     return passes;
 }
@@ -603,7 +567,7 @@ extern "C" int gs_set_radix_cfg(int which, int cfg) {
 
 extern "C" int gs_set_depth_sort_passes(int passes) {
     const int prev = depth_sort_passes();
-    if (passes == 0 || passes == 3 || passes == 4) depth_sort_passes() = passes;
+    if (passes == 3 || passes == 4) depth_sort_passes() = passes;
     return prev;
 }
 
@@ -614,10 +578,25 @@ extern "C" size_t gs_bin_fast_scratch_bytes(int N, int64_t I_cap, int T) {
 
 // N = elements of ALL views (view v owns [v * n_per_view, (v + 1) * n_per_view)); xy of element g at
 // xy_base + g * xy_stride floats (2 = an (N,2) array, 12 = the packed records); tile_bins has views * T rows.
+// Clears of gs_bin_fast_ex (tile ranges, look-back state) issued AHEAD of the kernels that feed it: gs_view_fwd calls this
+// before its preprocess launches so that no memset node sits between the preprocess kernel and the first radix pass
+// (every kernel of the chain is a programmatic dependent launch; a memset in between breaks the overlap). Returns 1 when
+// the clears were done (pass precleared = true to gs_bin_fast_ex), 0 when the call should do them itself, < 0 on error.
+int gs_bin_fast_clear(int N, int64_t I_cap, int T, int32_t *tile_bins, void *scratch, size_t scratch_bytes, void *stream) {
+    if (N <= 0 || T <= 0 || !tile_bins || !scratch || bin_impl() != 1) return 0;
+    const FastLayout L = fast_layout(N, I_cap);
+    if (scratch_bytes < L.total) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(tile_bins, 0, sizeof(int32_t) * 2 * (size_t)T, st) != cudaSuccess) return -1;
+    if (cudaMemsetAsync(reinterpret_cast<unsigned char *>(scratch) + L.ctl, 0, 2 * gs_scan_scratch_bytes(N), st) != cudaSuccess)
+        return -1;
+    return 1;
+}
+
 int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int xy_stride, const float *depths,
                    const int32_t *radii, const int32_t *tiles_hit, int tiles_x, int tiles_y, int32_t *ids_sorted,
                    int32_t *tile_bins, int32_t *total_dev, void *scratch, size_t scratch_bytes, void *stream,
-                   const uint32_t *depth_range) {
+                   bool precleared) {
     if (N < 0 || I_cap < 0 || tiles_x <= 0 || tiles_y <= 0 || n_per_view <= 0 || (N % n_per_view) != 0) return GS_ERR_BAD_ARG;
     if (!tile_bins || !total_dev || !scratch) return GS_ERR_BAD_ARG;
     if (I_cap >= (1ll << 31)) return GS_ERR_UNSUPPORTED;
@@ -627,7 +606,7 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
     const int tile_bits = T > 1 ? gs_ceil_log2(T) : 1;
     if (tile_bits > 22) return GS_ERR_UNSUPPORTED;
     cudaStream_t st = (cudaStream_t)stream;
-    GS_CUDA(cudaMemsetAsync(tile_bins, 0, sizeof(int32_t) * 2 * (size_t)T, st));
+    if (!precleared) GS_CUDA(cudaMemsetAsync(tile_bins, 0, sizeof(int32_t) * 2 * (size_t)T, st));
     if (N == 0) {
         GS_CUDA(cudaMemsetAsync(total_dev, 0, sizeof(int32_t), st));
         return 0;
@@ -653,27 +632,14 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
 
     // the scan's look-back state is cleared up front so that the kernel chain below is uninterrupted (every launch
     // is a programmatic dependent launch: the next kernel is resident before the previous one drains)
-    GS_CUDA(cudaMemsetAsync(ctl, 0, L.range + 256 - L.ctl, st));
+    if (!precleared) GS_CUDA(cudaMemsetAsync(ctl, 0, 2 * gs_scan_scratch_bytes(N), st));
     // 1. depth sort (values start as the element index; the first pass forms its keys from depths/radii on the fly,
     //    so there is no key-building kernel). Default: four passes of 8-bit digits; gs_set_depth_sort_passes(3) /
     //    GS_DEPTH_SORT_PASSES=3 selects three passes of 11/11/10-bit digits (fewer launches, but measured slower).
     //    Any split of the 32 bits into stable LSD passes yields the same order.
     const uint32_t *dkeys = reinterpret_cast<const uint32_t *>(depths);
     const uint32_t *order;
-    if (depth_sort_passes() == 0) {
-        // range of the visible depth keys: from the caller (the fused preprocess reduces it on the side), else one
-        // small reduction kernel
-        const uint32_t *range = depth_range;
-        if (!range) {
-            uint32_t *r = reinterpret_cast<uint32_t *>(p + L.range);
-            const int rb = N < 256 * 1184 ? (N + 255) / 256 : 1184;         // 8 CTAs per SM at most
-            GS_PDL_LAUNCH(depth_range_kernel, rb, 256, 0, st, N, dkeys, radii, r);
-            range = r;
-        }
-        if ((rc = gsradix::launch_depth_sort_planned(N, dkeys, radii, range, keyA, valA, keyB, valB, mat, st, radix_cfg(0, N))))
-            return rc;
-        order = valA;
-    } else if (depth_sort_passes() == 4) {
+    if (depth_sort_passes() == 4) {
         const int cd = radix_cfg(0, N);
         if ((rc = gsradix::launch_pass_cfg<uint32_t, 8, 1>(cd, N, nullptr, dkeys, nullptr, keyB, valB, 0, 8, mat, st, nullptr, 0,
                                                           radii))) return rc;
@@ -744,7 +710,7 @@ extern "C" int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *
                            int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
                            void *scratch, size_t scratch_bytes, void *stream) {
     return gs_bin_fast_ex(N, N > 0 ? N : 1, I_cap, xys, 2, depths, radii, tiles_hit, tiles_x, tiles_y, ids_sorted, tile_bins,
-                          total_dev, scratch, scratch_bytes, stream, nullptr);
+                          total_dev, scratch, scratch_bytes, stream, false);
 }
 
 // ==========================================================================================

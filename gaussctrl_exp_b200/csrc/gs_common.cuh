@@ -111,12 +111,13 @@ int gs_bin_bucket_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int
 int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int xy_stride, const float *depths,
                    const int32_t *radii, const int32_t *tiles_hit, int tiles_x, int tiles_y, int32_t *ids_sorted,
                    int32_t *tile_bins, int32_t *total_dev, void *scratch, size_t scratch_bytes, void *stream,
-                   const uint32_t *depth_range);      // 2 device words (radix.cuh: plan_resolve) or nullptr
+                   bool precleared);
+int gs_bin_fast_clear(int N, int64_t I_cap, int T, int32_t *tile_bins, void *scratch, size_t scratch_bytes, void *stream);
 // preprocess_fwd.cu / preprocess_bwd.cu: packed-record forms used by view.cu
 int gs_launch_preprocess_fwd_packed(int N, const float *means, const float *log_scales, const float *quats,
                                     const float *opac_logits, const float *feat_dc, const float *feat_rest, int use_sh,
                                     int sh_deg, const GsCamera *cam_host, const int32_t *subset, float *rec, float *depths,
-                                    int32_t *radii, int32_t *tiles_hit, uint32_t *depth_range, cudaStream_t st);
+                                    int32_t *radii, int32_t *tiles_hit, cudaStream_t st);
 int gs_launch_preprocess_bwd(int N, const float *means, const float *log_scales, const float *quats,
                              const float *opac_logits, int use_sh, int sh_deg, const GsCamera *cam_host,
                              const int32_t *radii, const float *rgbs, int rgb_stride, const float *v_xys,

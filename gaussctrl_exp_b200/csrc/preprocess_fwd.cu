@@ -39,7 +39,7 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
                       const __grid_constant__ GsCamera cam, float2 *__restrict__ xys, float *__restrict__ depths,
                       int32_t *__restrict__ radii, float *__restrict__ conics, int32_t *__restrict__ tiles_hit,
                       float *__restrict__ rgbs, float *__restrict__ opac, const int32_t *__restrict__ subset,
-                      float4 *__restrict__ rec, uint32_t *__restrict__ depth_range) {
+                      float4 *__restrict__ rec) {
     gs_pdl_sync();   // lets the first binning kernel become resident while this one drains
     __shared__ __align__(128) float rest_s[PP_TPB * PP_REST];
     __shared__ __align__(8) unsigned long long mbar;
@@ -151,34 +151,10 @@ preprocess_fwd_kernel(int N, const float *__restrict__ means, const float *__res
     // PACKED: the CTA's 128 records are one dense 6 144-byte span; they are assembled in shared memory (the SH stage,
     // free once every thread has consumed its row) and leave with fully coalesced 16-byte stores
     float4 q0 = make_float4(0.f, 0.f, -1.f, -1.f), q1 = make_float4(0.f, 0.f, 0.f, 0.f), q2 = q1;   // culled: zero row
-    const bool visible = i < N && o.radius > 0;
-    if (visible) gs_make_record(o.xy.x, o.xy.y, o.ca, o.cb, o.cc, op, r, g, b, o.depth, q0, q1, q2);
-    // spread of the visible depth keys, for the binning's depth sort (radix.cuh: plan_resolve): max of the key and of
-    // its complement per warp (one redux.sync each), per CTA through shared memory, then at most two atomics per CTA —
-    // and only when the CTA would move the running extremes (they settle after the first few CTAs)
-    __shared__ uint32_t s_hi[PP_TPB / 32], s_nlo[PP_TPB / 32];
-    if (depth_range) {
-        const uint32_t kb = __float_as_uint(o.depth);
-        const uint32_t hi = __reduce_max_sync(0xffffffffu, visible ? kb : 0u);
-        const uint32_t nlo = __reduce_max_sync(0xffffffffu, visible ? ~kb : 0u);
-        if ((tid & 31) == 0) {
-            s_hi[tid >> 5] = hi;
-            s_nlo[tid >> 5] = nlo;
-        }
-    }
+    if (i < N && o.radius > 0) gs_make_record(o.xy.x, o.xy.y, o.ca, o.cb, o.cc, op, r, g, b, o.depth, q0, q1, q2);
     __syncthreads();
     float4 *rs = reinterpret_cast<float4 *>(rest_s);
     rs[3 * tid] = q0; rs[3 * tid + 1] = q1; rs[3 * tid + 2] = q2;
-    if (depth_range && tid == 0) {
-        uint32_t hi = s_hi[0], nlo = s_nlo[0];
-#pragma unroll
-        for (int w = 1; w < PP_TPB / 32; ++w) {
-            hi = max(hi, s_hi[w]);
-            nlo = max(nlo, s_nlo[w]);
-        }
-        if (nlo > *reinterpret_cast<volatile uint32_t *>(depth_range)) atomicMax(depth_range, nlo);
-        if (hi > *reinterpret_cast<volatile uint32_t *>(depth_range + 1)) atomicMax(depth_range + 1, hi);
-    }
     __syncthreads();
     for (int f = tid; f < 3 * rows; f += PP_TPB) rec[3 * (size_t)g0 + f] = rs[f];
 }
@@ -194,7 +170,7 @@ static int launch_preprocess_fwd(int part, int N, const float *means, const floa
 #define GS_PP_ARGS                                                                                                       \
     N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, feat_dc, feat_rest, use_sh, sh_deg,       \
         *cam_host, reinterpret_cast<float2 *>(xys), depths, radii, conics, tiles_hit, rgbs, opac,                        \
-        (const int32_t *)nullptr, (float4 *)nullptr, (uint32_t *)nullptr
+        (const int32_t *)nullptr, (float4 *)nullptr
     if (part == 0) preprocess_fwd_kernel<0, false><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
     else if (part == 1) preprocess_fwd_kernel<1, false><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
     else preprocess_fwd_kernel<2, false><<<blocks, PP_TPB, 0, st>>>(GS_PP_ARGS);
@@ -207,13 +183,13 @@ static int launch_preprocess_fwd(int part, int N, const float *means, const floa
 int gs_launch_preprocess_fwd_packed(int N, const float *means, const float *log_scales, const float *quats,
                                     const float *opac_logits, const float *feat_dc, const float *feat_rest, int use_sh,
                                     int sh_deg, const GsCamera *cam_host, const int32_t *subset, float *rec, float *depths,
-                                    int32_t *radii, int32_t *tiles_hit, uint32_t *depth_range, cudaStream_t st) {
+                                    int32_t *radii, int32_t *tiles_hit, cudaStream_t st) {
     if (N <= 0) return 0;
     const int blocks = (N + PP_TPB - 1) / PP_TPB;
     preprocess_fwd_kernel<0, true><<<blocks, PP_TPB, 0, st>>>(
         N, means, log_scales, reinterpret_cast<const float4 *>(quats), opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
         *cam_host, (float2 *)nullptr, depths, radii, (float *)nullptr, tiles_hit, (float *)nullptr, (float *)nullptr,
-        subset, reinterpret_cast<float4 *>(rec), depth_range);
+        subset, reinterpret_cast<float4 *>(rec));
     GS_LAUNCH_CHECK();
     return 0;
 }
@@ -272,5 +248,5 @@ extern "C" int gs_preprocess_fwd_packed(int N, const float *means, const float *
     if (use_sh && sh_deg >= 1 && !feat_rest) return GS_ERR_BAD_ARG;
     if (!gs_aligned16(quats) || !gs_aligned16(feat_rest) || !gs_aligned16(rec)) return GS_ERR_MISALIGNED;
     return gs_launch_preprocess_fwd_packed(N, means, log_scales, quats, opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
-                                           cam_host, subset, rec, depths, radii, tiles_hit, nullptr, (cudaStream_t)stream);
+                                           cam_host, subset, rec, depths, radii, tiles_hit, (cudaStream_t)stream);
 }

@@ -5,11 +5,6 @@
 //               stable), stages it in shared memory in digit order and writes coalesced runs at
 //               digit_base + mat[digit][b] + local rank
 // MODE 1 passes read their keys straight from (depths, radii): key = bits(depth), culled -> 0xFFFFFFFF.
-// MODE 2 passes ("planned" depth sort) take digit position and width from a DEVICE-side plan: the keys are the depth
-// bits of the visible elements minus their minimum (culled -> range + 1), so only R = bitlen(max - min + 1) bits are
-// live — 25 for a typical view, i.e. THREE passes of <= 9 bits instead of four of 8. Four passes are always launched;
-// the ones the plan does not need (at the FRONT of the chain, so that the result always lands in the same buffer)
-// return at once, and the first active pass forms its keys from (depths, radii).
 //
 // Design for B200: at the sizes of this path (N ~ 1 M Gaussians, I ~ 3 M intersections) the whole
 // working set sits in the 126 MB L2, so a pass is bound by latency and launch count, not HBM.
@@ -45,39 +40,6 @@ __device__ __forceinline__ int64_t resolve_n(int64_t n_cap, const int32_t *n_dev
     return v > n_cap ? -1 : v;
 }
 
-// Planned depth sort (MODE 2). range[0] = max over the visible elements of ~bits(depth), range[1] = max of bits(depth)
-// (both start at 0, so one memset initialises them; view-space depths are positive floats: their bit patterns order
-// like the values). q = position of the launch in the chain of PLAN_LAUNCHES passes.
-constexpr int PLAN_LAUNCHES = 4;
-constexpr int PLAN_BITS = 9;       // widest digit of a planned pass
-struct PlanArg {
-    const uint32_t *range;
-    const uint32_t *dkeys;         // bits(depth) per element (what the first active pass reads instead of kin)
-    int q;
-};
-struct PlanPass {
-    uint32_t kmin, kcull;          // key = bits(depth) - kmin for a visible element, kcull for a culled one
-    int shift, bits;
-    bool first;                    // first active pass: keys from (dkeys, radii), values = element index
-};
-// false: launch q is not needed for this range (it sits in front of the first active pass)
-__host__ __device__ inline bool plan_resolve(uint32_t r0, uint32_t r1, int q, PlanPass &pp) {
-    uint32_t lo = ~r0, hi = r1;
-    if (hi < lo) lo = hi = 0;                      // nothing visible: every key is kcull = 1
-    pp.kmin = lo;
-    pp.kcull = hi - lo + 1u;                       // < 2^31: visible keys are bit patterns of positive floats
-    int R = 0;
-    while (R < 32 && (pp.kcull >> R)) ++R;         // live bits, >= 1
-    const int P = R <= PLAN_BITS ? 1 : R <= 2 * PLAN_BITS ? 2 : R <= 3 * PLAN_BITS ? 3 : 4;
-    const int a = q - (PLAN_LAUNCHES - P);
-    if (a < 0) return false;
-    const int base = R / P, rem = R % P;           // the first `rem` active passes take one bit more
-    pp.bits = base + (a < rem ? 1 : 0);
-    pp.shift = a * base + (a < rem ? a : rem);
-    pp.first = a == 0;
-    return true;
-}
-
 // key of element `at`: the key array, or (MODE 1) the depth bits of a visible Gaussian / 0xFFFFFFFF for a
 // culled one (sorts behind every visible Gaussian), so that no separate key-building kernel is needed
 template <typename KeyT, int MODE>
@@ -89,14 +51,6 @@ __device__ __forceinline__ KeyT load_key(const KeyT *__restrict__ kin, const int
     }
     return k;
 }
-__device__ __forceinline__ uint32_t load_key_planned(const PlanArg &pa, const PlanPass &pp, const uint32_t *__restrict__ kin,
-                                                     const int32_t *__restrict__ radii, int64_t at) {
-    if (!pp.first) return kin[at];
-    const uint32_t k = pa.dkeys[at];
-    const int32_t r = radii[at];
-    return r > 0 ? k - pp.kmin : pp.kcull;
-}
-
 // block-wide exclusive scan of one value per thread (TPB threads). tmp: >= 64 uint32.
 template <int WARPS>
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, uint32_t *total) {
@@ -130,7 +84,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, u
 template <typename KeyT, int BITS, int MODE, class C>
 __global__ void __launch_bounds__(C::TPB)
 hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
-            const int32_t *__restrict__ radii, int shift, int bits, uint32_t *__restrict__ mat, int pitch, PlanArg pa) {
+            const int32_t *__restrict__ radii, int shift, int bits, uint32_t *__restrict__ mat, int pitch) {
     constexpr int RADIX = 1 << BITS;
     constexpr int TPB = C::TPB, IPT = C::IPT, SUB = C::SUB;
     __shared__ uint32_t hist[RADIX];
@@ -138,12 +92,6 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
     const int64_t n = resolve_n(n_cap, n_dev);
     const int64_t base = (int64_t)blockIdx.x * SUB;
     if (n < 0 || base >= n) return;
-    PlanPass pp = {};
-    if (MODE == 2) {
-        if (!plan_resolve(pa.range[0], pa.range[1], pa.q, pp)) return;
-        shift = pp.shift;
-        bits = pp.bits;
-    }
     const uint32_t mask = (1u << bits) - 1u;
     for (int d = threadIdx.x; d < RADIX; d += TPB) hist[d] = 0;
     __syncthreads();
@@ -151,8 +99,7 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
         const int64_t at = base + i * TPB + threadIdx.x;
-        if (MODE == 2) key[i] = at < n ? (KeyT)load_key_planned(pa, pp, (const uint32_t *)kin, radii, at) : (KeyT)0;
-        else key[i] = at < n ? load_key<KeyT, MODE>(kin, radii, at) : (KeyT)0;
+        key[i] = at < n ? load_key<KeyT, MODE>(kin, radii, at) : (KeyT)0;
     }
 #pragma unroll
     for (int i = 0; i < IPT; ++i)
@@ -165,15 +112,11 @@ hist_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__rest
 template <int BITS, int MODE, int SUB>
 __global__ void __launch_bounds__(256)
 colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat, int pitch,
-               uint32_t *__restrict__ totals, PlanArg pa) {
+               uint32_t *__restrict__ totals) {
     constexpr int RADIX = 1 << BITS;
     gs_pdl_sync();
     const int64_t n = resolve_n(n_cap, n_dev);
     if (n < 0) return;
-    if (MODE == 2) {
-        PlanPass pp;
-        if (!plan_resolve(pa.range[0], pa.range[1], pa.q, pp)) return;
-    }
     const int nb = (int)((n + SUB - 1) / SUB);
     const int lane = threadIdx.x & 31;
     const int d = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -225,7 +168,7 @@ __global__ void __launch_bounds__(C::TPB)
 scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__restrict__ kin,
                const int32_t *__restrict__ radii, const uint32_t *__restrict__ vin, KeyT *__restrict__ kout,
                uint32_t *__restrict__ vout, int shift, int bits, const uint32_t *__restrict__ mat, int pitch,
-               const uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T, PlanArg pa) {
+               const uint32_t *__restrict__ totals, int32_t *__restrict__ bins_out, int bins_T) {
     constexpr int RADIX = 1 << BITS;
     constexpr int TPB = C::TPB, IPT = C::IPT, SUB = C::SUB, WARPS = C::WARPS;
     constexpr int DPT = (RADIX + TPB - 1) / TPB;  // digits per thread (contiguous)
@@ -235,13 +178,6 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
     const int64_t n = resolve_n(n_cap, n_dev);
     const int64_t base = (int64_t)blockIdx.x * SUB;
     if (n < 0 || base >= n) return;
-    PlanPass pp = {};
-    if (MODE == 2) {
-        if (!plan_resolve(pa.range[0], pa.range[1], pa.q, pp)) return;
-        shift = pp.shift;
-        bits = pp.bits;
-        if (pp.first) vin = nullptr;             // values start as the element index
-    }
     const int valid = (int)min((int64_t)SUB, n - base);
     const uint32_t mask = (1u << bits) - 1u;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -254,8 +190,7 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
 #pragma unroll
     for (int i = 0; i < IPT; ++i) {
         const int li = woff + i * 32 + lane;
-        if (MODE == 2) key[i] = li < valid ? (KeyT)load_key_planned(pa, pp, (const uint32_t *)kin, radii, base + li) : (KeyT) ~(KeyT)0;
-        else key[i] = li < valid ? load_key<KeyT, MODE>(kin, radii, base + li) : (KeyT) ~(KeyT)0;
+        key[i] = li < valid ? load_key<KeyT, MODE>(kin, radii, base + li) : (KeyT) ~(KeyT)0;
         val[i] = li < valid ? (vin ? vin[base + li] : (uint32_t)(base + li)) : 0u;
     }
     // global cursors of this CTA: digit base (exclusive scan of the digit totals) + keys of the same digit in the
@@ -375,11 +310,10 @@ scatter_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, const KeyT *__r
 template <typename KeyT, int BITS, int MODE = 0, class C = CfgDefault>
 inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, const uint32_t *vin, KeyT *kout,
                        uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st,
-                       int32_t *bins_out = nullptr, int bins_T = 0, const int32_t *radii = nullptr,
-                       PlanArg pa = PlanArg{nullptr, nullptr, 0}) {
+                       int32_t *bins_out = nullptr, int bins_T = 0, const int32_t *radii = nullptr) {
     constexpr int RADIX = 1 << BITS;
     if (n_cap <= 0) return 0;
-    if (bits > BITS || (MODE != 0 && !radii) || (MODE == 2 && (!pa.range || !pa.dkeys))) return GS_ERR_BAD_ARG;
+    if (bits > BITS || (MODE != 0 && !radii)) return GS_ERR_BAD_ARG;
     constexpr int TPB = C::TPB, SUB = C::SUB;
     const int nb = (int)((n_cap + SUB - 1) / SUB);
     uint32_t *totals = mat + (size_t)nb * RADIX;
@@ -391,10 +325,10 @@ inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, con
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
     }
-    GS_PDL_LAUNCH((hist_kernel<KeyT, BITS, MODE, C>), nb, TPB, 0, st, n_cap, n_dev, kin, radii, shift, bits, mat, nb, pa);
-    GS_PDL_LAUNCH((colscan_kernel<BITS, MODE, SUB>), (RADIX + 7) / 8, 256, 0, st, n_cap, n_dev, mat, nb, totals, pa);
+    GS_PDL_LAUNCH((hist_kernel<KeyT, BITS, MODE, C>), nb, TPB, 0, st, n_cap, n_dev, kin, radii, shift, bits, mat, nb);
+    GS_PDL_LAUNCH((colscan_kernel<BITS, MODE, SUB>), (RADIX + 7) / 8, 256, 0, st, n_cap, n_dev, mat, nb, totals);
     GS_PDL_LAUNCH((scatter_kernel<KeyT, BITS, MODE, C>), nb, TPB, smem, st, n_cap, n_dev, kin, radii, vin, kout, vout,
-                  shift, bits, (const uint32_t *)mat, nb, (const uint32_t *)totals, bins_out, bins_T, pa);
+                  shift, bits, (const uint32_t *)mat, nb, (const uint32_t *)totals, bins_out, bins_T);
     return 0;
 }
 
@@ -406,9 +340,9 @@ inline size_t mat_entries(int64_t n_cap, int radix) {
 template <typename KeyT, int BITS, int MODE = 0>
 inline int launch_pass_cfg(int cfg, int64_t n_cap, const int32_t *n_dev, const KeyT *kin, const uint32_t *vin, KeyT *kout,
                            uint32_t *vout, int shift, int bits, uint32_t *mat, cudaStream_t st, int32_t *bins_out = nullptr,
-                           int bins_T = 0, const int32_t *radii = nullptr, PlanArg pa = PlanArg{nullptr, nullptr, 0}) {
+                           int bins_T = 0, const int32_t *radii = nullptr) {
 #define GS_RADIX_GO(CFG) \
-    return launch_pass<KeyT, BITS, MODE, CFG>(n_cap, n_dev, kin, vin, kout, vout, shift, bits, mat, st, bins_out, bins_T, radii, pa)
+    return launch_pass<KeyT, BITS, MODE, CFG>(n_cap, n_dev, kin, vin, kout, vout, shift, bits, mat, st, bins_out, bins_T, radii)
     switch (cfg) {
         case 1: GS_RADIX_GO(Cfg512x8);
         case 2: GS_RADIX_GO(Cfg384x8);
@@ -416,24 +350,6 @@ inline int launch_pass_cfg(int cfg, int64_t n_cap, const int32_t *n_dev, const K
         default: GS_RADIX_GO(CfgDefault);
     }
 #undef GS_RADIX_GO
-}
-
-// The planned depth sort: PLAN_LAUNCHES passes over N elements; result (element indices in depth order, culled ones
-// last, ties in index order) in valA whatever the number of active passes. keyA/valA/keyB/valB: N words each.
-inline int launch_depth_sort_planned(int64_t N, const uint32_t *dkeys, const int32_t *radii, const uint32_t *range,
-                                     uint32_t *keyA, uint32_t *valA, uint32_t *keyB, uint32_t *valB, uint32_t *mat,
-                                     cudaStream_t st, int cfg = 0) {
-    int rc;
-    for (int q = 0; q < PLAN_LAUNCHES; ++q) {
-        const bool to_a = ((PLAN_LAUNCHES - 1 - q) & 1) == 0;          // the last launch writes A
-        const uint32_t *kin = to_a ? keyB : keyA, *vin = to_a ? valB : valA;
-        uint32_t *kout = q == PLAN_LAUNCHES - 1 ? nullptr : (to_a ? keyA : keyB);   // nobody reads the last pass's keys
-        uint32_t *vout = to_a ? valA : valB;
-        if ((rc = launch_pass_cfg<uint32_t, PLAN_BITS, 2>(cfg, N, nullptr, kin, vin, kout, vout, 0, PLAN_BITS, mat, st, nullptr, 0,
-                                                          radii, PlanArg{range, dkeys, q})))
-            return rc;
-    }
-    return 0;
 }
 
 }  // namespace gsradix

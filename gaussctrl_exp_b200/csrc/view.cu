@@ -79,19 +79,18 @@ extern "C" int gs_view_fwd(int n, int views, const float *means, const float *lo
     int32_t *order_fwd = reinterpret_cast<int32_t *>(p + L.order_fwd);
     int32_t *total = reinterpret_cast<int32_t *>(p + L.total);
 
-    // words 1, 2 of the `total` slot: spread of the visible depth keys over all views of the call, reduced by the
-    // preprocess kernels on the side (atomicMax from zero) and read by the binning's depth sort
-    uint32_t *depth_range = reinterpret_cast<uint32_t *>(total) + 1;
-    GS_CUDA(cudaMemsetAsync(total, 0, 16, st));
+    // the binning's clears go first: no memset node between the preprocess kernel and the first radix pass
+    const int cleared = gs_bin_fast_clear(n * views, I_cap, T_view * views, bins, scratch, scratch_bytes, stream);
+    if (cleared < 0) return (int)cudaGetLastError();
     for (int v = 0; v < views; ++v) {
         const size_t o = (size_t)v * n;
         rc = gs_launch_preprocess_fwd_packed(n, means, log_scales, quats, opac_logits, feat_dc, feat_rest, use_sh, sh_deg,
                                              cams_host + v, subset, rec + o * GS_REC_FLOATS, depths + o, radii + o,
-                                             hit + o, depth_range, st);
+                                             hit + o, st);
         if (rc) return rc;
     }
     rc = gs_bin_fast_ex(n * views, n, I_cap, rec, GS_REC_FLOATS, depths, radii, hit, c0.tiles_x, c0.tiles_y, ids_sorted,
-                        bins, total, scratch, scratch_bytes, stream, depth_range);
+                        bins, total, scratch, scratch_bytes, stream, cleared == 1);
     if (rc) return rc;
     if (total_host) GS_CUDA(cudaMemcpyAsync(total_host, total, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     // recorded BEFORE the compositing is enqueued: a host that waits on it waits for the binning only

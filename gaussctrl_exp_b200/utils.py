@@ -134,13 +134,12 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
         with torch.cuda.device(dev):
-            # gs_bin_fast. "lsd" (default): global depth sort (planned passes over the range-reduced depth keys) +
-            # scan/emission + stable partition by tile; "lsd4" / "lsd3": the same with four 8-bit / three 11/11/10-bit
-            # depth passes over the raw depth bits; "bucket": per-tile segments filled unordered, then sorted per tile
-            # in shared memory — identical output
-            if impl not in ("bucket", "lsd", "lsd3", "lsd4"):
+            # gs_bin_fast. "lsd" (default): global depth sort + scan/emission + stable partition by tile; "lsd3": the
+            # same with three 11/11/10-bit depth passes; "bucket": per-tile segments filled unordered, then sorted per
+            # tile in shared memory — identical output
+            if impl not in ("bucket", "lsd", "lsd3"):
                 raise ValueError(f"unknown binning implementation {impl!r}")
-            prev = L.gs_set_depth_sort_passes({"lsd3": 3, "lsd4": 4}.get(impl, 0)) if impl != "bucket" else None
+            prev = L.gs_set_depth_sort_passes(3 if impl == "lsd3" else 4) if impl != "bucket" else None
             prev_legacy = L.gs_set_bin_impl(0 if impl == "bucket" else 1)
             try:
                 scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")

@@ -92,12 +92,36 @@ def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
     assert np.array_equal(vs.cpu().numpy(), b.ids_sorted)
     assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
     # product paths: identical ids_sorted and tile ranges without 64-bit keys
-    for impl in ("bucket", "lsd", "lsd3", "lsd4"):
+    for impl in ("bucket", "lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         assert I2 == b.I, impl
         assert np.array_equal(ids2[:I2].cpu().numpy(), b.ids_sorted), impl
         assert np.array_equal(bins2.cpu().numpy(), b.tile_bins), impl
         assert bins2.shape == (T, 2)
+
+
+@pytest.mark.parametrize("N,W,H,s0", [(70000, 512, 512, 0.004), (9000, 1920, 1080, 0.05), (300, 64, 48, 0.1)])
+def test_radix_cta_shapes_identical(oracle, cuda_dev, N, W, H, s0):
+    """gs_set_radix_cfg: every CTA shape of the radix passes (depth sort x partition) gives the oracle's lists."""
+    from gaussctrl_exp_b200 import _lib, utils as U
+    d = projected(oracle, N=N, W=W, H=H, seed=11, s0=s0)
+    tb = d["tb"]
+    b = oracle.bin_and_sort(d["xys"], d["depths"], d["radii"], d["hit"], tb)
+    t = [_t(d[k], cuda_dev) for k in ("xys", "depths", "radii", "hit")]
+    L = _lib.lib()
+    try:
+        for cd in range(4):
+            for cp in range(4):
+                L.gs_set_radix_cfg(0, cd)
+                L.gs_set_radix_cfg(1, cp)
+                ids, bins, I = U.bin_fast(*t, tb, impl="lsd")
+                assert I == b.I, (cd, cp)
+                assert np.array_equal(ids[:I].cpu().numpy(), b.ids_sorted), (cd, cp)
+                assert np.array_equal(bins.cpu().numpy(), b.tile_bins), (cd, cp)
+    finally:
+        L.gs_set_radix_cfg(0, -1)
+        L.gs_set_radix_cfg(1, -1)
+    assert L.gs_set_radix_cfg(0, 99) == -1 and L.gs_set_radix_cfg(2, 0) != 0      # query only / bad selector
 
 
 def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
@@ -116,7 +140,7 @@ def test_binning_big_tiles_and_depth_ties(oracle, cuda_dev):
     b = oracle.bin_and_sort(xys, depths, radii, hit, tb)
     assert b.I == int(hit.sum()) and (b.tile_bins[:, 1] - b.tile_bins[:, 0]).max() > 50000
     t = [_t(a, cuda_dev) for a in (xys, depths, radii, hit)]
-    for impl in ("bucket", "lsd", "lsd3", "lsd4"):
+    for impl in ("bucket", "lsd", "lsd3"):
         ids2, bins2, I2 = U.bin_fast(*t, tb, impl=impl)
         assert I2 == b.I
         assert np.array_equal(bins2.cpu().numpy(), b.tile_bins), impl
@@ -178,7 +202,7 @@ def test_depth_sort_corner_cases(oracle, cuda_dev, case):
     ids, bins, I = U.bin_fast(*t, tb, impl="lsd")
     assert I == int(hit.sum())
     if case == "peaky_1m":
-        for impl in ("lsd3", "lsd4", "bucket"):
+        for impl in ("lsd3", "bucket"):
             ids4, bins4, I4 = U.bin_fast(*t, tb, impl=impl)
             assert I4 == I and torch.equal(bins, bins4) and torch.equal(ids[:I], ids4[:I]), impl
     else:
@@ -186,7 +210,7 @@ def test_depth_sort_corner_cases(oracle, cuda_dev, case):
         assert b.I == I
         assert np.array_equal(bins.cpu().numpy(), b.tile_bins)
         assert np.array_equal(ids[:I].cpu().numpy(), b.ids_sorted)
-        for impl in ("lsd3", "lsd4", "bucket"):
+        for impl in ("lsd3", "bucket"):
             ids4, bins4, I4 = U.bin_fast(*t, tb, impl=impl)
             assert I4 == I and torch.equal(bins, bins4) and torch.equal(ids[:I], ids4[:I]), impl
 

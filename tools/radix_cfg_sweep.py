@@ -25,14 +25,13 @@ for n, intr in ((200_000, None), (500_000, None), (1_000_000, None), (2_000_000,
             p["means"], p["scales"].exp(), 1, p["quats"] / p["quats"].norm(dim=-1, keepdim=True), V[:3].to(dev),
             (P @ V).to(dev), cam.fx, cam.fy, cam.cx, cam.cy, cam.H, cam.W, tb)
     T = tb[0] * tb[1]
-    ids0, bins0, I = U.bin_fast(xys, depths, radii, hit, tb, impl="lsd4")
+    ids0, bins0, I = U.bin_fast(xys, depths, radii, hit, tb, impl="lsd")
     ids0 = ids0[:I].clone()
     cap = I + 1024
     out = torch.empty(cap, device=dev, dtype=torch.int32)
     bins = torch.empty_like(bins0)
     total = torch.empty(1, device=dev, dtype=torch.int32)
     scratch = torch.empty(L.gs_bin_fast_scratch_bytes(n, cap, T), device=dev, dtype=torch.uint8)
-    L.gs_set_depth_sort_passes(4)
 
     def call():
         rc = L.gs_bin_fast(n, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tb[0], tb[1],
