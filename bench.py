@@ -596,15 +596,18 @@ def run_ours(args):
         slot = i % 2
         prefetch_target(i)                                  # no-op except on the very first step
         cur = torch.cuda.current_stream(dev)
-        cur.wait_event(tgt_ready[slot])
         tgt = tgt_dev[slot]
         prefetch_target(i + 1)                              # H2D of the NEXT step's target overlaps this step
         for p in params:
             p.grad = None
         out = model(cam)
+        # the step waits for ITS target where it first needs it — at the loss, not in front of the render (a wait node
+        # ahead of the preprocess kernel cost 23 us per step: tools/e2e_anatomy.py) — and hands the buffer back as soon
+        # as the subtraction has read it
+        cur.wait_event(tgt_ready[slot])
         loss = (out["rgb"] - tgt).abs().mean()
-        loss.backward()
         tgt_free[slot].record(cur)
+        loss.backward()
         reduce_grads()
         # D2H of the step's result: async copy into pinned memory, consumed one step later so the host
         # never idles the GPU (every step's loss is still read inside the timed region; see drain_losses)
