@@ -65,12 +65,11 @@ class _ProjectGaussians(Function):
         P = _f32c(projmat.to(dev)).reshape(-1)
         H, W = int(img_height), int(img_width)
         tx, ty = int(tile_bounds[0]), int(tile_bounds[1])
-        cov3d = torch.empty((N, 6), device=dev, dtype=torch.float32)
-        xys = torch.empty((N, 2), device=dev, dtype=torch.float32)
-        depths = torch.empty((N,), device=dev, dtype=torch.float32)
-        radii = torch.empty((N,), device=dev, dtype=torch.int32)
-        conics = torch.empty((N, 3), device=dev, dtype=torch.float32)
-        hit = torch.empty((N,), device=dev, dtype=torch.int32)
+        # one allocation for the six outputs (12 float + 2 int32 words per Gaussian), carved into the operator's shapes
+        buf = torch.empty((14 * N,), device=dev, dtype=torch.float32)
+        xys, cov3d, conics = buf[0:2 * N].view(N, 2), buf[2 * N:8 * N].view(N, 6), buf[8 * N:11 * N].view(N, 3)   # xys: 8 B aligned
+        depths = buf[11 * N:12 * N]
+        radii, hit = buf[12 * N:13 * N].view(torch.int32), buf[13 * N:].view(torch.int32)
         with torch.cuda.device(dev):
             rc = _lib.lib().gs_project_fwd(
                 N, _lib.ptr(means3d), _lib.ptr(scales), float(glob_scale), _lib.ptr(quats), _lib.ptr(V),
@@ -92,9 +91,8 @@ class _ProjectGaussians(Function):
         v_xys = torch.zeros((N, 2), device=dev) if v_xys is None else _f32c(v_xys)
         v_depths = torch.zeros((N,), device=dev) if v_depths is None else _f32c(v_depths)
         v_conics = torch.zeros((N, 3), device=dev) if v_conics is None else _f32c(v_conics)
-        v_means = torch.empty_like(means3d)
-        v_scales = torch.empty_like(scales)
-        v_quats = torch.empty_like(quats)
+        g = torch.empty((10 * N,), device=dev, dtype=torch.float32)          # one allocation for the three gradients
+        v_quats, v_means, v_scales = g[0:4 * N].view(N, 4), g[4 * N:7 * N].view(N, 3), g[7 * N:].view(N, 3)   # quats: 16 B aligned
         with torch.cuda.device(dev):
             rc = _lib.lib().gs_project_bwd(
                 N, _lib.ptr(means3d), _lib.ptr(scales), glob, _lib.ptr(quats), _lib.ptr(V), _lib.ptr(P),

@@ -24,21 +24,36 @@ _bin_cache = {}
 
 
 def _binning(xys, depths, radii, num_tiles_hit, H, W):
+    """-> ((ids_sorted, tile_bins, count | PendingCount), tile_bounds, cache slot | None). A PendingCount means the
+    count has not been read yet: the caller enqueues the compositing first and confirms the capacity afterwards
+    (`_confirm`), so the host never idles the device between binning and compositing."""
     if xys.dtype != torch.float32 or not xys.is_contiguous():
         xys = xys.float().contiguous()
     tile_bounds = ((W + 15) // 16, (H + 15) // 16, 1)
-    sig = None
+    slot = None
     if BINNING_CACHE:
         sig = (xys._version, depths._version, radii._version, H, W)
         hit = _bin_cache.get(xys.device.index)
         # weak references: the cache keeps neither the caller's tensors nor their autograd graph alive, and a
         # recycled allocation (same address, new tensor) can never hit
         if hit is not None and hit[0]() is xys and hit[1]() is depths and hit[2]() is radii and hit[3] == sig:
-            return hit[4], tile_bounds
-    res = bin_fast(xys, depths, radii, num_tiles_hit, tile_bounds)
-    if BINNING_CACHE:
-        _bin_cache[xys.device.index] = (weakref.ref(xys), weakref.ref(depths), weakref.ref(radii), sig, res)
-    return res, tile_bounds
+            return hit[4], tile_bounds, None
+        slot = (weakref.ref(xys), weakref.ref(depths), weakref.ref(radii), sig)
+    res = bin_fast(xys, depths, radii, num_tiles_hit, tile_bounds, defer=True)
+    return res, tile_bounds, slot
+
+
+def _confirm(res, slot, dev_index) -> bool:
+    """Waits for a deferred count; True if the lists fitted their capacity (then they may be cached)."""
+    ids_sorted, tile_bins, cnt = res
+    if not isinstance(cnt, int):
+        I, ok = cnt.wait()
+        if not ok:
+            return False
+        res = (ids_sorted, tile_bins, I)
+    if slot is not None:
+        _bin_cache[dev_index] = slot + (res,)
+    return True
 
 
 def clear_binning_cache():
@@ -82,10 +97,16 @@ def rasterize_gaussians(
         if return_alpha:
             return out_img, torch.zeros((H, W), device=xys.device, dtype=torch.float32) + zero
         return out_img
-    with torch.no_grad():
-        (ids_sorted, tile_bins, num_intersects), tb = _binning(xys, depths, radii, num_tiles_hit, H, W)
-    return _RasterizeGaussians.apply(xys, conics, colors, opacity, background, ids_sorted, tile_bins,
-                                     H, W, tb, return_alpha)
+    while True:
+        with torch.no_grad():
+            res, tb, slot = _binning(xys, depths, radii, num_tiles_hit, H, W)
+        # the compositing is enqueued BEFORE the intersection count is read: the host's wait ends when the binning is
+        # done, while the device goes on compositing (gsplat reads the count between the two and idles the device)
+        out = _RasterizeGaussians.apply(xys, conics, colors, opacity, background, res[0], res[1], H, W, tb, return_alpha)
+        if _confirm(res, slot, xys.device.index):
+            return out
+        # the tile lists did not fit their speculative capacity (nothing was written, the image above is the
+        # background): the capacity hint has been raised — bin and composite again
 
 
 class _RasterizeGaussians(Function):
@@ -146,10 +167,10 @@ class _RasterizeGaussians(Function):
         v_out_img = v_out_img.float().contiguous()
         if v_out_alpha is not None:
             v_out_alpha = v_out_alpha.float().contiguous()
-        v_xys = torch.zeros((N, 2), device=dev, dtype=torch.float32)
-        v_conics = torch.zeros((N, 3), device=dev, dtype=torch.float32)
-        v_colors = torch.zeros((N, C), device=dev, dtype=torch.float32)
-        v_opac = torch.zeros((N,), device=dev, dtype=torch.float32)
+        # the four gradient arrays are accumulated into by atomics: ONE zero-filled allocation, carved up
+        g = torch.zeros(((6 + C) * N,), device=dev, dtype=torch.float32)
+        v_xys, v_conics = g[0:2 * N].view(N, 2), g[2 * N:5 * N].view(N, 3)
+        v_colors, v_opac = g[5 * N:(5 + C) * N].view(N, C), g[(5 + C) * N:]
         L = _lib.lib()
         with torch.cuda.device(dev):
             st = _lib.stream_ptr()

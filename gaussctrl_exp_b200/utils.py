@@ -112,12 +112,43 @@ def bin_and_sort_gaussians(num_points: int, num_intersects: int, xys: Tensor, de
 _cap_hint = {}
 
 
+class PendingCount:
+    """Intersection count of a binning call that is on its way to a pinned host word (`bin_fast(..., defer=True)`):
+    `wait()` blocks until it has landed — i.e. until the BINNING is done, whatever was enqueued behind it — and returns
+    (count, fits the capacity)."""
+    __slots__ = ("pinned", "event", "cap", "key")
+    _free = []
+
+    def __init__(self, total: Tensor, cap: int, key):
+        if PendingCount._free:
+            self.pinned, self.event = PendingCount._free.pop()
+        else:
+            self.pinned, self.event = torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event()
+        self.cap, self.key = cap, key
+        self.pinned.copy_(total, non_blocking=True)
+        self.event.record(torch.cuda.current_stream(total.device))
+
+    def wait(self):
+        self.event.synchronize()
+        I = int(self.pinned[0])
+        PendingCount._free.append((self.pinned, self.event))
+        self.pinned = self.event = None
+        if I <= self.cap:
+            _cap_hint[self.key] = max(_cap_hint.get(self.key, 0), int(I * 1.25) + 1024)
+        else:
+            _cap_hint[self.key] = int(I * 1.25) + 1024
+        return I, I <= self.cap
+
+
 def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
-             tile_bounds: Tuple[int, int, int], impl: Optional[str] = None) -> Tuple[Tensor, Tensor, int]:
+             tile_bounds: Tuple[int, int, int], impl: Optional[str] = None, defer: bool = False):
     """Traffic-lean binning (gs_bin_fast): -> (ids_sorted int32 [>=I], tile_bins (T,2), I).
 
-    The capacity of ids_sorted is speculative (1.25x the last total for this N); the single host
-    read of the true total doubles as the overflow check, and an overflow simply re-runs."""
+    The capacity of ids_sorted is speculative (1.25x the largest total seen for this N); the single host
+    read of the true total doubles as the overflow check, and an overflow simply re-runs.
+    defer=True: nothing is read here; the third value is a PendingCount (or the count itself for an empty set) that
+    the caller waits on AFTER it has enqueued the work that consumes the lists — on overflow (wait() -> (I, False)) the
+    lists are empty (every tile range is [0, 0)), nothing was written out of bounds, and the caller calls again."""
     dev = xys.device
     N = xys.shape[0]
     tx, ty = int(tile_bounds[0]), int(tile_bounds[1])
@@ -131,28 +162,33 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
     total = torch.empty(1, device=dev, dtype=torch.int32)
     if impl is None:
         impl = "lsd"
+    if impl not in ("bucket", "lsd", "lsd3"):
+        raise ValueError(f"unknown binning implementation {impl!r}")
     while True:
         ids_sorted = torch.empty((cap,), device=dev, dtype=torch.int32)
         with torch.cuda.device(dev):
             # gs_bin_fast. "lsd" (default): global depth sort + scan/emission + stable partition by tile; "lsd3": the
             # same with three 11/11/10-bit depth passes; "bucket": per-tile segments filled unordered, then sorted per
             # tile in shared memory — identical output
-            if impl not in ("bucket", "lsd", "lsd3"):
-                raise ValueError(f"unknown binning implementation {impl!r}")
-            prev = L.gs_set_depth_sort_passes(3 if impl == "lsd3" else 4) if impl != "bucket" else None
-            prev_legacy = L.gs_set_bin_impl(0 if impl == "bucket" else 1)
+            special = impl != "lsd"
+            if special:
+                prev = L.gs_set_depth_sort_passes(3 if impl == "lsd3" else 4) if impl != "bucket" else None
+                prev_legacy = L.gs_set_bin_impl(0 if impl == "bucket" else 1)
             try:
                 scratch = _scratch(dev, L.gs_bin_fast_scratch_bytes(N, cap, T), "binfast")
                 rc = L.gs_bin_fast(N, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tx, ty,
                                    _lib.ptr(ids_sorted), _lib.ptr(bins), _lib.ptr(total), _lib.ptr(scratch),
                                    scratch.numel(), _lib.stream_ptr())
             finally:
-                if prev is not None:
-                    L.gs_set_depth_sort_passes(prev)
-                L.gs_set_bin_impl(prev_legacy)
+                if special:
+                    if prev is not None:
+                        L.gs_set_depth_sort_passes(prev)
+                    L.gs_set_bin_impl(prev_legacy)
         _lib.check(rc, "gs_bin_fast")
+        if defer:
+            return ids_sorted, bins, PendingCount(total, cap, key)
         I = int(total.item())
         if I <= cap:
-            _cap_hint[key] = max(int(I * 1.25) + 1024, 1024)
+            _cap_hint[key] = max(_cap_hint.get(key, 0), int(I * 1.25) + 1024)
             return ids_sorted, bins, I
         cap = int(I * 1.25) + 1024

@@ -437,3 +437,31 @@ def test_crop_box_and_downscale(oracle, cuda_dev):
                        out["accumulation"].detach().cpu().numpy(), ref2["accumulation"], 96, 128)
         out["rgb"].sum().backward()
         assert m2.means.grad.abs().max() > 0
+
+
+def test_api_rasterize_heals_capacity_overflow(oracle, cuda_dev):
+    """rasterize_gaussians enqueues the compositing before it reads the intersection count; a speculative capacity
+    that turns out too small must be healed inside the call (second binning + compositing), never show in the result."""
+    from gaussctrl_exp_b200 import rasterize_gaussians, utils as U
+    from gaussctrl_exp_b200 import rasterize as R
+    from util import projected
+    d = projected(oracle, N=6000, W=160, H=96, seed=21, s0=0.03)
+    rng = np.random.default_rng(3)
+    colors = rng.random((6000, 3)).astype(np.float32)
+    bg = np.array([0.2, 0.4, 0.6], np.float32)
+    t = {k: torch.from_numpy(np.ascontiguousarray(d[k])).to(cuda_dev) for k in ("xys", "depths", "radii", "conics", "hit")}
+    opac = torch.from_numpy(d["opac"].astype(np.float32)).to(cuda_dev)
+    col = torch.from_numpy(colors).to(cuda_dev).requires_grad_(True)
+    args = (t["xys"], t["depths"], t["radii"], t["conics"], t["hit"], col, opac, 96, 160, torch.from_numpy(bg).to(cuda_dev))
+    R.clear_binning_cache()
+    ref = rasterize_gaussians(*args)
+    key = (cuda_dev.index, 6000, d["tb"][0] * d["tb"][1])
+    I = int(d["hit"].sum())
+    assert U._cap_hint[key] >= I
+    U._cap_hint[key] = max(I // 4, 8)                     # far too small: the first attempt overflows
+    R.clear_binning_cache()
+    out = rasterize_gaussians(*args)
+    assert torch.equal(out, ref)
+    assert U._cap_hint[key] >= I                          # raised for the next call
+    out.sum().backward()
+    assert col.grad is not None and col.grad.abs().max().item() > 0
