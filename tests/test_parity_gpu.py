@@ -100,7 +100,8 @@ def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
         assert bins2.shape == (T, 2)
 
 
-@pytest.mark.parametrize("N,W,H,s0", [(70000, 512, 512, 0.004), (9000, 1920, 1080, 0.05), (300, 64, 48, 0.1)])
+@pytest.mark.parametrize("N,W,H,s0", [(70000, 512, 512, 0.004), (9000, 1920, 1080, 0.05), (300, 64, 48, 0.1),
+                                     (20000, 640, 640, 0.01)])      # 10-bit, 7+6-bit, 4-bit and 11-bit tile digits
 def test_radix_cta_shapes_identical(oracle, cuda_dev, N, W, H, s0):
     """gs_set_radix_cfg: every CTA shape of the radix passes (depth sort x partition) gives the oracle's lists."""
     from gaussctrl_exp_b200 import _lib, utils as U

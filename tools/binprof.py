@@ -26,7 +26,7 @@ for n, intr in SIZES[:1 if os.environ.get("ONESIZE") else 3]:
             (P @ V).to(dev), cam.fx, cam.fy, cam.cx, cam.cy, cam.H, cam.W, tb)
     T = tb[0] * tb[1]
     ref = None
-    for impl in [i for i in ("lsd", "bucket") if os.environ.get("ONLY", i) == i]:
+    for impl in [i for i in ("lsd", "lsd3", "bucket") if os.environ.get("ONLY", i) == i]:
         ids, bins, I = U.bin_fast(xys, depths, radii, hit, tb, impl=impl)
         if ref is None:
             ref = (ids[:I].clone(), bins.clone(), I)
@@ -36,7 +36,7 @@ for n, intr in SIZES[:1 if os.environ.get("ONESIZE") else 3]:
         out = torch.empty(cap, device=dev, dtype=torch.int32)
         total = torch.empty(1, device=dev, dtype=torch.int32)
         scratch = torch.empty(L.gs_bin_fast_scratch_bytes(n, cap, T), device=dev, dtype=torch.uint8)
-        prev = L.gs_set_bin_impl(0 if impl == "bucket" else 1)
+        prev = L.gs_set_bin_impl(0 if impl == "bucket" else 1); prevp = L.gs_set_depth_sort_passes(3 if impl == "lsd3" else 4)
 
         def call():
             rc = L.gs_bin_fast(n, cap, _lib.ptr(xys), _lib.ptr(depths), _lib.ptr(radii), _lib.ptr(hit), tb[0], tb[1],
@@ -52,7 +52,7 @@ for n, intr in SIZES[:1 if os.environ.get("ONESIZE") else 3]:
             call()
         b.record()
         torch.cuda.synchronize()
-        L.gs_set_bin_impl(prev)
+        L.gs_set_bin_impl(prev); L.gs_set_depth_sort_passes(prevp)
         us = a.elapsed_time(b) / REPS * 1e3
         print(f"N={n} {cam.W}x{cam.H} I={I} impl={impl}: {us:.1f} us  ({I / us / 1e3:.1f} G intersections/s)", flush=True)
     del p, xys, depths, radii, conics, hit
