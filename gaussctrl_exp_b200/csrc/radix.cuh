@@ -1,5 +1,5 @@
 // Stable LSD radix-sort building blocks (keys + 32-bit values), one pass = three small kernels:
-//     hist    : CTA b histograms its 4096-key chunk                  -> mat[digit][b]
+//     hist    : CTA b histograms its chunk (3 072 - 4 096 keys, Cfg)     -> mat[digit][b]
 //     colscan : one warp per digit scans its row over the CTAs       -> mat (exclusive), totals[digit]
 //     scatter : CTA b scans the digit totals itself (digit base), ranks its chunk (ballot matching,
 //               stable), stages it in shared memory in digit order and writes coalesced runs at
@@ -21,7 +21,8 @@ namespace gsradix {
 
 // CTA shape of a pass: TPB threads x IPT keys per thread = SUB keys per CTA. The passes over N ~ 1 M keys are one-wave,
 // latency-bound launches and want many warps per SM (512 x 8: 16 warps per CTA); the passes over I >= 6 M pairs are
-// throughput-bound and want smaller chunks (384 x 8 / 256 x 12) — measured per size, see select_cfg below.
+// throughput-bound and want smaller chunks (384 x 8 / 256 x 12) — measured per size (tools/radix_cfg_sweep.py); the
+// choice is made by the caller (binning.cu: radix_cfg) and handed to launch_pass_cfg below.
 template <int TPB_, int IPT_>
 struct Cfg {
     static constexpr int TPB = TPB_, IPT = IPT_, WARPS = TPB_ / 32, SUB = TPB_ * IPT_;
@@ -51,6 +52,7 @@ __device__ __forceinline__ KeyT load_key(const KeyT *__restrict__ kin, const int
     }
     return k;
 }
+
 // block-wide exclusive scan of one value per thread (TPB threads). tmp: >= 64 uint32.
 template <int WARPS>
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *tmp, uint32_t *total) {
