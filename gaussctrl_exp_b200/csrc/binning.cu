@@ -472,17 +472,39 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
     }
 }
 
+// tile ranges from the sorted tile ids (two-pass partition only). Four consecutive entries per thread (one 16-byte
+// load), the neighbours across threads by shuffle: the first version read tk[k-1], tk[k], tk[k+1] per entry and cost
+// 146 us for the 23 M pairs of an 8-view batch — as much as a whole radix pass.
 __global__ void __launch_bounds__(256)
 edges32_kernel(int64_t I_cap, const int32_t *__restrict__ total_dev, const uint32_t *__restrict__ tk,
                int32_t *__restrict__ bins) {
     gs_pdl_sync();
     const int64_t I = *total_dev;
     if (I > I_cap) return;
-    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= I) return;
-    const uint32_t t = tk[k];
-    if (k == 0 || tk[k - 1] != t) bins[2 * t] = (int32_t)k;
-    if (k == I - 1 || tk[k + 1] != t) bins[2 * t + 1] = (int32_t)(k + 1);
+    const int lane = threadIdx.x & 31;
+    const int64_t k0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int64_t w0 = k0 - 4 * lane;                         // first entry of the warp
+    if (w0 >= I) return;                                      // warp-uniform
+    uint32_t t[4] = {0u, 0u, 0u, 0u};
+    if (k0 + 4 <= I) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(tk + k0);
+        t[0] = v.x; t[1] = v.y; t[2] = v.z; t[3] = v.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (k0 + j < I) t[j] = tk[k0 + j];
+    }
+    uint32_t prev = __shfl_up_sync(0xffffffffu, t[3], 1), next = __shfl_down_sync(0xffffffffu, t[0], 1);
+    if (lane == 0 && k0 > 0) prev = tk[k0 - 1];
+    if (lane == 31 && k0 + 4 < I) next = tk[k0 + 4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int64_t k = k0 + j;
+        if (k >= I) break;
+        const uint32_t before = j ? t[j - 1] : prev, after = j < 3 ? t[j + 1] : next;
+        if (k == 0 || before != t[j]) bins[2 * t[j]] = (int32_t)k;
+        if (k == I - 1 || after != t[j]) bins[2 * t[j] + 1] = (int32_t)(k + 1);
+    }
 }
 
 struct FastLayout {
@@ -699,7 +721,7 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
 
     // 5. tile ranges (two-pass partition only)
     if (tk_sorted) {
-        edges32_kernel<<<(int)((I_cap + 255) / 256), 256, 0, st>>>(I_cap, total_dev, tk_sorted, tile_bins);
+        edges32_kernel<<<(int)((I_cap + 1023) / 1024), 256, 0, st>>>(I_cap, total_dev, tk_sorted, tile_bins);
         GS_LAUNCH_CHECK();
     }
     return 0;
