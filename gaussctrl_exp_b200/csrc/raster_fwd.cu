@@ -297,12 +297,61 @@ tile_order_kernel(int T, const int32_t *__restrict__ work, int work_is_range, in
     for (int o = 16; o > 0; o >>= 1) rank += __shfl_xor_sync(0xffffffffu, rank, o);
     if (lane == 0) order[rank] = t;
 }
+
+// More than 2 048 tiles (1080p views: 8 160; batches of views): the all-pairs ranking above grows with T^2 (37 us at
+// 8 192 tiles). A schedule does not need an exact sort: ONE CTA bins the tiles into 1 024 work levels relative to the
+// heaviest tile (shared-memory histogram, scan, cursor per level) and emits them heaviest level first; the order inside
+// a level is whatever the atomics give. `order` is a permutation of 0..T-1 by construction (counted and placed with
+// the same level function).
+constexpr int TO_LEVELS = 1024;
+__global__ void __launch_bounds__(TO_LEVELS)
+tile_order_levels_kernel(int T, const int32_t *__restrict__ work, int work_is_range, int32_t *__restrict__ order) {
+    __shared__ int s_cnt[TO_LEVELS];
+    __shared__ int s_red[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    gs_pdl_sync();
+    auto load = [&](int u) { return max(work_is_range ? work[2 * u + 1] - work[2 * u] : work[u], 0); };
+    s_cnt[tid] = 0;
+    int mx = 0;
+    for (int u = tid; u < T; u += TO_LEVELS) mx = max(mx, load(u));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) s_red[warp] = mx;
+    __syncthreads();
+    mx = s_red[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    const long long wmax = max(mx, 1);
+    auto level = [&](int w) { return (TO_LEVELS - 1) - (int)(((long long)w * (TO_LEVELS - 1)) / wmax); };   // 0 = heaviest
+    for (int u = tid; u < T; u += TO_LEVELS) atomicAdd(&s_cnt[level(load(u))], 1);
+    __syncthreads();
+    // exclusive scan of the level counts (one per thread)
+    const int c = s_cnt[tid];
+    int inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    __syncthreads();                 // every thread has read s_red above and its own count
+    if (lane == 31) s_red[warp] = inc;
+    __syncthreads();
+    int woff = 0;
+    for (int w = 0; w < warp; ++w) woff += s_red[w];
+    s_cnt[tid] = woff + inc - c;     // cursor of the level
+    __syncthreads();
+    for (int u = tid; u < T; u += TO_LEVELS) order[atomicAdd(&s_cnt[level(load(u))], 1)] = u;
+}
 }  // namespace
 
 extern "C" int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream) {
     if (T <= 0 || !work || !order) return GS_ERR_BAD_ARG;
-    GS_PDL_LAUNCH_IF(T <= GS_RASTER_PDL_MAX_TILES, tile_order_kernel, (T * 32 + 255) / 256, 256, 0, (cudaStream_t)stream, T,
-                     work, work_is_range, order);
+    if (T > GS_RASTER_PDL_MAX_TILES) {
+        tile_order_levels_kernel<<<1, TO_LEVELS, 0, (cudaStream_t)stream>>>(T, work, work_is_range, order);
+        GS_LAUNCH_CHECK();
+        return 0;
+    }
+    GS_PDL_LAUNCH(tile_order_kernel, (T * 32 + 255) / 256, 256, 0, (cudaStream_t)stream, T, work, work_is_range, order);
     return 0;
 }
 

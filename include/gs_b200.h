@@ -248,7 +248,8 @@ int gs_raster_fwd_rgbd(int H, int W, int tiles_x, int tiles_y,
 /* Tile scheduling (3-channel kernels): CTAs are dispatched in blockIdx order, so launching the tiles in
  * descending-work order (LPT) keeps the long tiles out of the tail. gs_tile_order ranks T tiles by
  * work[t] (work_is_range = 0) or by tile_bins[t].end - tile_bins[t].start (work_is_range = 1), ties by
- * tile id. The *_ordered variants take the permutation (NULL = natural order); the forward also writes
+ * tile id; above 2 048 tiles the ranking is by 1 024 work levels relative to the heaviest tile (heaviest level
+ * first, order inside a level unspecified) — `order` is a permutation of 0..T-1 either way. The *_ordered variants take the permutation (NULL = natural order); the forward also writes
  * tile_work[t] = depth of the deepest contributor of tile t (NULL = skip), which is the backward's work.
  * depths/out_depth NULL = RGB only. Results are identical to the un-ordered entry points. */
 int gs_tile_order(int T, const int32_t *work, int work_is_range, int32_t *order, void *stream);

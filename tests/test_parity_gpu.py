@@ -431,3 +431,32 @@ def test_fused_preprocess_matches_operator_chain(oracle, cuda_dev, N, W, H, deg,
             assert np.abs(got).max() == 0, k
         else:
             assert rel_linf(got, ref) < 1e-4, k
+
+
+@pytest.mark.parametrize("T", [1, 37, 1024, 2048, 2049, 8160, 70000])
+def test_tile_order_is_a_heaviest_first_permutation(cuda_dev, T):
+    """gs_tile_order: a permutation of the tiles, exact descending order (ties by tile id) up to 2 048 tiles, descending
+    by 1 024 work levels above; both input forms (work array, tile ranges)."""
+    from gaussctrl_exp_b200 import _lib
+    L = _lib.lib()
+    rng = np.random.default_rng(T)
+    work = (rng.gamma(1.5, 900.0, T)).astype(np.int32)
+    work[rng.random(T) < 0.2] = 0
+    if T > 3:
+        work[:3] = work.max()                                   # ties at the top
+    starts = np.concatenate([[0], np.cumsum(work)[:-1]]).astype(np.int32)
+    bins = np.stack([starts, starts + work], axis=1).astype(np.int32)
+    for is_range, arr in ((0, work), (1, bins)):
+        order = torch.full((T,), -1, device=cuda_dev, dtype=torch.int32)
+        a = torch.from_numpy(np.ascontiguousarray(arr)).to(cuda_dev)
+        assert L.gs_tile_order(T, a.data_ptr(), is_range, order.data_ptr(), _lib.stream_ptr()) == 0
+        o = order.cpu().numpy()
+        assert np.array_equal(np.sort(o), np.arange(T))         # every tile exactly once
+        w = work[o].astype(np.int64)
+        if T <= 2048:
+            want = np.lexsort((np.arange(T), -work.astype(np.int64)))
+            assert np.array_equal(o, want)
+        else:
+            wmax = max(int(work.max()), 1)
+            lev = 1023 - (w * 1023) // wmax
+            assert np.all(np.diff(lev) >= 0)                    # heaviest level first
