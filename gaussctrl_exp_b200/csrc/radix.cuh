@@ -15,6 +15,8 @@
 // between the scan that produces the count and the passes that consume it.
 // Stability: chunk order == CTA order, warp-striped items ranked in order.
 #pragma once
+#include <cstdlib>
+
 #include "gs_common.cuh"
 
 namespace gsradix {
@@ -146,6 +148,82 @@ colscan_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__res
         }
     }
     if (lane == 0) totals[d] = carry;
+}
+
+// Segmented column scan for passes with many chunks (5 M elements, 20-160 M pairs: 1 600 - 80 000 chunks). The kernel
+// above gives one warp a whole row, i.e. 32 CTAs walk 80 000 entries each — 253 us per pass on an 8-view 1080p batch,
+// as much as the histogram. Here a row is cut into segments of COLSEG chunks: (1) every (digit, segment) warp scans
+// its segment in place and leaves the segment total, (2) every warp adds the totals of the segments before its own;
+// the warps of segment 0 also write the digit totals.
+constexpr int COLSEG = 1024;
+
+template <int BITS, int SUB>
+__global__ void __launch_bounds__(256)
+colscan_seg_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat, int pitch,
+                   uint32_t *__restrict__ segtot, int nseg) {
+    constexpr int RADIX = 1 << BITS;
+    gs_pdl_sync();
+    const int64_t n = resolve_n(n_cap, n_dev);
+    if (n < 0) return;
+    const int nb = (int)((n + SUB - 1) / SUB);
+    const int lane = threadIdx.x & 31;
+    const int d = blockIdx.x * 8 + (threadIdx.x >> 5), seg = blockIdx.y;
+    if (d >= RADIX) return;
+    const int lo = seg * COLSEG, hi = min(nb, lo + COLSEG);
+    uint32_t *row = mat + (size_t)d * pitch;
+    uint32_t carry = 0;
+    for (int cb = lo; cb < hi; cb += 32 * 4) {
+        uint32_t c[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int bb = cb + u * 32 + lane;
+            c[u] = bb < hi ? row[bb] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int bb = cb + u * 32 + lane;
+            uint32_t inc = c[u];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t nn = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += nn;
+            }
+            if (bb < hi) row[bb] = carry + inc - c[u];
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
+    }
+    if (lane == 0) segtot[(size_t)d * nseg + seg] = carry;      // 0 for a segment behind the last chunk
+}
+
+template <int BITS, int SUB>
+__global__ void __launch_bounds__(256)
+colscan_fix_kernel(int64_t n_cap, const int32_t *__restrict__ n_dev, uint32_t *__restrict__ mat, int pitch,
+                   const uint32_t *__restrict__ segtot, int nseg, uint32_t *__restrict__ totals) {
+    constexpr int RADIX = 1 << BITS;
+    gs_pdl_sync();
+    const int64_t n = resolve_n(n_cap, n_dev);
+    if (n < 0) return;
+    const int nb = (int)((n + SUB - 1) / SUB);
+    const int lane = threadIdx.x & 31;
+    const int d = blockIdx.x * 8 + (threadIdx.x >> 5), seg = blockIdx.y;
+    if (d >= RADIX) return;
+    const uint32_t *st = segtot + (size_t)d * nseg;
+    uint32_t before = 0, all = 0;
+    for (int s = lane; s < nseg; s += 32) {
+        const uint32_t v = st[s];
+        all += v;
+        if (s < seg) before += v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        before += __shfl_xor_sync(0xffffffffu, before, o);
+        all += __shfl_xor_sync(0xffffffffu, all, o);
+    }
+    if (seg == 0 && lane == 0) totals[d] = all;
+    if (before == 0) return;
+    const int lo = seg * COLSEG, hi = min(nb, lo + COLSEG);
+    uint32_t *row = mat + (size_t)d * pitch;
+    for (int bb = lo + lane; bb < hi; bb += 32) row[bb] += before;
 }
 
 template <typename KeyT, int BITS, class C>
@@ -328,14 +406,31 @@ inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, con
         if (e != cudaSuccess) return (int)e;
     }
     GS_PDL_LAUNCH((hist_kernel<KeyT, BITS, MODE, C>), nb, TPB, 0, st, n_cap, n_dev, kin, radii, shift, bits, mat, nb);
-    GS_PDL_LAUNCH((colscan_kernel<BITS, MODE, SUB>), (RADIX + 7) / 8, 256, 0, st, n_cap, n_dev, mat, nb, totals);
+    static const int seg_min = [] {          // chunks above which the column scan is segmented (A/B: GS_COLSCAN_SEG_MIN)
+        const char *e = getenv("GS_COLSCAN_SEG_MIN");
+        return e ? atoi(e) : 4 * COLSEG;
+    }();
+    // measured on the 5 M / 1080p stress scene (tools: stress A/B by GS_COLSCAN_SEG_MIN): segmenting pays for the pair
+    // partitions (10 240 chunks: training 354.6 -> 358.1 views/s; 79 531 chunks of an 8-view batch: eval 672 -> 699)
+    // and costs on the depth passes of the batch (13 021 chunks: 699 -> 639) although the kernels themselves are
+    // faster under ncu (15 vs 57 us) — so only passes whose count comes from the device (the partitions) take it
+    if (nb > seg_min && n_dev != nullptr) {
+        const int nseg = (nb + COLSEG - 1) / COLSEG;
+        uint32_t *segtot = totals + RADIX;                       // behind the totals (mat_entries leaves room)
+        GS_PDL_LAUNCH((colscan_seg_kernel<BITS, SUB>), dim3((RADIX + 7) / 8, nseg), 256, 0, st, n_cap, n_dev, mat, nb, segtot, nseg);
+        GS_PDL_LAUNCH((colscan_fix_kernel<BITS, SUB>), dim3((RADIX + 7) / 8, nseg), 256, 0, st, n_cap, n_dev, mat, nb,
+                      (const uint32_t *)segtot, nseg, totals);
+    } else {
+        GS_PDL_LAUNCH((colscan_kernel<BITS, MODE, SUB>), (RADIX + 7) / 8, 256, 0, st, n_cap, n_dev, mat, nb, totals);
+    }
     GS_PDL_LAUNCH((scatter_kernel<KeyT, BITS, MODE, C>), nb, TPB, smem, st, n_cap, n_dev, kin, radii, vin, kout, vout,
                   shift, bits, (const uint32_t *)mat, nb, (const uint32_t *)totals, bins_out, bins_T);
     return 0;
 }
 
 inline size_t mat_entries(int64_t n_cap, int radix) {
-    return ((size_t)((n_cap + MIN_SUB - 1) / MIN_SUB) + 2) * (size_t)radix;
+    const size_t chunks = (size_t)((n_cap + MIN_SUB - 1) / MIN_SUB);
+    return (chunks + 2 + (chunks + COLSEG - 1) / COLSEG + 1) * (size_t)radix;     // counts | totals | segment totals
 }
 
 // launch_pass with the CTA shape chosen at run time: 0 = 256 x 16 (round 1), 1 = 512 x 8, 2 = 384 x 8, 3 = 256 x 12
