@@ -340,16 +340,26 @@ emit_sorted_kernel(int N, int64_t I_cap, const int32_t *__restrict__ total_dev, 
 // depth order (4 per thread), scans their areas, gets its global offset by decoupled look-back (ticket order, 32-wide
 // window) and writes its (tile, id) pairs. The total is published by the last tile; writes are bounded by the capacity
 // (if the total exceeds it the consumers see that in *total_dev and do nothing).
+// CTA shape of scan_emit_kernel: 128 threads x 4 elements with a 2 048-pair stage (measured against 256 / 4 096, the
+// round-2 form: 145.6 -> 142.7 us for the chain at 1 M / 512^2, 282.9 -> 271.8 us at 1080p; 64 / 1 024 the same)
+#ifndef GS_SE_TPB
+#define GS_SE_TPB 128
+#endif
+#ifndef GS_SE_STAGE
+#define GS_SE_STAGE 2048
+#endif
+constexpr int SE_TPB = GS_SE_TPB;
 constexpr int SE_IPT = 4;
-constexpr int SE_TILE = SCAN_TPB * SE_IPT;
-constexpr int SE_STAGE = 4096;       // pairs of one CTA staged in shared memory (a CTA's pairs are CONTIGUOUS in the output)
+constexpr int SE_TILE = SE_TPB * SE_IPT;
+constexpr int SE_STAGE = GS_SE_STAGE;
+static_assert(SE_TPB >= 64 && (SE_TPB & (SE_TPB - 1)) == 0, "scan_emit_kernel: power-of-two CTA sizes only (192 x 4 miscounts)");       // pairs of one CTA staged in shared memory (a CTA's pairs are CONTIGUOUS in the output)
 
-__global__ void __launch_bounds__(SCAN_TPB)
+__global__ void __launch_bounds__(SE_TPB)
 scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const float *__restrict__ xy_base, int xy_stride,
                  const int32_t *__restrict__ radii, int tiles_x, int tiles_y, int n_per_view, uint32_t *__restrict__ tkey,
                  uint32_t *__restrict__ tval, int32_t *__restrict__ total, ScanCtl *ctl, unsigned long long *status) {
     __shared__ unsigned int s_tile;
-    __shared__ int s_warp[SCAN_TPB / 32];
+    __shared__ int s_warp[SE_TPB / 32];
     __shared__ int s_prefix;
     // the pairs of this CTA form one contiguous run of the output: they are assembled here and stored with coalesced
     // 128-byte rows. Written straight from the threads, every lane of a store lands in a different sector (a thread
@@ -397,7 +407,7 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
     __syncthreads();
     int warp_off = 0, block_total = 0;
 #pragma unroll
-    for (int w = 0; w < SCAN_TPB / 32; ++w) {
+    for (int w = 0; w < SE_TPB / 32; ++w) {
         if (w < warp) warp_off += s_warp[w];
         block_total += s_warp[w];
     }
@@ -429,7 +439,7 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
     }
     __syncthreads();
     const int cta_off = s_prefix;
-    if (tile == (N - 1) / SE_TILE && tid == SCAN_TPB - 1) *total = s_prefix + block_total;
+    if (tile == (N - 1) / SE_TILE && tid == SE_TPB - 1) *total = s_prefix + block_total;
     const bool staged = block_total <= SE_STAGE;
     // pair `at` (index inside this CTA's run): shared-memory stage, or straight to the output when the run is too long
     auto put = [&](int at, uint32_t t, uint32_t id) {
@@ -464,7 +474,7 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
     }
     if (staged) {
         __syncthreads();
-        for (int at = tid; at < block_total; at += SCAN_TPB)
+        for (int at = tid; at < block_total; at += SE_TPB)
             if ((int64_t)cta_off + at < I_cap) {
                 tkey[cta_off + at] = s_key[at];
                 tval[cta_off + at] = s_val[at];
@@ -520,7 +530,7 @@ FastLayout fast_layout(int N, int64_t I_cap) {
     L.tkey = take(i4); L.tval = take(i4); L.tkey2 = take(i4); L.tval2 = take(i4);
     const size_t m = gsradix::mat_entries(N, 2048), mi = gsradix::mat_entries(I_cap, 2048);
     L.mat = take((m > mi ? m : mi) * 4);
-    L.ctl = take(2 * gs_scan_scratch_bytes(N));      // look-back state of scan_emit_kernel (1 024-element tiles)
+    L.ctl = take((SCAN_TILE / SE_TILE) * gs_scan_scratch_bytes(N));      // look-back state of scan_emit_kernel (SE_TILE-element tiles)
     L.total = at;
     return L;
 }
@@ -610,7 +620,7 @@ int gs_bin_fast_clear(int N, int64_t I_cap, int T, int32_t *tile_bins, void *scr
     if (scratch_bytes < L.total) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     if (cudaMemsetAsync(tile_bins, 0, sizeof(int32_t) * 2 * (size_t)T, st) != cudaSuccess) return -1;
-    if (cudaMemsetAsync(reinterpret_cast<unsigned char *>(scratch) + L.ctl, 0, 2 * gs_scan_scratch_bytes(N), st) != cudaSuccess)
+    if (cudaMemsetAsync(reinterpret_cast<unsigned char *>(scratch) + L.ctl, 0, (SCAN_TILE / SE_TILE) * gs_scan_scratch_bytes(N), st) != cudaSuccess)
         return -1;
     return 1;
 }
@@ -654,7 +664,7 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
 
     // the scan's look-back state is cleared up front so that the kernel chain below is uninterrupted (every launch
     // is a programmatic dependent launch: the next kernel is resident before the previous one drains)
-    if (!precleared) GS_CUDA(cudaMemsetAsync(ctl, 0, 2 * gs_scan_scratch_bytes(N), st));
+    if (!precleared) GS_CUDA(cudaMemsetAsync(ctl, 0, (SCAN_TILE / SE_TILE) * gs_scan_scratch_bytes(N), st));
     // 1. depth sort (values start as the element index; the first pass forms its keys from depths/radii on the fly,
     //    so there is no key-building kernel). Default: four passes of 8-bit digits; gs_set_depth_sort_passes(3) /
     //    GS_DEPTH_SORT_PASSES=3 selects three passes of 11/11/10-bit digits (fewer launches, but measured slower).
@@ -684,7 +694,7 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
     //        tiles_hit is not read at all.
     static const bool split_scan = getenv("GS_BIN_SPLIT_SCAN") != nullptr;
     if (!split_scan) {
-        GS_PDL_LAUNCH(scan_emit_kernel, (N + SE_TILE - 1) / SE_TILE, SCAN_TPB, 0, st, N, I_cap, order, xys, xy_stride, radii,
+        GS_PDL_LAUNCH(scan_emit_kernel, (N + SE_TILE - 1) / SE_TILE, SE_TPB, 0, st, N, I_cap, order, xys, xy_stride, radii,
                       tiles_x, tiles_y, n_per_view, tkey, tval, total_dev, ctl, status);
         if (I_cap == 0) return 0;
     } else {
