@@ -13,7 +13,10 @@
 
 namespace {
 
-constexpr int PB_TPB = 128;
+#ifndef GS_PB_TPB
+#define GS_PB_TPB 128
+#endif
+constexpr int PB_TPB = GS_PB_TPB;
 constexpr int PB_REST = 45;
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }

@@ -18,7 +18,10 @@
 
 namespace {
 
-constexpr int PP_TPB = 128;
+#ifndef GS_PP_TPB
+#define GS_PP_TPB 128
+#endif
+constexpr int PP_TPB = GS_PP_TPB;
 constexpr int PP_REST = 45;  // floats of features_rest per Gaussian (15 bases x 3 channels)
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
