@@ -410,7 +410,7 @@ inline int launch_pass(int64_t n_cap, const int32_t *n_dev, const KeyT *kin, con
         const char *e = getenv("GS_COLSCAN_SEG_MIN");
         return e ? atoi(e) : 4 * COLSEG;
     }();
-    // measured on the 5 M / 1080p stress scene (tools: stress A/B by GS_COLSCAN_SEG_MIN): segmenting pays for the pair
+    // measured on the 5 M / 1080p stress scene (tools/stress_ab.py with GS_COLSCAN_SEG_MIN): segmenting pays for the pair
     // partitions (10 240 chunks: training 354.6 -> 358.1 views/s; 79 531 chunks of an 8-view batch: eval 672 -> 699)
     // and costs on the depth passes of the batch (13 021 chunks: 699 -> 639) although the kernels themselves are
     // faster under ncu (15 vs 57 us) — so only passes whose count comes from the device (the partitions) take it
