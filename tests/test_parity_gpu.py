@@ -75,7 +75,8 @@ def test_sh(oracle, cuda_dev, K, deg):
 
 
 @pytest.mark.parametrize("N,W,H,seed,s0", [(8000, 128, 80, 1, 0.03), (50000, 512, 512, 0, 0.005), (300, 1920, 1080, 2, 0.3),
-                                           (5, 33, 17, 3, 0.05), (120000, 1920, 1080, 4, 0.004), (4097, 256, 256, 6, 0.02)])
+                                           (5, 33, 17, 3, 0.05), (120000, 1920, 1080, 4, 0.004), (4097, 256, 256, 6, 0.02),
+                                           (30000, 1920, 1080, 7, 0.03)])      # last: 15.6 M pairs -> segmented column scan
 def test_binning_bit_exact(oracle, cuda_dev, N, W, H, seed, s0):
     from gaussctrl_exp_b200 import utils as U
     d = projected(oracle, N=N, W=W, H=H, seed=seed, s0=s0)
