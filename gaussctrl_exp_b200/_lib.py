@@ -52,6 +52,7 @@ SIGNATURES = {
     "gs_sh_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "gs_scan_scratch_bytes": (_sz, [_i]),
     "gs_bin_scan": (_i, [_i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gs_bin_scan_static": (_i, [_i, _vp, _vp, _vp, _vp]),
     "gs_bin_emit": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "gs_sort_scratch_bytes": (_sz, [_i64]),
     "gs_bin_sort": (_i, [_i64, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

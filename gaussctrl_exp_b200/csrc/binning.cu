@@ -3,6 +3,7 @@
 // get_tile_bin_edges), reached from /root/reference/gaussctrl/gc_model.py:208 and :225.
 // Integer work, bit-exact against the oracle. HBM/L2-bound.
 #include <stdlib.h>
+#include <mutex>
 #define GS_PDL_GROUP 1
 #include "radix.cuh"
 
@@ -185,6 +186,84 @@ extern "C" int gs_bin_scan(int N, const int32_t *tiles_hit, int32_t *cum, int32_
     const size_t need = gs_scan_scratch_bytes(N);
     if (scratch_bytes < need) return GS_ERR_SCRATCH_SMALL;
     GS_CUDA(cudaMemsetAsync(scratch, 0, need, st));
+    ScanCtl *ctl = reinterpret_cast<ScanCtl *>(scratch);
+    unsigned long long *status = reinterpret_cast<unsigned long long *>(ctl + 1);
+    const int blocks = (N + SCAN_TILE - 1) / SCAN_TILE;
+    scan_kernel<<<blocks, SCAN_TPB, 0, st>>>(N, tiles_hit, nullptr, 0, cum, total_dev, ctl, status);
+    GS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// gs_bin_scan_static — gs_bin_scan for hosts that have no way to hand the library device memory of their own.
+//
+// Who needs it: gs_bin_scan wants a caller-provided look-back buffer (a ticket + one status word per 2 048-element
+// tile). A torch caller just slices one out of its caching allocator, but not every host of this ABI has an
+// allocator behind it: a plug-in that is only ever handed its input and output tensors by the application (an
+// inference server's custom-op slot, a DCC / renderer plug-in, a cgo or JNI binding whose runtime owns all device
+// memory and exposes no allocation call to native code), or code that runs at a point where cudaMalloc is off
+// limits because it synchronises the whole device or would fail the surrounding stream capture. Such a caller can
+// still pass tiles_hit / cum / total_dev, but has nowhere to get the scratch from — so here the scratch lives inside
+// the library image, as a file-scope __device__ array.
+//
+// What that costs: GS_SCAN_STATIC_BYTES (64 KiB + 16 B) of device memory on every GPU this library is loaded on,
+// held until the process exits, and a hard limit of GS_SCAN_STATIC_MAX_N elements per call (larger N is refused with
+// GS_ERR_UNSUPPORTED; use gs_bin_scan with your own scratch for those). No cudaMalloc / cudaFree / allocating
+// library call is made, on the first call or later.
+//
+// Sharing: there is ONE array per device and every call on that device uses it. Each call first clears the part it
+// needs (the ticket and status words of the previous call are still in there) with a memset on `stream`, so calls
+// that are ordered on the GPU — same stream, or ordered by events — are fine; two calls that can overlap on the GPU
+// (different streams without ordering, or two host threads) race on the ticket and produce wrong sums.
+//
+// First call on a device: `g_scan_static` below is, in host code, only a handle; the kernel needs the array's device
+// address, which cudaGetSymbolAddress returns for the CURRENT device. The first call made with a given device
+// current looks it up (and thereby loads this module on that device) and remembers it; make that first call outside
+// any stream capture. The device current at the call must be the one `stream` belongs to, as for every entry point.
+// ------------------------------------------------------------------------------------------
+namespace {
+constexpr int GS_SCAN_STATIC_MAX_N_ = 16 * 1024 * 1024;                                  // = GS_SCAN_STATIC_MAX_N
+constexpr int SCAN_STATIC_TILES = GS_SCAN_STATIC_MAX_N_ / SCAN_TILE + 1;                  // 8 193 status words
+constexpr size_t SCAN_STATIC_WORDS = sizeof(ScanCtl) / sizeof(unsigned long long) + SCAN_STATIC_TILES;
+static __device__ __align__(256) unsigned long long g_scan_static[SCAN_STATIC_WORDS];    // ticket | status[tiles]
+
+constexpr int SCAN_STATIC_MAX_DEVICES = 64;
+std::mutex g_scan_static_mu;
+void *g_scan_static_ptr[SCAN_STATIC_MAX_DEVICES] = {};   // per device: address of g_scan_static there
+}  // namespace
+
+extern "C" int gs_bin_scan_static(int N, const int32_t *tiles_hit, int32_t *cum, int32_t *total_dev, void *stream) {
+    static_assert(sizeof(ScanCtl) % sizeof(unsigned long long) == 0, "ticket block is a whole number of status words");
+    static_assert(GS_SCAN_STATIC_MAX_N_ == GS_SCAN_STATIC_MAX_N && sizeof(g_scan_static) == GS_SCAN_STATIC_BYTES,
+                  "header constants out of date");
+    if (N < 0) return GS_ERR_BAD_ARG;
+    if (N > GS_SCAN_STATIC_MAX_N) return GS_ERR_UNSUPPORTED;   // the built-in scratch has no room for more tiles
+    cudaStream_t st = (cudaStream_t)stream;
+    if (N == 0) {
+        if (total_dev) GS_CUDA(cudaMemsetAsync(total_dev, 0, sizeof(int32_t), st));
+        return 0;
+    }
+    if (!tiles_hit || !cum) return GS_ERR_BAD_ARG;
+    if (!gs_aligned16(tiles_hit) || !gs_aligned16(cum)) return GS_ERR_MISALIGNED;
+
+    // device address of the array on the current device, looked up once per device
+    int dev = -1;
+    GS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= SCAN_STATIC_MAX_DEVICES) return GS_ERR_UNSUPPORTED;
+    void *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_scan_static_mu);
+        if (!g_scan_static_ptr[dev]) {
+            void *p = nullptr;
+            GS_CUDA(cudaGetSymbolAddress(&p, g_scan_static));
+            if (!p) return GS_ERR_UNSUPPORTED;
+            g_scan_static_ptr[dev] = p;
+        }
+        scratch = g_scan_static_ptr[dev];
+    }
+
+    const size_t need = gs_scan_scratch_bytes(N);            // <= sizeof(g_scan_static) by the N check above
+    GS_CUDA(cudaMemsetAsync(scratch, 0, need, st));          // the last call's ticket and flags are still in there
     ScanCtl *ctl = reinterpret_cast<ScanCtl *>(scratch);
     unsigned long long *status = reinterpret_cast<unsigned long long *>(ctl + 1);
     const int blocks = (N + SCAN_TILE - 1) / SCAN_TILE;

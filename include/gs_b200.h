@@ -190,6 +190,21 @@ size_t gs_scan_scratch_bytes(int N);
  * (device int32) so the caller can copy it to pinned memory without reading cum[N-1]. */
 int gs_bin_scan(int N, const int32_t *tiles_hit, int32_t *cum, int32_t *total_dev,
                 void *scratch, size_t scratch_bytes, void *stream);
+/* gs_bin_scan without a scratch argument — NO COUNTERPART IN THE REFERENCE (gsplat calls torch.cumsum, which allocates
+ * through torch); it exists for hosts of this ABI that cannot give the library device memory of their own: plug-ins that
+ * only ever receive their input and output buffers from the application (custom-op slots of an inference server,
+ * cgo / JNI bindings whose runtime owns all device memory), and callers sitting at a point where cudaMalloc is not
+ * allowed because it synchronises the device or would break a stream capture in progress. The look-back state lives
+ * in an array inside the library image instead: GS_SCAN_STATIC_BYTES of device memory on every GPU the library is
+ * loaded on, kept until the process exits. Limit: N <= GS_SCAN_STATIC_MAX_N, larger N returns GS_ERR_UNSUPPORTED
+ * (use gs_bin_scan). The call allocates and frees nothing. Same outputs as gs_bin_scan, bit for bit.
+ * The array is shared by every call on a device: each call clears the part it uses on `stream` first, so calls ordered
+ * on the GPU are fine, calls that may overlap on the GPU (unordered streams, concurrent host threads) race. The first
+ * call made with a given device current resolves the array's address on that device (cudaGetSymbolAddress) and caches
+ * it; issue that first call outside any stream capture, with the device of `stream` current. */
+#define GS_SCAN_STATIC_MAX_N (16 * 1024 * 1024)
+#define GS_SCAN_STATIC_BYTES (16 + 8 * (GS_SCAN_STATIC_MAX_N / 2048 + 1))
+int gs_bin_scan_static(int N, const int32_t *tiles_hit, int32_t *cum, int32_t *total_dev, void *stream);
 /* 64-bit keys (tile_id << 32 | depth bits) + Gaussian ids, in emission order. */
 int gs_bin_emit(int N, const float *xys, const float *depths, const int32_t *radii,
                 const int32_t *cum, int tiles_x, int tiles_y, int64_t *keys, int32_t *ids,
