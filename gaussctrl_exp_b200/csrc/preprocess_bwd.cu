@@ -200,7 +200,7 @@ preprocess_bwd_multi_kernel(int N, int Np, int V, const float *__restrict__ view
     float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
     if (i < N) {
         p0 = means[3 * i]; p1 = means[3 * i + 1]; p2 = means[3 * i + 2];
-        s0 = expf(log_scales[3 * i]); s1 = expf(log_scales[3 * i + 1]); s2 = expf(log_scales[3 * i + 2]);
+        s0 = gs_exp_scale(log_scales[3 * i]); s1 = gs_exp_scale(log_scales[3 * i + 1]); s2 = gs_exp_scale(log_scales[3 * i + 2]);
         const float4 qr = quats[i];
         iq = 1.0f / sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
         q = make_float4(qr.x * iq, qr.y * iq, qr.z * iq, qr.w * iq);

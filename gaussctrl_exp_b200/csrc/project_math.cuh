@@ -15,6 +15,11 @@ struct ProjOut {
     int radius, hit;
 };
 
+// exp(log_scale) as every kernel of the path evaluates it: correctly rounded ((float) of the double result), so that the
+// forward, the single-view backward and the multi-view / data-parallel leaf backwards all differentiate at the SAME
+// scale (expf may differ by 1 ulp between builds and call sites; gc_model.py:172 torch.exp).
+__device__ __forceinline__ float gs_exp_scale(float log_scale) { return (float)exp((double)log_scale); }
+
 // V: 12 floats (3x4 row-major world->camera), P: 16 floats (P@V). q = (w,x,y,z) un-normalised.
 __device__ __forceinline__ void gs_project_one(const float *V, const float *P, float p0, float p1, float p2,
                                                float s0, float s1, float s2, float glob, float4 q, float fx,
