@@ -151,6 +151,18 @@ def check(rc: int, what: str):
     raise GsError(f"{what}: CUDA error {rc}")
 
 
+COUNT_SATURATED = 0x7FFFFFFF
+
+
+def check_count(I: int, what: str) -> int:
+    """Tile-intersection totals are int32 on the device (as gsplat's int32 cumsum is). The scans saturate at INT32_MAX
+    instead of wrapping, and nothing is written for such a view: report it instead of treating it as a count."""
+    if I < 0 or I >= COUNT_SATURATED:
+        raise GsError(f"{what}: the view has more than 2^31 - 2 tile intersections (int32 count saturated): "
+                      "GS_ERR_UNSUPPORTED")
+    return I
+
+
 def ptr(t):
     """Device pointer of a (contiguous) torch tensor, or NULL for None."""
     return None if t is None else t.data_ptr()

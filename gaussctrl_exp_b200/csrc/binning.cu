@@ -18,6 +18,13 @@ constexpr int SCAN_TILE = SCAN_TPB * SCAN_IPT;
 #define FLAG_AGG (1ull << 32)
 #define FLAG_INC (2ull << 32)
 
+// Prefixes beyond int32 (more than 2^31 - 1 tile intersections: huge radii at 1080p, many-view batches) SATURATE at
+// INT32_MAX instead of wrapping: a wrapped negative prefix would pass the `offset + at < I_cap` guards of the emission
+// and a wrapped total would pass `total > I_cap`. A saturated total is always above any capacity the entry points accept
+// (I_cap < INT32_MAX), so every consumer sees "does not fit" and the host reports the count as unsupported. Operands
+// are <= INT32_MAX, so the unsigned sum cannot wrap.
+__device__ __forceinline__ unsigned sat_add31(unsigned a, unsigned b) { return min(a + b, 0x7fffffffu); }
+
 struct ScanCtl {
     unsigned int ticket;
     unsigned int pad[3];
@@ -80,15 +87,15 @@ scan_kernel(int N, const int32_t *__restrict__ in, const uint32_t *__restrict__ 
             } while (__any_sync(0xffffffffu, (w >> 32) == 0));
             const unsigned inc_mask = __ballot_sync(0xffffffffu, (w >> 32) == 2);
             const int first = inc_mask ? __ffs(inc_mask) - 1 : 31;
-            int part = lane <= first ? (int)(unsigned int)w : 0;
+            unsigned part = lane <= first ? (unsigned int)w : 0u;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-            excl += part;
+            for (int o = 16; o > 0; o >>= 1) part = sat_add31(part, __shfl_xor_sync(0xffffffffu, part, o));
+            excl = (int)sat_add31((unsigned)excl, part);
             if (inc_mask) break;
             look -= 32;
         }
         if (lane == 0) {
-            if (tile > 0) atomicExch(&status[tile], FLAG_INC | (unsigned int)(excl + block_total));
+            if (tile > 0) atomicExch(&status[tile], FLAG_INC | sat_add31((unsigned)excl, (unsigned)block_total));
             s_prefix = excl;
         }
     }
@@ -106,7 +113,8 @@ scan_kernel(int N, const int32_t *__restrict__ in, const uint32_t *__restrict__ 
         for (int j = 0; j < SCAN_IPT; ++j)
             if (base + j < N) out[base + j] = v[j] + off;
     }
-    if (total && tile == (N - 1) / SCAN_TILE && tid == SCAN_TPB - 1) *total = s_prefix + block_total;
+    if (total && tile == (N - 1) / SCAN_TILE && tid == SCAN_TPB - 1)
+        *total = (int)sat_add31((unsigned)s_prefix, (unsigned)block_total);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -504,21 +512,21 @@ scan_emit_kernel(int N, int64_t I_cap, const uint32_t *__restrict__ order, const
             } while (__any_sync(0xffffffffu, (w >> 32) == 0));
             const unsigned inc_mask = __ballot_sync(0xffffffffu, (w >> 32) == 2);
             const int first = inc_mask ? __ffs(inc_mask) - 1 : 31;
-            int part = lane <= first ? (int)(unsigned int)w : 0;
+            unsigned part = lane <= first ? (unsigned int)w : 0u;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-            ex += part;
+            for (int o = 16; o > 0; o >>= 1) part = sat_add31(part, __shfl_xor_sync(0xffffffffu, part, o));
+            ex = (int)sat_add31((unsigned)ex, part);
             if (inc_mask) break;
             look -= 32;
         }
         if (lane == 0) {
-            if (tile > 0) atomicExch(&status[tile], FLAG_INC | (unsigned int)(ex + block_total));
+            if (tile > 0) atomicExch(&status[tile], FLAG_INC | sat_add31((unsigned)ex, (unsigned)block_total));
             s_prefix = ex;
         }
     }
     __syncthreads();
     const int cta_off = s_prefix;
-    if (tile == (N - 1) / SE_TILE && tid == SE_TPB - 1) *total = s_prefix + block_total;
+    if (tile == (N - 1) / SE_TILE && tid == SE_TPB - 1) *total = (int)sat_add31((unsigned)s_prefix, (unsigned)block_total);
     const bool staged = block_total <= SE_STAGE;
     // pair `at` (index inside this CTA's run): shared-memory stage, or straight to the output when the run is too long
     auto put = [&](int at, uint32_t t, uint32_t id) {
@@ -710,7 +718,7 @@ int gs_bin_fast_ex(int N, int n_per_view, int64_t I_cap, const float *xys, int x
                    bool precleared) {
     if (N < 0 || I_cap < 0 || tiles_x <= 0 || tiles_y <= 0 || n_per_view <= 0 || (N % n_per_view) != 0) return GS_ERR_BAD_ARG;
     if (!tile_bins || !total_dev || !scratch) return GS_ERR_BAD_ARG;
-    if (I_cap >= (1ll << 31)) return GS_ERR_UNSUPPORTED;
+    if (I_cap >= 0x7fffffffll) return GS_ERR_UNSUPPORTED;   // INT32_MAX is the saturated "too many pairs" total
     const int views = N > 0 ? N / n_per_view : 1;
     if ((int64_t)views * tiles_x * tiles_y >= (1ll << 22)) return GS_ERR_UNSUPPORTED;
     const int T = views * tiles_x * tiles_y;

@@ -1,4 +1,5 @@
-// Stage 2 — tile binning, bucket form (default implementation behind gs_bin_fast / gs_view_fwd; SURVEY.md App. A.3:
+// Stage 2 — tile binning, bucket form (the SECOND, opt-in implementation behind gs_bin_fast / gs_view_fwd, selected with
+// gs_set_bin_impl(0) / GS_BIN_IMPL=bucket — the default is the LSD pipeline of binning.cu, which measured faster; SURVEY.md App. A.3:
 // torch.cumsum + map_gaussian_to_intersects + torch.sort + get_tile_bin_edges inside gsplat's rasterize_gaussians,
 // reached from /root/reference/gaussctrl/gc_model.py:208 and :225). Same ids_sorted / tile_bins as a stable sort of
 // the 64-bit (tile << 32 | depth bits) keys, bit for bit, from FOUR launches:

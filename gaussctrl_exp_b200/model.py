@@ -198,7 +198,9 @@ class GaussianModel(nn.Module):
 
     def _get_outputs_fused(self, camera: Camera, background: Tensor, crop_ids: Optional[Tensor]):
         """Same outputs as the literal path below, through render.render_view / render.render_eval.
-        `camera` already carries the downscaled resolution."""
+        `camera` already carries the downscaled resolution. (None, None, None) = no Gaussian of a non-empty set reaches
+        the image (gc_model.py:189-190 `radii.sum() == 0`): a radius is positive exactly when the splat hits a tile, so
+        the intersection count the call has already read is the same test without another device read."""
         W, H = int(camera.W), int(camera.H)
         dev = self.device
         use_sh = self.sh_degree > 0
@@ -209,6 +211,8 @@ class GaussianModel(nn.Module):
                 n, use_sh, background, self.view_state, clamp_rgb=True,       # gc_model.py:222 inside the kernels
                 speculate=self.speculate)
             self.xys, self.radii = self.view_state.xys, radii
+            if self.num_points > 0 and self.view_state.num_intersects == 0:   # strict forward only: a speculative one has no count yet
+                return None, None, None
             return rgb, None, alpha[..., None]
         subset = None
         if crop_ids is not None:            # index list into the preprocess kernel instead of six gathered copies
@@ -226,6 +230,8 @@ class GaussianModel(nn.Module):
             self.means, self.scales, self.quats, self.opacities, self.features_dc, self.features_rest, [camera], n,
             use_sh, background, with_depth=not self.training, subset=subset)
         self.xys, self.radii = ws.xys, ws.radii
+        if ws.num_intersects == 0:
+            return None, None, None
         return rgb, depth_im, alpha
 
     def get_outputs(self, camera: Camera) -> Dict[str, Optional[Tensor]]:
@@ -241,6 +247,8 @@ class GaussianModel(nn.Module):
             viewmat0, projmat0 = self._caller_matrices(camera)
             if self.fused:
                 rgb, depth_im, alpha = self._get_outputs_fused(camera, background, crop_ids)
+                if rgb is None:                                       # :189-190 every Gaussian culled
+                    return {"rgb": background.repeat(H, W, 1)}
                 return {"rgb": rgb, "depth": depth_im, "accumulation": alpha,
                         "mat_view": viewmat0, "mat_proj": projmat0, "mat_c2w": camera.c2w}
             return self._get_outputs_literal(camera, background, crop_ids, viewmat0, projmat0)
@@ -310,7 +318,9 @@ class GaussianModel(nn.Module):
 
     @torch.no_grad()
     def get_outputs_for_camera(self, camera: Camera, obb_box=None) -> Dict[str, Optional[Tensor]]:
-        """gc_model.py:243-255: eval render (RGB + depth + accumulation) of one camera, cropped to `obb_box`."""
+        """gc_model.py:243-255: eval render (RGB + depth + accumulation) of one camera, cropped to `obb_box`.
+        Deliberate deviation: the reference ends with `self.training = True` whatever the flag was (:253-255); here
+        the previous flag is restored, so a model put in eval mode stays in eval mode."""
         assert camera is not None, "must provide camera to gaussian model"
         self.set_crop(obb_box)                                        # :250
         was_training = self.training

@@ -113,7 +113,7 @@ class _Pending:
         I = ctypes.c_int32.from_address(self.pinned.data_ptr()).value
         _pinned_free[self.dev.index].append((self.pinned, self.event))
         self.pinned = self.event = None
-        return I
+        return _lib.check_count(I, "gs_view_fwd")
 
 
 class CapacityOverflow(RuntimeError):
@@ -472,6 +472,7 @@ def render_eval(means, scales, quats, opacities, features_dc, features_rest, cam
         subset = subset.to(device=dev, dtype=torch.int32).contiguous()
     with torch.cuda.device(dev):
         ws, im, I, _ = forward_views(*args, cams, use_sh, sh_degree_to_use, bg, with_depth=with_depth, subset=subset)
+    ws.num_intersects = I                # host copy of the count the call already read (0 <=> every radius is 0)
     alpha = im.alpha[..., None]
     depth = None
     if with_depth:

@@ -18,8 +18,10 @@ _scratch_cache = {}
 
 
 def _scratch(dev, nbytes: int, tag: str) -> Tensor:
-    """Grow-only uint8 scratch per (device, tag). Owned by torch's caching allocator."""
-    key = (dev.index if dev.index is not None else torch.cuda.current_device(), tag)
+    """Grow-only uint8 scratch per (device, stream, tag), owned by torch's caching allocator: two streams binning on one
+    device never share radix ping-pong buffers, and a buffer outgrown on one stream is released on that stream."""
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    key = (idx, torch.cuda.current_stream(idx).cuda_stream, tag)
     buf = _scratch_cache.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(int(nbytes * 1.25) + 256, device=dev, dtype=torch.uint8)
@@ -43,7 +45,7 @@ def compute_cumulative_intersects(num_tiles_hit: Tensor) -> Tuple[int, Tensor]:
         rc = L.gs_bin_scan(N, _lib.ptr(hit), _lib.ptr(cum), _lib.ptr(total), _lib.ptr(scratch),
                            scratch.numel(), _lib.stream_ptr())
     _lib.check(rc, "gs_bin_scan")
-    return int(total.item()), cum
+    return _lib.check_count(int(total.item()), "gs_bin_scan"), cum
 
 
 def map_gaussian_to_intersects(num_points: int, num_intersects: int, xys: Tensor, depths: Tensor,
@@ -116,12 +118,13 @@ class PendingCount:
     """Intersection count of a binning call that is on its way to a pinned host word (`bin_fast(..., defer=True)`):
     `wait()` blocks until it has landed — i.e. until the BINNING is done, whatever was enqueued behind it — and returns
     (count, fits the capacity)."""
-    __slots__ = ("pinned", "event", "cap", "key")
-    _free = []
+    __slots__ = ("pinned", "event", "cap", "key", "free")
+    _free = {}          # device index -> recycled (pinned word, event): an event stays on the device that first recorded it
 
     def __init__(self, total: Tensor, cap: int, key):
-        if PendingCount._free:
-            self.pinned, self.event = PendingCount._free.pop()
+        self.free = PendingCount._free.setdefault(total.device.index, [])
+        if self.free:
+            self.pinned, self.event = self.free.pop()
         else:
             self.pinned, self.event = torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event()
         self.cap, self.key = cap, key
@@ -131,8 +134,9 @@ class PendingCount:
     def wait(self):
         self.event.synchronize()
         I = int(self.pinned[0])
-        PendingCount._free.append((self.pinned, self.event))
+        self.free.append((self.pinned, self.event))
         self.pinned = self.event = None
+        _lib.check_count(I, "gs_bin_fast")
         if I <= self.cap:
             _cap_hint[self.key] = max(_cap_hint.get(self.key, 0), int(I * 1.25) + 1024)
         else:
@@ -187,7 +191,7 @@ def bin_fast(xys: Tensor, depths: Tensor, radii: Tensor, num_tiles_hit: Tensor,
         _lib.check(rc, "gs_bin_fast")
         if defer:
             return ids_sorted, bins, PendingCount(total, cap, key)
-        I = int(total.item())
+        I = _lib.check_count(int(total.item()), "gs_bin_fast")
         if I <= cap:
             _cap_hint[key] = max(_cap_hint.get(key, 0), int(I * 1.25) + 1024)
             return ids_sorted, bins, I

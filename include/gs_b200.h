@@ -226,6 +226,9 @@ int gs_bin_fast(int N, int64_t I_cap, const float *xys, const float *depths, con
                 const int32_t *tiles_hit, int tiles_x, int tiles_y,
                 int32_t *ids_sorted, int32_t *tile_bins, int32_t *total_dev,
                 void *scratch, size_t scratch_bytes, void *stream);
+/* The gs_set_* knobs below are PROCESS-GLOBAL and not thread-safe: they exist for A/B measurements (every setting
+ * produces identical output), are meant to be set once before the first render, and must not be flipped while another
+ * host thread is inside a gs_* call. A default run never needs them. */
 /* Tuning knob of gs_bin_fast's depth sort: 4 (default; 8-bit digits, 12 launches) or 3 (11/11/10-bit digits, 9
  * launches; measured slower) stable LSD passes — identical output. Returns the previous setting; other values only query.
  * Initial value: environment variable GS_DEPTH_SORT_PASSES. */
