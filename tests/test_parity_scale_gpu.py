@@ -4,7 +4,9 @@
               (fused=False: the literal operator sequence of gc_model.py:172-222) and through the fused path;
   headline    1 M Gaussians, 512x512: one training view (RGB, accumulation, six leaf gradients, xys.grad)
               and one eval view (RGB, depth, accumulation)  — gc_model.py:174-238, gc_trainer.py:275;
-  stress      1 M Gaussians at 1920x1080 (configs[4]'s image size).
+  stress      1 M and 5 M Gaussians at 1920x1080 (configs[4]: its image size, then its Gaussian count), one training and
+              one eval view each, and an 8-CAMERA 1080p batch through the batched call the bench's stress line times
+              (65 280 tiles: camera folded into the tile id, two-pass partition, level tile order, segmented column scan).
 
 Integers (radii, num_tiles_hit, ids_sorted, tile ranges; final_idx wherever no decision sat on its threshold) are
 bit-exact. Floats follow the three-part contract of tests/util.py (forward_parity / gradient_parity): every pixel
@@ -102,6 +104,7 @@ CASES = [
     ("cfg1_500k_fused_512", 500_000, False, True),
     ("headline_1m_fused_512", 1_000_000, False, True),
     ("stress_1m_fused_1080p", 1_000_000, True, True),
+    ("stress_5m_fused_1080p", 5_000_000, True, True),       # configs[4] itself: ~20 M pairs per view, 384x8 radix CTAs
 ]
 
 
@@ -152,3 +155,49 @@ def test_eval_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
     rep["depth"] = depth_parity(depth, ref["depth"], ref["accumulation"], F)
     assert (depth[ref["accumulation"] == 0] == 1000).all()
     _save(name + "_eval", rep)
+
+
+def test_eight_camera_1080p_batch_vs_oracle(oracle, cuda_dev):
+    """The all-view loop's unit at the stress image size (gc_pipeline.py:222-228, gc_render.py:196-203: one
+    get_outputs_for_camera per view; here 8 cameras per gs_view_fwd call): every integer of the batched binning
+    bit-exact against the oracle's per-view binning (radii, num_tiles_hit; the batch's ids_sorted / tile ranges are the
+    per-view lists concatenated in camera order, ids offset by camera * N), images and depth per camera under the float
+    contract."""
+    from gaussctrl_exp_b200 import render
+    N, V = 1_000_000, 8
+    p, _ = _scene(N, hd=True)
+    from gaussctrl_exp_b200 import scene
+    cams = scene.make_cameras(40, 0, intrinsics=scene.HD_INTRINSICS)[3:3 + V]
+    H, W = cams[0].H, cams[0].W
+    T = ((H + 15) // 16) * ((W + 15) // 16)
+    assert V * T == 65_280
+    m = _model(p, cuda_dev, True)
+    ws, rgb, acc, depth = render.render_eval(m.means, m.scales, m.quats, m.opacities, m.features_dc, m.features_rest,
+                                             cams, 3, True, torch.tensor(BG), with_depth=True)
+    torch.cuda.synchronize()
+    radii, hit = ws.radii.cpu().numpy().reshape(V, N), ws.num_tiles_hit.cpu().numpy().reshape(V, N)
+    bins, ids = ws.tile_bins.cpu().numpy().reshape(V, T, 2), ws.ids_sorted.cpu().numpy()
+    I_total = int(ws.total.item())
+    assert I_total == ws.num_intersects
+    by_views = m.render_views(cams, batch=V)
+    rep = {"N": N, "image": [H, W], "cameras": V, "tiles": V * T, "pairs": I_total, "views": []}
+    off = 0
+    for v, cam in enumerate(cams):
+        ref, ctx = oracle.render_view(p, cam.as_dict(), 3, bg=BG, training=False)
+        b = ctx["b"]
+        assert np.array_equal(radii[v], ctx["radii"]) and np.array_equal(hit[v], ctx["hit"]), v
+        assert np.array_equal(ids[off:off + b.I] - v * N, b.ids_sorted), v
+        want = b.tile_bins.astype(np.int64)
+        nonempty = want[:, 1] > want[:, 0]
+        assert np.array_equal(bins[v][nonempty], want[nonempty] + off), v
+        assert (bins[v][~nonempty, 1] == bins[v][~nonempty, 0]).all(), v
+        off += b.I
+        fwd, F, _ = forward_parity(oracle, ctx, rgb[v].cpu().numpy(), ref["rgb"], acc[v].cpu().numpy(),
+                                   ref["accumulation"], H, W)
+        dp = depth_parity(depth[v].cpu().numpy(), ref["depth"], ref["accumulation"], F)
+        for k, t in (("rgb", rgb), ("depth", depth), ("accumulation", acc)):
+            assert torch.equal(by_views[v][k], t[v]), (v, k)
+        rep["views"].append({"I": int(b.I), "forward": fwd, "depth": dp})
+    assert off == I_total
+    rep["integers_bit_exact"] = {"radii": True, "num_tiles_hit": True, "ids_sorted": True, "tile_bins": True}
+    _save("stress_1m_8cam_1080p_batch_eval", rep)
