@@ -313,15 +313,34 @@ def stage_breakdown(model, cam, v_out, iters=20):
     return st, I, vis
 
 
+def csrc_sha16():
+    """sha256 (first 16 hex digits) over the CUDA sources of the library, in name order: what an ncu capture is OF.
+    tools/ncu_extract.py stores it in the metrics file; bench.py compares it with the tree it runs from."""
+    import hashlib
+    d = os.path.join(ROOT, "gaussctrl_exp_b200", "csrc")
+    h = hashlib.sha256()
+    for name in sorted(os.listdir(d)):
+        if name.endswith((".cu", ".cuh")) or name == "Makefile":
+            h.update(name.encode())
+            h.update(open(os.path.join(d, name), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def load_ncu_profile():
-    """profiles/r02_ncu_metrics.json: per-kernel metrics extracted (tools/ncu_extract.py) from the `ncu --set full`
-    capture of THIS build that is committed next to it. bench.py measures times live; instruction counts, issue
-    utilisation and DRAM traffic can only come from a profiler run, so they are read from that file."""
-    path = os.path.join(ROOT, "profiles", "r02_ncu_metrics.json")
+    """profiles/rNN_ncu_metrics.json (newest round): per-kernel metrics extracted (tools/ncu_extract.py) from the
+    `ncu --set full` capture committed next to it. bench.py measures times live; instruction counts, issue utilisation
+    and DRAM traffic can only come from a profiler run, so they are read from that file — and flagged as stale when
+    the CUDA sources have changed since the capture (the file records the source hash it was taken from)."""
+    prof_dir = os.path.join(ROOT, "profiles")
     try:
-        return json.load(open(path)), os.path.relpath(path, ROOT)
+        names = sorted(n for n in os.listdir(prof_dir) if n.endswith("_ncu_metrics.json"))
+        path = os.path.join(prof_dir, names[-1])
+        prof = json.load(open(path))
     except Exception:
-        return {}, None
+        return {}, None, None
+    captured = (prof.get("_source") or {}).get("csrc_sha16")
+    return prof, os.path.relpath(path, ROOT), {"captured_from_csrc_sha16": captured, "this_tree_csrc_sha16": csrc_sha16(),
+                                               "current": captured == csrc_sha16()}
 
 
 def time_model_steps(model, cams, v_out, steps, warmup, rank=0, world=1):
@@ -404,6 +423,25 @@ def config5_stress(dev, n_gauss=5_000_000, n_cams=64, batch=8):
            "raster_bwd_us": st["raster_bwd"][0] * 1e6, "peak_mem_GB": torch.cuda.max_memory_allocated() / 2**30}
     del m
     torch.cuda.empty_cache()
+    # configs[4] as worded: binning/sort and compositing throughput VS GAUSSIAN COUNT (one 1080p training view, camera 0)
+    point = lambda n, I_, vis_, st_, ms_: {
+        "n_gaussians": n, "intersections": int(I_), "visible": vis_, "train_fwd_bwd_views_per_s": 1e3 / ms_,
+        "bin_fast_us": st_["bin_fast"][0] * 1e6, "bin_fast_Gintersections_per_s": I_ / st_["bin_fast"][0] / 1e9,
+        "raster_fwd_us": st_["raster_fwd"][0] * 1e6, "raster_fwd_Gintersections_per_s": I_ / st_["raster_fwd"][0] / 1e9,
+        "raster_bwd_us": st_["raster_bwd"][0] * 1e6, "raster_bwd_Gintersections_per_s": I_ / st_["raster_bwd"][0] / 1e9}
+    sweep = []
+    for n in (1_000_000, 2_000_000):
+        if n >= n_gauss:
+            continue
+        ms_ = GaussianModel(scene.make_scene(n, 0), sh_degree=SH_DEG, background_color=torch.tensor(BG)).to(dev)
+        ms_.train()
+        t_ = time_model_steps(ms_, cams, v, 16, 3)
+        st_, I_, vis_ = stage_breakdown(ms_, cams[0], v, iters=5)
+        sweep.append(point(n, I_, vis_, st_, t_))
+        del ms_
+        torch.cuda.empty_cache()
+    sweep.append(point(n_gauss, I, vis, st, ms_train))
+    out["sweep_vs_gaussian_count"] = sweep
     return out
 
 
@@ -796,8 +834,17 @@ def run_ours(args):
                 "what": f"all-view RGB+depth+alpha render of {N_CAMS} cameras, 1M Gaussians, 512^2 (gc_pipeline.py:222-228), "
                         f"view-sharded over {world} GPU(s), batches of {args.render_batch} cameras per call"},
         }
+        line["config"]["forward_mode_of_value"] = "asynchronous (model.speculate=True)" if args.forward == "async" else "strict"
+        line["config"]["strict_forward_views_per_s"] = world * 1e3 / ms_strict
+        if grad_check is not None:
+            line["config"]["grad_exchange_check_max_rel_diff"] = grad_check["max_rel_diff"]
+            line["config"]["grad_exchange_check_ok"] = bool(
+                grad_check["max_rel_diff"] < 1e-5 and grad_check["nonzero"]
+                and grad_check.get("slices_partition_the_gaussians", grad_check.get("ranks_identical")))
         if finetune_opt is not None:
             line["config4_finetune_step_with_optimizer"] = finetune_opt
+            line["config"]["finetune_step_with_optimizer_views_per_s"] = finetune_opt["views_per_s"]
+            line["e2e"]["finetune_step_with_optimizer_views_per_s"] = finetune_opt["views_per_s"]
         if allreduce_ms is not None:
             line["config4_finetune_step_nccl_allreduce"] = {
                 "views_per_s": world * 1e3 / allreduce_ms, "ms_per_step": allreduce_ms, "n_gpus": world,
@@ -809,7 +856,7 @@ def run_ours(args):
         except Exception:
             pass
         hbm_peak, peak_src = (peaks.get("hbm_gbs"), "measured") if peaks.get("hbm_gbs") else (6650.0, "fallback")
-        prof, prof_path = load_ncu_profile()
+        prof, prof_path, prof_state = load_ncu_profile()
         if not args.no_stages:
             st, I, vis = stage_breakdown(model, cams[0], v_out)
             stages = {}
@@ -820,45 +867,58 @@ def run_ours(args):
             line["stages"] = stages
             line["intersections"] = I
             line["visible"] = vis
-            # `roofline` (schema object) = the dominant HBM-bound kernel of the step; the dominant kernel overall is
-            # SM-issue bound (no dense contraction anywhere on this path) -> `roofline_raster`.
-            step_hbm = {k: stages[k] for k in ("preprocess_fwd_packed", "preprocess_bwd") if k in stages}
-            top = max(step_hbm, key=lambda k: step_hbm[k]["us"])
-            kname = {"preprocess_fwd_packed": "preprocess_fwd_kernel", "preprocess_bwd": "preprocess_bwd_kernel"}[top]
-            pk = prof.get(kname, {}) if args.n_gaussians == N_GAUSS else {}
-            line["roofline"] = {"bound": "hbm", "kernel": kname, "achieved": step_hbm[top]["GBps"],
-                                "peak": hbm_peak, "peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)",
-                                "unit": "GB/s", "frac": step_hbm[top]["frac_hbm"],
-                                "alg_bytes_per_launch": step_hbm[top]["alg_bytes"],
-                                "traffic": pk.get("dram_bytes"), "traffic_source": prof_path if pk else None,
-                                "note": "dominant HBM-bound kernel of the step; the dominant kernel overall is "
-                                        "SM-issue bound, see roofline_raster; multi-kernel binning stage: roofline_binning"}
-            line["roofline_binning"] = {"bound": "hbm", "kernel": "gs_bin_fast (multi-kernel stage)",
-                                        "achieved": stages["bin_fast"]["GBps"], "peak": hbm_peak, "unit": "GB/s",
-                                        "frac": stages["bin_fast"]["frac_hbm"],
-                                        "projection_plus_sort_frac": (stages["preprocess_fwd_packed"]["alg_bytes"] + stages["bin_fast"]["alg_bytes"])
-                                        / (stages["preprocess_fwd_packed"]["us"] + stages["bin_fast"]["us"]) / 1e3 / hbm_peak,
-                                        "note": "L2-resident, latency-bound at this size (see DESIGN.md §4)"}
-            # dominant kernel: time measured live (CUDA events above), instruction / issue / shared-memory figures from the
-            # committed ncu capture of this build
+            use_prof = args.n_gaussians == N_GAUSS          # the capture is of the headline scene
             f_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
-            slots = 148 * 4 * f_clk                       # warp-instruction issue slots per second
-            rr = {"bound": "sm_issue", "kernel": "raster_bwd_direct_kernel", "us": stages["raster_bwd"]["us"],
-                  "peak": slots, "unit": "warp-inst/s", "sm_mhz": f_clk / 1e6, "metrics_source": prof_path}
-            for kname2, key in (("raster_bwd_direct_kernel", "bwd"), ("raster_fwd_packed_kernel", "fwd")):
-                pk2 = prof.get(kname2) if args.n_gaussians == N_GAUSS else None
-                us = stages["raster_" + key]["us"]
-                ent = {"us": us}
-                if pk2:
-                    ent.update({"smsp__inst_executed.sum": pk2.get("inst_executed"),
-                                "sm__issue_active.avg.pct_of_peak_sustained_elapsed": pk2.get("issue_active_pct"),
-                                "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum": pk2.get("smem_wavefronts"),
-                                "achieved_warp_inst_per_s": (pk2.get("inst_executed") or 0) / (us * 1e-6),
-                                "frac": (pk2.get("inst_executed") or 0) / (us * 1e-6) / slots})
-                rr[key] = ent
-            if "frac" in rr["bwd"]:
-                rr["achieved"], rr["frac"] = rr["bwd"]["achieved_warp_inst_per_s"], rr["bwd"]["frac"]
-            line["roofline_raster"] = rr
+            slots = 148 * 4 * f_clk                       # warp-instruction issue slots per second (4 schedulers per SM)
+            step_us = ms_strict * 1e3
+
+            def hbm_entry(stage, kname):
+                pk = prof.get(kname, {}) if use_prof else {}
+                e = stages[stage]
+                return {"bound": "hbm", "kernel": kname, "us": e["us"], "share_of_step": e["us"] / step_us,
+                        "achieved": e["GBps"], "peak": hbm_peak, "unit": "GB/s", "frac": e["frac_hbm"],
+                        "alg_bytes_per_launch": e["alg_bytes"], "traffic": pk.get("dram_bytes")}
+
+            def issue_entry(stage, kname):
+                pk = prof.get(kname) if use_prof else None
+                e = {"bound": "sm_issue", "kernel": kname, "us": stages[stage]["us"],
+                     "share_of_step": stages[stage]["us"] / step_us, "peak": slots, "unit": "warp-inst/s"}
+                if pk and pk.get("inst_executed"):
+                    e.update({"achieved": pk["inst_executed"] / (e["us"] * 1e-6),
+                              "frac": pk["inst_executed"] / (e["us"] * 1e-6) / slots,
+                              "smsp__inst_executed.sum": pk["inst_executed"],
+                              "sm__issue_active.avg.pct_of_peak_sustained_elapsed": pk.get("issue_active_pct"),
+                              "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum": pk.get("smem_wavefronts"),
+                              "traffic": pk.get("dram_bytes")})
+                return e
+            # `roofline` = the DOMINANT kernel of the step. It has no dense contraction and moves 77 MB: it is bound by
+            # the SMs' instruction issue rate, so achieved / peak are warp-instructions per second (time measured live
+            # with CUDA events, instruction count from the committed ncu capture of the same sources). The HBM-bound
+            # kernels and the multi-kernel binning stage are nested under `stages` so that the record keeps them.
+            dom = issue_entry("raster_bwd", "raster_bwd_direct_kernel")
+            dom.update({"sm_mhz": f_clk / 1e6, "peak_source": "148 SMs x 4 schedulers x measured SM clock",
+                        "hbm_peak": hbm_peak, "hbm_peak_source": peak_src + " (MEASURED_PEAKS.json hbm_gbs)",
+                        "metrics_source": prof_path, "metrics_state": prof_state,
+                        "step_us_strict_forward": step_us})
+            bin_e = {"bound": "hbm", "kernel": "gs_bin_fast (multi-kernel stage)", "us": stages["bin_fast"]["us"],
+                     "share_of_step": stages["bin_fast"]["us"] / step_us, "achieved": stages["bin_fast"]["GBps"],
+                     "peak": hbm_peak, "unit": "GB/s", "frac": stages["bin_fast"]["frac_hbm"],
+                     "alg_bytes_per_launch": stages["bin_fast"]["alg_bytes"],
+                     "projection_plus_sort_frac": (stages["preprocess_fwd_packed"]["alg_bytes"] + stages["bin_fast"]["alg_bytes"])
+                     / (stages["preprocess_fwd_packed"]["us"] + stages["bin_fast"]["us"]) / 1e3 / hbm_peak,
+                     "note": "L2-resident, latency-bound at this size (DESIGN.md §4)"}
+            dom["stages"] = {"raster_fwd_packed_kernel": issue_entry("raster_fwd", "raster_fwd_packed_kernel"),
+                             "preprocess_bwd_kernel": hbm_entry("preprocess_bwd", "preprocess_bwd_kernel"),
+                             "preprocess_fwd_kernel": hbm_entry("preprocess_fwd_packed", "preprocess_fwd_kernel"),
+                             "gs_bin_fast": bin_e}
+            if "frac" not in dom:       # no capture for this scene size: fall back to the largest HBM-bound kernel
+                top = max(("preprocess_bwd_kernel", "preprocess_fwd_kernel"), key=lambda k: dom["stages"][k]["us"])
+                dom = dict(dom["stages"][top], stages=dom["stages"], note="no ncu capture for this scene size: largest "
+                           "HBM-bound kernel; the dominant kernel is raster_bwd_direct_kernel (SM-issue bound)")
+            line["roofline"] = dom
+            line["roofline_binning"] = bin_e              # round-2 key names, same objects
+            line["roofline_raster"] = {"bwd": issue_entry("raster_bwd", "raster_bwd_direct_kernel"),
+                                       "fwd": dom["stages"]["raster_fwd_packed_kernel"], "metrics_state": prof_state}
         if world == 1 and not args.no_cpu:
             ref = CpuReference(args.n_gaussians)
             out0, _ = ref.orc.render_view(ref.p, ref.cams[0].as_dict(), SH_DEG, bg=BG, training=True)

@@ -87,7 +87,9 @@ def main():
         if name not in kernels:
             order.append(name)
         kernels[name] = ent
-    kernels["_source"] = {"report": rep, "command": "ncu --set full --clock-control none --import-source on (tools/ncu_round.sh)",
+    sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
+    from bench import csrc_sha16        # the capture is of the tree this script runs in: do not edit csrc/ in between
+    kernels["_source"] = {"csrc_sha16": csrc_sha16(), "report": rep, "command": "ncu --set full --clock-control none --import-source on (tools/ncu_round.sh)",
                           "note": "last captured launch per kernel name; times under ncu are serialised and cold-cache, "
                                   "bench.py measures times live"}
     json.dump(kernels, open(out + "_ncu_metrics.json", "w"), indent=1)
