@@ -42,6 +42,8 @@ def workload_config(n_gauss, world):
                     f"upstream grad randn/(H*W), bg {BG}",
         "n_gaussians": n_gauss, "image": [512, 512], "sh_degree": SH_DEG, "views_per_step": world,
         "parallelism": f"view-parallel dp{world}" + (" + grad exchange every step" if world > 1 else ""),
+        "view_sampling": "next_train semantics (random permutation of the 40 cameras per epoch, seed 0), rank r takes "
+                         "draw step * world + r (dist.ViewSampler)",
         "l2": "working set (236 MB params + 236 MB grads) exceeds the 126 MB L2; no explicit flush",
     }
 
@@ -122,10 +124,12 @@ class CpuReference:
         self.cores = orc.num_threads()
         self.p = {k: v.numpy() for k, v in scene.make_scene(n_gauss, 0).items()}
         self.cams = scene.make_cameras(N_CAMS, 0)
+        from gaussctrl_exp_b200.dist import ViewSampler
+        self.sampler = ViewSampler(N_CAMS, 0, 1, seed=0)      # the job's draw sequence: view k of the CPU arm = draw k
         self.v_out = (np.random.default_rng(1234).standard_normal((512, 512, 3)) / (512 * 512)).astype(np.float32)
 
     def view(self, i):
-        out, ctx = self.orc.render_view(self.p, self.cams[i % N_CAMS].as_dict(), SH_DEG, bg=BG, training=True)
+        out, ctx = self.orc.render_view(self.p, self.cams[self.sampler.draw(i)].as_dict(), SH_DEG, bg=BG, training=True)
         self.orc.render_view_backward(self.p, ctx, self.v_out)
 
     def run(self, views, first=0):
@@ -345,12 +349,14 @@ def load_ncu_profile():
 
 def time_model_steps(model, cams, v_out, steps, warmup, rank=0, world=1):
     import torch
+    from gaussctrl_exp_b200.dist import ViewSampler
     params = [model.means, model.scales, model.quats, model.features_dc, model.features_rest, model.opacities]
+    sampler = ViewSampler(len(cams), rank, world, seed=0)
 
     def once(i):
         for p in params:
             p.grad = None
-        model(cams[(i * world + rank) % len(cams)])["rgb"].backward(v_out)
+        model(cams[sampler.view(i)])["rgb"].backward(v_out)
 
     def step(i):
         from gaussctrl_exp_b200 import render as grender
@@ -463,6 +469,9 @@ def run_ours(args):
     model.train()
     params = [model.means, model.scales, model.quats, model.features_dc, model.features_rest, model.opacities]
     cams = scene.make_cameras(N_CAMS, 0)
+    # training views: the reference's next_train sampling (a random permutation of the cameras per epoch), the same on
+    # every rank; rank r takes draw i * world + r of step i (gc_datamanager.py:213-235)
+    sampler_v = gdist.ViewSampler(N_CAMS, rank, world, seed=0)
     g = torch.Generator().manual_seed(1234)
     v_host = (torch.randn(H, W, 3, generator=g) / (H * W)).pin_memory()
     v_out = v_host.to(dev)
@@ -521,7 +530,7 @@ def run_ours(args):
             _step(i)
 
     def _step(i):
-        cam = cams[(i * world + rank) % N_CAMS]
+        cam = cams[sampler_v.view(i)]
         for p in params:
             p.grad = None
         out = model(cam)
@@ -540,7 +549,7 @@ def run_ours(args):
             model.view_state.view_block_buffer = None
             for p in params:
                 p.grad = None
-            model(cams[(i * world + rank) % N_CAMS])["rgb"].backward(v_out)
+            model(cams[sampler_v.view(i)])["rgb"].backward(v_out)
             gdist.allreduce_flat(model.view_state.flat_grads)
             flat = model.view_state.flat_grads
             model.view_state.defer_leaf_grads = gather_mode
@@ -630,7 +639,7 @@ def run_ours(args):
             _step_e2e(i)
 
     def _step_e2e(i):
-        cam = cams[(i * world + rank) % N_CAMS]
+        cam = cams[sampler_v.view(i)]
         slot = i % 2
         prefetch_target(i)                                  # no-op except on the very first step
         cur = torch.cuda.current_stream(dev)

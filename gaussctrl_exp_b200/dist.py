@@ -40,6 +40,45 @@ def shard_views(num_views: int, rank: int, world: int) -> List[int]:
     return list(range(rank, num_views, world))
 
 
+class ViewSampler:
+    """The reference's training-view sampling (gc_datamanager.py:213-235 `next_train`: pop a random camera from the
+    unseen list, refill the list when it is exhausted — i.e. one random permutation of the cameras per epoch), made
+    rank-deterministic for data-parallel training: every rank derives the SAME permutation of epoch e
+    from (seed, e), the k-th draw of the job is element k mod num_views of epoch k // num_views, and step i hands draw
+    i * world + r to rank r — the views `world` successive next_train calls would have returned. No communication, no
+    state: view(i) can be asked for any step in any order (a resumed run continues the sequence), the ranks of one step
+    never render the same view twice within an epoch, and every camera visits every rank over time instead of the
+    same few cameras staying on one rank (a static i * world + r mod num_views assignment pins the expensive views
+    to the same ranks whenever world divides num_views)."""
+
+    def __init__(self, num_views: int, rank: int = 0, world: int = 1, seed: int = 0):
+        if num_views <= 0 or not (0 <= rank < world):
+            raise ValueError("ViewSampler: num_views > 0 and 0 <= rank < world expected")
+        self.num_views, self.rank, self.world, self.seed = int(num_views), int(rank), int(world), int(seed)
+        self._epochs: Dict[int, List[int]] = {}
+
+    def _epoch(self, e: int) -> List[int]:
+        perm = self._epochs.get(e)
+        if perm is None:
+            import numpy as np
+            if len(self._epochs) > 64:
+                self._epochs.clear()
+            perm = self._epochs[e] = np.random.default_rng([self.seed, e]).permutation(self.num_views).tolist()
+        return perm
+
+    def draw(self, k: int) -> int:
+        """The k-th view of the whole job (k = 0, 1, ...), identical on every rank."""
+        return self._epoch(k // self.num_views)[k % self.num_views]
+
+    def view(self, step: int) -> int:
+        """Index of the view this rank renders in `step`."""
+        return self.draw(step * self.world + self.rank)
+
+    def views_of_step(self, step: int) -> List[int]:
+        """The views of all ranks in `step`, in rank order."""
+        return [self.draw(step * self.world + r) for r in range(self.world)]
+
+
 def owner_of_view(view: int, world: int) -> int:
     return view % world
 

@@ -289,3 +289,26 @@ def test_reference_written_checkpoint_loads_and_resumes():
         assert ref.param_groups[0]["lr"] == opt[name]["lr"]
         err = (ours[name] - prm.data).abs().max().item()
         assert err <= 1e-7 + 1e-6 * prm.data.abs().max().item(), (name, err)
+
+
+def test_view_sampler_is_next_train_made_rank_deterministic():
+    """dist.ViewSampler against the semantics of gc_datamanager.py:213-235 (pop a random unseen camera, refill when
+    exhausted): every epoch of the job's draw sequence is a permutation of all cameras; all ranks agree on the sequence
+    without communicating; the ranks of one step get different draws; cameras rotate over the ranks."""
+    from gaussctrl_exp_b200.dist import ViewSampler
+    for world in (1, 2, 3, 8):
+        ranks = [ViewSampler(40, r, world, seed=5) for r in range(world)]
+        seq = [ranks[0].draw(k) for k in range(400)]
+        for e in range(5):
+            assert sorted(seq[40 * e:40 * (e + 1)]) == list(range(40))          # unseen list: no repeat inside an epoch
+        assert seq[:40] != seq[40:80]                                            # a fresh permutation per epoch
+        for step in (0, 1, 7, 13, 26):
+            got = [s.view(step) for s in ranks]
+            assert got == seq[step * world:(step + 1) * world] == ranks[-1].views_of_step(step)
+        assert [ViewSampler(40, 0, world, seed=5).view(s) for s in (9, 3)] == [ranks[0].view(9), ranks[0].view(3)]  # stateless
+        if world > 1:
+            seen_by_rank0 = {ranks[0].view(s) for s in range(200)}
+            assert len(seen_by_rank0) > 40 // world                              # not pinned to a fixed subset
+    assert [ViewSampler(40, 0, 1, seed=1).draw(k) for k in range(40)] != [ViewSampler(40, 0, 1, seed=2).draw(k) for k in range(40)]
+    with pytest.raises(ValueError):
+        ViewSampler(40, 2, 2)
