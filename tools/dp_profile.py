@@ -23,7 +23,7 @@ STEPS, WARM = 40, 10
 ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(STEPS)]
 for i in range(WARM + STEPS):
     k = i - WARM
-    cam = cams[(i * world + rank) % 40]
+    cam = cams[gd.ViewSampler(40, rank, world, seed=0).view(i)]
     for q in m.parameters():
         q.grad = None
     if k >= 0:
