@@ -6,8 +6,11 @@ rendered view before ControlNet, and where the Gaussians come from.
 * splatfacto checkpoint I/O  gc_trainer.py:147-174 (torch.save dict; parameter names gc_model.py:157-170)
 
 CUDA tensors go through the C ABI (csrc/postops.cu: gs_ray_directions, gs_depth_to_world, gs_depth_to_disparity —
-one streaming kernel each, no host synchronisation; a missing library raises). CPU tensors are the host mirror of
-the same arithmetic in torch ops (the reference's per-pixel Python double loop vectorised). Both are pinned
+one streaming kernel each, no host synchronisation; a missing library raises): that is the PRODUCT path, and a CUDA
+tensor never falls back to the branch below. CPU tensors take the host mirror of the same arithmetic in torch ops (the
+reference's per-pixel Python double loop vectorised) — the reference's own post-ops run on CPU numpy arrays
+(gc_pipeline.py:230-236 calls `.cpu().numpy()` first), so a caller that still hands over CPU data gets the reference's
+behaviour; it is kept for that caller and for the golden-vector tests, not as a fallback. Both are pinned
 against the reference's own functions by tests/golden/reference_postops.npz; the checkpoint reader against a file
 written by the reference's own `save_checkpoint` (tests/golden/reference_step-000029999.ckpt).
 """
