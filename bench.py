@@ -399,6 +399,32 @@ def config1_api_500k(dev, steps=20):
     return out
 
 
+def scene_large_splats(dev, v_out, hbm_peak):
+    """Second workload (scene.LARGE_SPLATS): large anisotropic splats, tens of tiles each — where the per-warp 8x4 box
+    cull and the direct red.global backward of the compositing kernels stop being cheap. 512^2 training view."""
+    import torch
+    from gaussctrl_exp_b200 import scene
+    from gaussctrl_exp_b200.model import GaussianModel
+    spec = scene.LARGE_SPLATS
+    cams = scene.make_cameras(N_CAMS, 0)
+    m = GaussianModel(scene.make_scene(spec["n"], 0, s0=spec["s0"], log_sigma=spec["log_sigma"]), sh_degree=SH_DEG,
+                      background_color=torch.tensor(BG)).to(dev)
+    m.train()
+    ms = time_model_steps(m, cams, v_out, 30, 8)
+    st, I, vis = stage_breakdown(m, cams[0], v_out, iters=5)
+    out = {"workload": f"synthetic {spec['n']} Gaussians, s0 {spec['s0']}, log-scale sigma {spec['log_sigma']}, SH deg 3, 512x512",
+           "views_per_s": 1e3 / ms, "ms_per_step": ms, "intersections_cam0": int(I), "visible_cam0": vis,
+           "intersections_per_gaussian": I / spec["n"], "intersections_per_visible": I / max(vis, 1),
+           "stages_us": {k: st[k][0] * 1e6 for k in ("preprocess_fwd_packed", "bin_fast", "raster_fwd", "raster_bwd", "preprocess_bwd") if k in st},
+           "bin_fast_Gintersections_per_s": I / st["bin_fast"][0] / 1e9,
+           "raster_fwd_Gintersections_per_s": I / st["raster_fwd"][0] / 1e9,
+           "raster_bwd_Gintersections_per_s": I / st["raster_bwd"][0] / 1e9,
+           "bin_fast_frac_hbm": st["bin_fast"][1] / st["bin_fast"][0] / 1e9 / hbm_peak if st["bin_fast"][1] else None}
+    del m
+    torch.cuda.empty_cache()
+    return out
+
+
 def config5_stress(dev, n_gauss=5_000_000, n_cams=64, batch=8):
     """BASELINE.json configs[4]: 5 M Gaussians at 1920x1080, a 64-camera batch: eval render (batched
     render_views), training step, and binning / compositing throughput in intersections/s."""
@@ -956,6 +982,7 @@ def run_ours(args):
                                   "what": "the training-view loop on 200 K Gaussians (512^2): where the host cost per step "
                                           "(host_only_ms_per_step) is of the order of the device time"}
             del small
+            line["scene_large_splats"] = scene_large_splats(dev, v_out, hbm_peak)
             line["config1_api_500k"] = config1_api_500k(dev)
             del model
             torch.cuda.empty_cache()

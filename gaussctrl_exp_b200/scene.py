@@ -31,13 +31,19 @@ def default_scale(n: int) -> float:
     return 0.002
 
 
-def make_scene(n: int, seed: int = 0, s0: float | None = None, device="cpu") -> Dict[str, torch.Tensor]:
-    """Leaf parameters in splatfacto's raw (pre-activation) form."""
+# Second synthetic workload: LARGE, anisotropic splats (the long tail of a trained splatfacto scene, scripts/garden.sh:3,
+# which the small-splat headline scene of SURVEY.md 8d does not have): 4x the headline scene's median scale and a
+# log-scale spread of 1.0 instead of 0.5, so a splat covers tens of tiles and axis ratios of 10+ are common.
+LARGE_SPLATS = dict(n=300_000, s0=0.012, log_sigma=1.0)
+
+
+def make_scene(n: int, seed: int = 0, s0: float | None = None, device="cpu", log_sigma: float = 0.5) -> Dict[str, torch.Tensor]:
+    """Leaf parameters in splatfacto's raw (pre-activation) form. log-scales ~ N(log s0, log_sigma^2)."""
     g = torch.Generator().manual_seed(seed)
     s0 = default_scale(n) if s0 is None else s0
     p = {
         "means": torch.randn(n, 3, generator=g) * 0.3,
-        "scales": math.log(s0) + 0.5 * torch.randn(n, 3, generator=g),
+        "scales": math.log(s0) + log_sigma * torch.randn(n, 3, generator=g),
         "quats": torch.randn(n, 4, generator=g),
         "features_dc": torch.randn(n, 3, generator=g),
         "features_rest": 0.1 * torch.randn(n, 15, 3, generator=g),

@@ -30,9 +30,10 @@ LEAVES = ("means", "scales", "quats", "features_dc", "features_rest", "opacities
 _REPORT = {}
 
 
-def _scene(N, hd=False, cam_index=0):
+def _scene(N, hd=False, cam_index=0, large=False):
     from gaussctrl_exp_b200 import scene
-    p = {k: v.numpy() for k, v in scene.make_scene(N, 0).items()}
+    spec = dict(s0=scene.LARGE_SPLATS["s0"], log_sigma=scene.LARGE_SPLATS["log_sigma"]) if large else {}
+    p = {k: v.numpy() for k, v in scene.make_scene(N, 0, **spec).items()}
     cams = scene.make_cameras(40, 0, intrinsics=scene.HD_INTRINSICS if hd else None)
     return p, cams[cam_index]
 
@@ -110,7 +111,7 @@ CASES = [
 
 @pytest.mark.parametrize("name,N,hd,fused", CASES, ids=[c[0] for c in CASES])
 def test_training_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
-    p, cam = _scene(N, hd, cam_index=1)
+    p, cam = _scene(N, hd, cam_index=1, large=name.startswith("large_splats"))
     H, W = cam.H, cam.W
     ref, ctx = oracle.render_view(p, cam.as_dict(), 3, bg=BG, training=True)
     v = (np.random.default_rng(1234).standard_normal((H, W, 3)) / (H * W)).astype(np.float32)
@@ -141,7 +142,7 @@ def test_training_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
 
 @pytest.mark.parametrize("name,N,hd,fused", CASES, ids=[c[0] for c in CASES])
 def test_eval_view_vs_oracle(oracle, cuda_dev, name, N, hd, fused):
-    p, cam = _scene(N, hd, cam_index=2)
+    p, cam = _scene(N, hd, cam_index=2, large=name.startswith("large_splats"))
     H, W = cam.H, cam.W
     ref, ctx = oracle.render_view(p, cam.as_dict(), 3, bg=BG, training=False)
     m = _model(p, cuda_dev, fused)
